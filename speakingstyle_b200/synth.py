@@ -1,0 +1,248 @@
+"""Deterministic synthetic weights and batches.
+
+There are no checkpoints and no datasets offline, so every test and the benchmark run on
+random-init weights of the reference architecture and on synthetic inputs of the shapes
+BASELINE.json names.  Everything is drawn from ``torch.Generator`` objects seeded on the CPU, so
+the very same tensors are produced here, on the GPU box, and by oracle/make_golden.py (which
+loads them into the real reference with ``strict=True`` - that load is also the check that the
+key names and shapes below are the reference's state_dict contract).
+
+Choices that differ from the reference's *default* initialisers, on purpose:
+* ``duration_predictor.linear_layer.bias = duration_bias`` (default 2.1) so an utterance of ~100
+  phonemes expands to ~800 frames;
+* LayerNorm / BatchNorm affine terms, BatchNorm running statistics and the FiLM scalars are
+  perturbed away from (1, 0) so a kernel that ignored them could not pass parity;
+* HiFi-GAN convolutions are drawn variance-preserving (the default N(0, 0.01) init gives a nearly
+  silent wave) and stored in checkpoint form (``weight_g``/``weight_v``).
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import configs as C
+
+
+def sinusoid_table(n_position, d_hid):
+    """float64 sinusoid table cast to float32 - transformer/Models.py:10-30, vectorised."""
+    pos = np.arange(n_position, dtype=np.float64)[:, None]
+    j = np.arange(d_hid)
+    denom = np.power(10000, 2 * (j // 2) / d_hid)[None, :]
+    table = pos / denom
+    table[:, 0::2] = np.sin(table[:, 0::2])
+    table[:, 1::2] = np.cos(table[:, 1::2])
+    return torch.from_numpy(table.astype(np.float32))
+
+
+class _Rng:
+    def __init__(self, seed):
+        self.g = torch.Generator(device="cpu")
+        self.g.manual_seed(int(seed))
+
+    def uniform(self, shape, bound):
+        return (torch.rand(shape, generator=self.g, dtype=torch.float32) * 2.0 - 1.0) * bound
+
+    def normal(self, shape, std=1.0, mean=0.0):
+        return torch.randn(shape, generator=self.g, dtype=torch.float32) * std + mean
+
+    def randint(self, lo, hi, shape):
+        return torch.randint(lo, hi, shape, generator=self.g, dtype=torch.int64)
+
+
+def _dense(r, sd, name, out_f, in_f, k=None, bias=True):
+    fan_in = in_f * (k or 1)
+    bound = 1.0 / math.sqrt(fan_in)
+    shape = (out_f, in_f) if k is None else (out_f, in_f, k)
+    sd[name + ".weight"] = r.uniform(shape, bound)
+    if bias:
+        sd[name + ".bias"] = r.uniform((out_f,), bound)
+
+
+def _layer_norm(r, sd, name, n):
+    sd[name + ".weight"] = 1.0 + r.uniform((n,), 0.2)
+    sd[name + ".bias"] = r.uniform((n,), 0.1)
+
+
+def _fft_block(r, sd, p, d_model, d_inner, kernel, film):
+    for w in ("w_qs", "w_ks", "w_vs"):
+        _dense(r, sd, f"{p}.slf_attn.{w}", d_model, d_model)
+    _layer_norm(r, sd, f"{p}.slf_attn.layer_norm", d_model)
+    _dense(r, sd, f"{p}.slf_attn.fc", d_model, d_model)
+    _dense(r, sd, f"{p}.pos_ffn.w_1", d_inner, d_model, kernel[0])
+    _dense(r, sd, f"{p}.pos_ffn.w_2", d_model, d_inner, kernel[1])
+    _layer_norm(r, sd, f"{p}.pos_ffn.layer_norm", d_model)
+    if film:
+        sd[f"{p}.film.s_gamma"] = 1.0 + r.uniform((1,), 0.3)
+        sd[f"{p}.film.s_beta"] = 1.0 + r.uniform((1,), 0.3)
+
+
+def _variance_predictor(r, sd, p, d, filt, k):
+    _dense(r, sd, f"{p}.conv_layer.conv1d_1.conv", filt, d, k)
+    _layer_norm(r, sd, f"{p}.conv_layer.layer_norm_1", filt)
+    _dense(r, sd, f"{p}.conv_layer.conv1d_2.conv", filt, filt, k)
+    _layer_norm(r, sd, f"{p}.conv_layer.layer_norm_2", filt)
+    sd[f"{p}.film.s_gamma"] = 1.0 + r.uniform((1,), 0.3)
+    sd[f"{p}.film.s_beta"] = 1.0 + r.uniform((1,), 0.3)
+    _dense(r, sd, f"{p}.linear_layer", 1, filt)
+
+
+def fastspeech2_state_dict(model_config, dataset="BC2013", seed=1234, duration_bias=2.1, n_mel=80):
+    """Full FastSpeech2 + ReferenceEncoder state_dict with the reference's keys and shapes."""
+    r = _Rng(seed)
+    sd = {}
+    tr = model_config["transformer"]
+    re = model_config["reference_encoder"]
+    vp = model_config["variance_predictor"]
+    n_pos = model_config["max_seq_len"] + 1
+    d = tr["encoder_hidden"]
+
+    emb = r.normal((C.N_SRC_VOCAB, d))
+    emb[0].zero_()  # padding_idx = PAD = 0 (transformer/Models.py:56-58)
+    sd["encoder.src_word_emb.weight"] = emb
+    sd["encoder.position_enc"] = sinusoid_table(n_pos, d).unsqueeze(0)
+    for i in range(tr["encoder_layer"]):
+        _fft_block(r, sd, f"encoder.layer_stack.{i}", d, tr["conv_filter_size"], tr["conv_kernel_size"], True)
+
+    filt = re["conv_filter_size"]
+    sd["reference_encoder.position_enc"] = sinusoid_table(n_pos, filt).unsqueeze(0)
+    for i in range(re["conv_layer"]):
+        _dense(r, sd, f"reference_encoder.layer_stack.{i}.0.conv", filt, n_mel if i == 0 else filt,
+               re["conv_kernel_size"])
+        _layer_norm(r, sd, f"reference_encoder.layer_stack.{i}.2", filt)
+    dm = re["encoder_hidden"]
+    _dense(r, sd, "reference_encoder.fftb_linear.linear", dm, filt, bias=False)
+    for i in range(re["encoder_layer"]):
+        _fft_block(r, sd, f"reference_encoder.fftb_stack.{i}", dm, filt,
+                   [re["conv_kernel_size"], re["conv_kernel_size"]], False)
+    _dense(r, sd, "reference_encoder.feature_wise_affine.linear", 2 * dm, dm, bias=False)
+    # keep FiLM modulation O(0.3) so (gamma+1) stays well away from 0
+    sd["reference_encoder.feature_wise_affine.linear.weight"] *= 2.0
+
+    stats = C.STATS[dataset]
+    nb = model_config["variance_embedding"]["n_bins"]
+    sd["variance_adaptor.pitch_bins"] = torch.linspace(stats["pitch"][0], stats["pitch"][1], nb - 1)
+    sd["variance_adaptor.energy_bins"] = torch.linspace(stats["energy"][0], stats["energy"][1], nb - 1)
+    for name in ("duration_predictor", "pitch_predictor", "energy_predictor"):
+        _variance_predictor(r, sd, f"variance_adaptor.{name}", d, vp["filter_size"], vp["kernel_size"])
+    sd["variance_adaptor.duration_predictor.linear_layer.bias"] = torch.full((1,), float(duration_bias))
+    # spread pitch / energy predictions over many buckets instead of two or three
+    sd["variance_adaptor.pitch_predictor.linear_layer.weight"] *= 8.0
+    sd["variance_adaptor.energy_predictor.linear_layer.weight"] *= 8.0
+    sd["variance_adaptor.pitch_embedding.weight"] = r.normal((nb, d))
+    sd["variance_adaptor.energy_embedding.weight"] = r.normal((nb, d))
+
+    dd = tr["decoder_hidden"]
+    sd["decoder.position_enc"] = sinusoid_table(n_pos, dd).unsqueeze(0)
+    for i in range(tr["decoder_layer"]):
+        _fft_block(r, sd, f"decoder.layer_stack.{i}", dd, tr["conv_filter_size"], tr["conv_kernel_size"], True)
+
+    _dense(r, sd, "mel_linear", n_mel, dd)
+    chans = [n_mel, 512, 512, 512, 512, n_mel]
+    for i in range(5):
+        p = f"postnet.convolutions.{i}"
+        _dense(r, sd, f"{p}.0.conv", chans[i + 1], chans[i], 5)
+        sd[f"{p}.1.weight"] = 1.0 + r.uniform((chans[i + 1],), 0.2)
+        sd[f"{p}.1.bias"] = r.uniform((chans[i + 1],), 0.1)
+        sd[f"{p}.1.running_mean"] = r.uniform((chans[i + 1],), 0.1)
+        sd[f"{p}.1.running_var"] = 1.0 + r.uniform((chans[i + 1],), 0.3)
+        sd[f"{p}.1.num_batches_tracked"] = torch.tensor(0, dtype=torch.int64)
+
+    if model_config["multi_speaker"]:
+        sd["speaker_emb.weight"] = r.normal((C.N_SPEAKERS[dataset], d), std=0.3)
+    return sd
+
+
+def hifigan_state_dict(h=None, seed=4321, gain=1.0):
+    """Generator state_dict in checkpoint form (weight_g, weight_v, bias) - hifigan/models.py:113-147."""
+    h = h or C.hifigan_config()
+    r = _Rng(seed)
+    sd = {}
+
+    def wn_conv(name, out_c, in_c, k, transposed=False, g=1.0):
+        # weight_norm(dim=0): one gain per slice along dim 0.  For a Conv1d row norm g the output
+        # variance is g^2 * var(x) for iid x, so g ~ 1 preserves variance.
+        shape = (in_c, out_c, k) if transposed else (out_c, in_c, k)
+        v = r.normal(shape)
+        sd[name + ".weight_v"] = v
+        sd[name + ".weight_g"] = g * (1.0 + r.uniform((shape[0], 1, 1), 0.1))
+        sd[name + ".bias"] = r.uniform((out_c,), 0.05)
+
+    c0 = h["upsample_initial_channel"]
+    wn_conv("conv_pre", c0, h["num_mels"], 7, g=gain)
+    ch = c0
+    for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+        cin, cout = c0 // (2 ** i), c0 // (2 ** (i + 1))
+        wn_conv(f"ups.{i}", cout, cin, k, transposed=True, g=1.4 * gain * math.sqrt(u * cout / cin))
+        ch = cout
+        for j, (rk, rd) in enumerate(zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"])):
+            idx = i * len(h["resblock_kernel_sizes"]) + j
+            for m in range(len(rd)):
+                wn_conv(f"resblocks.{idx}.convs1.{m}", ch, ch, rk, g=0.9 * gain)
+                wn_conv(f"resblocks.{idx}.convs2.{m}", ch, ch, rk, g=0.35 * gain)
+    wn_conv("conv_post", 1, ch, 7, g=0.5 * gain)
+    return sd
+
+
+def fold_weight_norm(sd):
+    """weight = g * v / ||v|| per output row (dim 0) - what remove_weight_norm() leaves behind
+    (hifigan/models.py:105-109, 167-174).  Keys already holding a plain ``weight`` pass through."""
+    out = {}
+    for k, v in sd.items():
+        if k.endswith(".weight_v"):
+            base = k[: -len(".weight_v")]
+            g = sd[base + ".weight_g"]
+            norm = v.flatten(1).norm(dim=1).view(-1, *([1] * (v.dim() - 1)))
+            out[base + ".weight"] = v * (g / norm)
+        elif k.endswith(".weight_g"):
+            continue
+        else:
+            out[k] = v
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# synthetic batches
+# ---------------------------------------------------------------------------------------------
+def make_batch(batch, src_len_range, ref_len_range, n_speakers=1, seed=1, n_mel=80, fixed_ref_len=None):
+    """Batch tuple in the reference's layout (dataset.py:198-217 minus ids/raw_texts):
+    speakers[B] i64, texts[B,L] i64 (0 = PAD beyond src_len), src_lens[B] i64, max_src_len,
+    mels[B,Tr,80] f32 (zero beyond mel_len, utils/tools.py:298-316), mel_lens[B] i64, max_mel_len."""
+    r = _Rng(seed)
+    lo, hi = src_len_range
+    src_lens = r.randint(lo, hi + 1, (batch,))
+    if fixed_ref_len is not None:
+        mel_lens = torch.full((batch,), int(fixed_ref_len), dtype=torch.int64)
+    else:
+        mel_lens = r.randint(ref_len_range[0], ref_len_range[1] + 1, (batch,))
+    L = int(src_lens.max())
+    Tr = int(mel_lens.max())
+    texts = r.randint(1, C.N_SRC_VOCAB, (batch, L))
+    texts = texts * (torch.arange(L)[None, :] < src_lens[:, None])
+    mels = r.normal((batch, Tr, n_mel))
+    mels = mels * (torch.arange(Tr)[None, :, None] < mel_lens[:, None, None])
+    speakers = r.randint(0, n_speakers, (batch,))
+    return {
+        "speakers": speakers,
+        "texts": texts,
+        "src_lens": src_lens,
+        "max_src_len": L,
+        "mels": mels,
+        "mel_lens": mel_lens,
+        "max_mel_len": Tr,
+    }
+
+
+WORKLOADS = {
+    # name: (dataset, batch, src_len_range, ref_len_range, fixed_ref_len, vocoder)
+    "tiny": ("BC2013", 3, (5, 12), (9, 24), None, True),
+    "tiny_ms": ("LibriTTS", 2, (4, 9), (8, 16), None, True),
+    "cfg1": ("LJSpeech", 16, (80, 120), (200, 400), None, False),
+    "cfg2": ("BC2013", 64, (80, 120), (800, 800), 800, False),
+    "cfg3": ("LibriTTS", 32, (80, 120), (200, 400), None, True),
+}
+
+
+def make_workload(name, seed=1):
+    ds, b, sl, rl, fixed, voc = WORKLOADS[name]
+    batch = make_batch(b, sl, rl, n_speakers=C.N_SPEAKERS[ds], seed=seed, fixed_ref_len=fixed)
+    return ds, batch, voc
