@@ -1,0 +1,215 @@
+/*
+ * speakingstyle_b200 - C ABI of the B200-native text -> mel -> wave inference path.
+ *
+ * The reference (lordzuko/SpeakingStyle) is pure Python/PyTorch and has no FFI of its own
+ * (SURVEY.md section 8b); each entry point below replaces the ATen call sequence of the reference lines it
+ * cites, so that a Python `nn.Module` with the reference's signature can be a thin shim over it
+ * (speakingstyle_b200/ holds those shims; INTEGRATION.md shows the ctypes binding).
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *   - activations are channels-last, row-major: [B, S, C] with C contiguous (the reference's own
+ *     layout between modules; its transposes around Conv1d disappear);
+ *   - the library never allocates or frees device memory and keeps no mutable global state:
+ *     the caller owns inputs, outputs and workspaces (ss_*_workspace_bytes tells the size);
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), nothing synchronises
+ *     unless stated;
+ *   - return value: SS_OK (0) or a negative ss_status; ss_status_string() names it and
+ *     ss_last_error() returns a per-thread message with the failing check.  No exceptions cross
+ *     the boundary; there is no CPU fallback - without a CUDA device every compute entry point
+ *     returns SS_ERR_CUDA.
+ */
+#ifndef SPEAKINGSTYLE_B200_H_
+#define SPEAKINGSTYLE_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SS_API __attribute__((visibility("default")))
+
+typedef enum {
+  SS_OK = 0,
+  SS_ERR_INVALID = -1,     /* bad shape / null pointer / unsupported combination */
+  SS_ERR_UNSUPPORTED = -2, /* valid request this build has no kernel for */
+  SS_ERR_CUDA = -3,        /* a CUDA runtime call or launch failed */
+  SS_ERR_ALIGNMENT = -4    /* pointer or stride not aligned as documented */
+} ss_status;
+
+/* activation codes shared by the epilogues */
+enum { SS_ACT_NONE = 0, SS_ACT_RELU = 1, SS_ACT_TANH = 2, SS_ACT_LRELU = 3 };
+/* element types of activations at the boundary */
+enum { SS_F32 = 0, SS_BF16 = 1 };
+
+SS_API const char* ss_status_string(int status);
+SS_API const char* ss_last_error(void);
+SS_API int ss_version(void);
+/* Number of kernels this library has launched from the calling process (bench.py's
+ * `gpu_launches`); ss_launch_count_reset() zeroes it. */
+SS_API int64_t ss_launch_count(void);
+SS_API void ss_launch_count_reset(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Encoder input: out[b,l,:] = emb[texts[b,l],:] + pe[l,:]
+ * replaces transformer/Models.py:89-91 (src_word_emb + position_enc; PAD row of emb is zero).
+ * texts [B,L] int64, emb [V,D] f32, pe [>=L, D] f32, out [B,L,D] f32.  D % 4 == 0.
+ * ------------------------------------------------------------------------------------------ */
+SS_API int ss_embed_posenc(const int64_t* texts, const float* emb, const float* pe, float* out, int B, int L,
+                           int D, int V, void* stream);
+
+/* out[b,t,:] = x[b,t,:] + pe[t,:]  - the position add of transformer/Models.py:158-160 for a
+ * caller that uses Decoder on its own (inside FastSpeech2 the LengthRegulator kernel fuses it). */
+SS_API int ss_add_posenc(const float* x, const float* pe, float* out, int B, int S, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * 1-D convolution / linear layer as an implicit GEMM over channels-last activations, fp32 FMA
+ * accumulation (the accuracy class of the reference; used wherever an integer output is decided).
+ * replaces nn.Conv1d / nn.Linear / nn.ConvTranspose1d call sites:
+ *   transformer/SubLayers.py:39-41,54 (w_qs/w_ks/w_vs/fc), :88 (w_1, w_2),
+ *   model/modules.py:216-237 (predictor convs), :329-339 (reference-encoder conv stack),
+ *   model/blocks.py:68 (LinearNorm), model/fastspeech2.py:105 (mel_linear),
+ *   transformer/Layers.py:140-148 (PostNet, BatchNorm folded by the caller),
+ *   hifigan/models.py:150 (conv_pre), :152-153 (ups, via the phase form below), :96-103 (ResBlock).
+ *
+ * For output row t of batch b and tap j the input row is  t + j*dilation - pad  (zero outside
+ * [0, S_in)).  acc[n] = sum_{j,ci} in_act(x[b, row, ci]) * w[(j*Cin + ci)*Cout + n].
+ * epilogue: v = act(acc + bias[n]); v += residual[...] (if given); v = 0 where t >= lens[b] (if
+ * given); y[...] = v;  accum[...] = (accum_init ? 0 : accum[...]) + accum_scale * v (if given).
+ * The output element (b, t, n) lives at  y + b*y_batch_stride + y_offset + t*y_row_stride + n  and is
+ * written only if  0 <= y_offset + t*y_row_stride + n < y_batch_elems  (this window is what lets a
+ * ConvTranspose1d run as a k/stride-tap convolution with Cout = stride*C_out whose rows interleave
+ * into the up-sampled sequence); residual and accum use the same addressing.
+ * Requirements: Cin % 4 == 0, Cout % 4 == 0, strides and offsets % 4 == 0, 16-byte aligned pointers.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const float* x;          /* [B, S_in, Cin] */
+  int64_t x_batch_stride;  /* elements */
+  int64_t x_row_stride;    /* elements, >= Cin */
+  const float* w;          /* [k*Cin, Cout] packed by the caller */
+  const float* bias;       /* [Cout] or NULL */
+  const float* residual;   /* same addressing as y, or NULL */
+  const int32_t* lens;     /* [B] valid rows, or NULL */
+  float* y;
+  float* accum;            /* or NULL */
+  int64_t y_batch_stride, y_row_stride, y_offset, y_batch_elems;
+  int32_t B, S_in, S_out, Cin, Cout, k, dilation, pad;
+  int32_t in_act;          /* SS_ACT_NONE or SS_ACT_LRELU, applied to x on load */
+  float in_slope;
+  int32_t act;             /* SS_ACT_* applied after bias */
+  float slope;
+  float accum_scale;
+  int32_t accum_init;
+} ss_conv1d_f32_params;
+SS_API int ss_conv1d_f32(const ss_conv1d_f32_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Row-wise LayerNorm with the element-wise steps the reference applies around it, one pass:
+ *   v = x (+ residual); v = relu(v) if pre_relu; y = LN(v)*ln_w + ln_b  (eps 1e-5, biased var);
+ *   FiLM (model/blocks.py:60-62): y = (s_gamma*gamma[b,:] + 1)*y + s_beta*beta[b,:] if gamma given;
+ *   y = 0 where t >= lens[b] (masked_fill, transformer/Layers.py:27-28,34-35; modules.py:370-371);
+ *   y += pe[t,:] if pe given (modules.py:385-387).
+ * replaces nn.LayerNorm at SubLayers.py:55,91; modules.py:231,243,334.  C in {256, 1024}.
+ * s_gamma/s_beta are device scalars (the learnable FiLM scales).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const float* x;
+  const float* residual; /* or NULL */
+  const float* ln_w;
+  const float* ln_b;
+  const float* gamma;    /* [B, C] or NULL */
+  const float* beta;     /* [B, C] */
+  const float* s_gamma;  /* [1] */
+  const float* s_beta;   /* [1] */
+  const int32_t* lens;   /* [B] or NULL */
+  const float* pe;       /* [>=S, C] or NULL */
+  float* y;
+  int32_t B, S, C, pre_relu;
+} ss_layernorm_params;
+SS_API int ss_layernorm(const ss_layernorm_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Masked multi-head self-attention, softmax fused, scores never stored.
+ * replaces transformer/SubLayers.py:42-52 + transformer/Modules.py:14-23:
+ *   ctx[b,q,h*dk:(h+1)*dk] = softmax_k( Q_h[b,q,:].K_h[b,k,:] / sqrt(dk),  k < lens[b] ) . V_h[b,k,:]
+ * qkv [B,S,3*D] f32 holds Q | K | V (the three projections computed by ONE ss_conv1d_f32 call with
+ * concatenated weights); head h uses columns h*dk.. of each third.  ctx [B,S,D] f32.
+ * Query rows >= lens[b] are written as zeros (the reference masks them right after the following
+ * LayerNorm).  dk in {32, 128}; D = H*dk.
+ * ------------------------------------------------------------------------------------------ */
+SS_API int ss_attention_f32(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, int dk,
+                            void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Variance predictor tail: LayerNorm_2 -> [FiLM] -> Linear(C->1) -> mask, one warp per token.
+ * replaces model/modules.py:243-258 (h is the output of conv1d_2 + ReLU).
+ * pred[b,l] = (lens && l >= lens[b]) ? 0 : dot(FiLM(LN(h[b,l,:])), lin_w) + lin_b
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const float* h;       /* [B, L, C] */
+  const float* ln_w;
+  const float* ln_b;
+  const float* gamma;   /* [B, C] or NULL */
+  const float* beta;
+  const float* s_gamma;
+  const float* s_beta;
+  const float* lin_w;   /* [C] */
+  const float* lin_b;   /* [1] */
+  const int32_t* lens;
+  float* pred;          /* [B, L] */
+  int32_t B, L, C;
+} ss_predictor_head_params;
+SS_API int ss_predictor_head(const ss_predictor_head_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * pitch / energy quantisation + embedding add, in place:
+ *   pred[b,l] *= control;  idx = #(edges < pred[b,l])  (torch.bucketize right=False; NaN -> n_edges);
+ *   x[b,l,:] += table[idx,:];  idx_out[b,l] = idx (if idx_out given)
+ * replaces model/modules.py:88-91,126 and :99-102,131.  edges ascending, n_edges <= 1024.
+ * ------------------------------------------------------------------------------------------ */
+SS_API int ss_bucket_embed_add(float* pred, float control, const float* edges, int n_edges, const float* table,
+                               float* x, int32_t* idx_out, int B, int L, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Duration rounding + LengthRegulator, two calls around ONE host read of mel_len_expand:
+ *
+ * ss_duration_scan  (model/modules.py:137-140,143 and the int() / max(.,0) of :193-194)
+ *   d_rounded[b,l] = clamp(round_half_even(exp(log_d[b,l]) - 1) * d_control, min 0)    (if log_d given;
+ *                    otherwise `d_rounded` is read as the caller's durations, e.g. d_targets)
+ *   reps = max(trunc(d_rounded), 0);  ends[b,l] = inclusive prefix sum of reps   (int32)
+ *   mel_len_expand[b] = ends[b,L-1]                (what LengthRegulator.LR returns, modules.py:181)
+ *   mel_len_sum[b]    = (int32) sum_l d_rounded[b,l]  in float32, index order   (modules.py:143)
+ *
+ * ss_length_regulate  (model/modules.py:174-197 + utils/tools.py:319-337, + transformer/Models.py:158-160)
+ *   out[b,t,:] = x[b, i, :] (+ pe[t,:] if pe given)   with i = #{ j : ends[b,j] <= t }   for t < ends[b,L-1]
+ *   out[b,t,:] = 0 (+ pe[t,:])                         for the padding rows up to T
+ *   mel2phone[b,t] = i, or -1 on padding (if given).  C % 4 == 0.
+ * ------------------------------------------------------------------------------------------ */
+SS_API int ss_duration_scan(const float* log_d, float d_control, float* d_rounded, int32_t* ends,
+                            int32_t* mel_len_expand, int32_t* mel_len_sum, int B, int L, void* stream);
+SS_API int ss_length_regulate(const float* x, const int32_t* ends, const float* pe, float* out,
+                              int32_t* mel2phone, int B, int L, int T, int C, void* stream);
+
+/* mask[b,t] = (t >= lens[b])  as bytes (torch.bool storage) - utils/tools.py:110-118 */
+SS_API int ss_length_mask(const int32_t* lens, uint8_t* mask, int B, int T, void* stream);
+
+/* out[b,:] = (1/S) * sum_t x[b,t,:]   over the PADDED length S (model/modules.py:398). */
+SS_API int ss_mean_pool(const float* x, float* out, int B, int S, int C, void* stream);
+
+/* x[b,l,:] += table[ids[b],:] for every l, padding included (model/fastspeech2.py:74-77). */
+SS_API int ss_add_speaker(float* x, const int64_t* ids, const float* table, int B, int L, int C, int n_speakers,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * HiFi-GAN output head: wave = tanh(conv_post(leaky_relu(x, 0.01)))  (hifigan/models.py:161-163)
+ * x [B,T,C] f32 (C <= 64), w [k*C] packed tap-major, one output channel.
+ * wave [B,T] f32 (if given) and/or pcm [B,T] int16 = trunc(wave * pcm_scale) (utils/model.py:105-108).
+ * ------------------------------------------------------------------------------------------ */
+SS_API int ss_hifigan_post(const float* x, const float* w, const float* bias, float* wave, int16_t* pcm,
+                           float pcm_scale, float in_slope, int B, int T, int C, int k, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPEAKINGSTYLE_B200_H_ */

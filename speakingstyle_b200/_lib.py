@@ -1,0 +1,93 @@
+"""ctypes binding of include/speakingstyle_b200.h.
+
+The shared library is the product: if it is missing or cannot be loaded this module raises - there
+is no eager/PyTorch fallback anywhere in the package.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libspeakingstyle_b200.so")
+
+vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+ACT_NONE, ACT_RELU, ACT_TANH, ACT_LRELU = 0, 1, 2, 3
+
+
+class Conv1dF32Params(C.Structure):
+    _fields_ = [
+        ("x", vp), ("x_batch_stride", i64), ("x_row_stride", i64), ("w", vp), ("bias", vp), ("residual", vp),
+        ("lens", vp), ("y", vp), ("accum", vp), ("y_batch_stride", i64), ("y_row_stride", i64), ("y_offset", i64),
+        ("y_batch_elems", i64), ("B", i32), ("S_in", i32), ("S_out", i32), ("Cin", i32), ("Cout", i32), ("k", i32),
+        ("dilation", i32), ("pad", i32), ("in_act", i32), ("in_slope", f32), ("act", i32), ("slope", f32),
+        ("accum_scale", f32), ("accum_init", i32),
+    ]
+
+
+class LayerNormParams(C.Structure):
+    _fields_ = [
+        ("x", vp), ("residual", vp), ("ln_w", vp), ("ln_b", vp), ("gamma", vp), ("beta", vp), ("s_gamma", vp),
+        ("s_beta", vp), ("lens", vp), ("pe", vp), ("y", vp), ("B", i32), ("S", i32), ("C", i32), ("pre_relu", i32),
+    ]
+
+
+class PredictorHeadParams(C.Structure):
+    _fields_ = [
+        ("h", vp), ("ln_w", vp), ("ln_b", vp), ("gamma", vp), ("beta", vp), ("s_gamma", vp), ("s_beta", vp),
+        ("lin_w", vp), ("lin_b", vp), ("lens", vp), ("pred", vp), ("B", i32), ("L", i32), ("C", i32),
+    ]
+
+
+_SIGNATURES = {
+    "ss_status_string": (C.c_char_p, [C.c_int]),
+    "ss_last_error": (C.c_char_p, []),
+    "ss_version": (C.c_int, []),
+    "ss_launch_count": (i64, []),
+    "ss_launch_count_reset": (None, []),
+    "ss_embed_posenc": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_add_posenc": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_conv1d_f32": (C.c_int, [C.POINTER(Conv1dF32Params), vp]),
+    "ss_layernorm": (C.c_int, [C.POINTER(LayerNormParams), vp]),
+    "ss_attention_f32": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_predictor_head": (C.c_int, [C.POINTER(PredictorHeadParams), vp]),
+    "ss_bucket_embed_add": (C.c_int, [vp, f32, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_duration_scan": (C.c_int, [vp, f32, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
+    "ss_length_regulate": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_length_mask": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
+    "ss_mean_pool": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_add_speaker": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_hifigan_post": (C.c_int, [vp, vp, vp, vp, vp, f32, f32, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+}
+
+_lib = None
+
+
+def exported_names():
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """The loaded C-ABI library.  Raises (loudly) when the CUDA extension has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m speakingstyle_b200.build` "
+                "(or __graft_entry__.build()).  speakingstyle_b200 has no CPU or eager fallback.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the header and the library diverge
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+class SSError(RuntimeError):
+    pass
+
+
+def check(status):
+    if status != 0:
+        h = lib()
+        raise SSError(f"{h.ss_status_string(status).decode()} ({status}): {h.ss_last_error().decode()}")

@@ -3,7 +3,7 @@
 The reference passes three YAML dicts around (synthesize.py:235-240); only two of them are read
 by the path (model/fastspeech2.py:16, model/modules.py:23-81, 310-322, transformer/Models.py:36-51).
 The values below restate the shipped YAML/JSON files so that tests and the benchmark can run on a
-machine where /root/reference does not exist:
+machine where the reference checkout does not exist:
 
 * config/BC2013/model.yaml (the only model.yaml that carries a ``reference_encoder`` block, lines 13-20)
 * config/{LJSpeech,LibriTTS}/model.yaml + that block

@@ -1,0 +1,166 @@
+// Duration rounding, prefix scan and the LengthRegulator frame expansion.
+//
+// The reference does this with a Python double loop and one .item() host sync per phoneme
+// (model/modules.py:174-197).  Here: one tiny scan kernel (a warp per utterance) produces the
+// integer repeat counts' inclusive prefix sums, the host reads B int32 once to size the output,
+// and one bandwidth-bound kernel writes every output row exactly once - gathered source row,
+// optional decoder position row added on the fly (transformer/Models.py:158-160), zeros on the
+// padding - with 128-bit streaming stores.  The source rows (B*L*C floats) are re-read ~8x but
+// stay in L2; algorithmic HBM bytes = 4*C*(sum_b src_len_b + B*T) + 4*B*L + 4*B.
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float round_duration(float log_d, float control) {
+  // same op order as the reference: exp, minus one, round half-to-even, times control, clamp
+  const float v = rintf(expf(log_d) - 1.0f) * control;
+  return v < 0.0f ? 0.0f : v;  // keeps NaN and -0.0 like torch.clamp(min=0)
+}
+
+__global__ void __launch_bounds__(128) duration_scan_kernel(const float* __restrict__ log_d, float control,
+                                                            float* __restrict__ d_rounded,
+                                                            int32_t* __restrict__ ends,
+                                                            int32_t* __restrict__ mel_len_expand,
+                                                            int32_t* __restrict__ mel_len_sum, int B, int L) {
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  const int lane = threadIdx.x & 31;
+  const float* ld = log_d ? log_d + (int64_t)b * L : nullptr;
+  float* dr = d_rounded + (int64_t)b * L;
+  int32_t* eb = ends + (int64_t)b * L;
+  int carry = 0;
+  for (int base = 0; base < L; base += 32) {
+    const int l = base + lane;
+    int reps = 0;
+    if (l < L) {
+      float d;
+      if (ld) {
+        d = round_duration(ld[l], control);
+        dr[l] = d;
+      } else {
+        d = dr[l];
+      }
+      reps = max((int)d, 0);  // int(): truncation toward zero
+    }
+    int incl = reps;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    if (l < L) eb[l] = carry + incl;
+    carry += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) {
+    if (mel_len_expand) mel_len_expand[b] = carry;
+    if (mel_len_sum) {
+      // float32 running sum in index order, then .int() (modules.py:143)
+      float s = 0.0f;
+      for (int l = 0; l < L; ++l) s += ld ? round_duration(ld[l], control) : dr[l];
+      mel_len_sum[b] = (int32_t)s;
+    }
+  }
+}
+
+constexpr int LR_WARPS = 8;
+constexpr int LR_FRAMES_PER_WARP = 4;
+constexpr int LR_FRAMES_PER_CTA = LR_WARPS * LR_FRAMES_PER_WARP;
+
+__global__ void __launch_bounds__(LR_WARPS * 32) length_regulate_kernel(const float* __restrict__ x,
+                                                                        const int32_t* __restrict__ ends,
+                                                                        const float* __restrict__ pe,
+                                                                        float* __restrict__ out,
+                                                                        int32_t* __restrict__ mel2phone, int L,
+                                                                        int T, int C) {
+  extern __shared__ int32_t s_ends[];
+  const int b = blockIdx.y;
+  const int32_t* eb = ends + (int64_t)b * L;
+  for (int i = threadIdx.x; i < L; i += blockDim.x) s_ends[i] = eb[i];
+  __syncthreads();
+  const int total = L > 0 ? s_ends[L - 1] : 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tbase = blockIdx.x * LR_FRAMES_PER_CTA + warp * LR_FRAMES_PER_WARP;
+
+  int src[LR_FRAMES_PER_WARP];
+#pragma unroll
+  for (int f = 0; f < LR_FRAMES_PER_WARP; ++f) {
+    const int t = tbase + f;
+    int idx = -1;
+    if (t < T && t < total) {
+      // number of prefix sums <= t  (upper bound); all lanes search the same value
+      int lo = 0, hi = L;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (s_ends[mid] <= t) lo = mid + 1; else hi = mid;
+      }
+      idx = lo;
+    }
+    src[f] = idx;
+    if (mel2phone && lane == 0 && t < T) mel2phone[(int64_t)b * T + t] = idx;
+  }
+
+  const int C4 = C >> 2;
+  const float4* xb = reinterpret_cast<const float4*>(x + (int64_t)b * L * C);
+  for (int c = lane; c < C4; c += 32) {
+    float4 v[LR_FRAMES_PER_WARP];
+#pragma unroll
+    for (int f = 0; f < LR_FRAMES_PER_WARP; ++f) {
+      v[f] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (src[f] >= 0) v[f] = __ldg(xb + (int64_t)src[f] * C4 + c);
+    }
+    if (pe) {
+#pragma unroll
+      for (int f = 0; f < LR_FRAMES_PER_WARP; ++f) {
+        const int t = tbase + f;
+        if (t < T) {
+          const float4 q = __ldg(reinterpret_cast<const float4*>(pe + (int64_t)t * C) + c);
+          v[f].x += q.x; v[f].y += q.y; v[f].z += q.z; v[f].w += q.w;
+        }
+      }
+    }
+#pragma unroll
+    for (int f = 0; f < LR_FRAMES_PER_WARP; ++f) {
+      const int t = tbase + f;
+      if (t < T) ss::st_stream(reinterpret_cast<float4*>(out + ((int64_t)b * T + t) * C) + c, v[f]);
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int ss_duration_scan(const float* log_d, float d_control, float* d_rounded, int32_t* ends, int32_t* mel_len_expand,
+                     int32_t* mel_len_sum, int B, int L, void* stream) {
+  SS_REQUIRE(d_rounded && ends, SS_ERR_INVALID, "ss_duration_scan: null pointer");
+  SS_REQUIRE(B > 0 && L > 0, SS_ERR_INVALID, "ss_duration_scan: bad shape B=%d L=%d", B, L);
+  const int warps = 4;
+  duration_scan_kernel<<<(B + warps - 1) / warps, warps * 32, 0, (cudaStream_t)stream>>>(
+      log_d, d_control, d_rounded, ends, mel_len_expand, mel_len_sum, B, L);
+  SS_CHECK_LAUNCH("ss_duration_scan");
+  return SS_OK;
+}
+
+int ss_length_regulate(const float* x, const int32_t* ends, const float* pe, float* out, int32_t* mel2phone, int B,
+                       int L, int T, int C, void* stream) {
+  SS_REQUIRE(x && ends && out, SS_ERR_INVALID, "ss_length_regulate: null pointer");
+  SS_REQUIRE(B > 0 && L > 0 && T >= 0 && C > 0 && C % 4 == 0, SS_ERR_INVALID,
+             "ss_length_regulate: bad shape B=%d L=%d T=%d C=%d", B, L, T, C);
+  SS_REQUIRE(B <= 65535, SS_ERR_UNSUPPORTED, "ss_length_regulate: B > 65535");
+  SS_REQUIRE((size_t)L * 4 <= 200 * 1024, SS_ERR_UNSUPPORTED, "ss_length_regulate: L=%d too long for smem", L);
+  SS_REQUIRE(ss::aligned16(x) && ss::aligned16(out) && ss::aligned16(pe), SS_ERR_ALIGNMENT,
+             "ss_length_regulate: pointers must be 16-byte aligned");
+  if (T == 0) return SS_OK;
+  const size_t smem = (size_t)L * sizeof(int32_t);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(length_regulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_length_regulate: smem opt-in");
+  }
+  dim3 grid((T + LR_FRAMES_PER_CTA - 1) / LR_FRAMES_PER_CTA, B);
+  length_regulate_kernel<<<grid, LR_WARPS * 32, smem, (cudaStream_t)stream>>>(x, ends, pe, out, mel2phone, L, T, C);
+  SS_CHECK_LAUNCH("ss_length_regulate");
+  return SS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,106 @@
+"""Drop-in for model/fastspeech2.py: ``FastSpeech2(preprocess_config, model_config)`` with the
+reference's forward signature, 10-tuple return and state_dict keys, running on hand-written
+sm_100a kernels through the C ABI.  Inference (eval / no_grad) only; no CPU fallback."""
+import json
+import os
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .modules import ReferenceEncoder, VarianceAdaptor, _as_lens
+from .transformer import Decoder, Dense, Encoder, ParamCache, PostNet, pack_conv
+
+
+class FastSpeech2(nn.Module, ParamCache):
+    """model/fastspeech2.py:13-120."""
+
+    def __init__(self, preprocess_config, model_config):
+        super().__init__()
+        self.model_config = model_config
+        self.encoder = Encoder(model_config)
+        self.reference_encoder = ReferenceEncoder(preprocess_config, model_config)
+        self.variance_adaptor = VarianceAdaptor(preprocess_config, model_config)
+        self.decoder = Decoder(model_config)
+        self.mel_linear = Dense(model_config["transformer"]["decoder_hidden"],
+                                preprocess_config["preprocessing"]["mel"]["n_mel_channels"])
+        self.postnet = PostNet()
+        self.speaker_emb = None
+        if model_config["multi_speaker"]:
+            with open(os.path.join(preprocess_config["path"]["preprocessed_path"], "speakers.json"), "r") as f:
+                n_speaker = len(json.load(f))
+            self.speaker_emb = nn.Embedding(n_speaker, model_config["transformer"]["encoder_hidden"])
+        for p in self.parameters():
+            p.requires_grad_(False)
+        self.eval()
+
+    def _pack(self):
+        return {"mel_w": pack_conv(self.mel_linear.weight)}
+
+    def packed(self):  # only mel_linear's own parameters key this cache
+        srcs = [self.mel_linear.weight]
+        key = tuple((t.data_ptr(), t._version) for t in srcs)
+        if self.__dict__.get("_pack_key") != key:
+            with torch.no_grad():
+                self.__dict__["_pack_val"] = self._pack()
+            self.__dict__["_pack_key"] = key
+        return self.__dict__["_pack_val"]
+
+    @property
+    def device(self):
+        return self.mel_linear.weight.device
+
+    def train(self, mode=True):
+        if mode:
+            raise NotImplementedError("speakingstyle_b200.FastSpeech2 is an inference path; training "
+                                      "(train.py:45-101) stays with the reference implementation")
+        return super().train(False)
+
+    @torch.no_grad()
+    def forward(self, speakers, texts, src_lens, max_src_len, mels=None, mel_lens=None, max_mel_len=None,
+                p_targets=None, e_targets=None, d_targets=None, p_control=1.0, e_control=1.0, d_control=1.0,
+                return_extra=False):
+        dev = self.device
+        if dev.type != "cuda":
+            raise RuntimeError("speakingstyle_b200.FastSpeech2 needs a CUDA device (.to('cuda')); no CPU fallback")
+        if mels is None or mel_lens is None:
+            # the reference dereferences mel_masks / mask unconditionally (fastspeech2.py:79, modules.py:384)
+            raise AttributeError("a reference mel (mels, mel_lens, max_mel_len) is mandatory at inference")
+        if p_targets is not None or e_targets is not None:
+            raise NotImplementedError("p_targets / e_targets are training inputs")
+        nb = True
+        speakers = torch.as_tensor(speakers).to(dev, torch.int64, non_blocking=nb).contiguous()
+        texts = torch.as_tensor(texts).to(dev, torch.int64, non_blocking=nb).contiguous()
+        src_lens_in = torch.as_tensor(src_lens).to(dev, non_blocking=nb)
+        mels = torch.as_tensor(mels).to(dev, torch.float32, non_blocking=nb).contiguous()
+        max_src_len, max_mel_len = int(max_src_len), int(max_mel_len)
+        if texts.shape[1] != max_src_len or mels.shape[1] != max_mel_len:
+            raise ValueError("texts / mels must be padded to max_src_len / max_mel_len (dataset.py:198-217)")
+        src_lens32 = _as_lens(src_lens_in, dev)
+        ref_lens32 = _as_lens(torch.as_tensor(mel_lens), dev)
+
+        src_masks = ops.length_mask(src_lens32, max_src_len)
+        gammas, betas = self.reference_encoder(mels, max_mel_len, None, lens=ref_lens32)
+        x = self.encoder(texts, None, gammas, betas, lens=src_lens32)
+        if self.speaker_emb is not None:
+            x = ops.add_speaker(x, speakers, self.speaker_emb.weight)  # pads included (fastspeech2.py:74-77)
+
+        (x, p_pred, e_pred, log_d, d_rounded, mel_lens_out, mel_masks, extra) = self.variance_adaptor(
+            x, src_masks, None, max_mel_len, p_targets, e_targets, d_targets, p_control, e_control, d_control,
+            gammas, betas, src_lens=src_lens32, decoder_pe=lambda T: self.decoder._pe(T, self.decoder.d_model),
+            return_extra=True, inplace=True)
+        if d_targets is not None:
+            raise NotImplementedError("teacher-forced durations go through LengthRegulator directly (SURVEY 8f-3)")
+        T = extra["T"]
+        # decoder key mask = mask from mel_len cropped to the expanded length (Models.py:154-162)
+        dec_lens = torch.clamp(mel_lens_out, max=T) if mel_masks.shape[1] != T else mel_lens_out
+        if mel_masks.shape[1] != T:
+            mel_masks = ops.length_mask(dec_lens, T)
+        x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True)
+        mel = ops.conv1d(x, self.packed()["mel_w"], self.mel_linear.bias)
+        postnet_mel = self.postnet(mel, residual=mel)
+        out = (mel, postnet_mel, p_pred, e_pred, log_d, d_rounded, src_masks, mel_masks, src_lens_in, mel_lens_out)
+        if return_extra:
+            extra.update(gammas=gammas, betas=betas)
+            return out, extra
+        return out

@@ -1,0 +1,184 @@
+"""Drop-in for hifigan/models.py ``Generator`` (HiFi-GAN V1) over the C ABI.  Inference only.
+
+``Generator(h).forward(mel [B,80,T]) -> wave [B,1,256*T]`` with the reference's attribute names
+(conv_pre, ups, resblocks, conv_post), ``remove_weight_norm()`` and a ``state_dict`` that accepts
+either checkpoint form (``weight_g``/``weight_v``, utils/model.py:81-92) or folded ``weight`` keys.
+
+Kernel mapping:
+  conv_pre                  -> ss_conv1d (k=7)
+  leaky_relu + ConvTranspose -> ss_conv1d in phase form: k/stride taps, stride*C_out GEMM columns
+                               whose rows interleave into the up-sampled sequence; lrelu on load
+  ResBlock conv pairs       -> ss_conv1d with lrelu on load; c1's epilogue needs nothing else, c2's
+                               epilogue adds the residual; the last c2 of each ResBlock also
+                               accumulates (1/3) into the stage mean (xs / num_kernels)
+  leaky_relu(0.01) + conv_post + tanh -> ss_hifigan_post (optionally straight to int16 PCM)
+"""
+import torch
+import torch.nn as nn
+
+from . import ops
+from .configs import AttrDict  # noqa: F401  (same helper as hifigan/__init__.py)
+from .transformer import ParamCache, pack_conv
+
+LRELU_SLOPE = 0.1
+
+
+def get_padding(kernel_size, dilation=1):
+    return int((kernel_size * dilation - dilation) / 2)
+
+
+class WNConv(nn.Module):
+    """Parameter holder for weight_norm(Conv1d) / weight_norm(ConvTranspose1d): holds
+    (weight_g, weight_v, bias) until remove_weight_norm(), then (weight, bias)."""
+
+    def __init__(self, shape, out_channels, std=0.01):
+        super().__init__()
+        v = torch.randn(shape) * std
+        self.weight_g = nn.Parameter(v.flatten(1).norm(dim=1).view(-1, 1, 1), requires_grad=False)
+        self.weight_v = nn.Parameter(v, requires_grad=False)
+        self.bias = nn.Parameter(torch.zeros(out_channels), requires_grad=False)
+
+    @property
+    def normalized(self):
+        return "weight_g" in self._parameters
+
+    def folded_weight(self):
+        if not self.normalized:
+            return self.weight
+        v = self.weight_v
+        return v * (self.weight_g / v.flatten(1).norm(dim=1).view(-1, 1, 1))
+
+    def remove_weight_norm(self):
+        if self.normalized:
+            w = self.folded_weight().detach().clone()
+            del self._parameters["weight_g"], self._parameters["weight_v"]
+            self.weight = nn.Parameter(w, requires_grad=False)
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        has_plain = prefix + "weight" in state_dict
+        has_wn = prefix + "weight_v" in state_dict
+        if self.normalized and has_plain and not has_wn:
+            # folded checkpoint into a weight-normed module: g = ||w||, v = w reproduces w exactly
+            w = state_dict.pop(prefix + "weight")
+            state_dict[prefix + "weight_v"] = w
+            state_dict[prefix + "weight_g"] = w.flatten(1).norm(dim=1).view(-1, 1, 1)
+        elif not self.normalized and has_wn and not has_plain:
+            v = state_dict.pop(prefix + "weight_v")
+            g = state_dict.pop(prefix + "weight_g")
+            state_dict[prefix + "weight"] = v * (g / v.flatten(1).norm(dim=1).view(-1, 1, 1))
+        return super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
+
+class ResBlock(nn.Module):
+    """hifigan/models.py:20-109."""
+
+    def __init__(self, h, channels, kernel_size=3, dilation=(1, 3, 5)):
+        super().__init__()
+        self.h = h
+        self.channels, self.kernel_size, self.dilation = channels, kernel_size, tuple(dilation)
+        self.convs1 = nn.ModuleList([WNConv((channels, channels, kernel_size), channels) for _ in dilation])
+        self.convs2 = nn.ModuleList([WNConv((channels, channels, kernel_size), channels) for _ in dilation])
+
+    def remove_weight_norm(self):
+        for m in list(self.convs1) + list(self.convs2):
+            m.remove_weight_norm()
+
+
+class Generator(nn.Module, ParamCache):
+    """hifigan/models.py:112-174."""
+
+    def __init__(self, h):
+        super().__init__()
+        self.h = h
+        self.num_kernels = len(h["resblock_kernel_sizes"])
+        self.num_upsamples = len(h["upsample_rates"])
+        c0 = h["upsample_initial_channel"]
+        self.conv_pre = WNConv((c0, h.get("num_mels", 80), 7), c0)
+        self.ups = nn.ModuleList()
+        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+            if k % u != 0:
+                raise NotImplementedError("ConvTranspose1d phase form needs kernel_size % stride == 0")
+            self.ups.append(WNConv((c0 // (2 ** i), c0 // (2 ** (i + 1)), k), c0 // (2 ** (i + 1))))
+        self.resblocks = nn.ModuleList()
+        ch = c0
+        for i in range(len(self.ups)):
+            ch = c0 // (2 ** (i + 1))
+            for k, d in zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"]):
+                self.resblocks.append(ResBlock(h, ch, k, d))
+        self.conv_post = WNConv((1, ch, 7), 1)
+        self.eval()
+
+    def remove_weight_norm(self):
+        for m in self.ups:
+            m.remove_weight_norm()
+        for m in self.resblocks:
+            m.remove_weight_norm()
+        self.conv_pre.remove_weight_norm()
+        self.conv_post.remove_weight_norm()
+
+    def train(self, mode=True):
+        if mode:
+            raise NotImplementedError("speakingstyle_b200 Generator is inference-only")
+        return super().train(False)
+
+    # ---------------------------------------------------------------------------------------
+    def _pack(self):
+        h = self.h
+        pk = {"pre": pack_conv(self.conv_pre.folded_weight()), "ups": [], "res": []}
+        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+            w = self.ups[i].folded_weight()  # [Cin, Cout, k]
+            cin, cout, _ = w.shape
+            taps = k // u
+            # row s of the phase-form GEMM covers output samples u*s + r - pad, r in [0,u); tap j' reads
+            # input row s - (taps-1-j') and uses kernel index r + (taps-1-j')*u
+            w4 = w.reshape(cin, cout, taps, u).permute(2, 0, 3, 1).flip(0)  # [j', ci, r, co]
+            pk["ups"].append((w4.reshape(taps * cin, u * cout).contiguous(), self.ups[i].bias.repeat(u).contiguous()))
+        for rb in self.resblocks:
+            pk["res"].append(([pack_conv(c.folded_weight()) for c in rb.convs1],
+                              [pack_conv(c.folded_weight()) for c in rb.convs2]))
+        wp = self.conv_post.folded_weight()  # [1, C, k] -> [k*C]
+        pk["post"] = wp[0].t().contiguous().reshape(-1)
+        return pk
+
+    @torch.no_grad()
+    def forward(self, x, channels_last=False, pcm=False):
+        """x: mel [B,80,T] (reference layout) or [B,T,80] with channels_last=True.
+        Returns wave [B,1,256*T] float32; with pcm=True returns (wave, int16 [B,256*T])."""
+        if not x.is_cuda:
+            raise RuntimeError("speakingstyle_b200 Generator needs CUDA tensors; there is no CPU fallback")
+        h = self.h
+        pk = self.packed()
+        if not channels_last:
+            x = x.transpose(1, 2)
+        x = x.to(torch.float32).contiguous()
+        x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3)
+        nk = self.num_kernels
+        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+            wu, bu = pk["ups"][i]
+            x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, taps=k // u,
+                                     pad=(k - u) // 2, in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE)
+            # four buffers per stage: x (stage input, read by all three ResBlocks), xs (their mean),
+            # tbuf (output of c1) and ybuf (the running residual stream of one ResBlock).  c2 may write
+            # in place over its residual operand (same element, same thread) but never over its conv input.
+            xs, tbuf, ybuf = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+            for j in range(nk):
+                rb = self.resblocks[i * nk + j]
+                w1s, w2s = pk["res"][i * nk + j]
+                y = x
+                nd = len(rb.dilation)
+                rk = rb.kernel_size
+                for m, dil in enumerate(rb.dilation):
+                    t = ops.conv1d(y, w1s[m], rb.convs1[m].bias, k=rk, dilation=dil, pad=get_padding(rk, dil),
+                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, out=tbuf)
+                    if m < nd - 1:
+                        y = ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1),
+                                       in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, out=ybuf)
+                    else:  # last pair: x_j = c2(..) + y goes straight into the stage mean
+                        ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1),
+                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, write_y=False,
+                                   accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0))
+            x = xs
+        wave, pcm16 = ops.hifigan_post(x, pk["post"], self.conv_post.bias, k=7, in_slope=0.01, want_wave=True,
+                                       want_pcm=pcm)
+        wave = wave.unsqueeze(1)
+        return (wave, pcm16) if pcm else wave

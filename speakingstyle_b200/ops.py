@@ -1,0 +1,221 @@
+"""Tensor-level wrappers over the C ABI (include/speakingstyle_b200.h).
+
+torch is used for device memory and streams only: every function here unwraps tensors to raw
+device pointers and enqueues ONE library call on torch's current stream.  Nothing in this file
+computes with torch operators.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, check  # noqa: F401
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _chk(t, dtype, name):
+    if t is None:
+        return
+    if not t.is_cuda:
+        raise _lib.SSError(f"{name}: expected a CUDA tensor (speakingstyle_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise _lib.SSError(f"{name}: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise _lib.SSError(f"{name}: expected a contiguous tensor")
+
+
+def launch_count():
+    return int(_lib.lib().ss_launch_count())
+
+
+def launch_count_reset():
+    _lib.lib().ss_launch_count_reset()
+
+
+# ---------------------------------------------------------------------------------------------
+def embed_posenc(texts, emb, pe):
+    _chk(texts, torch.int64, "texts"); _chk(emb, torch.float32, "emb"); _chk(pe, torch.float32, "pe")
+    B, L = texts.shape
+    V, D = emb.shape
+    if pe.shape[0] < L or pe.shape[1] != D:
+        raise _lib.SSError("embed_posenc: position table too small")
+    out = torch.empty((B, L, D), dtype=torch.float32, device=texts.device)
+    check(_lib.lib().ss_embed_posenc(_ptr(texts), _ptr(emb), _ptr(pe), _ptr(out), B, L, D, V, _stream()))
+    return out
+
+
+def add_position(x, pe):
+    _chk(x, torch.float32, "x"); _chk(pe, torch.float32, "pe")
+    B, S, Cc = x.shape
+    if pe.shape[0] < S or pe.shape[1] != Cc:
+        raise _lib.SSError("add_position: position table too small")
+    out = torch.empty_like(x)
+    check(_lib.lib().ss_add_posenc(_ptr(x), _ptr(pe), _ptr(out), B, S, Cc, _stream()))
+    return out
+
+
+def conv1d(x, w, bias=None, *, k=1, dilation=1, pad=0, act=ACT_NONE, slope=0.0, in_act=ACT_NONE, in_slope=0.0,
+           residual=None, lens=None, out=None, accum=None, accum_scale=1.0, accum_init=False, write_y=True):
+    """x [B,S,Cin] f32, w packed [k*Cin, Cout] -> y [B,S,Cout] (see ss_conv1d_f32)."""
+    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w"); _chk(bias, torch.float32, "bias")
+    _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
+    B, S, Cin = x.shape
+    Cout = w.shape[1]
+    if w.shape[0] != k * Cin:
+        raise _lib.SSError(f"conv1d: packed weight has {w.shape[0]} rows, expected k*Cin = {k * Cin}")
+    y = None
+    if write_y:
+        y = out if out is not None else torch.empty((B, S, Cout), dtype=torch.float32, device=x.device)
+        _chk(y, torch.float32, "out")
+    p = _lib.Conv1dF32Params(
+        x=x.data_ptr(), x_batch_stride=S * Cin, x_row_stride=Cin, w=w.data_ptr(),
+        bias=None if bias is None else bias.data_ptr(), residual=None if residual is None else residual.data_ptr(),
+        lens=None if lens is None else lens.data_ptr(), y=None if y is None else y.data_ptr(),
+        accum=None if accum is None else accum.data_ptr(), y_batch_stride=S * Cout, y_row_stride=Cout, y_offset=0,
+        y_batch_elems=S * Cout, B=B, S_in=S, S_out=S, Cin=Cin, Cout=Cout, k=k, dilation=dilation, pad=pad,
+        in_act=in_act, in_slope=in_slope, act=act, slope=slope, accum_scale=accum_scale, accum_init=int(accum_init))
+    check(_lib.lib().ss_conv1d_f32(C.byref(p), _stream()))
+    return y
+
+
+def conv_transpose1d(x, w, bias, *, cout, stride, taps, pad, in_act=ACT_NONE, in_slope=0.0):
+    """ConvTranspose1d in phase form: x [B,S,Cin], w packed [taps*Cin, stride*cout] (weights.pack_conv_transpose),
+    bias tiled to [stride*cout].  Output [B, T_out, cout] with T_out = (S-1)*stride - 2*pad + taps*stride."""
+    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w"); _chk(bias, torch.float32, "bias")
+    B, S, Cin = x.shape
+    k_full = taps * stride
+    T_out = (S - 1) * stride - 2 * pad + k_full
+    S_out = (T_out - 1 + pad) // stride + 1
+    y = torch.empty((B, T_out, cout), dtype=torch.float32, device=x.device)
+    p = _lib.Conv1dF32Params(
+        x=x.data_ptr(), x_batch_stride=S * Cin, x_row_stride=Cin, w=w.data_ptr(), bias=bias.data_ptr(), residual=None,
+        lens=None, y=y.data_ptr(), accum=None, y_batch_stride=T_out * cout, y_row_stride=stride * cout,
+        y_offset=-pad * cout, y_batch_elems=T_out * cout, B=B, S_in=S, S_out=S_out, Cin=Cin, Cout=stride * cout,
+        k=taps, dilation=1, pad=taps - 1, in_act=in_act, in_slope=in_slope, act=ACT_NONE, slope=0.0,
+        accum_scale=0.0, accum_init=0)
+    check(_lib.lib().ss_conv1d_f32(C.byref(p), _stream()))
+    return y
+
+
+def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pre_relu=False, out=None):
+    """film = (gamma [B,C], beta [B,C], s_gamma [1], s_beta [1]) or None."""
+    _chk(x, torch.float32, "x"); _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens")
+    _chk(pe, torch.float32, "pe"); _chk(ln_w, torch.float32, "ln_w"); _chk(ln_b, torch.float32, "ln_b")
+    B, S, Cc = x.shape
+    if pe is not None and (pe.shape[0] < S or pe.shape[1] != Cc):
+        raise _lib.SSError("layernorm: position table too small")
+    y = out if out is not None else torch.empty_like(x)
+    g = be = sg = sb = None
+    if film is not None:
+        g, be, sg, sb = film
+        for t, n in ((g, "gamma"), (be, "beta"), (sg, "s_gamma"), (sb, "s_beta")):
+            _chk(t, torch.float32, n)
+    p = _lib.LayerNormParams(
+        x=x.data_ptr(), residual=None if residual is None else residual.data_ptr(), ln_w=ln_w.data_ptr(),
+        ln_b=ln_b.data_ptr(), gamma=None if g is None else g.data_ptr(), beta=None if be is None else be.data_ptr(),
+        s_gamma=None if sg is None else sg.data_ptr(), s_beta=None if sb is None else sb.data_ptr(),
+        lens=None if lens is None else lens.data_ptr(), pe=None if pe is None else pe.data_ptr(), y=y.data_ptr(),
+        B=B, S=S, C=Cc, pre_relu=int(pre_relu))
+    check(_lib.lib().ss_layernorm(C.byref(p), _stream()))
+    return y
+
+
+def attention(qkv, lens, n_head):
+    _chk(qkv, torch.float32, "qkv"); _chk(lens, torch.int32, "lens")
+    B, S, D3 = qkv.shape
+    D = D3 // 3
+    ctx = torch.empty((B, S, D), dtype=torch.float32, device=qkv.device)
+    check(_lib.lib().ss_attention_f32(_ptr(qkv), _ptr(lens), _ptr(ctx), B, S, n_head, D // n_head, _stream()))
+    return ctx
+
+
+def predictor_head(h, ln_w, ln_b, lin_w, lin_b, *, film=None, lens=None):
+    _chk(h, torch.float32, "h"); _chk(lens, torch.int32, "lens")
+    B, L, Cc = h.shape
+    pred = torch.empty((B, L), dtype=torch.float32, device=h.device)
+    g = be = sg = sb = None
+    if film is not None:
+        g, be, sg, sb = film
+    p = _lib.PredictorHeadParams(
+        h=h.data_ptr(), ln_w=ln_w.data_ptr(), ln_b=ln_b.data_ptr(), gamma=None if g is None else g.data_ptr(),
+        beta=None if be is None else be.data_ptr(), s_gamma=None if sg is None else sg.data_ptr(),
+        s_beta=None if sb is None else sb.data_ptr(), lin_w=lin_w.data_ptr(), lin_b=lin_b.data_ptr(),
+        lens=None if lens is None else lens.data_ptr(), pred=pred.data_ptr(), B=B, L=L, C=Cc)
+    check(_lib.lib().ss_predictor_head(C.byref(p), _stream()))
+    return pred
+
+
+def bucket_embed_add(pred, control, edges, table, x, want_idx=False):
+    """In place: pred *= control; x += table[bucketize(pred, edges)].  Returns idx (int32) if asked."""
+    _chk(pred, torch.float32, "pred"); _chk(edges, torch.float32, "edges"); _chk(table, torch.float32, "table")
+    _chk(x, torch.float32, "x")
+    B, L, Cc = x.shape
+    idx = torch.empty((B, L), dtype=torch.int32, device=x.device) if want_idx else None
+    check(_lib.lib().ss_bucket_embed_add(_ptr(pred), float(control), _ptr(edges), edges.numel(), _ptr(table), _ptr(x),
+                                         _ptr(idx), B, L, Cc, _stream()))
+    return idx
+
+
+def duration_scan(log_d, d_control, durations=None):
+    """Returns (d_rounded f32 [B,L], ends i32 [B,L], lens2 i32 [2,B] = (expanded length, int(float sum)))."""
+    src = log_d if log_d is not None else durations
+    _chk(src, torch.float32, "durations")
+    B, L = src.shape
+    d_rounded = torch.empty_like(src) if log_d is not None else durations
+    ends = torch.empty((B, L), dtype=torch.int32, device=src.device)
+    lens2 = torch.empty((2, B), dtype=torch.int32, device=src.device)
+    check(_lib.lib().ss_duration_scan(_ptr(log_d), float(d_control), _ptr(d_rounded), _ptr(ends), _ptr(lens2[0]),
+                                      _ptr(lens2[1]), B, L, _stream()))
+    return d_rounded, ends, lens2
+
+
+def length_regulate(x, ends, T, pe=None, want_mel2phone=False):
+    _chk(x, torch.float32, "x"); _chk(ends, torch.int32, "ends"); _chk(pe, torch.float32, "pe")
+    B, L, Cc = x.shape
+    if pe is not None and (pe.shape[0] < T or pe.shape[1] != Cc):
+        raise _lib.SSError("length_regulate: position table too small")
+    out = torch.empty((B, T, Cc), dtype=torch.float32, device=x.device)
+    m2p = torch.empty((B, T), dtype=torch.int32, device=x.device) if want_mel2phone else None
+    check(_lib.lib().ss_length_regulate(_ptr(x), _ptr(ends), _ptr(pe), _ptr(out), _ptr(m2p), B, L, int(T), Cc,
+                                        _stream()))
+    return (out, m2p) if want_mel2phone else out
+
+
+def length_mask(lens, T):
+    _chk(lens, torch.int32, "lens")
+    B = lens.shape[0]
+    mask = torch.empty((B, int(T)), dtype=torch.bool, device=lens.device)
+    check(_lib.lib().ss_length_mask(_ptr(lens), _ptr(mask), B, int(T), _stream()))
+    return mask
+
+
+def mean_pool(x):
+    _chk(x, torch.float32, "x")
+    B, S, Cc = x.shape
+    out = torch.empty((B, Cc), dtype=torch.float32, device=x.device)
+    check(_lib.lib().ss_mean_pool(_ptr(x), _ptr(out), B, S, Cc, _stream()))
+    return out
+
+
+def add_speaker(x, ids, table):
+    _chk(x, torch.float32, "x"); _chk(ids, torch.int64, "speakers"); _chk(table, torch.float32, "speaker table")
+    B, L, Cc = x.shape
+    check(_lib.lib().ss_add_speaker(_ptr(x), _ptr(ids), _ptr(table), B, L, Cc, table.shape[0], _stream()))
+    return x
+
+
+def hifigan_post(x, w, bias, *, k, in_slope=0.01, want_wave=True, want_pcm=False, pcm_scale=32768.0):
+    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w")
+    B, T, Cc = x.shape
+    wave = torch.empty((B, T), dtype=torch.float32, device=x.device) if want_wave else None
+    pcm = torch.empty((B, T), dtype=torch.int16, device=x.device) if want_pcm else None
+    check(_lib.lib().ss_hifigan_post(_ptr(x), _ptr(w), _ptr(bias), _ptr(wave), _ptr(pcm), float(pcm_scale),
+                                     float(in_slope), B, T, Cc, k, _stream()))
+    return wave, pcm

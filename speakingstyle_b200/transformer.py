@@ -1,0 +1,291 @@
+"""Host-side mirror of the reference's ``transformer`` package over the C ABI.
+
+Same class names, constructor arguments, attribute names and ``state_dict`` keys as
+transformer/{Models,Layers,SubLayers}.py, so a checkpoint of the reference loads unchanged.  The
+sub-modules only HOLD parameters (no torch operator is ever applied to them); ``forward`` enqueues
+calls of speakingstyle_b200.ops, which are the hand-written sm_100a kernels.  Inference only.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .configs import N_SRC_VOCAB
+from .synth import sinusoid_table
+
+PAD = 0  # transformer/Constants.py:1
+
+
+class ParamCache:
+    """Kernel-layout copies of parameters, rebuilt when a source parameter changes."""
+
+    def packed(self):
+        srcs = [p for p in self.parameters(recurse=True)] + [b for b in self.buffers(recurse=True)]
+        key = tuple((t.data_ptr(), t._version) for t in srcs)
+        if self.__dict__.get("_pack_key") != key:
+            with torch.no_grad():
+                self.__dict__["_pack_val"] = self._pack()
+            self.__dict__["_pack_key"] = key
+        return self.__dict__["_pack_val"]
+
+
+def pack_conv(weight):
+    """[Cout, Cin, k] (nn.Conv1d) or [out, in] (nn.Linear) -> [k*Cin, Cout], tap-major rows."""
+    if weight.dim() == 2:
+        return weight.t().contiguous()
+    cout, cin, k = weight.shape
+    return weight.permute(2, 1, 0).reshape(k * cin, cout).contiguous()
+
+
+class Dense(nn.Module):
+    """Parameter holder with nn.Linear's / nn.Conv1d's names, shapes and default initialiser."""
+
+    def __init__(self, in_f, out_f, kernel_size=None, bias=True):
+        super().__init__()
+        shape = (out_f, in_f) if kernel_size is None else (out_f, in_f, kernel_size)
+        bound = 1.0 / math.sqrt(in_f * (kernel_size or 1))
+        self.weight = nn.Parameter(torch.empty(shape).uniform_(-bound, bound), requires_grad=False)
+        if bias:
+            self.bias = nn.Parameter(torch.empty(out_f).uniform_(-bound, bound), requires_grad=False)
+        else:
+            self.register_parameter("bias", None)
+
+    def forward(self, *a, **k):
+        raise RuntimeError("parameter holder: compute goes through speakingstyle_b200.ops")
+
+
+class Norm(nn.Module):
+    """nn.LayerNorm parameter holder."""
+
+    def __init__(self, n):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(n), requires_grad=False)
+        self.bias = nn.Parameter(torch.zeros(n), requires_grad=False)
+
+    def forward(self, *a, **k):
+        raise RuntimeError("parameter holder: compute goes through speakingstyle_b200.ops")
+
+
+class FiLM(nn.Module):
+    """model/blocks.py:43-62 - the two learnable scales; the modulation is fused into ss_layernorm."""
+
+    def __init__(self):
+        super().__init__()
+        self.s_gamma = nn.Parameter(torch.ones(1), requires_grad=False)
+        self.s_beta = nn.Parameter(torch.ones(1), requires_grad=False)
+
+
+def film_args(film, gammas, betas):
+    if film is None or gammas is None or betas is None:
+        return None
+    B = gammas.shape[0]
+    return (gammas.reshape(B, -1).contiguous(), betas.reshape(B, -1).contiguous(), film.s_gamma, film.s_beta)
+
+
+def lens_from_mask(mask):
+    """Key-padding masks on this path are always prefix masks (utils/tools.py:110-118), so a
+    [B,S] bool mask (True = pad) is equivalent to per-row lengths, which is what the kernels take."""
+    return (mask.shape[1] - mask.sum(dim=1)).to(torch.int32)
+
+
+class MultiHeadAttention(nn.Module, ParamCache):
+    """transformer/SubLayers.py:8-57."""
+
+    def __init__(self, n_head, d_model, d_k, d_v, dropout=0.1):
+        super().__init__()
+        assert d_k == d_v and n_head * d_k == d_model
+        self.n_head, self.d_k, self.d_v = n_head, d_k, d_v
+        self.w_qs = Dense(d_model, n_head * d_k)
+        self.w_ks = Dense(d_model, n_head * d_k)
+        self.w_vs = Dense(d_model, n_head * d_v)
+        self.layer_norm = Norm(d_model)
+        self.fc = Dense(n_head * d_v, d_model)
+
+    def _pack(self):
+        return {
+            "wqkv": torch.cat([pack_conv(self.w_qs.weight), pack_conv(self.w_ks.weight), pack_conv(self.w_vs.weight)],
+                              dim=1).contiguous(),
+            "bqkv": torch.cat([self.w_qs.bias, self.w_ks.bias, self.w_vs.bias]).contiguous(),
+            "wfc": pack_conv(self.fc.weight),
+        }
+
+    def forward(self, x, lens, mask_rows=True):
+        """x [B,S,D] -> LayerNorm(fc(attention) + x), rows >= lens zeroed (Layers.py:27-28)."""
+        pk = self.packed()
+        qkv = ops.conv1d(x, pk["wqkv"], pk["bqkv"])
+        ctx = ops.attention(qkv, lens, self.n_head)
+        y = ops.conv1d(ctx, pk["wfc"], self.fc.bias, residual=x)
+        return ops.layernorm(y, self.layer_norm.weight, self.layer_norm.bias, lens=lens if mask_rows else None, out=y)
+
+
+class PositionwiseFeedForward(nn.Module, ParamCache):
+    """transformer/SubLayers.py:60-93."""
+
+    def __init__(self, d_in, d_hid, kernel_size, dropout=0.1):
+        super().__init__()
+        self.kernel_size = list(kernel_size)
+        self.w_1 = Dense(d_in, d_hid, kernel_size[0])
+        self.w_2 = Dense(d_hid, d_in, kernel_size[1])
+        self.layer_norm = Norm(d_in)
+
+    def _pack(self):
+        return {"w1": pack_conv(self.w_1.weight), "w2": pack_conv(self.w_2.weight)}
+
+    def forward(self, x, lens=None, film=None):
+        pk = self.packed()
+        k1, k2 = self.kernel_size
+        h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU)
+        y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x)
+        return ops.layernorm(y, self.layer_norm.weight, self.layer_norm.bias, film=film, lens=lens, out=y)
+
+
+class FFTBlock(nn.Module):
+    """transformer/Layers.py:11-37."""
+
+    def __init__(self, d_model, n_head, d_k, d_v, d_inner, kernel_size, dropout=0.1, film=True):
+        super().__init__()
+        self.slf_attn = MultiHeadAttention(n_head, d_model, d_k, d_v, dropout=dropout)
+        self.pos_ffn = PositionwiseFeedForward(d_model, d_inner, kernel_size, dropout=dropout)
+        if film:
+            self.film = FiLM()
+
+    def forward(self, enc_input, gammas=None, betas=None, mask=None, slf_attn_mask=None, lens=None):
+        """Returns (output, None): the attention probabilities the reference returns here are
+        dropped by every caller (Models.py:98-101) and are never materialised."""
+        if lens is None:
+            lens = lens_from_mask(mask)
+        x = self.slf_attn(enc_input, lens)
+        x = self.pos_ffn(x, lens=lens, film=film_args(getattr(self, "film", None), gammas, betas))
+        return x, None
+
+
+class _PositionTable:
+    """position_enc parameter + on-demand longer table (Models.py:82-87,145-152; modules.py:374-380)."""
+
+    def _pe(self, n, width):
+        table = self.position_enc[0]
+        if n <= table.shape[0]:
+            return table
+        cache = self.__dict__.setdefault("_long_pe", {})
+        if n not in cache:
+            cache.clear()
+            cache[n] = sinusoid_table(n, width).to(table.device)
+        return cache[n]
+
+
+class Encoder(nn.Module, _PositionTable):
+    """transformer/Models.py:33-101."""
+
+    def __init__(self, config):
+        super().__init__()
+        tr = config["transformer"]
+        n_position = config["max_seq_len"] + 1
+        d = tr["encoder_hidden"]
+        self.max_seq_len = config["max_seq_len"]
+        self.d_model = d
+        self.src_word_emb = nn.Embedding(N_SRC_VOCAB, d, padding_idx=PAD)
+        self.src_word_emb.weight.requires_grad_(False)
+        self.position_enc = nn.Parameter(sinusoid_table(n_position, d).unsqueeze(0), requires_grad=False)
+        self.layer_stack = nn.ModuleList([
+            FFTBlock(d, tr["encoder_head"], d // tr["encoder_head"], d // tr["encoder_head"], tr["conv_filter_size"],
+                     tr["conv_kernel_size"], dropout=tr["encoder_dropout"]) for _ in range(tr["encoder_layer"])])
+
+    def forward(self, src_seq, mask, gammas=None, betas=None, return_attns=False, lens=None):
+        if lens is None:
+            lens = lens_from_mask(mask)
+        x = ops.embed_posenc(src_seq.contiguous(), self.src_word_emb.weight, self._pe(src_seq.shape[1], self.d_model))
+        for layer in self.layer_stack:
+            x, _ = layer(x, gammas=gammas, betas=betas, lens=lens)
+        return x
+
+
+class Decoder(nn.Module, _PositionTable):
+    """transformer/Models.py:104-170.  ``forward`` takes the sequence with the position table
+    ALREADY added when ``pe_added`` (the LengthRegulator kernel writes x + PE in its one pass)."""
+
+    def __init__(self, config):
+        super().__init__()
+        tr = config["transformer"]
+        n_position = config["max_seq_len"] + 1
+        d = tr["decoder_hidden"]
+        self.max_seq_len = config["max_seq_len"]
+        self.d_model = d
+        self.position_enc = nn.Parameter(sinusoid_table(n_position, d).unsqueeze(0), requires_grad=False)
+        self.layer_stack = nn.ModuleList([
+            FFTBlock(d, tr["decoder_head"], d // tr["decoder_head"], d // tr["decoder_head"], tr["conv_filter_size"],
+                     tr["conv_kernel_size"], dropout=tr["decoder_dropout"]) for _ in range(tr["decoder_layer"])])
+
+    def forward(self, enc_seq, mask, gammas=None, betas=None, return_attns=False, lens=None, pe_added=False):
+        T = enc_seq.shape[1]
+        mask = mask[:, :T]
+        if lens is None:
+            lens = lens_from_mask(mask)
+        x = enc_seq
+        if not pe_added:
+            x = ops.add_position(enc_seq, self._pe(T, self.d_model))
+        for layer in self.layer_stack:
+            x, _ = layer(x, gammas=gammas, betas=betas, lens=lens)
+        return x, mask
+
+
+class ConvNorm(nn.Module):
+    """transformer/Layers.py:39-77 parameter holder (``.conv.weight`` / ``.conv.bias``)."""
+
+    def __init__(self, in_channels, out_channels, kernel_size=1, stride=1, padding=None, dilation=1, bias=True,
+                 w_init_gain="linear", transform=False):
+        super().__init__()
+        if padding is None:
+            assert kernel_size % 2 == 1
+            padding = int(dilation * (kernel_size - 1) / 2)
+        assert stride == 1
+        self.kernel_size, self.padding, self.dilation = kernel_size, padding, dilation
+        self.conv = Dense(in_channels, out_channels, kernel_size, bias=bias)
+        self.transform = transform
+
+
+class _BatchNormHolder(nn.Module):
+    def __init__(self, n):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(n), requires_grad=False)
+        self.bias = nn.Parameter(torch.zeros(n), requires_grad=False)
+        self.register_buffer("running_mean", torch.zeros(n))
+        self.register_buffer("running_var", torch.ones(n))
+        self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
+        self.eps = 1e-5
+
+
+class PostNet(nn.Module, ParamCache):
+    """transformer/Layers.py:80-148.  BatchNorm1d (eval) is folded into each convolution's weight
+    and bias when the parameters are packed; tanh is the convolution kernel's epilogue."""
+
+    def __init__(self, n_mel_channels=80, postnet_embedding_dim=512, postnet_kernel_size=5, postnet_n_convolutions=5):
+        super().__init__()
+        self.kernel_size = postnet_kernel_size
+        chans = [n_mel_channels] + [postnet_embedding_dim] * (postnet_n_convolutions - 1) + [n_mel_channels]
+        self.convolutions = nn.ModuleList()
+        for i in range(postnet_n_convolutions):
+            self.convolutions.append(nn.Sequential(
+                ConvNorm(chans[i], chans[i + 1], kernel_size=postnet_kernel_size, stride=1,
+                         padding=int((postnet_kernel_size - 1) / 2), dilation=1),
+                _BatchNormHolder(chans[i + 1])))
+
+    def _pack(self):
+        out = []
+        for conv, bn in self.convolutions:
+            scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
+            w = conv.conv.weight * scale[:, None, None]
+            b = (conv.conv.bias - bn.running_mean) * scale + bn.bias
+            out.append((pack_conv(w), b.contiguous()))
+        return out
+
+    def forward(self, x, residual=None):
+        """x [B,T,n_mel] -> postnet(x) (+ residual fused into the last convolution if given)."""
+        pk = self.packed()
+        k = self.kernel_size
+        n = len(pk)
+        for i, (w, b) in enumerate(pk):
+            last = i == n - 1
+            x = ops.conv1d(x, w, b, k=k, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
+                           residual=residual if last else None)
+        return x

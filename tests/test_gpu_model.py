@@ -1,0 +1,200 @@
+"""End-to-end parity of the drop-in modules (which run only C-ABI kernels) against
+(a) the committed golden fixtures produced by the real reference and (b) the oracle run live on the
+same seeded weights and batches.  Tolerances are north_star's: integers bit-exact (durations,
+mel_lens, masks, bucket ids, mel2phone); fp32 mel / wave max-abs <= 1e-3."""
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import fs2_oracle as O  # noqa: E402
+from speakingstyle_b200 import configs as C  # noqa: E402
+from speakingstyle_b200 import synth as S  # noqa: E402
+
+DEV = "cuda:0"
+TOL = 1e-3
+
+
+_models = {}
+
+
+def get_models(ds):
+    import speakingstyle_b200 as ss
+
+    if ds not in _models:
+        d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
+        mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+        sd = S.fastspeech2_state_dict(mc, ds)
+        _models[ds] = (ss.get_model(pc, mc, DEV, sd), mc, sd)
+    return _models[ds]
+
+
+_voc = {}
+
+
+def get_vocoder():
+    import speakingstyle_b200 as ss
+
+    if not _voc:
+        h = C.hifigan_config()
+        vsd = S.hifigan_state_dict(h)
+        _voc["v"] = (ss.get_vocoder(h, DEV, vsd), h, S.fold_weight_norm(vsd))
+    return _voc["v"]
+
+
+def run(model, batch, controls=(1.0, 1.0, 1.0), extra=False):
+    return model(batch["speakers"], batch["texts"], batch["src_lens"], batch["max_src_len"], batch["mels"],
+                 batch["mel_lens"], batch["max_mel_len"], p_control=controls[0], e_control=controls[1],
+                 d_control=controls[2], return_extra=extra)
+
+
+def maxabs(a, b):
+    return (a.detach().cpu().double() - torch.as_tensor(b).double()).abs().max().item()
+
+
+@pytest.mark.parametrize("name,tag,controls", [("tiny", "tiny", (1.0, 1.0, 1.0)), ("tiny_ms", "tiny_ms", (1.0, 1.0, 1.0)),
+                                                ("tiny", "tiny_ctl", (1.2, 0.8, 1.3))])
+def test_fastspeech2_small_vs_golden(golden, name, tag, controls):
+    g = golden(tag)
+    ds, batch, voc = S.make_workload(name)
+    model, mc, sd = get_models(ds)
+    out, extra = run(model, batch, controls, extra=True)
+    mel, post, pitch, energy, log_d, d_rounded, src_masks, mel_masks, src_lens, mel_lens = out
+    # dtypes / shapes of the 10-tuple
+    assert mel.dtype == torch.float32 and d_rounded.dtype == torch.float32
+    assert src_masks.dtype == torch.bool and mel_masks.dtype == torch.bool and mel_lens.dtype == torch.int32
+    # integers: bit-exact
+    assert np.array_equal(d_rounded.cpu().numpy(), g["d_rounded"])
+    assert np.array_equal(src_masks.cpu().numpy(), g["src_masks"])
+    assert np.array_equal(src_lens.cpu().numpy(), g["src_lens"])
+    if controls[2] == 1.0:
+        assert np.array_equal(mel_lens.cpu().numpy(), g["mel_lens"])
+        assert np.array_equal(mel_masks.cpu().numpy(), g["mel_masks"])
+    else:
+        # non-integer durations: mel_len = int(float32 sum) depends on the summation order, which differs
+        # between ATen's vectorised CPU sum and an index-order sum when the sum sits on an integer
+        assert np.abs(mel_lens.cpu().numpy().astype(np.int64) - g["mel_lens"]).max() <= 1
+    assert mel.shape == g["mel"].shape
+    # floats
+    for key, val in (("gammas", extra["gammas"]), ("betas", extra["betas"]), ("pitch", pitch), ("energy", energy),
+                     ("log_d", log_d), ("mel", mel), ("postnet_mel", post)):
+        assert maxabs(val, g[key]) <= TOL, key
+    # bucket ids and frame->phoneme map against the oracle
+    with torch.no_grad():
+        r = O.fastspeech2_forward(sd, mc, batch, *controls, intermediates=True)
+    assert torch.equal(extra["pitch_idx"].cpu().long(), r["pitch_idx"])
+    assert torch.equal(extra["energy_idx"].cpu().long(), r["energy_idx"])
+    assert torch.equal(extra["mel2phone"].cpu().long(), r["mel2phone"])
+    if voc:
+        gen, h, vsd = get_vocoder()
+        wave, pcm = gen(post, channels_last=True, pcm=True)
+        assert wave.shape == g["wave"].shape
+        assert maxabs(wave, g["wave"]) <= TOL
+        # mean-removed relative L2 (a DC-dominated wave would hide errors in max-abs)
+        gw = torch.from_numpy(g["wave"]).double()
+        ac = gw - gw.mean()
+        rel = ((wave.cpu().double() - gw).norm() / ac.norm()).item()
+        assert rel <= 1e-3, rel
+        assert np.abs(pcm.cpu().numpy().astype(np.int32) - g["wave_int16"].astype(np.int32)).max() <= 33
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg3"])
+def test_fastspeech2_baseline_configs_vs_golden(golden, name):
+    """BASELINE.json configs 1-3 at full size against the strided golden samples."""
+    g = golden(name)
+    ds, batch, voc = S.make_workload(name)
+    model, mc, sd = get_models(ds)
+    out = run(model, batch)
+    st = int(g["stride"])
+    d_equal = np.array_equal(out[5].cpu().numpy(), g["d_rounded"])
+    if not d_equal:  # report the rounding margin of every mismatching token before failing
+        bad = np.argwhere(out[5].cpu().numpy() != g["d_rounded"])
+        v = np.exp(g["log_d"][tuple(bad.T)]) - 1
+        pytest.fail(f"{len(bad)} duration mismatches; distance to .5 boundary: {np.abs((v % 1) - 0.5)}")
+    assert np.array_equal(out[9].cpu().numpy(), g["mel_lens"])
+    assert np.array_equal(out[8].cpu().numpy(), g["src_lens"])
+    for key, val in (("gammas", None), ("pitch", out[2]), ("energy", out[3]), ("log_d", out[4])):
+        if val is not None:
+            assert maxabs(val, g[key]) <= TOL, key
+    assert maxabs(out[0][:, ::st], g["mel_s"]) <= TOL
+    assert maxabs(out[1][:, ::st], g["postnet_mel_s"]) <= TOL
+    assert abs(out[1].double().sum(dim=(1, 2)).cpu() - torch.from_numpy(g["postnet_mel_sum"])).max().item() <= 0.5
+    if voc:
+        gen, h, vsd = get_vocoder()
+        wave = gen(out[1], channels_last=True)
+        ws = int(g["wave_stride"])
+        assert maxabs(wave[:, 0, ::ws], g["wave_s"]) <= TOL
+        rel = (abs(wave.double().abs().sum(dim=(1, 2)).cpu() - torch.from_numpy(g["wave_abs"])) /
+               torch.from_numpy(g["wave_abs"])).max().item()
+        assert rel <= 1e-4
+
+
+def test_hifigan_small_vs_golden_and_stages(golden):
+    g = golden("hifigan_small")
+    gen, h, vsd = get_vocoder()
+    mel = torch.from_numpy(g["mel"]).to(DEV)
+    wave, pcm = gen(mel, pcm=True)
+    assert wave.shape == g["wave"].shape
+    assert maxabs(wave, g["wave"]) <= 1e-4
+    assert np.abs(pcm.cpu().numpy().astype(np.int32) - g["wave_int16"].astype(np.int32)).max() <= 4
+    # channels_last entry gives the same result
+    wave2 = gen(mel.transpose(1, 2).contiguous(), channels_last=True)
+    assert torch.equal(wave, wave2)
+    # odd length (not a multiple of any tile) against the oracle
+    mel3 = torch.randn(3, 80, 37, generator=torch.Generator().manual_seed(8))
+    with torch.no_grad():
+        ref = O.hifigan_forward(vsd, h, mel3)
+    assert maxabs(gen(mel3.to(DEV)), ref) <= 1e-4
+
+
+def test_modules_standalone_api():
+    """The sub-modules keep the reference's own signatures."""
+    import speakingstyle_b200 as ss
+
+    ds, batch, _ = S.make_workload("tiny")
+    model, mc, sd = get_models(ds)
+    with torch.no_grad():
+        r = O.fastspeech2_forward(sd, mc, batch, intermediates=True)
+    mels = batch["mels"].to(DEV)
+    ref_mask = ss.get_mask_from_lengths(batch["mel_lens"].to(DEV), batch["max_mel_len"])
+    gammas, betas = model.reference_encoder(mels, batch["max_mel_len"], ref_mask)
+    assert gammas.shape == (3, 1, 256) and maxabs(gammas, r["gammas"]) <= 1e-4 and maxabs(betas, r["betas"]) <= 1e-4
+    src_mask = ss.get_mask_from_lengths(batch["src_lens"].to(DEV), batch["max_src_len"])
+    enc = model.encoder(batch["texts"].to(DEV), src_mask, gammas, betas)
+    assert maxabs(enc, r["encoder"]) <= 1e-4
+    va = model.variance_adaptor(enc, src_mask, None, None, None, None, None, 1.0, 1.0, 1.0, gammas, betas)
+    assert len(va) == 7 and maxabs(va[0], r["x"]) <= 1e-4 and torch.equal(va[4].cpu(), r["d_rounded"])
+    assert maxabs(enc, r["encoder"]) <= 1e-4  # the adaptor did not modify its input
+    dec, dec_mask = model.decoder(va[0], va[6], gammas, betas)
+    assert maxabs(dec, r["decoder"]) <= 2e-4
+    # LengthRegulator(x, duration, max_len) -> (out, mel_len) with integer targets (teacher forcing)
+    lr = ss.LengthRegulator()
+    x = torch.randn(2, 5, 8, generator=torch.Generator().manual_seed(2))
+    dur = torch.tensor([[1, 0, 3, 2, 0], [0, 0, 4, 0, 1]])
+    out, mel_len = lr(x.to(DEV), dur.to(DEV), None)
+    want, want_len, _ = O.length_regulate(x, dur.float())
+    assert torch.equal(out.cpu(), want) and torch.equal(mel_len.cpu(), want_len) and mel_len.dtype == torch.int64
+    out, _ = lr(x.to(DEV), dur.to(DEV), 9)
+    assert out.shape == (2, 9, 8)
+    # PostNet on its own
+    post = model.postnet(torch.from_numpy(np.ascontiguousarray(r["out"][0].numpy())).to(DEV))
+    assert maxabs(post, r["out"][1] - r["out"][0]) <= 1e-4
+
+
+def test_outputs_depend_on_batch_composition_like_the_reference():
+    """Padding leaks are part of the contract: the same utterance alone and inside
+    a padded batch gives different results in the reference; the drop-in must follow the oracle in both."""
+    ds, batch, _ = S.make_workload("tiny")
+    model, mc, sd = get_models(ds)
+    j = int(torch.argmin(batch["src_lens"]))
+    L, Tr = int(batch["src_lens"][j]), int(batch["mel_lens"][j])
+    solo = {"speakers": batch["speakers"][j:j + 1], "texts": batch["texts"][j:j + 1, :L].contiguous(),
+            "src_lens": batch["src_lens"][j:j + 1], "max_src_len": L,
+            "mels": batch["mels"][j:j + 1, :Tr].contiguous(), "mel_lens": batch["mel_lens"][j:j + 1], "max_mel_len": Tr}
+    out = run(model, solo)
+    with torch.no_grad():
+        ref = O.fastspeech2_forward(sd, mc, solo)
+    assert torch.equal(out[5].cpu(), ref[5]) and maxabs(out[1], ref[1]) <= TOL
