@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the batched text -> mel (-> wave) path.  Contract: see DESIGN.md "Measurement".
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg1|cfg3]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step is ONE pass of the hot path over one synthetic batch of the named BASELINE.json config
+(default cfg2: BC2013 FastSpeech2 + FiLM reference encoder, batch 64, 800-frame reference mels,
+text+reference -> mel; with --workload cfg3 the HiFi-GAN generator runs too).  Rank r runs its own
+batch (seed 1+r, weights replicated): utterances are independent, so there is no collective on the
+data path and scaling is weak.  One JSON line is printed by rank 0.
+
+--impl reference times the CPU restatement of the reference (oracle/, kind "port": the reference is
+pure Python and cannot travel to the GPU box) on the host cores, on a bounded sample of the same
+workload.
+"""
+import argparse
+import json
+import os
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from speakingstyle_b200 import configs as C  # noqa: E402
+from speakingstyle_b200 import synth as S  # noqa: E402
+
+HOP, SR = 256, 22050
+WORKLOAD_DESC = {
+    "cfg1": "BASELINE configs[0]: LJSpeech(+ref-enc) B=16, L~U[80,120], Tr~U[200,400], text->mel",
+    "cfg2": "BASELINE configs[1]: BC2013 FastSpeech2+ReferenceEncoder B=64, L~U[80,120], Tr=800, text+ref->mel",
+    "cfg3": "BASELINE configs[2]: LibriTTS multi-speaker FastSpeech2 + HiFi-GAN B=32, text->22.05kHz wave",
+}
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "tflops_burst": p["bf16_tflops"],
+                "tflops_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons during the timed region (pynvml, 100 ms period)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                mask = get(h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+                time.sleep(0.1)
+        except Exception as e:  # pragma: no cover
+            self.reasons.add(f"sampler_error:{type(e).__name__}")
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def pin(batch):
+    return {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in batch.items()}
+
+
+def to_dev(batch, dev):
+    return {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) else v) for k, v in batch.items()}
+
+
+def call(model, b):
+    return model(b["speakers"], b["texts"], b["src_lens"], b["max_src_len"], b["mels"], b["mel_lens"], b["max_mel_len"])
+
+
+def sub_batch(batch, n):
+    """First n utterances, re-padded (a shard is a batch as composed)."""
+    L, Tr = int(batch["src_lens"][:n].max()), int(batch["mel_lens"][:n].max())
+    return {"speakers": batch["speakers"][:n], "texts": batch["texts"][:n, :L].contiguous(),
+            "src_lens": batch["src_lens"][:n], "max_src_len": L, "mels": batch["mels"][:n, :Tr].contiguous(),
+            "mel_lens": batch["mel_lens"][:n], "max_mel_len": Tr}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm (oracle port of the reference) - also the cpu_baseline leg of the GPU arm
+# ---------------------------------------------------------------------------------------------
+def cpu_pass(sd, mc, batch, vsd=None, h=None):
+    from oracle import fs2_oracle as O
+
+    with torch.no_grad():
+        out = O.fastspeech2_forward(sd, mc, batch)
+        if vsd is not None:
+            O.hifigan_forward(vsd, h, out[1].transpose(1, 2))
+    return int(out[9].sum())
+
+
+def cpu_baseline(sd, mc, batch, vocoder, budget_s=20.0, n_utts=None):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    h = C.hifigan_config() if vocoder else None
+    vsd = S.fold_weight_norm(S.hifigan_state_dict(h)) if vocoder else None
+    n = n_utts or min(8, batch["texts"].shape[0])
+    sb = sub_batch(batch, n)
+    t0 = time.perf_counter()
+    frames = cpu_pass(sd, mc, sb, vsd, h)  # first pass doubles as warm-up and calibration
+    dt = time.perf_counter() - t0
+    passes, total_frames, total_t = 0, 0, 0.0
+    while passes < 3 and (passes == 0 or total_t + dt < budget_s):
+        t0 = time.perf_counter()
+        frames = cpu_pass(sd, mc, sb, vsd, h)
+        dt = time.perf_counter() - t0
+        total_t += dt
+        total_frames += frames
+        passes += 1
+    return {"value": total_frames / total_t, "unit": "mel-frames/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"first {n} utterances of the {batch['texts'].shape[0]}-utterance batch, {passes} timed passes "
+                      f"after 1 warm-up, torch {torch.__version__} CPU fp32, oracle/fs2_oracle.py"}
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    ds, batch, voc = S.make_workload(args.workload, seed=1)
+    mc = C.model_config(ds)
+    sd = S.fastspeech2_state_dict(mc, ds)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    h = C.hifigan_config() if voc else None
+    vsd = S.fold_weight_norm(S.hifigan_state_dict(h)) if voc else None
+    # calibrate the sample so that warmup+steps passes end within ~150 s
+    n = min(4, batch["texts"].shape[0])
+    t0 = time.perf_counter()
+    cpu_pass(sd, mc, sub_batch(batch, n), vsd, h)
+    per_utt = (time.perf_counter() - t0) / n
+    budget = 150.0 / max(1, args.steps + args.warmup)
+    n = int(max(1, min(batch["texts"].shape[0], budget / max(per_utt, 1e-6))))
+    sb = sub_batch(batch, n)
+    for _ in range(args.warmup):
+        cpu_pass(sd, mc, sb, vsd, h)
+    t0 = time.perf_counter()
+    frames = 0
+    for _ in range(args.steps):
+        frames += cpu_pass(sd, mc, sb, vsd, h)
+    dt = time.perf_counter() - t0
+    value = frames / dt
+    sample = (f"first {n} utterances of the {batch['texts'].shape[0]}-utterance {args.workload} batch per step, "
+              f"oracle port of the reference (torch {torch.__version__} CPU fp32)")
+    line = {
+        "impl": "reference", "metric": "mel_frames_per_s", "value": value, "unit": "mel-frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "audio_seconds_per_s": value * HOP / SR,
+        "config": {"workload": args.workload, "desc": WORKLOAD_DESC[args.workload], "vocoder": bool(voc)},
+        "cpu_baseline": {"value": value, "unit": "mel-frames/s", "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "mel-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+def lr_roofline(dev, pk):
+    """LengthRegulator kernel alone at a BASELINE cfg5-like shard size, L2 flushed between launches."""
+    from speakingstyle_b200 import ops
+
+    B, L, Cc = 256, 100, 256
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(B, L, Cc, generator=g).to(dev)
+    d = torch.randint(4, 12, (B, L), generator=g).float().to(dev)
+    _, ends, lens2 = ops.duration_scan(None, 1.0, durations=d)
+    T = int(lens2[0].max())
+    pe = torch.randn(T, Cc, generator=g).to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    times = []
+    for i in range(8):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        ops.length_regulate(x, ends, T, pe=pe)
+        b.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            times.append(a.elapsed_time(b))
+    ms = sum(times) / len(times)
+    nbytes = 4 * Cc * (B * L + B * T) + 4 * B * L + 4 * B
+    ach = nbytes / (ms * 1e-3) / 1e9
+    return {"kernel": "length_regulate_kernel", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
+            "frac": ach / pk["hbm_gbs"], "traffic": None, "shape": f"B={B} L={L} T={T} C={Cc}", "ms": ms,
+            "peak_source": pk["source"]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOAD_DESC))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch.distributed as dist
+
+    import speakingstyle_b200 as ss
+    from speakingstyle_b200 import ops
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: speakingstyle_b200 has no CPU path "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    ds, batch, voc = S.make_workload(args.workload, seed=1 + rank)
+    d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    sd = S.fastspeech2_state_dict(mc, ds)
+    model = ss.get_model(pc, mc, dev, sd)
+    gen = ss.get_vocoder(C.hifigan_config(), dev, S.hifigan_state_dict()) if voc else None
+    host = pin(batch)
+    resident = to_dev(batch, dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step(b):
+        out = call(model, b)
+        wave = gen(out[1], channels_last=True, pcm=True)[1] if gen is not None else None
+        return out, wave
+
+    for _ in range(args.warmup):
+        out, wave = step(resident)
+    torch.cuda.synchronize()
+    frames = int(out[9].sum())
+    T = out[1].shape[1]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ----
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    timer = ops.KernelTimer()
+    ops.conv_timer = timer
+    ops.launch_count_reset()
+    barrier()
+    wall0 = time.perf_counter()
+    evs = []
+    for _ in range(args.steps):
+        flush.zero_()  # L2 flush between timed iterations (outside the event pair)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step(resident)
+        b.record()
+        evs.append((a, b))
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = ops.launch_count()
+    ops.conv_timer = None
+    clocks = sampler.stop()
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+
+    # ---- end-to-end timing through the public API with host buffers ----
+    out_host = torch.empty(out[1].shape, dtype=torch.float32).pin_memory()
+    len_host = torch.empty(out[9].shape, dtype=torch.int32).pin_memory()
+    wave_host = torch.empty(wave.shape, dtype=wave.dtype).pin_memory() if wave is not None else None
+    barrier()
+    e_evs = []
+    for _ in range(args.steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        o, w = step(host)  # H2D of the pinned inputs happens inside forward()
+        out_host.copy_(o[1], non_blocking=True)
+        len_host.copy_(o[9], non_blocking=True)
+        if w is not None:
+            wave_host.copy_(w, non_blocking=True)
+        b.record()
+        e_evs.append((a, b))
+    barrier()
+    e2e_ms = sum(a.elapsed_time(b) for a, b in e_evs)
+    h2d = sum(v.numel() * v.element_size() for v in host.values() if torch.is_tensor(v))
+    d2h = out_host.numel() * 4 + len_host.numel() * 4 + (wave_host.numel() * wave_host.element_size() if w is not None else 0)
+
+    # ---- max over ranks ----
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    f = torch.tensor([frames], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(f, op=dist.ReduceOp.SUM)
+    dev_ms_max, e2e_ms_max = t.tolist()
+    total_frames = f.item()
+
+    if rank == 0:
+        pk = peaks()
+        value = total_frames * args.steps / (dev_ms_max * 1e-3)
+        e2e_value = total_frames * args.steps / (e2e_ms_max * 1e-3)
+        calls, conv_ms, conv_flops = timer.summary()
+        ach = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
+        roof = {"kernel": "conv1d_f32_kernel (fp32 FFMA implicit-GEMM conv/linear)", "bound": "tensor", "achieved": ach,
+                "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tflops_sustained"], "traffic": None,
+                "launches": calls, "avg_launch_ms": conv_ms / max(calls, 1), "share_of_step": conv_ms / dev_ms,
+                "peak_source": pk["source"] + " bf16 dense (sustained)"}
+        line = {
+            "metric": "mel_frames_per_s", "value": value, "unit": "mel-frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "audio_seconds_per_s": value * HOP / SR,
+            "config": {"workload": args.workload, "desc": WORKLOAD_DESC[args.workload], "vocoder": bool(voc),
+                       "batch_per_gpu": int(batch["texts"].shape[0]), "padded_frames": int(T),
+                       "valid_frames_per_step": total_frames, "precision_mode": "fp32",
+                       "l2": "256 MiB buffer written between timed iterations", "wall_s": wall},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "mel-frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms_max / args.steps, "audio_seconds_per_s": e2e_value * HOP / SR},
+            "gpu_launches": launches,
+            "roofline": roof,
+        }
+        try:
+            line["roofline_length_regulator"] = lr_roofline(dev, pk)
+        except Exception as e:  # pragma: no cover
+            line["roofline_length_regulator"] = {"error": str(e)}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(sd, mc, batch, voc)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

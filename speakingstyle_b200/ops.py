@@ -31,6 +31,36 @@ def _chk(t, dtype, name):
         raise _lib.SSError(f"{name}: expected a contiguous tensor")
 
 
+class KernelTimer:
+    """Optional per-call CUDA-event timing of one kernel family, used by bench.py to measure the
+    dominant kernel's average launch duration inside the timed region (events are recorded on the
+    stream the kernel is launched on).  Costs two event records per call while installed."""
+
+    def __init__(self):
+        self.records = []  # (start_event, end_event, work)
+
+    def run(self, work, fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        status = fn()
+        b.record()
+        self.records.append((a, b, work))
+        return status
+
+    def summary(self):
+        """(calls, total_ms, total_work) - call after a synchronize."""
+        ms = sum(a.elapsed_time(b) for a, b, _ in self.records)
+        return len(self.records), ms, sum(w for _, _, w in self.records)
+
+
+conv_timer = None  # set to a KernelTimer to time every ss_conv1d_f32 launch; work = algorithmic FLOPs
+
+
+def _run_conv(p, flops):
+    fn = lambda: _lib.lib().ss_conv1d_f32(C.byref(p), _stream())  # noqa: E731
+    check(conv_timer.run(flops, fn) if conv_timer is not None else fn())
+
+
 def launch_count():
     return int(_lib.lib().ss_launch_count())
 
@@ -81,7 +111,7 @@ def conv1d(x, w, bias=None, *, k=1, dilation=1, pad=0, act=ACT_NONE, slope=0.0, 
         accum=None if accum is None else accum.data_ptr(), y_batch_stride=S * Cout, y_row_stride=Cout, y_offset=0,
         y_batch_elems=S * Cout, B=B, S_in=S, S_out=S, Cin=Cin, Cout=Cout, k=k, dilation=dilation, pad=pad,
         in_act=in_act, in_slope=in_slope, act=act, slope=slope, accum_scale=accum_scale, accum_init=int(accum_init))
-    check(_lib.lib().ss_conv1d_f32(C.byref(p), _stream()))
+    _run_conv(p, 2.0 * B * S * Cout * k * Cin)
     return y
 
 
@@ -100,7 +130,7 @@ def conv_transpose1d(x, w, bias, *, cout, stride, taps, pad, in_act=ACT_NONE, in
         y_offset=-pad * cout, y_batch_elems=T_out * cout, B=B, S_in=S, S_out=S_out, Cin=Cin, Cout=stride * cout,
         k=taps, dilation=1, pad=taps - 1, in_act=in_act, in_slope=in_slope, act=ACT_NONE, slope=0.0,
         accum_scale=0.0, accum_init=0)
-    check(_lib.lib().ss_conv1d_f32(C.byref(p), _stream()))
+    _run_conv(p, 2.0 * B * T_out * cout * taps * Cin)
     return y
 
 
