@@ -105,6 +105,45 @@ typedef struct {
 SS_API int ss_conv1d_f32(const ss_conv1d_f32_params* p, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * The same convolution on the 5th-generation tensor cores: tcgen05.mma with bf16 operands and fp32
+ * accumulation in TMEM, operands fetched by TMA (zero padding and the halo across utterances come
+ * from TMA's out-of-bounds fill; no im2col).  This is the throughput kernel of the bf16 precision
+ * mode (Decoder, PostNet, HiFi-GAN: north_star tolerance relative L2 <= 1e-2); call sites as for
+ * ss_conv1d_f32.  x [B,S_in,Cin] bf16; w [k, Cout, Cin] bf16 (tap-major, Cin contiguous).
+ * epilogue: v = act(acc + bias); v += residual (f32 or bf16); v = 0 where t >= lens[b];
+ *   y = v (f32 or bf16, if given);
+ *   if accum: accum = (accum_init ? 0 : accum) + accum_scale*v (f32) and v <- that new value;
+ *   y_act = bf16(act2(v)) (if given) - the activated copy the NEXT convolution consumes as its A
+ *   operand (HiFi-GAN's leaky_relu -> conv pairs cannot apply the activation between TMA and MMA).
+ * Output addressing / window as in ss_conv1d_f32.  Cin % 8 == 0, Cout % 8 == 0, strides % 8 == 0.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* x;           /* bf16 */
+  int64_t x_batch_stride;  /* elements */
+  int64_t x_row_stride;
+  const void* w;           /* bf16 [k, Cout, Cin] */
+  const float* bias;       /* f32 [Cout] or NULL */
+  const void* residual;    /* residual_dtype, or NULL */
+  const int32_t* lens;
+  void* y;                 /* y_dtype, or NULL */
+  void* y_act;             /* bf16, or NULL */
+  float* accum;            /* f32, or NULL */
+  int64_t y_batch_stride, y_row_stride, y_offset, y_batch_elems;
+  int32_t B, S_in, S_out, Cin, Cout, k, dilation, pad;
+  int32_t act;
+  float slope;
+  int32_t act2;
+  float slope2;
+  int32_t y_dtype, residual_dtype; /* SS_F32 / SS_BF16 */
+  float accum_scale;
+  int32_t accum_init;
+} ss_conv1d_tc_params;
+SS_API int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream);
+
+/* out = bf16(act(x)) element-wise over n elements (n % 8 == 0): the entry into the bf16 path. */
+SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Row-wise LayerNorm with the element-wise steps the reference applies around it, one pass:
  *   v = x (+ residual); v = relu(v) if pre_relu; y = LN(v)*ln_w + ln_b  (eps 1e-5, biased var);
  *   FiLM (model/blocks.py:60-62): y = (s_gamma*gamma[b,:] + 1)*y + s_beta*beta[b,:] if gamma given;

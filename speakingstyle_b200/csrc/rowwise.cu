@@ -1,6 +1,8 @@
 // Bandwidth-bound row-wise kernels: embedding + position table, LayerNorm with its surrounding
 // element-wise steps, variance-predictor tail, bucketize + embedding add, masks, mean pool.
 // All are one-warp-per-row, 128-bit vectorised, each activation row read once and written once.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace {
@@ -252,6 +254,22 @@ __global__ void add_posenc_kernel(const float* __restrict__ x, const float* __re
   }
 }
 
+__global__ void cast_bf16_kernel(const float* __restrict__ x, uint4* __restrict__ out, int64_t n8, int act,
+                                 float slope) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = ss::ld_stream(reinterpret_cast<const float4*>(x) + 2 * i);
+    const float4 b = ss::ld_stream(reinterpret_cast<const float4*>(x) + 2 * i + 1);
+    float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    uint32_t u[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(ss::apply_act(f[2 * j], act, slope), ss::apply_act(f[2 * j + 1], act, slope));
+      u[j] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    out[i] = make_uint4(u[0], u[1], u[2], u[3]);
+  }
+}
+
 inline int row_grid(int64_t rows) { return (int)((rows + ROWS_PER_CTA - 1) / ROWS_PER_CTA); }
 
 }  // namespace
@@ -271,6 +289,17 @@ int ss_add_posenc(const float* x, const float* pe, float* out, int B, int S, int
   SS_REQUIRE(x && pe && out && B > 0 && S > 0 && C > 0 && C % 4 == 0, SS_ERR_INVALID, "ss_add_posenc: bad argument");
   add_posenc_kernel<<<row_grid((int64_t)B * S), 256, 0, (cudaStream_t)stream>>>(x, pe, out, B, S, C);
   SS_CHECK_LAUNCH("ss_add_posenc");
+  return SS_OK;
+}
+
+int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream) {
+  SS_REQUIRE(x && out && n > 0 && n % 8 == 0, SS_ERR_INVALID, "ss_cast_bf16: bad argument (n must be a multiple of 8)");
+  SS_REQUIRE(ss::aligned16(x) && ss::aligned16(out), SS_ERR_ALIGNMENT, "ss_cast_bf16: 16-byte alignment");
+  const int64_t n8 = n / 8;
+  const int64_t want = (n8 + 255) / 256;
+  const int grid = (int)(want < 148 * 16 ? want : 148 * 16);
+  cast_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(out), n8, act, slope);
+  SS_CHECK_LAUNCH("ss_cast_bf16");
   return SS_OK;
 }
 

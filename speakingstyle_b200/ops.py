@@ -134,6 +134,78 @@ def conv_transpose1d(x, w, bias, *, cout, stride, taps, pad, in_act=ACT_NONE, in
     return y
 
 
+F32, BF16 = 0, 1
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def cast_bf16(x, act=ACT_NONE, slope=0.0):
+    """bf16(act(x)) - the entry into the tensor-core path."""
+    _chk(x, torch.float32, "x")
+    out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().ss_cast_bf16(_ptr(x), _ptr(out), x.numel(), act, float(slope), _stream()))
+    return out
+
+
+def pack_conv_tc(weight):
+    """[Cout, Cin, k] or [out, in] fp32 -> bf16 [k, Cout, Cin] (tap-major, Cin contiguous) for ss_conv1d_tc."""
+    if weight.dim() == 2:
+        weight = weight.unsqueeze(-1)
+    return weight.permute(2, 0, 1).contiguous().to(torch.bfloat16)
+
+
+def _tc_call(p, flops):
+    fn = lambda: _lib.lib().ss_conv1d_tc(C.byref(p), _stream())  # noqa: E731
+    check(conv_timer.run(flops, fn) if conv_timer is not None else fn())
+
+
+def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, residual=None, lens=None,
+              out_dtype=torch.float32, want_y=True, out=None, act2=None, slope2=0.0, accum=None, accum_scale=1.0,
+              accum_init=False):
+    """Tensor-core convolution.  x [B,S,Cin] bf16, w [k,Cout,Cin] bf16 (pack_conv_tc).
+    Returns (y or None, y_act or None); y_act (bf16) is produced when act2 is not None."""
+    _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(bias, torch.float32, "bias")
+    _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
+    B, S, Cin = x.shape
+    k, Cout, cin_w = w.shape
+    if cin_w != Cin:
+        raise _lib.SSError(f"conv1d_tc: weight Cin {cin_w} != input Cin {Cin}")
+    y = None
+    if want_y:
+        y = out if out is not None else torch.empty((B, S, Cout), dtype=out_dtype, device=x.device)
+    y_act = torch.empty((B, S, Cout), dtype=torch.bfloat16, device=x.device) if act2 is not None else None
+    p = _lib.Conv1dTcParams(
+        x=x.data_ptr(), x_batch_stride=S * Cin, x_row_stride=Cin, w=w.data_ptr(),
+        bias=None if bias is None else bias.data_ptr(), residual=None if residual is None else residual.data_ptr(),
+        lens=None if lens is None else lens.data_ptr(), y=None if y is None else y.data_ptr(),
+        y_act=None if y_act is None else y_act.data_ptr(), accum=None if accum is None else accum.data_ptr(),
+        y_batch_stride=S * Cout, y_row_stride=Cout, y_offset=0, y_batch_elems=S * Cout, B=B, S_in=S, S_out=S, Cin=Cin,
+        Cout=Cout, k=k, dilation=dilation, pad=pad, act=act, slope=slope, act2=act2 or 0, slope2=slope2,
+        y_dtype=_DT[y.dtype] if y is not None else F32, residual_dtype=_DT[residual.dtype] if residual is not None else F32,
+        accum_scale=accum_scale, accum_init=int(accum_init))
+    _tc_call(p, 2.0 * B * S * Cout * k * Cin)
+    return y, y_act
+
+
+def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True):
+    """ConvTranspose1d in phase form on tensor cores.  x [B,S,Cin] bf16; w [taps, stride*cout, Cin] bf16;
+    bias tiled to [stride*cout] f32.  Returns (y f32 [B,T_out,cout] or None, y_act bf16 or None)."""
+    _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(bias, torch.float32, "bias")
+    B, S, Cin = x.shape
+    taps = w.shape[0]
+    T_out = (S - 1) * stride - 2 * pad + taps * stride
+    S_out = (T_out - 1 + pad) // stride + 1
+    y = torch.empty((B, T_out, cout), dtype=torch.float32, device=x.device) if want_y else None
+    y_act = torch.empty((B, T_out, cout), dtype=torch.bfloat16, device=x.device) if act2 is not None else None
+    p = _lib.Conv1dTcParams(
+        x=x.data_ptr(), x_batch_stride=S * Cin, x_row_stride=Cin, w=w.data_ptr(), bias=bias.data_ptr(), residual=None,
+        lens=None, y=None if y is None else y.data_ptr(), y_act=None if y_act is None else y_act.data_ptr(), accum=None,
+        y_batch_stride=T_out * cout, y_row_stride=stride * cout, y_offset=-pad * cout, y_batch_elems=T_out * cout, B=B,
+        S_in=S, S_out=S_out, Cin=Cin, Cout=stride * cout, k=taps, dilation=1, pad=taps - 1, act=ACT_NONE, slope=0.0,
+        act2=act2 or 0, slope2=slope2, y_dtype=F32, residual_dtype=F32, accum_scale=0.0, accum_init=0)
+    _tc_call(p, 2.0 * B * T_out * cout * taps * Cin)
+    return y, y_act
+
+
 def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pre_relu=False, out=None):
     """film = (gamma [B,C], beta [B,C], s_gamma [1], s_beta [1]) or None."""
     _chk(x, torch.float32, "x"); _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens")
