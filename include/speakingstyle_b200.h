@@ -164,6 +164,7 @@ typedef struct {
   const int32_t* lens;   /* [B] or NULL */
   const float* pe;       /* [>=S, C] or NULL */
   float* y;
+  void* y_bf16;          /* optional bf16 copy of y (A operand of the next tensor-core convolution), or NULL */
   int32_t B, S, C, pre_relu;
 } ss_layernorm_params;
 SS_API int ss_layernorm(const ss_layernorm_params* p, void* stream);

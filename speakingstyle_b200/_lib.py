@@ -37,7 +37,7 @@ class Conv1dTcParams(C.Structure):
 class LayerNormParams(C.Structure):
     _fields_ = [
         ("x", vp), ("residual", vp), ("ln_w", vp), ("ln_b", vp), ("gamma", vp), ("beta", vp), ("s_gamma", vp),
-        ("s_beta", vp), ("lens", vp), ("pe", vp), ("y", vp), ("B", i32), ("S", i32), ("C", i32), ("pre_relu", i32),
+        ("s_beta", vp), ("lens", vp), ("pe", vp), ("y", vp), ("y_bf16", vp), ("B", i32), ("S", i32), ("C", i32), ("pre_relu", i32),
     ]
 
 

@@ -29,6 +29,11 @@ __global__ void embed_posenc_kernel(const int64_t* __restrict__ texts, const flo
 }
 
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint2 pack4_bf16(const float4& o) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(o.x, o.y), b = __floats2bfloat162_rn(o.z, o.w);
+  return make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+}
+
 // LayerNorm over C = 128*V4 floats held in registers (V4 float4 per lane).
 template <int V4>
 __device__ __forceinline__ void ln_normalize(float4 (&v)[V4], int C) {
@@ -58,6 +63,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
   const int C = p.C;
   const bool masked = p.lens && t >= p.lens[b];
   float4* y = reinterpret_cast<float4*>(p.y + (int64_t)row * C);
+  uint2* yb = p.y_bf16 ? reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y_bf16) + (int64_t)row * C) : nullptr;
   if (masked) {  // result is known without touching x
 #pragma unroll
     for (int i = 0; i < V4; ++i) {
@@ -65,6 +71,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
       float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
       if (p.pe) o = __ldg(reinterpret_cast<const float4*>(p.pe + (int64_t)t * C) + c);
       y[c] = o;
+      if (yb) yb[c] = pack4_bf16(o);
     }
     return;
   }
@@ -109,6 +116,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
       o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
     }
     y[c] = o;
+    if (yb) yb[c] = pack4_bf16(o);
   }
 }
 

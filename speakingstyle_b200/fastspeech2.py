@@ -15,9 +15,15 @@ from .transformer import Decoder, Dense, Encoder, ParamCache, PostNet, pack_conv
 class FastSpeech2(nn.Module, ParamCache):
     """model/fastspeech2.py:13-120."""
 
-    def __init__(self, preprocess_config, model_config):
+    def __init__(self, preprocess_config, model_config, precision="fp32"):
         super().__init__()
         self.model_config = model_config
+        # "fp32": every kernel accumulates in fp32 FMA (mel max-abs <= 1e-3 vs the reference);
+        # "bf16": Decoder / mel_linear / PostNet run on tcgen05 with bf16 operands (relative L2 <= 1e-2);
+        # durations, bucket ids and mel_lens are computed in fp32 in both modes and are identical.
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        self.precision = precision
         self.encoder = Encoder(model_config)
         self.reference_encoder = ReferenceEncoder(preprocess_config, model_config)
         self.variance_adaptor = VarianceAdaptor(preprocess_config, model_config)
@@ -35,7 +41,7 @@ class FastSpeech2(nn.Module, ParamCache):
         self.eval()
 
     def _pack(self):
-        return {"mel_w": pack_conv(self.mel_linear.weight)}
+        return {"mel_w": pack_conv(self.mel_linear.weight), "mel_w_tc": ops.pack_conv_tc(self.mel_linear.weight)}
 
     def packed(self):  # only mel_linear's own parameters key this cache
         srcs = [self.mel_linear.weight]
@@ -96,9 +102,17 @@ class FastSpeech2(nn.Module, ParamCache):
         dec_lens = torch.clamp(mel_lens_out, max=T) if mel_masks.shape[1] != T else mel_lens_out
         if mel_masks.shape[1] != T:
             mel_masks = ops.length_mask(dec_lens, T)
-        x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True)
-        mel = ops.conv1d(x, self.packed()["mel_w"], self.mel_linear.bias)
-        postnet_mel = self.postnet(mel, residual=mel)
+        if self.precision == "bf16":
+            # Decoder, mel_linear and PostNet on the tensor cores (bf16 operands, fp32 accumulation and
+            # fp32 residual stream).  Everything before this point decides integers and stays fp32.
+            (x, xb), _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True, precision="bf16",
+                                      return_bf16=True)
+            mel, melb = ops.conv1d_tc(xb, self.packed()["mel_w_tc"], self.mel_linear.bias, act2=ops.ACT_NONE)
+            postnet_mel = self.postnet(mel, residual=mel, precision="bf16", xb=melb)
+        else:
+            x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True)
+            mel = ops.conv1d(x, self.packed()["mel_w"], self.mel_linear.bias)
+            postnet_mel = self.postnet(mel, residual=mel)
         out = (mel, postnet_mel, p_pred, e_pred, log_d, d_rounded, src_masks, mel_masks, src_lens_in, mel_lens_out)
         if return_extra:
             extra.update(gammas=gammas, betas=betas)

@@ -87,9 +87,12 @@ class ResBlock(nn.Module):
 class Generator(nn.Module, ParamCache):
     """hifigan/models.py:112-174."""
 
-    def __init__(self, h):
+    def __init__(self, h, precision="fp32"):
         super().__init__()
         self.h = h
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        self.precision = precision  # "bf16": tcgen05 convolutions (wave relative L2 <= 1e-2)
         self.num_kernels = len(h["resblock_kernel_sizes"])
         self.num_upsamples = len(h["upsample_rates"])
         c0 = h["upsample_initial_channel"]
@@ -138,7 +141,55 @@ class Generator(nn.Module, ParamCache):
                               [pack_conv(c.folded_weight()) for c in rb.convs2]))
         wp = self.conv_post.folded_weight()  # [1, C, k] -> [k*C]
         pk["post"] = wp[0].t().contiguous().reshape(-1)
+        # tensor-core layouts (bf16, [taps, Cout, Cin])
+        pk["pre_tc"] = ops.pack_conv_tc(self.conv_pre.folded_weight())
+        pk["ups_tc"] = []
+        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+            w = self.ups[i].folded_weight()
+            cin, cout, _ = w.shape
+            taps = k // u
+            w4 = w.reshape(cin, cout, taps, u).permute(2, 3, 1, 0).flip(0)  # [j', r, co, ci]
+            pk["ups_tc"].append(w4.reshape(taps, u * cout, cin).contiguous().to(torch.bfloat16))
+        pk["res_tc"] = [([ops.pack_conv_tc(c.folded_weight()) for c in rb.convs1],
+                         [ops.pack_conv_tc(c.folded_weight()) for c in rb.convs2]) for rb in self.resblocks]
         return pk
+
+    def _forward_bf16(self, x, pcm):
+        """Tensor-core path.  Convolution operands are bf16; the residual stream of every ResBlock and
+        the stage mean stay fp32.  Each epilogue also emits the leaky-ReLU'd bf16 copy that the next
+        convolution consumes (the activation cannot sit between TMA and the MMA)."""
+        h, pk, nk = self.h, self.packed(), self.num_kernels
+        L = ops.ACT_LRELU
+        xa = ops.conv1d_tc(ops.cast_bf16(x), pk["pre_tc"], self.conv_pre.bias, pad=3, want_y=False, act2=L,
+                           slope2=LRELU_SLOPE)[1]
+        n_up = self.num_upsamples
+        xs = None
+        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+            x32, xa = ops.conv_transpose1d_tc(xa, pk["ups_tc"][i], pk["ups"][i][1], cout=self.ups[i].bias.numel(),
+                                              stride=u, pad=(k - u) // 2, act2=L, slope2=LRELU_SLOPE)
+            xs, ybuf = torch.empty_like(x32), torch.empty_like(x32)
+            for j in range(nk):
+                rb = self.resblocks[i * nk + j]
+                w1s, w2s = pk["res_tc"][i * nk + j]
+                y32, ya = x32, xa
+                nd, rk = len(rb.dilation), rb.kernel_size
+                for m, dil in enumerate(rb.dilation):
+                    ta = ops.conv1d_tc(ya, w1s[m], rb.convs1[m].bias, dilation=dil, pad=get_padding(rk, dil),
+                                       want_y=False, act2=L, slope2=LRELU_SLOPE)[1]
+                    if m < nd - 1:
+                        y32, ya = ops.conv1d_tc(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y32,
+                                                out=ybuf, act2=L, slope2=LRELU_SLOPE)
+                    else:
+                        last_rb = j == nk - 1
+                        feeds_ups = last_rb and i < n_up - 1  # the next ConvTranspose reads lrelu(mean)
+                        nxt = ops.conv1d_tc(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y32,
+                                            want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0),
+                                            act2=L if feeds_ups else None, slope2=LRELU_SLOPE)[1]
+            xa = nxt
+        wave, pcm16 = ops.hifigan_post(xs, pk["post"], self.conv_post.bias, k=7, in_slope=0.01, want_wave=True,
+                                       want_pcm=pcm)
+        wave = wave.unsqueeze(1)
+        return (wave, pcm16) if pcm else wave
 
     @torch.no_grad()
     def forward(self, x, channels_last=False, pcm=False):
@@ -151,6 +202,8 @@ class Generator(nn.Module, ParamCache):
         if not channels_last:
             x = x.transpose(1, 2)
         x = x.to(torch.float32).contiguous()
+        if self.precision == "bf16":
+            return self._forward_bf16(x, pcm)
         x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3)
         nk = self.num_kernels
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):

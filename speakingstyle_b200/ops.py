@@ -206,14 +206,16 @@ def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0,
     return y, y_act
 
 
-def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pre_relu=False, out=None):
-    """film = (gamma [B,C], beta [B,C], s_gamma [1], s_beta [1]) or None."""
+def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pre_relu=False, out=None,
+              want_bf16=False):
+    """film = (gamma [B,C], beta [B,C], s_gamma [1], s_beta [1]) or None.  With want_bf16 returns (y, y_bf16)."""
     _chk(x, torch.float32, "x"); _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens")
     _chk(pe, torch.float32, "pe"); _chk(ln_w, torch.float32, "ln_w"); _chk(ln_b, torch.float32, "ln_b")
     B, S, Cc = x.shape
     if pe is not None and (pe.shape[0] < S or pe.shape[1] != Cc):
         raise _lib.SSError("layernorm: position table too small")
     y = out if out is not None else torch.empty_like(x)
+    yb = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if want_bf16 else None
     g = be = sg = sb = None
     if film is not None:
         g, be, sg, sb = film
@@ -224,9 +226,9 @@ def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pr
         ln_b=ln_b.data_ptr(), gamma=None if g is None else g.data_ptr(), beta=None if be is None else be.data_ptr(),
         s_gamma=None if sg is None else sg.data_ptr(), s_beta=None if sb is None else sb.data_ptr(),
         lens=None if lens is None else lens.data_ptr(), pe=None if pe is None else pe.data_ptr(), y=y.data_ptr(),
-        B=B, S=S, C=Cc, pre_relu=int(pre_relu))
+        y_bf16=None if yb is None else yb.data_ptr(), B=B, S=S, C=Cc, pre_relu=int(pre_relu))
     check(_lib.lib().ss_layernorm(C.byref(p), _stream()))
-    return y
+    return (y, yb) if want_bf16 else y
 
 
 def attention(qkv, lens, n_head):

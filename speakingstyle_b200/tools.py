@@ -6,17 +6,17 @@ from .fastspeech2 import FastSpeech2
 from .hifigan import Generator
 
 
-def get_model(preprocess_config, model_config, device="cuda", state_dict=None):
+def get_model(preprocess_config, model_config, device="cuda", state_dict=None, precision="fp32"):
     """utils/model.py:11-45 without the checkpoint-file handling: build, load, eval, move."""
-    model = FastSpeech2(preprocess_config, model_config)
+    model = FastSpeech2(preprocess_config, model_config, precision=precision)
     if state_dict is not None:
         model.load_state_dict(state_dict, strict=True)
     return model.to(device)
 
 
-def get_vocoder(h=None, device="cuda", state_dict=None):
+def get_vocoder(h=None, device="cuda", state_dict=None, precision="fp32"):
     """utils/model.py:62-94: Generator(h), load ckpt["generator"], eval, remove_weight_norm, move."""
-    gen = Generator(h or configs.hifigan_config())
+    gen = Generator(h or configs.hifigan_config(), precision=precision)
     if state_dict is not None:
         gen.load_state_dict(state_dict, strict=True)
     gen.remove_weight_norm()

@@ -103,20 +103,30 @@ class MultiHeadAttention(nn.Module, ParamCache):
         self.fc = Dense(n_head * d_v, d_model)
 
     def _pack(self):
+        wqkv = torch.cat([self.w_qs.weight, self.w_ks.weight, self.w_vs.weight], dim=0)  # [3D, D]
         return {
-            "wqkv": torch.cat([pack_conv(self.w_qs.weight), pack_conv(self.w_ks.weight), pack_conv(self.w_vs.weight)],
-                              dim=1).contiguous(),
+            "wqkv": pack_conv(wqkv),
             "bqkv": torch.cat([self.w_qs.bias, self.w_ks.bias, self.w_vs.bias]).contiguous(),
             "wfc": pack_conv(self.fc.weight),
+            "wqkv_tc": ops.pack_conv_tc(wqkv),
+            "wfc_tc": ops.pack_conv_tc(self.fc.weight),
         }
 
-    def forward(self, x, lens, mask_rows=True):
-        """x [B,S,D] -> LayerNorm(fc(attention) + x), rows >= lens zeroed (Layers.py:27-28)."""
+    def forward(self, x, lens, mask_rows=True, xb=None):
+        """x [B,S,D] -> LayerNorm(fc(attention) + x), rows >= lens zeroed (Layers.py:27-28).
+        With ``xb`` (bf16 copy of x) the two projections run on the tensor cores and the result is
+        returned as (fp32, bf16)."""
         pk = self.packed()
+        ln = self.layer_norm
+        if xb is not None:
+            qkv, _ = ops.conv1d_tc(xb, pk["wqkv_tc"], pk["bqkv"])
+            ctx = ops.attention(qkv, lens, self.n_head)
+            y, _ = ops.conv1d_tc(ops.cast_bf16(ctx), pk["wfc_tc"], self.fc.bias, residual=x)
+            return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y, want_bf16=True)
         qkv = ops.conv1d(x, pk["wqkv"], pk["bqkv"])
         ctx = ops.attention(qkv, lens, self.n_head)
         y = ops.conv1d(ctx, pk["wfc"], self.fc.bias, residual=x)
-        return ops.layernorm(y, self.layer_norm.weight, self.layer_norm.bias, lens=lens if mask_rows else None, out=y)
+        return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y)
 
 
 class PositionwiseFeedForward(nn.Module, ParamCache):
@@ -130,14 +140,21 @@ class PositionwiseFeedForward(nn.Module, ParamCache):
         self.layer_norm = Norm(d_in)
 
     def _pack(self):
-        return {"w1": pack_conv(self.w_1.weight), "w2": pack_conv(self.w_2.weight)}
+        return {"w1": pack_conv(self.w_1.weight), "w2": pack_conv(self.w_2.weight),
+                "w1_tc": ops.pack_conv_tc(self.w_1.weight), "w2_tc": ops.pack_conv_tc(self.w_2.weight)}
 
-    def forward(self, x, lens=None, film=None):
+    def forward(self, x, lens=None, film=None, xb=None):
         pk = self.packed()
         k1, k2 = self.kernel_size
+        ln = self.layer_norm
+        if xb is not None:  # tensor-core path: the 1024-channel intermediate only ever exists in bf16
+            h, _ = ops.conv1d_tc(xb, pk["w1_tc"], self.w_1.bias, pad=(k1 - 1) // 2, act=ops.ACT_RELU,
+                                 out_dtype=torch.bfloat16)
+            y, _ = ops.conv1d_tc(h, pk["w2_tc"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x)
+            return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y, want_bf16=True)
         h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU)
         y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x)
-        return ops.layernorm(y, self.layer_norm.weight, self.layer_norm.bias, film=film, lens=lens, out=y)
+        return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y)
 
 
 class FFTBlock(nn.Module):
@@ -150,13 +167,19 @@ class FFTBlock(nn.Module):
         if film:
             self.film = FiLM()
 
-    def forward(self, enc_input, gammas=None, betas=None, mask=None, slf_attn_mask=None, lens=None):
+    def forward(self, enc_input, gammas=None, betas=None, mask=None, slf_attn_mask=None, lens=None, xb=None):
         """Returns (output, None): the attention probabilities the reference returns here are
-        dropped by every caller (Models.py:98-101) and are never materialised."""
+        dropped by every caller (Models.py:98-101) and are never materialised.
+        With ``xb`` (bf16 copy of the input) the block runs its projections and convolutions on the
+        tensor cores and returns ((fp32, bf16), None)."""
         if lens is None:
             lens = lens_from_mask(mask)
+        film = film_args(getattr(self, "film", None), gammas, betas)
+        if xb is not None:
+            x, xb = self.slf_attn(enc_input, lens, xb=xb)
+            return self.pos_ffn(x, lens=lens, film=film, xb=xb), None
         x = self.slf_attn(enc_input, lens)
-        x = self.pos_ffn(x, lens=lens, film=film_args(getattr(self, "film", None), gammas, betas))
+        x = self.pos_ffn(x, lens=lens, film=film)
         return x, None
 
 
@@ -216,7 +239,8 @@ class Decoder(nn.Module, _PositionTable):
             FFTBlock(d, tr["decoder_head"], d // tr["decoder_head"], d // tr["decoder_head"], tr["conv_filter_size"],
                      tr["conv_kernel_size"], dropout=tr["decoder_dropout"]) for _ in range(tr["decoder_layer"])])
 
-    def forward(self, enc_seq, mask, gammas=None, betas=None, return_attns=False, lens=None, pe_added=False):
+    def forward(self, enc_seq, mask, gammas=None, betas=None, return_attns=False, lens=None, pe_added=False,
+                precision="fp32", return_bf16=False):
         T = enc_seq.shape[1]
         mask = mask[:, :T]
         if lens is None:
@@ -224,6 +248,11 @@ class Decoder(nn.Module, _PositionTable):
         x = enc_seq
         if not pe_added:
             x = ops.add_position(enc_seq, self._pe(T, self.d_model))
+        if precision == "bf16":
+            xb = ops.cast_bf16(x)
+            for layer in self.layer_stack:
+                (x, xb), _ = layer(x, gammas=gammas, betas=betas, lens=lens, xb=xb)
+            return ((x, xb), mask) if return_bf16 else (x, mask)
         for layer in self.layer_stack:
             x, _ = layer(x, gammas=gammas, betas=betas, lens=lens)
         return x, mask
@@ -276,15 +305,24 @@ class PostNet(nn.Module, ParamCache):
             scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
             w = conv.conv.weight * scale[:, None, None]
             b = (conv.conv.bias - bn.running_mean) * scale + bn.bias
-            out.append((pack_conv(w), b.contiguous()))
+            out.append((pack_conv(w), b.contiguous(), ops.pack_conv_tc(w)))
         return out
 
-    def forward(self, x, residual=None):
-        """x [B,T,n_mel] -> postnet(x) (+ residual fused into the last convolution if given)."""
+    def forward(self, x, residual=None, precision="fp32", xb=None):
+        """x [B,T,n_mel] -> postnet(x) (+ residual fused into the last convolution if given).
+        precision="bf16": tensor-core convolutions, bf16 activations between layers (xb = bf16 copy of x)."""
         pk = self.packed()
         k = self.kernel_size
         n = len(pk)
-        for i, (w, b) in enumerate(pk):
+        if precision == "bf16":
+            h = xb if xb is not None else ops.cast_bf16(x)
+            for i, (_, b, wtc) in enumerate(pk):
+                last = i == n - 1
+                h, _ = ops.conv1d_tc(h, wtc, b, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
+                                     residual=residual if last else None,
+                                     out_dtype=torch.float32 if last else torch.bfloat16)
+            return h
+        for i, (w, b, _) in enumerate(pk):
             last = i == n - 1
             x = ops.conv1d(x, w, b, k=k, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
                            residual=residual if last else None)

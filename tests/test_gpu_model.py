@@ -239,3 +239,65 @@ def test_outputs_depend_on_batch_composition_like_the_reference():
     with torch.no_grad():
         ref = O.fastspeech2_forward(sd, mc, solo)
     assert torch.equal(out[5].cpu(), ref[5]) and maxabs(out[1], ref[1]) <= TOL
+
+
+# ---------------------------------------------------------------------------------------------
+# bf16 precision mode (tcgen05 convolutions): integers identical, floats within relative L2 1e-2
+# ---------------------------------------------------------------------------------------------
+def rel_l2(a, b):
+    a, b = a.detach().cpu().double(), torch.as_tensor(b).double()
+    return ((a - b).norm() / b.norm()).item()
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny_ms", "cfg1", "cfg3"])
+def test_bf16_mode_matches_within_relative_l2(golden, name):
+    g = golden(name)
+    ds, batch, voc = S.make_workload(name)
+    model, mc, sd = get_models(ds)
+    model.precision = "bf16"
+    try:
+        out = run(model, batch)
+    finally:
+        model.precision = "fp32"
+    # the integer-deciding chain is fp32 in both modes: identical integers
+    assert np.array_equal(out[5].cpu().numpy(), g["d_rounded"])
+    assert np.array_equal(out[9].cpu().numpy(), g["mel_lens"])
+    if "mel" in g:
+        mel_ref, post_ref, sl = g["mel"], g["postnet_mel"], slice(None)
+    else:
+        st = int(g["stride"])
+        mel_ref, post_ref, sl = g["mel_s"], g["postnet_mel_s"], slice(None, None, st)
+    r_mel, r_post = rel_l2(out[0][:, sl], mel_ref), rel_l2(out[1][:, sl], post_ref)
+    _report(f"{name} bf16 mode: mel rel-L2 {r_mel:.3e}, postnet rel-L2 {r_post:.3e}")
+    assert r_mel <= 1e-2 and r_post <= 1e-2
+    if voc:
+        gen, h, vsd = get_vocoder()
+        gen.precision = "bf16"
+        try:
+            wave = gen(out[1], channels_last=True)
+        finally:
+            gen.precision = "fp32"
+        if "wave" in g:
+            ref = torch.from_numpy(g["wave"])
+            got = wave.cpu()
+        else:
+            ws = int(g["wave_stride"])
+            ref, got = torch.from_numpy(g["wave_s"]), wave[:, 0, ::ws].cpu()
+        r = rel_l2(got, ref)
+        ac = ref.double() - ref.double().mean()
+        r_ac = ((got.double() - ref.double()).norm() / ac.norm()).item()  # against the mean-removed signal
+        _report(f"{name} bf16 mode: wave rel-L2 {r:.3e} (mean-removed {r_ac:.3e})")
+        assert r <= 1e-2 and r_ac <= 1.5e-2
+
+
+def test_hifigan_bf16_alone(golden):
+    g = golden("hifigan_small")
+    gen, h, vsd = get_vocoder()
+    gen.precision = "bf16"
+    try:
+        wave, pcm = gen(torch.from_numpy(g["mel"]).to(DEV), pcm=True)
+    finally:
+        gen.precision = "fp32"
+    r = rel_l2(wave, g["wave"])
+    _report(f"hifigan_small bf16 mode: wave rel-L2 {r:.3e}")
+    assert wave.shape == g["wave"].shape and r <= 1e-2
