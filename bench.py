@@ -227,6 +227,7 @@ def main():
                     help="fp32: all kernels fp32-accurate (mel max-abs <= 1e-3); bf16: Decoder/PostNet/HiFi-GAN "
                          "on tcgen05 with bf16 operands (relative L2 <= 1e-2); integers identical in both")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--conv-breakdown", action="store_true", help="print per-shape conv timings to stderr")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -335,6 +336,11 @@ def main():
         value = total_frames * args.steps / (dev_ms_max * 1e-3)
         e2e_value = total_frames * args.steps / (e2e_ms_max * 1e-3)
         calls, conv_ms, conv_flops = timer.summary()
+        if args.conv_breakdown:
+            for tag, (c, ms, w) in timer.by_tag().items():
+                sys.stderr.write(f"{ms / args.steps:9.3f} ms/step {c // args.steps:4d} calls/step "
+                                 f"{w / (ms * 1e-3) / 1e12:8.1f} TFLOP/s  {tag}\n")
+            sys.stderr.write(f"step {dev_ms / args.steps:.3f} ms, convs {conv_ms / args.steps:.3f} ms\n")
         ach = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
         roof = {"kernel": "conv1d_f32_kernel + conv1d_tc_kernel (all implicit-GEMM conv/linear launches)"
                 if args.precision == "bf16" else "conv1d_f32_kernel (fp32 FFMA implicit-GEMM conv/linear)",

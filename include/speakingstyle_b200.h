@@ -140,6 +140,42 @@ typedef struct {
 } ss_conv1d_tc_params;
 SS_API int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * fp32-ACCURATE convolution on the tensor cores: 3xTF32 error-compensated tcgen05.mma (kind::tf32),
+ * fp32 activations in and out - a drop-in for ss_conv1d_f32 (same call sites, same epilogue, same
+ * addressing) for the chain that decides integers and for the fp32 precision mode.  The fp32 input
+ * tile is split on chip into hi = tf32(x), lo = tf32(x - hi) (after the optional leaky-ReLU on load);
+ * the weights arrive pre-split: w_hi = tf32(w), w_lo = tf32(w - w_hi), both [k, Cout, Cin] fp32.
+ * acc = lo*w_hi + hi*w_lo + hi*w_hi  in fp32.  y is fp32; y_act (optional) = bf16(act2(v)).
+ * Cin % 4 == 0, Cout % 4 == 0, strides/offsets % 4 == 0, 16-byte aligned pointers.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const float* x;
+  int64_t x_batch_stride;
+  int64_t x_row_stride;
+  const float* w_hi;       /* [k, Cout, Cin] */
+  const float* w_lo;       /* [k, Cout, Cin] */
+  const float* bias;
+  const float* residual;   /* f32 or NULL */
+  const int32_t* lens;
+  float* y;
+  void* y_act;             /* bf16 or NULL */
+  float* accum;
+  int64_t y_batch_stride, y_row_stride, y_offset, y_batch_elems;
+  int32_t B, S_in, S_out, Cin, Cout, k, dilation, pad;
+  int32_t in_act;
+  float in_slope;
+  int32_t act;
+  float slope;
+  int32_t act2;
+  float slope2;
+  float accum_scale;
+  int32_t accum_init;
+  int32_t k_group;         /* 32-channel chunks per accumulator restart (0 = default 4): tcgen05 accumulates with
+                              truncation, so partial sums are re-added in registers every k_group*4 MMAs */
+} ss_conv1d_tf32_params;
+SS_API int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream);
+
 /* out = bf16(act(x)) element-wise over n elements (n % 8 == 0): the entry into the bf16 path. */
 SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream);
 

@@ -34,6 +34,17 @@ class Conv1dTcParams(C.Structure):
     ]
 
 
+class Conv1dTf32Params(C.Structure):
+    _fields_ = [
+        ("x", vp), ("x_batch_stride", i64), ("x_row_stride", i64), ("w_hi", vp), ("w_lo", vp), ("bias", vp),
+        ("residual", vp), ("lens", vp), ("y", vp), ("y_act", vp), ("accum", vp), ("y_batch_stride", i64),
+        ("y_row_stride", i64), ("y_offset", i64), ("y_batch_elems", i64), ("B", i32), ("S_in", i32), ("S_out", i32),
+        ("Cin", i32), ("Cout", i32), ("k", i32), ("dilation", i32), ("pad", i32), ("in_act", i32), ("in_slope", f32),
+        ("act", i32), ("slope", f32), ("act2", i32), ("slope2", f32), ("accum_scale", f32), ("accum_init", i32),
+        ("k_group", i32),
+    ]
+
+
 class LayerNormParams(C.Structure):
     _fields_ = [
         ("x", vp), ("residual", vp), ("ln_w", vp), ("ln_b", vp), ("gamma", vp), ("beta", vp), ("s_gamma", vp),
@@ -58,6 +69,7 @@ _SIGNATURES = {
     "ss_add_posenc": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_conv1d_f32": (C.c_int, [C.POINTER(Conv1dF32Params), vp]),
     "ss_conv1d_tc": (C.c_int, [C.POINTER(Conv1dTcParams), vp]),
+    "ss_conv1d_tf32x3": (C.c_int, [C.POINTER(Conv1dTf32Params), vp]),
     "ss_cast_bf16": (C.c_int, [vp, vp, i64, C.c_int, f32, vp]),
     "ss_layernorm": (C.c_int, [C.POINTER(LayerNormParams), vp]),
     "ss_attention_f32": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),

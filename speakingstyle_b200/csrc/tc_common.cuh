@@ -1,0 +1,273 @@
+// Shared pieces of the tcgen05 convolution kernels (bf16 and 3xTF32): PTX wrappers for mbarrier,
+// TMA, tcgen05 / TMEM, the shared-memory matrix descriptor, and the epilogue that drains one
+// accumulator tile from TMEM to global memory with coalesced 128-bit accesses.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace sstc {
+
+constexpr int BM = 128;          // rows per tile = TMEM lanes
+constexpr int ROW_BYTES = 128;   // one K-chunk row = one 128-byte swizzle row (64 bf16 or 32 tf32)
+constexpr int A_BYTES = BM * ROW_BYTES;
+constexpr int STG_PITCH = 36;    // floats; 32 + 4 keeps both the float4 writes and reads conflict-free
+constexpr int STG_BYTES = 4 * 32 * STG_PITCH * 4;  // one 32x32 fp32 staging tile per epilogue warp
+
+struct TcArgs {
+  const float* bias;
+  const void* residual;
+  const int32_t* lens;
+  void* y;
+  __nv_bfloat16* y_act;
+  float* accum;
+  int64_t y_batch_stride, y_row_stride, y_offset, y_batch_elems;
+  int32_t B, S_out, Cin, Cout, k, dilation, pad;
+  int32_t m_tiles, n_tiles;
+  int32_t act, act2, y_dtype, residual_dtype, accum_init;
+  float slope, slope2, accum_scale;
+};
+
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                            int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::
+          "r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// generic-proxy shared-memory writes -> visible to the async proxy (tcgen05.mma operand reads)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t slot_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// start>>4 [0,14) | LBO>>4 [16,30) (unused for swizzled K-major, 1) | SBO>>4 [32,46) = 1024 B between
+// 8-row groups | version=1 [46,48) | layout_type=2 (SWIZZLE_128B) [61,64)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): c=f32 [4,6)=1, a_format [7,10), b_format [10,13)
+// (1 = bf16, 2 = tf32), a/b K-major (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29)
+__device__ __forceinline__ uint32_t make_idesc(uint32_t fmt, int n) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ void unpack_bf16(uint32_t u, float& a, float& b) {
+  a = __uint_as_float(u << 16);
+  b = __uint_as_float(u & 0xFFFF0000u);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Drain one 128 x BN fp32 accumulator tile.  Called by the four epilogue warps; warp `lg` owns TMEM
+// lanes [32*lg, 32*lg+32).  tcgen05.ld hands each thread one ROW (32 consecutive columns); a global
+// store from that layout would touch 32 different cache lines per instruction, so each 32x32 block
+// goes through a per-warp shared-memory staging tile and is re-read with lanes running along the
+// row: every global access below covers 4 rows x 128 contiguous bytes.
+// All fused element-wise work (bias, activation, residual, row mask, running mean, activated bf16
+// copy) happens in that coalesced domain, where a lane's four columns are the same for all rows.
+// ---------------------------------------------------------------------------------------------
+// One 32-column block: v[] holds this thread's ROW (TMEM lane) of the block; n_blk = first column.
+__device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane, int b,
+                                            int mt, int n_blk, int len) {
+  const int col = (lane & 7) * 4;
+  const int rsub = lane >> 3;
+  const int64_t ybase = (int64_t)b * p.y_batch_stride;
+  float* my = stg + lane * STG_PITCH;
+  __syncwarp();  // the previous block has been fully read back
+#pragma unroll
+  for (int q = 0; q < 8; ++q)
+    *reinterpret_cast<float4*>(my + q * 4) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+  __syncwarp();
+  const int n = n_blk + col;
+  if (n >= p.Cout) return;
+  float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int rr = it * 4 + rsub;
+    const int t = mt * BM + lg * 32 + rr;
+    if (t >= p.S_out) continue;
+    const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + n;
+    if (off < 0 || off >= p.y_batch_elems) continue;
+    float4 f = *reinterpret_cast<const float4*>(stg + rr * STG_PITCH + col);
+    f.x = ss::apply_act(f.x + bias4.x, p.act, p.slope);
+    f.y = ss::apply_act(f.y + bias4.y, p.act, p.slope);
+    f.z = ss::apply_act(f.z + bias4.z, p.act, p.slope);
+    f.w = ss::apply_act(f.w + bias4.w, p.act, p.slope);
+    if (p.residual) {
+      if (p.residual_dtype == SS_F32) {
+        const float4 r = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + ybase + off));
+        f.x += r.x; f.y += r.y; f.z += r.z; f.w += r.w;
+      } else {
+        const uint2 r = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + ybase + off));
+        float a, c;
+        unpack_bf16(r.x, a, c); f.x += a; f.y += c;
+        unpack_bf16(r.y, a, c); f.z += a; f.w += c;
+      }
+    }
+    if (t >= len) f = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.y) {
+      if (p.y_dtype == SS_F32)
+        *reinterpret_cast<float4*>(static_cast<float*>(p.y) + ybase + off) = f;
+      else
+        *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y) + ybase + off) =
+            make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+    }
+    if (p.accum) {  // running mean; the activated copy below then follows the accumulated value
+      float4* ap = reinterpret_cast<float4*>(p.accum + ybase + off);
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!p.accum_init) a = *ap;
+      f.x = fmaf(p.accum_scale, f.x, a.x);
+      f.y = fmaf(p.accum_scale, f.y, a.y);
+      f.z = fmaf(p.accum_scale, f.z, a.z);
+      f.w = fmaf(p.accum_scale, f.w, a.w);
+      *ap = f;
+    }
+    if (p.y_act) {
+      f.x = ss::apply_act(f.x, p.act2, p.slope2);
+      f.y = ss::apply_act(f.y, p.act2, p.slope2);
+      f.z = ss::apply_act(f.z, p.act2, p.slope2);
+      f.w = ss::apply_act(f.w, p.act2, p.slope2);
+      *reinterpret_cast<uint2*>(p.y_act + ybase + off) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+    }
+  }
+}
+
+template <int BN>
+__device__ __forceinline__ void drain_tile(const TcArgs& p, uint32_t taddr, float* stg, int lg, int lane, int b, int mt,
+                                           int n0) {
+  const int len = p.lens ? p.lens[b] : 0x7fffffff;
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    float v[32];
+    __syncwarp();  // reconverge: tcgen05.ld is .sync.aligned
+    tmem_ld32(taddr + c0, v);
+    drain_block(p, v, stg, lg, lane, b, mt, n0 + c0, len);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host helpers
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// 3-D tensor map {d0 (contiguous), d1, d2} with a {box0, box1, 1} box and the 128-byte swizzle.
+inline int make_map_3d(CUtensorMap* m, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
+                       uint64_t s1_bytes, uint64_t s2_bytes, uint32_t box0, uint32_t box1) {
+  EncodeTiledFn fn = encode_fn();
+  SS_REQUIRE(fn != nullptr, SS_ERR_CUDA, "tensor-core conv: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[3] = {d0, d1, d2};
+  cuuint64_t strides[2] = {s1_bytes, s2_bytes};
+  cuuint32_t box[3] = {box0, box1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(m, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SS_REQUIRE(r == CUDA_SUCCESS, SS_ERR_CUDA, "tensor-core conv: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return SS_OK;
+}
+
+inline int sm_count() {
+  static int n = []() {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    return v;
+  }();
+  return n;
+}
+
+}  // namespace sstc

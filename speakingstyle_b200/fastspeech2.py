@@ -41,7 +41,7 @@ class FastSpeech2(nn.Module, ParamCache):
         self.eval()
 
     def _pack(self):
-        return {"mel_w": pack_conv(self.mel_linear.weight), "mel_w_tc": ops.pack_conv_tc(self.mel_linear.weight)}
+        return {"mel_w": pack_conv(self.mel_linear.weight)}
 
     def packed(self):  # only mel_linear's own parameters key this cache
         srcs = [self.mel_linear.weight]
@@ -107,7 +107,7 @@ class FastSpeech2(nn.Module, ParamCache):
             # fp32 residual stream).  Everything before this point decides integers and stays fp32.
             (x, xb), _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True, precision="bf16",
                                       return_bf16=True)
-            mel, melb = ops.conv1d_tc(xb, self.packed()["mel_w_tc"], self.mel_linear.bias, act2=ops.ACT_NONE)
+            mel, melb = ops.conv1d_tc(xb, self.packed()["mel_w"], self.mel_linear.bias, act2=ops.ACT_NONE)
             postnet_mel = self.postnet(mel, residual=mel, precision="bf16", xb=melb)
         else:
             x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True)

@@ -128,30 +128,14 @@ class Generator(nn.Module, ParamCache):
     def _pack(self):
         h = self.h
         pk = {"pre": pack_conv(self.conv_pre.folded_weight()), "ups": [], "res": []}
-        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
-            w = self.ups[i].folded_weight()  # [Cin, Cout, k]
-            cin, cout, _ = w.shape
-            taps = k // u
-            # row s of the phase-form GEMM covers output samples u*s + r - pad, r in [0,u); tap j' reads
-            # input row s - (taps-1-j') and uses kernel index r + (taps-1-j')*u
-            w4 = w.reshape(cin, cout, taps, u).permute(2, 0, 3, 1).flip(0)  # [j', ci, r, co]
-            pk["ups"].append((w4.reshape(taps * cin, u * cout).contiguous(), self.ups[i].bias.repeat(u).contiguous()))
+        for i, u in enumerate(h["upsample_rates"]):
+            pk["ups"].append((ops.pack_conv_transpose(self.ups[i].folded_weight(), u),
+                              self.ups[i].bias.repeat(u).contiguous()))
         for rb in self.resblocks:
             pk["res"].append(([pack_conv(c.folded_weight()) for c in rb.convs1],
                               [pack_conv(c.folded_weight()) for c in rb.convs2]))
         wp = self.conv_post.folded_weight()  # [1, C, k] -> [k*C]
         pk["post"] = wp[0].t().contiguous().reshape(-1)
-        # tensor-core layouts (bf16, [taps, Cout, Cin])
-        pk["pre_tc"] = ops.pack_conv_tc(self.conv_pre.folded_weight())
-        pk["ups_tc"] = []
-        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
-            w = self.ups[i].folded_weight()
-            cin, cout, _ = w.shape
-            taps = k // u
-            w4 = w.reshape(cin, cout, taps, u).permute(2, 3, 1, 0).flip(0)  # [j', r, co, ci]
-            pk["ups_tc"].append(w4.reshape(taps, u * cout, cin).contiguous().to(torch.bfloat16))
-        pk["res_tc"] = [([ops.pack_conv_tc(c.folded_weight()) for c in rb.convs1],
-                         [ops.pack_conv_tc(c.folded_weight()) for c in rb.convs2]) for rb in self.resblocks]
         return pk
 
     def _forward_bf16(self, x, pcm):
@@ -160,17 +144,17 @@ class Generator(nn.Module, ParamCache):
         convolution consumes (the activation cannot sit between TMA and the MMA)."""
         h, pk, nk = self.h, self.packed(), self.num_kernels
         L = ops.ACT_LRELU
-        xa = ops.conv1d_tc(ops.cast_bf16(x), pk["pre_tc"], self.conv_pre.bias, pad=3, want_y=False, act2=L,
+        xa = ops.conv1d_tc(ops.cast_bf16(x), pk["pre"], self.conv_pre.bias, pad=3, want_y=False, act2=L,
                            slope2=LRELU_SLOPE)[1]
         n_up = self.num_upsamples
         xs = None
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
-            x32, xa = ops.conv_transpose1d_tc(xa, pk["ups_tc"][i], pk["ups"][i][1], cout=self.ups[i].bias.numel(),
+            x32, xa = ops.conv_transpose1d_tc(xa, pk["ups"][i][0], pk["ups"][i][1], cout=self.ups[i].bias.numel(),
                                               stride=u, pad=(k - u) // 2, act2=L, slope2=LRELU_SLOPE)
             xs, ybuf = torch.empty_like(x32), torch.empty_like(x32)
             for j in range(nk):
                 rb = self.resblocks[i * nk + j]
-                w1s, w2s = pk["res_tc"][i * nk + j]
+                w1s, w2s = pk["res"][i * nk + j]
                 y32, ya = x32, xa
                 nd, rk = len(rb.dilation), rb.kernel_size
                 for m, dil in enumerate(rb.dilation):
@@ -208,8 +192,8 @@ class Generator(nn.Module, ParamCache):
         nk = self.num_kernels
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
             wu, bu = pk["ups"][i]
-            x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, taps=k // u,
-                                     pad=(k - u) // 2, in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE)
+            x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, pad=(k - u) // 2,
+                                     in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE)
             # four buffers per stage: x (stage input, read by all three ResBlocks), xs (their mean),
             # tbuf (output of c1) and ybuf (the running residual stream of one ResBlock).  c2 may write
             # in place over its residual operand (same element, same thread) but never over its conv input.

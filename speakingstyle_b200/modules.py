@@ -231,7 +231,7 @@ class ReferenceEncoder(nn.Module, ParamCache, _PositionTable):
         for blk in self.fftb_stack:
             x, _ = blk(x, lens=lens)
         pooled = ops.mean_pool(x)  # mean over the PADDED length (modules.py:398)
-        gb = ops.conv1d(pooled.unsqueeze(0), pk["affine"], None)[0]  # [B, 2d]
+        gb = ops.conv1d(pooled.unsqueeze(0), pk["affine"], None, backend="ffma")[0]  # [B, 2d]: one tiny GEMV
         d = self.d_model
         gammas = gb[:, :d].unsqueeze(1)
         betas = gb[:, d:].unsqueeze(1)

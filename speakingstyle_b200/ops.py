@@ -39,26 +39,38 @@ class KernelTimer:
     def __init__(self):
         self.records = []  # (start_event, end_event, work)
 
-    def run(self, work, fn):
+    def run(self, work, fn, tag=None):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         status = fn()
         b.record()
-        self.records.append((a, b, work))
+        self.records.append((a, b, work, tag))
         return status
 
     def summary(self):
         """(calls, total_ms, total_work) - call after a synchronize."""
-        ms = sum(a.elapsed_time(b) for a, b, _ in self.records)
-        return len(self.records), ms, sum(w for _, _, w in self.records)
+        ms = sum(a.elapsed_time(b) for a, b, _, _ in self.records)
+        return len(self.records), ms, sum(w for _, _, w, _ in self.records)
+
+    def by_tag(self):
+        """{tag: (calls, ms, work)} sorted by time, for the per-shape breakdown bench.py can print."""
+        agg = {}
+        for a, b, w, tag in self.records:
+            c, ms, ww = agg.get(tag, (0, 0.0, 0.0))
+            agg[tag] = (c + 1, ms + a.elapsed_time(b), ww + w)
+        return dict(sorted(agg.items(), key=lambda kv: -kv[1][1]))
 
 
 conv_timer = None  # set to a KernelTimer to time every ss_conv1d_f32 launch; work = algorithmic FLOPs
 
 
+def _tag(kind, p):
+    return f"{kind} B={p.B} S={p.S_in} Cin={p.Cin} Cout={p.Cout} k={p.k} dil={p.dilation}"
+
+
 def _run_conv(p, flops):
     fn = lambda: _lib.lib().ss_conv1d_f32(C.byref(p), _stream())  # noqa: E731
-    check(conv_timer.run(flops, fn) if conv_timer is not None else fn())
+    check(conv_timer.run(flops, fn, _tag("f32", p)) if conv_timer is not None else fn())
 
 
 def launch_count():
@@ -91,19 +103,103 @@ def add_position(x, pe):
     return out
 
 
-def conv1d(x, w, bias=None, *, k=1, dilation=1, pad=0, act=ACT_NONE, slope=0.0, in_act=ACT_NONE, in_slope=0.0,
-           residual=None, lens=None, out=None, accum=None, accum_scale=1.0, accum_init=False, write_y=True):
-    """x [B,S,Cin] f32, w packed [k*Cin, Cout] -> y [B,S,Cout] (see ss_conv1d_f32)."""
-    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w"); _chk(bias, torch.float32, "bias")
+fp32_backend = "tf32x3"  # "tf32x3": 3xTF32 tcgen05 kernel (default); "ffma": the FP32-pipe kernel
+tf32_k_group = 0         # 0 = library default (accumulator restart every 4 chunks = 128 channels)
+
+
+def tf32_round(t):
+    """Nearest TF32 value (10 explicit mantissa bits), ties away from zero in magnitude, as an fp32 tensor."""
+    return ((t.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+class ConvW:
+    """One convolution weight in the layouts the kernels want, built lazily from the canonical
+    [k, Cout, Cin] fp32 tensor: .ffma [k*Cin, Cout] (ss_conv1d_f32), .tf32 = (hi, lo) [k, Cout, Cin]
+    (ss_conv1d_tf32x3), .bf16 [k, Cout, Cin] (ss_conv1d_tc)."""
+
+    def __init__(self, kcc):
+        self.kcc = kcc.contiguous()
+        self.k, self.cout, self.cin = self.kcc.shape
+        self._ffma = self._tf32 = self._bf16 = None
+
+    @property
+    def ffma(self):
+        if self._ffma is None:
+            self._ffma = self.kcc.permute(0, 2, 1).reshape(self.k * self.cin, self.cout).contiguous()
+        return self._ffma
+
+    @property
+    def tf32(self):
+        if self._tf32 is None:
+            hi = tf32_round(self.kcc)
+            self._tf32 = (hi, tf32_round(self.kcc - hi))
+        return self._tf32
+
+    @property
+    def bf16(self):
+        if self._bf16 is None:
+            self._bf16 = self.kcc.to(torch.bfloat16)
+        return self._bf16
+
+
+def pack_conv(weight):
+    """nn.Conv1d weight [Cout, Cin, k] or nn.Linear weight [out, in] -> ConvW."""
+    if weight.dim() == 2:
+        weight = weight.unsqueeze(-1)
+    return ConvW(weight.permute(2, 0, 1))
+
+
+def pack_conv_transpose(weight, stride):
+    """nn.ConvTranspose1d weight [Cin, Cout, k] (k % stride == 0) -> ConvW of the phase form: taps = k/stride,
+    stride*Cout GEMM columns ordered (phase r, co); tap j' reads input row s-(taps-1-j') with kernel index
+    r + (taps-1-j')*stride."""
+    cin, cout, k = weight.shape
+    taps = k // stride
+    w4 = weight.reshape(cin, cout, taps, stride).permute(2, 3, 1, 0).flip(0)  # [j', r, co, ci]
+    return ConvW(w4.reshape(taps, stride * cout, cin))
+
+
+def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y_batch_stride, y_row_stride,
+               y_offset, y_batch_elems, dilation, pad, in_act, in_slope, act, slope, act2, slope2, accum_scale,
+               accum_init, flops):
+    hi, lo = W.tf32
+    p = _lib.Conv1dTf32Params(
+        x=x.data_ptr(), x_batch_stride=S_in * W.cin, x_row_stride=W.cin, w_hi=hi.data_ptr(), w_lo=lo.data_ptr(),
+        bias=None if bias is None else bias.data_ptr(), residual=None if residual is None else residual.data_ptr(),
+        lens=None if lens is None else lens.data_ptr(), y=None if y is None else y.data_ptr(),
+        y_act=None if y_act is None else y_act.data_ptr(), accum=None if accum is None else accum.data_ptr(),
+        y_batch_stride=y_batch_stride, y_row_stride=y_row_stride, y_offset=y_offset, y_batch_elems=y_batch_elems,
+        B=B, S_in=S_in, S_out=S_out, Cin=W.cin, Cout=W.cout, k=W.k, dilation=dilation, pad=pad, in_act=in_act,
+        in_slope=in_slope, act=act, slope=slope, act2=act2 or 0, slope2=slope2, accum_scale=accum_scale,
+        accum_init=int(accum_init), k_group=tf32_k_group)
+    fn = lambda: _lib.lib().ss_conv1d_tf32x3(C.byref(p), _stream())  # noqa: E731
+    check(conv_timer.run(flops, fn, _tag("tf32x3", p)) if conv_timer is not None else fn())
+
+
+def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.0, in_act=ACT_NONE, in_slope=0.0,
+           residual=None, lens=None, out=None, accum=None, accum_scale=1.0, accum_init=False, write_y=True,
+           backend=None):
+    """fp32-accurate convolution: x [B,S,Cin] f32, w a ConvW -> y [B,S,Cout] f32.
+    backend (default ops.fp32_backend): "tf32x3" = ss_conv1d_tf32x3, "ffma" = ss_conv1d_f32."""
+    _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias")
     _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
     B, S, Cin = x.shape
-    Cout = w.shape[1]
-    if w.shape[0] != k * Cin:
-        raise _lib.SSError(f"conv1d: packed weight has {w.shape[0]} rows, expected k*Cin = {k * Cin}")
+    if not isinstance(w, ConvW):
+        raise _lib.SSError("conv1d: weight must be a ConvW (ops.pack_conv)")
+    if w.cin != Cin or (k is not None and k != w.k):
+        raise _lib.SSError(f"conv1d: weight is [k={w.k}, Cout={w.cout}, Cin={w.cin}] but x has Cin={Cin}, k={k}")
+    k, Cout = w.k, w.cout
     y = None
     if write_y:
         y = out if out is not None else torch.empty((B, S, Cout), dtype=torch.float32, device=x.device)
         _chk(y, torch.float32, "out")
+    if (backend or fp32_backend) == "tf32x3":
+        _tf32_call(x, w, bias, residual, lens, y, None, accum, B=B, S_in=S, S_out=S, y_batch_stride=S * Cout,
+                   y_row_stride=Cout, y_offset=0, y_batch_elems=S * Cout, dilation=dilation, pad=pad, in_act=in_act,
+                   in_slope=in_slope, act=act, slope=slope, act2=None, slope2=0.0, accum_scale=accum_scale,
+                   accum_init=accum_init, flops=2.0 * B * S * Cout * k * Cin)
+        return y
+    w = w.ffma
     p = _lib.Conv1dF32Params(
         x=x.data_ptr(), x_batch_stride=S * Cin, x_row_stride=Cin, w=w.data_ptr(),
         bias=None if bias is None else bias.data_ptr(), residual=None if residual is None else residual.data_ptr(),
@@ -115,15 +211,23 @@ def conv1d(x, w, bias=None, *, k=1, dilation=1, pad=0, act=ACT_NONE, slope=0.0, 
     return y
 
 
-def conv_transpose1d(x, w, bias, *, cout, stride, taps, pad, in_act=ACT_NONE, in_slope=0.0):
-    """ConvTranspose1d in phase form: x [B,S,Cin], w packed [taps*Cin, stride*cout] (weights.pack_conv_transpose),
-    bias tiled to [stride*cout].  Output [B, T_out, cout] with T_out = (S-1)*stride - 2*pad + taps*stride."""
-    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w"); _chk(bias, torch.float32, "bias")
+def conv_transpose1d(x, w, bias, *, cout, stride, pad, in_act=ACT_NONE, in_slope=0.0, backend=None):
+    """ConvTranspose1d in phase form: x [B,S,Cin] f32, w = pack_conv_transpose(weight, stride), bias tiled to
+    [stride*cout].  Output [B, T_out, cout] with T_out = (S-1)*stride - 2*pad + taps*stride."""
+    _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias")
     B, S, Cin = x.shape
+    taps = w.k
     k_full = taps * stride
     T_out = (S - 1) * stride - 2 * pad + k_full
     S_out = (T_out - 1 + pad) // stride + 1
     y = torch.empty((B, T_out, cout), dtype=torch.float32, device=x.device)
+    if (backend or fp32_backend) == "tf32x3":
+        _tf32_call(x, w, bias, None, None, y, None, None, B=B, S_in=S, S_out=S_out, y_batch_stride=T_out * cout,
+                   y_row_stride=stride * cout, y_offset=-pad * cout, y_batch_elems=T_out * cout, dilation=1,
+                   pad=taps - 1, in_act=in_act, in_slope=in_slope, act=ACT_NONE, slope=0.0, act2=None, slope2=0.0,
+                   accum_scale=0.0, accum_init=False, flops=2.0 * B * T_out * cout * taps * Cin)
+        return y
+    w = w.ffma
     p = _lib.Conv1dF32Params(
         x=x.data_ptr(), x_batch_stride=S * Cin, x_row_stride=Cin, w=w.data_ptr(), bias=bias.data_ptr(), residual=None,
         lens=None, y=y.data_ptr(), accum=None, y_batch_stride=T_out * cout, y_row_stride=stride * cout,
@@ -148,14 +252,12 @@ def cast_bf16(x, act=ACT_NONE, slope=0.0):
 
 def pack_conv_tc(weight):
     """[Cout, Cin, k] or [out, in] fp32 -> bf16 [k, Cout, Cin] (tap-major, Cin contiguous) for ss_conv1d_tc."""
-    if weight.dim() == 2:
-        weight = weight.unsqueeze(-1)
-    return weight.permute(2, 0, 1).contiguous().to(torch.bfloat16)
+    return pack_conv(weight).bf16
 
 
 def _tc_call(p, flops):
     fn = lambda: _lib.lib().ss_conv1d_tc(C.byref(p), _stream())  # noqa: E731
-    check(conv_timer.run(flops, fn) if conv_timer is not None else fn())
+    check(conv_timer.run(flops, fn, _tag("tc", p)) if conv_timer is not None else fn())
 
 
 def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, residual=None, lens=None,
@@ -163,6 +265,8 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
               accum_init=False):
     """Tensor-core convolution.  x [B,S,Cin] bf16, w [k,Cout,Cin] bf16 (pack_conv_tc).
     Returns (y or None, y_act or None); y_act (bf16) is produced when act2 is not None."""
+    if isinstance(w, ConvW):
+        w = w.bf16
     _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(bias, torch.float32, "bias")
     _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
     B, S, Cin = x.shape
@@ -189,6 +293,8 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
 def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True):
     """ConvTranspose1d in phase form on tensor cores.  x [B,S,Cin] bf16; w [taps, stride*cout, Cin] bf16;
     bias tiled to [stride*cout] f32.  Returns (y f32 [B,T_out,cout] or None, y_act bf16 or None)."""
+    if isinstance(w, ConvW):
+        w = w.bf16
     _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(bias, torch.float32, "bias")
     B, S, Cin = x.shape
     taps = w.shape[0]

@@ -30,12 +30,7 @@ class ParamCache:
         return self.__dict__["_pack_val"]
 
 
-def pack_conv(weight):
-    """[Cout, Cin, k] (nn.Conv1d) or [out, in] (nn.Linear) -> [k*Cin, Cout], tap-major rows."""
-    if weight.dim() == 2:
-        return weight.t().contiguous()
-    cout, cin, k = weight.shape
-    return weight.permute(2, 1, 0).reshape(k * cin, cout).contiguous()
+pack_conv = ops.pack_conv  # nn.Conv1d / nn.Linear weight -> ops.ConvW (all kernel layouts, built lazily)
 
 
 class Dense(nn.Module):
@@ -108,8 +103,6 @@ class MultiHeadAttention(nn.Module, ParamCache):
             "wqkv": pack_conv(wqkv),
             "bqkv": torch.cat([self.w_qs.bias, self.w_ks.bias, self.w_vs.bias]).contiguous(),
             "wfc": pack_conv(self.fc.weight),
-            "wqkv_tc": ops.pack_conv_tc(wqkv),
-            "wfc_tc": ops.pack_conv_tc(self.fc.weight),
         }
 
     def forward(self, x, lens, mask_rows=True, xb=None):
@@ -119,9 +112,9 @@ class MultiHeadAttention(nn.Module, ParamCache):
         pk = self.packed()
         ln = self.layer_norm
         if xb is not None:
-            qkv, _ = ops.conv1d_tc(xb, pk["wqkv_tc"], pk["bqkv"])
+            qkv, _ = ops.conv1d_tc(xb, pk["wqkv"], pk["bqkv"])
             ctx = ops.attention(qkv, lens, self.n_head)
-            y, _ = ops.conv1d_tc(ops.cast_bf16(ctx), pk["wfc_tc"], self.fc.bias, residual=x)
+            y, _ = ops.conv1d_tc(ops.cast_bf16(ctx), pk["wfc"], self.fc.bias, residual=x)
             return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y, want_bf16=True)
         qkv = ops.conv1d(x, pk["wqkv"], pk["bqkv"])
         ctx = ops.attention(qkv, lens, self.n_head)
@@ -140,17 +133,16 @@ class PositionwiseFeedForward(nn.Module, ParamCache):
         self.layer_norm = Norm(d_in)
 
     def _pack(self):
-        return {"w1": pack_conv(self.w_1.weight), "w2": pack_conv(self.w_2.weight),
-                "w1_tc": ops.pack_conv_tc(self.w_1.weight), "w2_tc": ops.pack_conv_tc(self.w_2.weight)}
+        return {"w1": pack_conv(self.w_1.weight), "w2": pack_conv(self.w_2.weight)}
 
     def forward(self, x, lens=None, film=None, xb=None):
         pk = self.packed()
         k1, k2 = self.kernel_size
         ln = self.layer_norm
         if xb is not None:  # tensor-core path: the 1024-channel intermediate only ever exists in bf16
-            h, _ = ops.conv1d_tc(xb, pk["w1_tc"], self.w_1.bias, pad=(k1 - 1) // 2, act=ops.ACT_RELU,
+            h, _ = ops.conv1d_tc(xb, pk["w1"], self.w_1.bias, pad=(k1 - 1) // 2, act=ops.ACT_RELU,
                                  out_dtype=torch.bfloat16)
-            y, _ = ops.conv1d_tc(h, pk["w2_tc"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x)
+            y, _ = ops.conv1d_tc(h, pk["w2"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x)
             return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y, want_bf16=True)
         h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU)
         y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x)
@@ -305,7 +297,7 @@ class PostNet(nn.Module, ParamCache):
             scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
             w = conv.conv.weight * scale[:, None, None]
             b = (conv.conv.bias - bn.running_mean) * scale + bn.bias
-            out.append((pack_conv(w), b.contiguous(), ops.pack_conv_tc(w)))
+            out.append((pack_conv(w), b.contiguous()))
         return out
 
     def forward(self, x, residual=None, precision="fp32", xb=None):
@@ -316,13 +308,13 @@ class PostNet(nn.Module, ParamCache):
         n = len(pk)
         if precision == "bf16":
             h = xb if xb is not None else ops.cast_bf16(x)
-            for i, (_, b, wtc) in enumerate(pk):
+            for i, (wtc, b) in enumerate(pk):
                 last = i == n - 1
                 h, _ = ops.conv1d_tc(h, wtc, b, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
                                      residual=residual if last else None,
                                      out_dtype=torch.float32 if last else torch.bfloat16)
             return h
-        for i, (w, b, _) in enumerate(pk):
+        for i, (w, b) in enumerate(pk):
             last = i == n - 1
             x = ops.conv1d(x, w, b, k=k, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
                            residual=residual if last else None)

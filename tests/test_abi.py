@@ -43,8 +43,9 @@ def test_struct_layouts_match_c(lib):
     """sizeof of every params struct as the C compiler sees it == ctypes.sizeof."""
     from speakingstyle_b200 import _lib
 
-    src = '#include <stdio.h>\n#include "speakingstyle_b200.h"\nint main(){printf("%zu %zu %zu\\n",' \
-          'sizeof(ss_conv1d_f32_params),sizeof(ss_layernorm_params),sizeof(ss_predictor_head_params));return 0;}'
+    src = '#include <stdio.h>\n#include "speakingstyle_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu\\n",' \
+          'sizeof(ss_conv1d_f32_params),sizeof(ss_layernorm_params),sizeof(ss_predictor_head_params),' \
+          'sizeof(ss_conv1d_tc_params),sizeof(ss_conv1d_tf32_params));return 0;}'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c")
         open(c, "w").write(src)
@@ -52,7 +53,8 @@ def test_struct_layouts_match_c(lib):
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
         sizes = [int(v) for v in subprocess.check_output([exe]).split()]
     assert sizes == [ctypes.sizeof(_lib.Conv1dF32Params), ctypes.sizeof(_lib.LayerNormParams),
-                     ctypes.sizeof(_lib.PredictorHeadParams)]
+                     ctypes.sizeof(_lib.PredictorHeadParams), ctypes.sizeof(_lib.Conv1dTcParams),
+                     ctypes.sizeof(_lib.Conv1dTf32Params)]
 
 
 def test_compute_entry_points_reject_bad_arguments_without_a_gpu(lib):
