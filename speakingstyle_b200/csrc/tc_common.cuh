@@ -146,12 +146,25 @@ __device__ __forceinline__ void unpack_bf16(uint32_t u, float& a, float& b) {
 // All fused element-wise work (bias, activation, residual, row mask, running mean, activated bf16
 // copy) happens in that coalesced domain, where a lane's four columns are the same for all rows.
 // ---------------------------------------------------------------------------------------------
+// Activation on four values with ONE dispatch (the epilogue is instruction-cache sensitive: it runs on
+// four warps, one per scheduler, so its body must stay small - tanhf is kept out of line).
+static __device__ __noinline__ float4 tanh4(float4 f) { return make_float4(tanhf(f.x), tanhf(f.y), tanhf(f.z), tanhf(f.w)); }
+__device__ __forceinline__ float4 act4(float4 f, int act, float slope) {
+  if (act == SS_ACT_NONE) return f;
+  if (act == SS_ACT_TANH) return tanh4(f);
+  const float neg = act == SS_ACT_RELU ? 0.f : slope;  // relu is leaky-relu with slope 0
+  f.x = f.x > 0.f ? f.x : f.x * neg;
+  f.y = f.y > 0.f ? f.y : f.y * neg;
+  f.z = f.z > 0.f ? f.z : f.z * neg;
+  f.w = f.w > 0.f ? f.w : f.w * neg;
+  return f;
+}
+
 // One 32-column block: v[] holds this thread's ROW (TMEM lane) of the block; n_blk = first column.
 __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane, int b,
                                             int mt, int n_blk, int len) {
   const int col = (lane & 7) * 4;
   const int rsub = lane >> 3;
-  const int64_t ybase = (int64_t)b * p.y_batch_stride;
   float* my = stg + lane * STG_PITCH;
   __syncwarp();  // the previous block has been fully read back
 #pragma unroll
@@ -162,53 +175,99 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
   if (n >= p.Cout) return;
   float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
   if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + n));
-#pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int rr = it * 4 + rsub;
-    const int t = mt * BM + lg * 32 + rr;
-    if (t >= p.S_out) continue;
-    const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + n;
-    if (off < 0 || off >= p.y_batch_elems) continue;
-    float4 f = *reinterpret_cast<const float4*>(stg + rr * STG_PITCH + col);
-    f.x = ss::apply_act(f.x + bias4.x, p.act, p.slope);
-    f.y = ss::apply_act(f.y + bias4.y, p.act, p.slope);
-    f.z = ss::apply_act(f.z + bias4.z, p.act, p.slope);
-    f.w = ss::apply_act(f.w + bias4.w, p.act, p.slope);
-    if (p.residual) {
-      if (p.residual_dtype == SS_F32) {
-        const float4 r = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + ybase + off));
-        f.x += r.x; f.y += r.y; f.z += r.z; f.w += r.w;
-      } else {
-        const uint2 r = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + ybase + off));
+  const int t_first = mt * BM + lg * 32 + rsub;
+  const int64_t ybase = (int64_t)b * p.y_batch_stride;
+  const float* src = stg + rsub * STG_PITCH + col;
+  const bool pre_res = p.residual != nullptr && p.residual_dtype == SS_F32;
+  const bool pre_acc = p.accum != nullptr && !p.accum_init;
+  if (!pre_res && !pre_acc) {
+    // No global reads to wait for: a compact rolled loop (the epilogue runs on four warps, one per
+    // scheduler, and is instruction-cache sensitive - keep the common case small).
+#pragma unroll 1
+    for (int it = 0; it < 8; ++it) {
+      const int t = t_first + it * 4;
+      const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + n;
+      if (t >= p.S_out || off < 0 || off >= p.y_batch_elems) continue;
+      float4 f = *reinterpret_cast<const float4*>(src + it * 4 * STG_PITCH);
+      f.x += bias4.x; f.y += bias4.y; f.z += bias4.z; f.w += bias4.w;
+      f = act4(f, p.act, p.slope);
+      const int64_t g = ybase + off;
+      if (p.residual) {  // bf16 residual
+        const uint2 r = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + g));
         float a, c;
         unpack_bf16(r.x, a, c); f.x += a; f.y += c;
         unpack_bf16(r.y, a, c); f.z += a; f.w += c;
       }
+      if (t >= len) f = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p.y) {
+        if (p.y_dtype == SS_F32)
+          *reinterpret_cast<float4*>(static_cast<float*>(p.y) + g) = f;
+        else
+          *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y) + g) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+      }
+      if (p.accum) {  // accum_init: plain store of the scaled value
+        f.x *= p.accum_scale; f.y *= p.accum_scale; f.z *= p.accum_scale; f.w *= p.accum_scale;
+        *reinterpret_cast<float4*>(p.accum + g) = f;
+      }
+      if (p.y_act) {
+        f = act4(f, p.act2, p.slope2);
+        *reinterpret_cast<uint2*>(p.y_act + g) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+      }
     }
-    if (t >= len) f = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (p.y) {
-      if (p.y_dtype == SS_F32)
-        *reinterpret_cast<float4*>(static_cast<float*>(p.y) + ybase + off) = f;
-      else
-        *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y) + ybase + off) =
-            make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+    return;
+  }
+  // Two half-loops of four rows: the global reads of a half (residual, running mean) are all issued
+  // before any of them is consumed, so four loads are in flight per lane instead of one.
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    float4 rpre[4], apre[4];
+    int64_t g[4];
+    bool ok[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t_first + (half * 4 + u) * 4;
+      const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + n;
+      ok[u] = t < p.S_out && off >= 0 && off < p.y_batch_elems;
+      g[u] = ybase + off;
+      rpre[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      apre[u] = rpre[u];
+      if (ok[u] && pre_res) rpre[u] = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + g[u]));
+      if (ok[u] && pre_acc) apre[u] = *reinterpret_cast<const float4*>(p.accum + g[u]);
     }
-    if (p.accum) {  // running mean; the activated copy below then follows the accumulated value
-      float4* ap = reinterpret_cast<float4*>(p.accum + ybase + off);
-      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (!p.accum_init) a = *ap;
-      f.x = fmaf(p.accum_scale, f.x, a.x);
-      f.y = fmaf(p.accum_scale, f.y, a.y);
-      f.z = fmaf(p.accum_scale, f.z, a.z);
-      f.w = fmaf(p.accum_scale, f.w, a.w);
-      *ap = f;
-    }
-    if (p.y_act) {
-      f.x = ss::apply_act(f.x, p.act2, p.slope2);
-      f.y = ss::apply_act(f.y, p.act2, p.slope2);
-      f.z = ss::apply_act(f.z, p.act2, p.slope2);
-      f.w = ss::apply_act(f.w, p.act2, p.slope2);
-      *reinterpret_cast<uint2*>(p.y_act + ybase + off) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (!ok[u]) continue;
+      const int t = t_first + (half * 4 + u) * 4;
+      float4 f = *reinterpret_cast<const float4*>(src + (half * 4 + u) * 4 * STG_PITCH);
+      f.x += bias4.x; f.y += bias4.y; f.z += bias4.z; f.w += bias4.w;
+      f = act4(f, p.act, p.slope);
+      if (pre_res) {
+        f.x += rpre[u].x; f.y += rpre[u].y; f.z += rpre[u].z; f.w += rpre[u].w;
+      } else if (p.residual) {
+        const uint2 r = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + g[u]));
+        float a, c;
+        unpack_bf16(r.x, a, c); f.x += a; f.y += c;
+        unpack_bf16(r.y, a, c); f.z += a; f.w += c;
+      }
+      if (t >= len) f = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p.y) {
+        if (p.y_dtype == SS_F32)
+          *reinterpret_cast<float4*>(static_cast<float*>(p.y) + g[u]) = f;
+        else
+          *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y) + g[u]) =
+              make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+      }
+      if (p.accum) {  // running mean; the activated copy below then follows the accumulated value
+        f.x = fmaf(p.accum_scale, f.x, apre[u].x);
+        f.y = fmaf(p.accum_scale, f.y, apre[u].y);
+        f.z = fmaf(p.accum_scale, f.z, apre[u].z);
+        f.w = fmaf(p.accum_scale, f.w, apre[u].w);
+        *reinterpret_cast<float4*>(p.accum + g[u]) = f;
+      }
+      if (p.y_act) {
+        f = act4(f, p.act2, p.slope2);
+        *reinterpret_cast<uint2*>(p.y_act + g[u]) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+      }
     }
   }
 }
