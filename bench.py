@@ -190,7 +190,7 @@ def lr_roofline(dev, pk):
     """LengthRegulator kernel alone at a BASELINE cfg5-like shard size, L2 flushed between launches."""
     from speakingstyle_b200 import ops
 
-    B, L, Cc = 256, 100, 256
+    B, L, Cc = 1024, 100, 256  # ~1 GB of output: large enough that launch latency is not what is measured
     g = torch.Generator().manual_seed(3)
     x = torch.randn(B, L, Cc, generator=g).to(dev)
     d = torch.randint(4, 12, (B, L), generator=g).float().to(dev)
@@ -342,12 +342,16 @@ def main():
                                  f"{w / (ms * 1e-3) / 1e12:8.1f} TFLOP/s  {tag}\n")
             sys.stderr.write(f"step {dev_ms / args.steps:.3f} ms, convs {conv_ms / args.steps:.3f} ms\n")
         ach = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
-        roof = {"kernel": "conv1d_f32_kernel + conv1d_tc_kernel (all implicit-GEMM conv/linear launches)"
-                if args.precision == "bf16" else "conv1d_f32_kernel (fp32 FFMA implicit-GEMM conv/linear)",
+        roof = {"kernel": "conv1d_tf32_kernel (3xTF32 tcgen05) + conv1d_tc_kernel (bf16 tcgen05): all conv/linear launches"
+                if args.precision == "bf16" else "conv1d_tf32_kernel (3xTF32 tcgen05 implicit-GEMM conv/linear, fp32-accurate)",
                 "bound": "tensor", "achieved": ach,
                 "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tflops_sustained"], "traffic": None,
                 "launches": calls, "avg_launch_ms": conv_ms / max(calls, 1), "share_of_step": conv_ms / dev_ms,
-                "peak_source": pk["source"] + " bf16 dense (sustained)"}
+                "peak_source": pk["source"] + " bf16 dense (sustained)",
+                "note": "achieved = algorithmic FLOPs / CUDA-event time; a 3xTF32 kernel issues 3 TF32 MMAs (half the bf16 "
+                        "rate) per algorithmic MAC, so its ceiling is peak/6"}
+        if args.precision == "fp32":
+            roof["frac_of_3xtf32_ceiling"] = ach / (pk["tflops_sustained"] / 6.0)
         line = {
             "metric": "mel_frames_per_s", "value": value, "unit": "mel-frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak",

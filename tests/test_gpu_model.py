@@ -301,3 +301,35 @@ def test_hifigan_bf16_alone(golden):
     r = rel_l2(wave, g["wave"])
     _report(f"hifigan_small bf16 mode: wave rel-L2 {r:.3e}")
     assert wave.shape == g["wave"].shape and r <= 1e-2
+
+
+def test_sharded_run_matches_oracle_per_shard():
+    """A shard is a reference batch: the GPU path run shard by shard (one rank's view of the plan)
+    equals the oracle run on the very same shards."""
+    from speakingstyle_b200 import shard as SH
+
+    model, mc, sd = get_models("BC2013")
+    g = torch.Generator().manual_seed(21)
+    n = 7
+    texts = [torch.randint(1, C.N_SRC_VOCAB, (int(torch.randint(5, 14, (1,), generator=g)),), generator=g) for _ in range(n)]
+    mels = [torch.randn(int(torch.randint(10, 50, (1,), generator=g)), 80, generator=g) for _ in range(n)]
+    plan = SH.plan_shards([t.numel() for t in texts], [m.shape[0] for m in mels], max_batch=3, bucket_width=4, n_ranks=2,
+                          vocoder=False)
+
+    def gpu(batch):
+        out = run(model, batch)
+        return {"postnet_mel": out[1].cpu(), "d_rounded": out[5].cpu(), "mel_len": out[9].cpu()}
+
+    def cpu(batch):
+        with torch.no_grad():
+            out = O.fastspeech2_forward(sd, mc, batch)
+        return {"postnet_mel": out[1], "d_rounded": out[5], "mel_len": out[9]}
+
+    for rank in range(2):
+        a = SH.run_rank(plan, rank, gpu, [0] * n, texts, mels)
+        b = SH.run_rank(plan, rank, cpu, [0] * n, texts, mels)
+        assert sorted(a) == sorted(b) and len(a) > 0
+        for uid in a:
+            assert torch.equal(a[uid]["d_rounded"], b[uid]["d_rounded"])
+            assert int(a[uid]["mel_len"]) == int(b[uid]["mel_len"])
+            assert maxabs(a[uid]["postnet_mel"], b[uid]["postnet_mel"]) <= TOL
