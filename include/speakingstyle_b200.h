@@ -267,6 +267,37 @@ SS_API int ss_duration_scan(const float* log_d, float d_control, float* d_rounde
 SS_API int ss_length_regulate(const float* x, const int32_t* ends, const float* pe, float* out,
                               int32_t* mel2phone, int B, int L, int T, int C, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * ss_length_regulate_noalloc - LengthRegulator in ONE call that needs no buffer beyond its inputs and
+ * outputs.  (No counterpart in the reference: it exists for callers of this library, not of the model.)
+ *
+ * Who needs it: a caller that cannot obtain device memory at call time - a synthesis worker that was
+ * given a fixed set of device buffers at start-up and must not call cudaMalloc on its request path
+ * (it synchronises the whole device and can fail once memory is fragmented), or a plug-in living in
+ * a host runtime that keeps its allocator to itself.  ss_duration_scan + ss_length_regulate make such
+ * a caller supply a [B, L] int32 buffer for the prefix sums; here that buffer is an array inside the
+ * library image (SS_LR_NOALLOC_MAX_TOKENS int32 = 256 KiB, resident on every GPU that loads the
+ * library until the process exits).
+ *
+ *   reps = max(trunc(durations[b,l]), 0);  mel_len[b] = sum_l reps            (int32, written for every b)
+ *   out[b,t,:] = x[b, i, :] (+ pe[t,:])  with i = #{ j : prefix[b,j] <= t }   for t < min(mel_len[b], T)
+ *   out[b,t,:] = 0 (+ pe[t,:])                                                 for the remaining rows up to T
+ * i.e. LengthRegulator.forward(x, duration, max_len=T) of model/modules.py:199-201; the caller fixes T
+ * (its output buffer is [B, T, C]); an utterance longer than T is cut at T, as F.pad would not allow.
+ *
+ * Limits and rules:
+ *   - B*L <= SS_LR_NOALLOC_MAX_TOKENS, otherwise SS_ERR_UNSUPPORTED (use the two-call form);
+ *   - no cudaMalloc / cudaFree / allocating library call is made, ever;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *     that device current) - make that first call outside any stream capture;
+ *   - all calls on a device share the one array: each call overwrites the part it uses before reading
+ *     it (nothing needs clearing), but two calls whose kernels can overlap on the GPU - different
+ *     streams without an ordering between them - race on it.  Serialise them.
+ * ------------------------------------------------------------------------------------------ */
+#define SS_LR_NOALLOC_MAX_TOKENS 65536
+SS_API int ss_length_regulate_noalloc(const float* x, const float* durations, const float* pe, float* out,
+                                      int32_t* mel_len, int B, int L, int T, int C, void* stream);
+
 /* mask[b,t] = (t >= lens[b])  as bytes (torch.bool storage) - utils/tools.py:110-118 */
 SS_API int ss_length_mask(const int32_t* lens, uint8_t* mask, int B, int T, void* stream);
 

@@ -77,6 +77,7 @@ _SIGNATURES = {
     "ss_bucket_embed_add": (C.c_int, [vp, f32, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_duration_scan": (C.c_int, [vp, f32, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
     "ss_length_regulate": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_length_regulate_noalloc": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_length_mask": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
     "ss_mean_pool": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_add_speaker": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),

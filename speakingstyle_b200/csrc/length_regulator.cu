@@ -164,3 +164,80 @@ int ss_length_regulate(const float* x, const int32_t* ends, const float* pe, flo
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// LengthRegulator for callers that cannot allocate device memory.
+//
+// The two-step form above needs a [B, L] int32 buffer of prefix sums between its two kernels, and
+// the caller has to provide it.  Some callers have nowhere to get it from: a synthesis worker that
+// was handed a fixed set of device buffers at start-up and runs inside a latency budget where a
+// cudaMalloc (a device-wide synchronising call that can also fail late, once memory is fragmented)
+// is not acceptable, or a plug-in hosted by another runtime that owns the allocator and does not
+// expose it.  For them the prefix sums live in the array below, which is part of the library image:
+// every GPU that loads the library carries these 256 KiB until the process exits.
+//
+// g_lr_prefix is a DEVICE symbol.  In host code its name is only a handle - passing it to a kernel
+// would hand the kernel a host address - so the device address is looked up once per device with
+// cudaGetSymbolAddress (below) and that pointer is what the kernels receive.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kNoAllocMaxTokens = SS_LR_NOALLOC_MAX_TOKENS;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) int32_t g_lr_prefix[kNoAllocMaxTokens];
+
+// Device address of g_lr_prefix on the CURRENT device, resolved on the first call made with that
+// device current (each device has its own copy of the array, hence its own address).
+int noalloc_prefix_ptr(int32_t** out) {
+  static int32_t* cache[kNoAllocMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return ss::cuda_fail(e, "ss_length_regulate_noalloc: cudaGetDevice");
+  SS_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, SS_ERR_UNSUPPORTED,
+             "ss_length_regulate_noalloc: device ordinal %d is beyond the %d this entry point tracks", dev,
+             kNoAllocMaxDevices);
+  int32_t* p = __atomic_load_n(&cache[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_lr_prefix);
+    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_length_regulate_noalloc: cudaGetSymbolAddress");
+    SS_REQUIRE(sym != nullptr, SS_ERR_CUDA, "ss_length_regulate_noalloc: null symbol address");
+    p = static_cast<int32_t*>(sym);
+    __atomic_store_n(&cache[dev], p, __ATOMIC_RELEASE);  // racing first calls store the same value
+  }
+  *out = p;
+  return SS_OK;
+}
+
+}  // namespace
+
+extern "C" int ss_length_regulate_noalloc(const float* x, const float* durations, const float* pe, float* out,
+                                          int32_t* mel_len, int B, int L, int T, int C, void* stream) {
+  SS_REQUIRE(x && durations && out && mel_len, SS_ERR_INVALID, "ss_length_regulate_noalloc: null pointer");
+  SS_REQUIRE(B > 0 && L > 0 && T >= 0 && C > 0 && C % 4 == 0, SS_ERR_INVALID,
+             "ss_length_regulate_noalloc: bad shape B=%d L=%d T=%d C=%d", B, L, T, C);
+  SS_REQUIRE((int64_t)B * L <= kNoAllocMaxTokens, SS_ERR_UNSUPPORTED,
+             "ss_length_regulate_noalloc: B*L = %lld exceeds the built-in scratch of %d prefix sums; use "
+             "ss_duration_scan + ss_length_regulate with a caller-provided buffer",
+             (long long)B * L, kNoAllocMaxTokens);
+  SS_REQUIRE(B <= 65535, SS_ERR_UNSUPPORTED, "ss_length_regulate_noalloc: B > 65535");
+  SS_REQUIRE((size_t)L * 4 <= 48 * 1024, SS_ERR_UNSUPPORTED, "ss_length_regulate_noalloc: L=%d too long", L);
+  SS_REQUIRE(ss::aligned16(x) && ss::aligned16(out) && ss::aligned16(pe), SS_ERR_ALIGNMENT,
+             "ss_length_regulate_noalloc: pointers must be 16-byte aligned");
+  int32_t* prefix = nullptr;
+  const int rc = noalloc_prefix_ptr(&prefix);
+  if (rc != SS_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // Every prefix sum this call reads ([0, B*L)) is written by the scan first, so nothing in the
+  // array has to be cleared; whatever an earlier call left beyond B*L is never looked at.
+  const int warps = 4;
+  duration_scan_kernel<<<(B + warps - 1) / warps, warps * 32, 0, st>>>(nullptr, 1.0f, const_cast<float*>(durations),
+                                                                      prefix, mel_len, nullptr, B, L);
+  SS_CHECK_LAUNCH("ss_length_regulate_noalloc (scan)");
+  if (T == 0) return SS_OK;
+  dim3 grid((T + LR_FRAMES_PER_CTA - 1) / LR_FRAMES_PER_CTA, B);
+  length_regulate_kernel<<<grid, LR_WARPS * 32, (size_t)L * sizeof(int32_t), st>>>(x, prefix, pe, out, nullptr, L, T, C);
+  SS_CHECK_LAUNCH("ss_length_regulate_noalloc (expand)");
+  return SS_OK;
+}
