@@ -24,7 +24,9 @@ namespace {
 using namespace sstc;
 
 constexpr int KCHUNK = 64;    // bf16 elements per 128-byte swizzle row
-constexpr int NTHREADS = 192;
+// epilogue warps per TMEM lane group: the epilogue is global-memory-latency bound, and a lane group can
+// only be read by warps with the same (warp id % 4), so more parallelism means more warps per group
+template <int BN> struct EpiG { static constexpr int value = BN <= 128 ? 2 : 1; };
 
 // ---------------------------------------------------------------------------------------------
 template <int BN, int STAGES>
@@ -33,24 +35,28 @@ struct Cfg {
   static constexpr int stage_bytes = A_BYTES + b_bytes;
   static constexpr int tmem_cols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
   static constexpr int bar_bytes = (2 * STAGES + 4) * 8 + 16;
-  static constexpr int smem_bytes = STAGES * stage_bytes + STG_BYTES + bar_bytes + 1024;  // +1024: alignment slack
+  static constexpr int G = EpiG<BN>::value;
+  static constexpr int stg_bytes = 4 * G * STG_WARP_BYTES;
+  static constexpr int nthreads = 64 + 128 * G;
+  static constexpr int smem_bytes = STAGES * stage_bytes + stg_bytes + bar_bytes + 1024;  // +1024: alignment slack
+  static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
 };
 
 template <int BN, int STAGES>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __launch_bounds__(Cfg<BN, STAGES>::nthreads, 1)
 conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcArgs p) {
   using C = Cfg<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B tiles need 1024-byte alignment
   const uint32_t smA = smem0;
   const uint32_t smB = smem0 + STAGES * A_BYTES;
-  const uint32_t bars = smem0 + STAGES * C::stage_bytes + STG_BYTES;
+  const uint32_t bars = smem0 + STAGES * C::stage_bytes + C::stg_bytes;
   const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 16;
   const uint32_t tslot = tempty0 + 16;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
   float* stg_all = reinterpret_cast<float*>(smem_al + STAGES * C::stage_bytes);
   volatile uint32_t* tslot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + STG_BYTES + (2 * STAGES + 4) * 8);
+      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + C::stg_bytes + (2 * STAGES + 4) * 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
@@ -66,7 +72,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull0 + 8 * a, 1);
-      mbar_init(tempty0 + 8 * a, 4);  // one arrival per epilogue warp
+      mbar_init(tempty0 + 8 * a, 4 * C::G);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -133,8 +139,9 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else {
     // ================= epilogue (warps 2..5) =================
-    const int lg = warp & 3;  // TMEM lane group this warp may access
-    float* stg = stg_all + lg * 32 * STG_PITCH;
+    const int lg = warp & 3;         // TMEM lane group this warp may access
+    const int sub = (warp - 2) >> 2;  // which of the G warps of that group
+    float* stg = stg_all + (warp - 2) * 32 * STG_PITCH;
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int nt = tile % p.n_tiles;
@@ -145,7 +152,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t aphase = (local >> 1) & 1;
       mbar_wait(tfull0 + 8 * as, aphase);
       tc_fence_after();
-      drain_tile<BN>(p, tmem_base + ((uint32_t)(lg * 32) << 16) + as * BN, stg, lg, lane, b, mt, nt * BN);
+      drain_tile<BN, C::G>(p, tmem_base + ((uint32_t)(lg * 32) << 16) + as * BN, stg, lg, lane, b, mt, nt * BN, sub);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * as);
@@ -181,7 +188,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, TcArgs a, cudaStream_
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tc: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  conv1d_tc_kernel<BN, STAGES><<<grid, NTHREADS, C::smem_bytes, st>>>(tmA, tmB, a);
+  conv1d_tc_kernel<BN, STAGES><<<grid, C::nthreads, C::smem_bytes, st>>>(tmA, tmB, a);
   SS_CHECK_LAUNCH("ss_conv1d_tc");
   return SS_OK;
 }
@@ -225,8 +232,8 @@ extern "C" int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return launch<256, 4>(tmA, tmB, a, st);
-    case 128: return launch<128, 6>(tmA, tmB, a, st);
-    case 64: return launch<64, 8>(tmA, tmB, a, st);
+    case 128: return launch<128, 5>(tmA, tmB, a, st);
+    case 64: return launch<64, 7>(tmA, tmB, a, st);
     default: return launch<32, 8>(tmA, tmB, a, st);
   }
 }

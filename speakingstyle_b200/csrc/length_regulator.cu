@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(128) duration_scan_kernel(const float* __restr
 }
 
 constexpr int LR_WARPS = 8;
-constexpr int LR_FRAMES_PER_WARP = 4;
+constexpr int LR_FRAMES_PER_WARP = 8;
 constexpr int LR_FRAMES_PER_CTA = LR_WARPS * LR_FRAMES_PER_WARP;
 
 __global__ void __launch_bounds__(LR_WARPS * 32) length_regulate_kernel(const float* __restrict__ x,
@@ -81,23 +81,24 @@ __global__ void __launch_bounds__(LR_WARPS * 32) length_regulate_kernel(const fl
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tbase = blockIdx.x * LR_FRAMES_PER_CTA + warp * LR_FRAMES_PER_WARP;
 
-  int src[LR_FRAMES_PER_WARP];
-#pragma unroll
-  for (int f = 0; f < LR_FRAMES_PER_WARP; ++f) {
-    const int t = tbase + f;
-    int idx = -1;
-    if (t < T && t < total) {
-      // number of prefix sums <= t  (upper bound); all lanes search the same value
-      int lo = 0, hi = L;
+  // lane f (< 8) finds the source row of frame tbase+f; the eight searches run side by side instead of
+  // one after the other, then every lane picks the results up by shuffle
+  int my_idx = -1;
+  {
+    const int t = tbase + lane;
+    if (lane < LR_FRAMES_PER_WARP && t < T && t < total) {
+      int lo = 0, hi = L;  // number of prefix sums <= t  (upper bound)
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
         if (s_ends[mid] <= t) lo = mid + 1; else hi = mid;
       }
-      idx = lo;
+      my_idx = lo;
     }
-    src[f] = idx;
-    if (mel2phone && lane == 0 && t < T) mel2phone[(int64_t)b * T + t] = idx;
+    if (mel2phone && lane < LR_FRAMES_PER_WARP && t < T) mel2phone[(int64_t)b * T + t] = my_idx;
   }
+  int src[LR_FRAMES_PER_WARP];
+#pragma unroll
+  for (int f = 0; f < LR_FRAMES_PER_WARP; ++f) src[f] = __shfl_sync(0xffffffffu, my_idx, f);
 
   const int C4 = C >> 2;
   const float4* xb = reinterpret_cast<const float4*>(x + (int64_t)b * L * C);

@@ -13,7 +13,8 @@ constexpr int BM = 128;          // rows per tile = TMEM lanes
 constexpr int ROW_BYTES = 128;   // one K-chunk row = one 128-byte swizzle row (64 bf16 or 32 tf32)
 constexpr int A_BYTES = BM * ROW_BYTES;
 constexpr int STG_PITCH = 36;    // floats; 32 + 4 keeps both the float4 writes and reads conflict-free
-constexpr int STG_BYTES = 4 * 32 * STG_PITCH * 4;  // one 32x32 fp32 staging tile per epilogue warp
+constexpr int STG_WARP_BYTES = 32 * STG_PITCH * 4;  // one 32x32 fp32 staging tile per epilogue warp
+constexpr int STG_BYTES = 4 * STG_WARP_BYTES;       // four epilogue warps (one per TMEM lane group)
 
 struct TcArgs {
   const float* bias;
@@ -272,12 +273,13 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
   }
 }
 
-template <int BN>
+// G epilogue warps share one TMEM lane group; warp `sub` of the group takes every G-th 32-column block.
+template <int BN, int G = 1>
 __device__ __forceinline__ void drain_tile(const TcArgs& p, uint32_t taddr, float* stg, int lg, int lane, int b, int mt,
-                                           int n0) {
+                                           int n0, int sub = 0) {
   const int len = p.lens ? p.lens[b] : 0x7fffffff;
 #pragma unroll 1
-  for (int c0 = 0; c0 < BN; c0 += 32) {
+  for (int c0 = sub * 32; c0 < BN; c0 += 32 * G) {
     float v[32];
     __syncwarp();  // reconverge: tcgen05.ld is .sync.aligned
     tmem_ld32(taddr + c0, v);
