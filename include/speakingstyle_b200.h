@@ -217,6 +217,13 @@ SS_API int ss_layernorm(const ss_layernorm_params* p, void* stream);
 SS_API int ss_attention_f32(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, int dk,
                             void* stream);
 
+/* The same operation, same arguments and same fp32 accuracy class, on the tensor cores (dk == 32 only - the
+ * ReferenceEncoder's 8 heads, modules.py:353): S = Q.K^T and O = P.V are 3xTF32 tcgen05.mma with accumulators
+ * in TMEM, operands by TMA, V consumed as an MN-major operand (no transpose), P written by the softmax warps
+ * directly in the swizzled layout the MMA reads; output accumulation across key tiles in fp32 registers. */
+SS_API int ss_attention_tc(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, int dk,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Variance predictor tail: LayerNorm_2 -> [FiLM] -> Linear(C->1) -> mask, one warp per token.
  * replaces model/modules.py:243-258 (h is the output of conv1d_2 + ReLU).

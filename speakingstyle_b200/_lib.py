@@ -73,6 +73,7 @@ _SIGNATURES = {
     "ss_cast_bf16": (C.c_int, [vp, vp, i64, C.c_int, f32, vp]),
     "ss_layernorm": (C.c_int, [C.POINTER(LayerNormParams), vp]),
     "ss_attention_f32": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_attention_tc": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_predictor_head": (C.c_int, [C.POINTER(PredictorHeadParams), vp]),
     "ss_bucket_embed_add": (C.c_int, [vp, f32, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_duration_scan": (C.c_int, [vp, f32, vp, vp, vp, vp, C.c_int, C.c_int, vp]),

@@ -308,7 +308,8 @@ inline EncodeTiledFn encode_fn() {
 
 // 3-D tensor map {d0 (contiguous), d1, d2} with a {box0, box1, 1} box and the 128-byte swizzle.
 inline int make_map_3d(CUtensorMap* m, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
-                       uint64_t s1_bytes, uint64_t s2_bytes, uint32_t box0, uint32_t box1) {
+                       uint64_t s1_bytes, uint64_t s2_bytes, uint32_t box0, uint32_t box1,
+                       CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_fn();
   SS_REQUIRE(fn != nullptr, SS_ERR_CUDA, "tensor-core conv: cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t dims[3] = {d0, d1, d2};
@@ -316,7 +317,7 @@ inline int make_map_3d(CUtensorMap* m, CUtensorMapDataType dt, const void* base,
   cuuint32_t box[3] = {box0, box1, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(m, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SS_REQUIRE(r == CUDA_SUCCESS, SS_ERR_CUDA, "tensor-core conv: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return SS_OK;
 }

@@ -154,8 +154,12 @@ def test_layernorm_variants(ops, C):
 
 
 @pytest.mark.parametrize("H,dk,S,lens", [(2, 128, 150, [150, 64, 1]), (8, 32, 203, [203, 129, 65]),
+                                          (8, 32, 800, [800, 513, 64, 1]), (3, 32, 127, [127, 128 - 64, 5]),
                                           (2, 128, 30, [30, 7, 12]), (4, 64, 70, [70, 70, 3])])
-def test_attention_matches_oracle_math(ops, H, dk, S, lens):
+@pytest.mark.parametrize("backend", ["simt", "tc"])
+def test_attention_matches_oracle_math(ops, backend, H, dk, S, lens):
+    if backend == "tc" and dk != 32:
+        pytest.skip("the tcgen05 attention kernel is specialised for head size 32")
     B, D = len(lens), H * dk
     qkv = rnd(B, S, 3 * D, seed=18)
     lens_t = torch.tensor(lens, dtype=torch.int32)
@@ -164,7 +168,7 @@ def test_attention_matches_oracle_math(ops, H, dk, S, lens):
     pad = torch.arange(S)[None, :] >= lens_t[:, None]
     score = score.masked_fill(pad[:, None, None, :], -math.inf)
     ref = (torch.softmax(score, -1) @ v).transpose(1, 2).reshape(B, S, D)
-    ctx = ops.attention(qkv.to(DEV), lens_t.to(DEV), H).cpu().double()
+    ctx = ops.attention(qkv.to(DEV), lens_t.to(DEV), H, backend=backend).cpu().double()
     valid = ~pad
     assert (ctx - ref)[valid].abs().max().item() <= 2e-5
     assert ctx[pad].abs().max().item() == 0.0  # padded query rows are written as zeros
