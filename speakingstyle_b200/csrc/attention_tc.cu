@@ -7,8 +7,8 @@
 //   warp 0      TMA: Q once, then K_j / V_j tiles into a 2-stage ring (rows outside [0,S) zero-filled)
 //   warp 1      one thread issues  S_j = Q.K_j^T  (12 MMAs, N = 64) and  O_j = P_j.V_j  (24 MMAs, N = 32);
 //               S_{j+1} is issued before O_j so it overlaps the softmax of tile j
-//   warps 2-5   softmax: thread = query row.  tcgen05.ld S_j -> scale by 1/sqrt(dk) (a true division, like
-//               the reference) -> mask keys >= len -> online max/sum -> P_j = exp(s - m), split into TF32
+//   warps 2-5   softmax: thread = query row.  tcgen05.ld S_j -> scale by log2(e)/sqrt(dk) -> mask keys >= len
+//               -> online max/sum in the base-2 domain -> P_j = 2^(t - m) (MUFU.EX2), split into TF32
 //               hi/lo and written straight into the 128-byte-swizzled K-major layout the MMA reads;
 //               then  o = o*alpha_j + O_j  in registers once O_j lands (fp32 round-to-nearest adds, so the
 //               truncating TMEM accumulation never runs longer than one tile)
@@ -172,6 +172,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int r = lg * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
     float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
+    const float scale_log2 = 1.4426950408889634f / temperature;
     float o[DK];
 #pragma unroll
     for (int i = 0; i < DK; ++i) o[i] = 0.f;
@@ -202,21 +203,24 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       __syncwarp();
       if (lane == 0) mbar_arrive(s_empty0 + 8 * sb);
 
+      // softmax in the base-2 domain: t = s * log2(e)/sqrt(dk); p = 2^(t - m).  One FMUL and one MUFU.EX2 per
+      // score (the four softmax warps are the busiest part of this kernel; libm expf and a true division
+      // cost ~10x more issue slots).  Relative error of p <= ~3e-7, far inside the kernel's 1e-6 class.
       const int kbase = j * BKV;
       float mx = -INFINITY;
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        s0[i] = (kbase + i < len) ? s0[i] / temperature : -INFINITY;
-        s1[i] = (kbase + 32 + i < len) ? s1[i] / temperature : -INFINITY;
+        s0[i] = (kbase + i < len) ? s0[i] * scale_log2 : -INFINITY;
+        s1[i] = (kbase + 32 + i < len) ? s1[i] * scale_log2 : -INFINITY;
         mx = fmaxf(mx, fmaxf(s0[i], s1[i]));
       }
       const float m_new = fmaxf(m, mx);  // finite: every tile holds at least one valid key
-      const float alpha = expf(m - m_new);
+      const float alpha = exp2f(m - m_new);
       float sum = 0.f;
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        s0[i] = expf(s0[i] - m_new);
-        s1[i] = expf(s1[i] - m_new);
+        s0[i] = exp2f(s0[i] - m_new);
+        s1[i] = exp2f(s1[i] - m_new);
         sum += s0[i] + s1[i];
       }
       l = l * alpha + sum;
