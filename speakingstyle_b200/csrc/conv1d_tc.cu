@@ -27,13 +27,19 @@ constexpr int KCHUNK = 64;    // bf16 elements per 128-byte swizzle row
 // epilogue warps per TMEM lane group: the epilogue is global-memory-latency bound, and a lane group can
 // only be read by warps with the same (warp id % 4), so more parallelism means more warps per group
 template <int BN> struct EpiG { static constexpr int value = BN <= 128 ? 2 : 1; };
+// M sub-tiles per scheduling unit.  With few output channels a 128 x BN tile is tiny (a 32-channel k=3
+// convolution is 12 MMAs), and the TMA -> MMA -> epilogue -> MMA hand-offs, not the work, set the pace; so a
+// unit is MT consecutive 128-row tiles that share one accumulator buffer (MT*BN columns) and one hand-off.
+template <int BN> struct SubTiles { static constexpr int value = BN >= 256 ? 1 : 256 / BN; };
 
 // ---------------------------------------------------------------------------------------------
 template <int BN, int STAGES>
 struct Cfg {
   static constexpr int b_bytes = BN * KCHUNK * 2;
   static constexpr int stage_bytes = A_BYTES + b_bytes;
-  static constexpr int tmem_cols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int MT = SubTiles<BN>::value;
+  static constexpr int acc_cols = MT * BN;  // columns of one accumulator buffer
+  static constexpr int tmem_cols = (2 * acc_cols <= 32) ? 32 : (2 * acc_cols <= 64) ? 64 : (2 * acc_cols <= 128) ? 128 : (2 * acc_cols <= 256) ? 256 : 512;
   static constexpr int bar_bytes = (2 * STAGES + 4) * 8 + 16;
   static constexpr int G = EpiG<BN>::value;
   static constexpr int stg_bytes = 4 * G * STG_WARP_BYTES;
@@ -61,7 +67,9 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
   const int KT = p.k * nchunk;
-  const int num_tiles = p.B * p.m_tiles * p.n_tiles;
+  constexpr int MT = C::MT;
+  const int m_units = (p.m_tiles + MT - 1) / MT;
+  const int num_tiles = p.B * m_units * p.n_tiles;  // scheduling units
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -92,17 +100,22 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int nt = tile % p.n_tiles;
         const int rest = tile / p.n_tiles;
-        const int mt = rest % p.m_tiles;
-        const int b = rest / p.m_tiles;
-        const int t0 = mt * BM, n0 = nt * BN;
-        for (int it = 0; it < KT; ++it) {
-          const int j = it / nchunk;
-          const int c0 = (it - j * nchunk) * KCHUNK;
-          mbar_wait(empty0 + 8 * stage, phase ^ 1);
-          mbar_expect_tx(full0 + 8 * stage, C::stage_bytes);
-          tma_load_3d(smA + stage * A_BYTES, &tmA, full0 + 8 * stage, c0, t0 + j * p.dilation - p.pad, b);
-          tma_load_3d(smB + stage * C::b_bytes, &tmB, full0 + 8 * stage, c0, n0, j);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        const int um = rest % m_units;
+        const int b = rest / m_units;
+        const int n0 = nt * BN;
+        for (int sub = 0; sub < MT; ++sub) {
+          const int mt = um * MT + sub;
+          if (mt >= p.m_tiles) break;
+          const int t0 = mt * BM;
+          for (int it = 0; it < KT; ++it) {
+            const int j = it / nchunk;
+            const int c0 = (it - j * nchunk) * KCHUNK;
+            mbar_wait(empty0 + 8 * stage, phase ^ 1);
+            mbar_expect_tx(full0 + 8 * stage, C::stage_bytes);
+            tma_load_3d(smA + stage * A_BYTES, &tmA, full0 + 8 * stage, c0, t0 + j * p.dilation - p.pad, b);
+            tma_load_3d(smB + stage * C::b_bytes, &tmB, full0 + 8 * stage, c0, n0, j);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
@@ -120,21 +133,25 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t aphase = (local >> 1) & 1;
         mbar_wait(tempty0 + 8 * as, aphase ^ 1);  // epilogue has drained this accumulator buffer
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int it = 0; it < KT; ++it) {
-          mbar_wait(full0 + 8 * stage, phase);
-          tc_fence_after();
-          const uint32_t a_addr = smA + stage * A_BYTES;
-          const uint32_t b_addr = smB + stage * C::b_bytes;
+        const int um = (tile / p.n_tiles) % m_units;
+        for (int sub = 0; sub < MT; ++sub) {
+          if (um * MT + sub >= p.m_tiles) break;
+          const uint32_t d_tmem = tmem_base + as * C::acc_cols + sub * BN;
+          for (int it = 0; it < KT; ++it) {
+            mbar_wait(full0 + 8 * stage, phase);
+            tc_fence_after();
+            const uint32_t a_addr = smA + stage * A_BYTES;
+            const uint32_t b_addr = smB + stage * C::b_bytes;
 #pragma unroll
-          for (int kk = 0; kk < KCHUNK / 16; ++kk) {
-            // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle row: bump the start address
-            umma_bf16(d_tmem, make_desc(a_addr + kk * 32), make_desc(b_addr + kk * 32), idesc, (it | kk) != 0);
+            for (int kk = 0; kk < KCHUNK / 16; ++kk) {
+              // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle row: bump the start address
+              umma_bf16(d_tmem, make_desc(a_addr + kk * 32), make_desc(b_addr + kk * 32), idesc, (it | kk) != 0);
+            }
+            umma_commit(empty0 + 8 * stage);  // frees the smem slot once these MMAs have read it
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          umma_commit(empty0 + 8 * stage);  // frees the smem slot once these MMAs have read it
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tfull0 + 8 * as);  // accumulator complete -> epilogue
+        umma_commit(tfull0 + 8 * as);  // accumulators of the whole unit complete -> epilogue
       }
     }
   } else {
@@ -146,13 +163,30 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int nt = tile % p.n_tiles;
       const int rest = tile / p.n_tiles;
-      const int mt = rest % p.m_tiles;
-      const int b = rest / p.m_tiles;
+      const int um = rest % m_units;
+      const int b = rest / m_units;
       const int as = local & 1;
       const uint32_t aphase = (local >> 1) & 1;
       mbar_wait(tfull0 + 8 * as, aphase);
       tc_fence_after();
-      drain_tile<BN, C::G>(p, tmem_base + ((uint32_t)(lg * 32) << 16) + as * BN, stg, lg, lane, b, mt, nt * BN, sub);
+      const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + as * C::acc_cols;
+      if constexpr (MT == 1) {
+        drain_tile<BN, C::G>(p, acc, stg, lg, lane, b, um, nt * BN, sub);
+      } else {
+        // the G warps of a lane group share the unit's 32-column blocks round-robin across its sub-tiles
+        constexpr int BLK = BN / 32;
+        const int len = p.lens ? p.lens[b] : 0x7fffffff;
+#pragma unroll 1
+        for (int q = sub; q < MT * BLK; q += C::G) {
+          const int st = q / BLK, c0 = (q - st * BLK) * 32;
+          const int mt = um * MT + st;
+          if (mt >= p.m_tiles) break;
+          float v[32];
+          __syncwarp();
+          tmem_ld32(acc + st * BN + c0, v);
+          drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+        }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * as);
@@ -176,7 +210,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, TcArgs a, cudaStream_
   using C = Cfg<BN, STAGES>;
   a.n_tiles = (a.Cout + BN - 1) / BN;
   a.m_tiles = (a.S_out + BM - 1) / BM;
-  const int64_t tiles = (int64_t)a.B * a.m_tiles * a.n_tiles;
+  const int64_t tiles = (int64_t)a.B * ((a.m_tiles + C::MT - 1) / C::MT) * a.n_tiles;  // scheduling units
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tc: too many tiles");
   static bool attr_set = false;  // per template instantiation
   if (!attr_set) {
