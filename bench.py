@@ -211,9 +211,60 @@ def lr_roofline(dev, pk):
     ms = sum(times) / len(times)
     nbytes = 4 * Cc * (B * L + B * T) + 4 * B * L + 4 * B
     ach = nbytes / (ms * 1e-3) / 1e9
+    traffic = None
+    try:  # DRAM bytes of this very launch shape from the committed ncu capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get(f"length_regulate_kernel B={B} L={L} T={T} C={Cc}", {}).get("bytes")
+    except Exception:
+        pass
     return {"kernel": "length_regulate_kernel", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
-            "frac": ach / pk["hbm_gbs"], "traffic": None, "shape": f"B={B} L={L} T={T} C={Cc}", "ms": ms,
+            "frac": ach / pk["hbm_gbs"], "traffic": traffic, "algorithmic_bytes": nbytes,
+            "shape": f"B={B} L={L} T={T} C={Cc}", "ms": ms,
             "peak_source": pk["source"]}
+
+
+def quick_measure(workload, precision, dev, steps=3, warmup=3):
+    """Secondary numbers for the same JSON line: device-resident and end-to-end throughput of another
+    workload / precision mode, same timing rules as the headline (events per step, L2 flushed)."""
+    import speakingstyle_b200 as ss
+
+    ds, batch, voc = S.make_workload(workload, seed=1)
+    d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    model = ss.get_model(pc, mc, dev, S.fastspeech2_state_dict(mc, ds), precision=precision)
+    gen = ss.get_vocoder(C.hifigan_config(), dev, S.hifigan_state_dict(), precision=precision) if voc else None
+    host, resident = pin(batch), to_dev(batch, dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step(b):
+        out = call(model, b)
+        pcm = gen(out[1], channels_last=True, pcm=True)[1] if gen is not None else None
+        return out, pcm
+
+    for _ in range(warmup):
+        out, pcm = step(resident)
+    torch.cuda.synchronize()
+    frames = int(out[9].sum())
+    res = {}
+    for name, src in (("value", resident), ("e2e", host)):
+        ms = 0.0
+        for _ in range(steps):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            o, w = step(src)
+            if name == "e2e":
+                (w if w is not None else o[1]).to("cpu", non_blocking=False)
+            b.record()
+            torch.cuda.synchronize()
+            ms += a.elapsed_time(b)
+        res[name] = frames * steps / (ms * 1e-3)
+        res[name + "_ms_per_step"] = ms / steps
+    return {"workload": workload, "desc": WORKLOAD_DESC[workload], "precision_mode": precision,
+            "mel_frames_per_s": res["value"], "audio_seconds_per_s": res["value"] * HOP / SR,
+            "ms_per_step": res["value_ms_per_step"], "e2e_mel_frames_per_s": res["e2e"],
+            "e2e_audio_seconds_per_s": res["e2e"] * HOP / SR, "e2e_ms_per_step": res["e2e_ms_per_step"],
+            "valid_frames_per_step": frames, "steps": steps}
 
 
 def main():
@@ -227,6 +278,7 @@ def main():
                     help="fp32: all kernels fp32-accurate (mel max-abs <= 1e-3); bf16: Decoder/PostNet/HiFi-GAN "
                          "on tcgen05 with bf16 operands (relative L2 <= 1e-2); integers identical in both")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads / bf16 mode block")
     ap.add_argument("--conv-breakdown", action="store_true", help="print per-shape conv timings to stderr")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -352,6 +404,11 @@ def main():
                         "rate) per algorithmic MAC, so its ceiling is peak/6"}
         if args.precision == "fp32":
             roof["frac_of_3xtf32_ceiling"] = ach / (pk["tflops_sustained"] / 6.0)
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            roof["traffic_example"] = {k: v for k, v in tj.items() if k.startswith("conv1d_tf32")}
+        except Exception:
+            pass
         line = {
             "metric": "mel_frames_per_s", "value": value, "unit": "mel-frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -371,6 +428,18 @@ def main():
             line["roofline_length_regulator"] = lr_roofline(dev, pk)
         except Exception as e:  # pragma: no cover
             line["roofline_length_regulator"] = {"error": str(e)}
+        if world == 1 and not args.no_extra:
+            del model, gen, resident, host  # free the headline model before building the secondary ones
+            torch.cuda.empty_cache()
+            extra = []
+            other = "bf16" if args.precision == "fp32" else "fp32"
+            for wl, pr in ((args.workload, other), ("cfg3", "fp32"), ("cfg3", "bf16")):
+                try:
+                    extra.append(quick_measure(wl, pr, dev))
+                except Exception as e:  # pragma: no cover
+                    extra.append({"workload": wl, "precision_mode": pr, "error": str(e)})
+                torch.cuda.empty_cache()
+            line["extra"] = extra
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(sd, mc, batch, voc)
         print(json.dumps(line), flush=True)
