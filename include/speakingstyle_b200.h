@@ -175,6 +175,9 @@ typedef struct {
                               truncation, so partial sums are re-added in registers every k_group*4 MMAs */
 } ss_conv1d_tf32_params;
 SS_API int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream);
+/* Same contract; the split activations are kept in tensor memory (tcgen05.st) and the MMAs take their A
+ * operand from there, which removes the shared-memory re-reads that bound the variant above. */
+SS_API int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream);
 
 /* out = bf16(act(x)) element-wise over n elements (n % 8 == 0): the entry into the bf16 path. */
 SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream);

@@ -1,0 +1,346 @@
+// 3xTF32 implicit-GEMM convolution, A operand in TENSOR MEMORY (the "TS" form of tcgen05.mma).
+//
+// Same mathematics, interface, accuracy measures (separate correction accumulator, main accumulator
+// restarted every k_group chunks, partial tiles summed in registers) and epilogue as conv1d_tf32.cu;
+// what changes is where the split activations live.  In conv1d_tf32.cu the split warps write hi and lo
+// back to shared memory and every one of the 12 MMAs of a chunk re-reads a 4 KB A slice from it: the
+// shared-memory pipe, not the tensor pipe, sets the pace (ncu: 59 % tensor, 53 % LSU wavefronts).
+// Here the split warps read the TMA-landed fp32 tile ONCE (thread = row, un-swizzling the eight 16-byte
+// units of its row), split it in registers and store hi / lo with tcgen05.st into TMEM, from where the
+// MMAs take A for free; shared memory then only carries the TMA fill and the B (weight) reads.
+//
+// TMEM columns (BN = 128): main accumulator x2 (256) | correction accumulator (128) | A hi/lo, 2 slots x
+// (32 + 32) columns (128) = 512.  Shared memory per stage: x tile 16 KB + W_hi + W_lo.
+#include "tc_common.cuh"
+
+namespace {
+
+using namespace sstc;
+
+constexpr int KCHUNK = 32;  // fp32 elements per 128-byte swizzle row
+constexpr int NTHREADS = 320;
+constexpr int A_SLOTS = 2;
+constexpr int A_SLOT_COLS = 2 * KCHUNK;  // hi | lo
+
+template <int BN, int STAGES>
+struct Cfg {
+  static constexpr int b_bytes = BN * ROW_BYTES;
+  static constexpr int stage_bytes = A_BYTES + 2 * b_bytes;  // x (fp32), W_hi, W_lo
+  static constexpr int a_col0 = 3 * BN;                      // after main0, main1, corr
+  static constexpr int used_cols = a_col0 + A_SLOTS * A_SLOT_COLS;
+  static constexpr int tmem_cols = used_cols <= 32 ? 32 : used_cols <= 64 ? 64 : used_cols <= 128 ? 128 : used_cols <= 256 ? 256 : 512;
+  static_assert(used_cols <= 512, "TMEM budget");
+  static constexpr int n_bars = 2 * STAGES + 2 * A_SLOTS + 4 + 2;
+  static constexpr int smem_bytes = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16 + 1024;
+  static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
+};
+
+__device__ __forceinline__ float tf32_rn(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+}
+
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(db), "r"(idesc), "r"(accum)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15])),
+      "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])), "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])),
+      "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+      "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
+      "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(NTHREADS, 1)
+conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
+                      const __grid_constant__ CUtensorMap tmBl, const TcArgs p, const int in_act, const float in_slope,
+                      const int group) {
+  using C = Cfg<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
+  auto off_a = [](int s) { return s * C::stage_bytes; };
+  auto off_bh = [](int s) { return s * C::stage_bytes + A_BYTES; };
+  auto off_bl = [](int s) { return s * C::stage_bytes + A_BYTES + C::b_bytes; };
+  float* stg_all = reinterpret_cast<float*>(smem_al + STAGES * C::stage_bytes);
+  const uint32_t bars = smem0 + STAGES * C::stage_bytes + STG_BYTES;
+  const uint32_t full0 = bars, empty0 = full0 + 8 * STAGES, tafull0 = empty0 + 8 * STAGES,
+                 taempty0 = tafull0 + 8 * A_SLOTS, tfull0 = taempty0 + 8 * A_SLOTS, tempty0 = tfull0 + 16,
+                 cfull = tempty0 + 16, cempty = cfull + 8, tslot = cempty + 8;
+  volatile uint32_t* tslot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + STG_BYTES + C::n_bars * 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
+  const int KT = p.k * nchunk;
+  const int num_tiles = p.B * p.m_tiles * p.n_tiles;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmBh);
+    prefetch_tmap(&tmBl);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    for (int t = 0; t < A_SLOTS; ++t) {
+      mbar_init(tafull0 + 8 * t, 4);  // one arrival per split warp
+      mbar_init(taempty0 + 8 * t, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull0 + 8 * a, 1);
+      mbar_init(tempty0 + 8 * a, 4);
+    }
+    mbar_init(cfull, 1);
+    mbar_init(cempty, 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tslot, (uint32_t)C::tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tslot_ptr;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int nt = tile % p.n_tiles;
+        const int rest = tile / p.n_tiles;
+        const int mt = rest % p.m_tiles;
+        const int b = rest / p.m_tiles;
+        const int t0 = mt * BM, n0 = nt * BN;
+        for (int it = 0; it < KT; ++it) {
+          const int j = it / nchunk;
+          const int c0 = (it - j * nchunk) * KCHUNK;
+          mbar_wait(empty0 + 8 * stage, phase ^ 1);
+          mbar_expect_tx(full0 + 8 * stage, C::stage_bytes);
+          tma_load_3d(smem0 + off_a(stage), &tmA, full0 + 8 * stage, c0, t0 + j * p.dilation - p.pad, b);
+          tma_load_3d(smem0 + off_bh(stage), &tmBh, full0 + 8 * stage, c0, n0, j);
+          tma_load_3d(smem0 + off_bl(stage), &tmBl, full0 + 8 * stage, c0, n0, j);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(2u, BN);  // tf32 x tf32 -> f32
+      int stage = 0, slot = 0;
+      uint32_t phase = 0, sphase = 0;
+      int local = 0, gcount = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+        mbar_wait(cempty, (local & 1) ^ 1);  // the epilogue has drained the correction accumulator
+        const uint32_t c_tmem = tmem_base + 2 * BN;
+        for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
+          const int as = gcount & 1;
+          mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * BN;
+          const int it1 = min(it0 + group, KT);
+          for (int it = it0; it < it1; ++it) {
+            mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of this chunk are in TMEM (so its TMA has landed too)
+            tc_fence_after();
+            const uint32_t a_hi = tmem_base + C::a_col0 + slot * A_SLOT_COLS, a_lo = a_hi + KCHUNK;
+            const uint32_t b_hi = smem0 + off_bh(stage), b_lo = smem0 + off_bl(stage);
+#pragma unroll
+            for (int kk = 0; kk < KCHUNK / 8; ++kk) {  // K = 8 tf32 per instruction: 8 TMEM columns / 32 bytes of B
+              umma_tf32_ts(c_tmem, a_lo + kk * 8, make_desc(b_hi + kk * 32), idesc, (it | kk) != 0);
+              umma_tf32_ts(c_tmem, a_hi + kk * 8, make_desc(b_lo + kk * 32), idesc, 1u);
+              umma_tf32_ts(d_tmem, a_hi + kk * 8, make_desc(b_hi + kk * 32), idesc, ((it - it0) | kk) != 0);
+            }
+            umma_commit(empty0 + 8 * stage);    // smem stage free (x was consumed by the split warps earlier)
+            umma_commit(taempty0 + 8 * slot);   // TMEM A slot free
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
+          }
+          umma_commit(tfull0 + 8 * as);
+        }
+        umma_commit(cfull);
+      }
+    }
+  } else if (warp < 6) {
+    // ================= epilogue (warps 2..5) =================
+    const int lg = warp & 3;
+    float* stg = stg_all + lg * 32 * STG_PITCH;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
+    int local = 0, gcount = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      const int nt = tile % p.n_tiles;
+      const int rest = tile / p.n_tiles;
+      const int mt = rest % p.m_tiles;
+      const int b = rest / p.m_tiles;
+      float acc[BN];
+#pragma unroll
+      for (int i = 0; i < BN; ++i) acc[i] = 0.f;
+      for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
+        const int as = gcount & 1;
+        mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          float v[32];
+          tmem_ld32(lane_base + as * BN + c0, v);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];  // round-to-nearest fp32 adds
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty0 + 8 * as);
+      }
+      mbar_wait(cfull, local & 1);
+      tc_fence_after();
+      const int len = p.lens ? p.lens[b] : 0x7fffffff;
+#pragma unroll
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float v[32];
+        tmem_ld32(lane_base + 2 * BN + c0, v);
+        if (c0 + 32 >= BN) {  // last read of the correction accumulator: hand it back before the stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(cempty);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += acc[c0 + i];
+        drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+      }
+    }
+  } else {
+    // ================= operand split (warps 6..9): thread = row, shared memory -> registers -> TMEM =========
+    const int lg = warp & 3;  // TMEM lane group this warp may write
+    const int r = lg * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16) + C::a_col0;
+    const int sw = r & 7;
+    int stage = 0, slot = 0;
+    uint32_t phase = 0, sphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int it = 0; it < KT; ++it) {
+        mbar_wait(full0 + 8 * stage, phase);
+        const uint8_t* row = smem_al + off_a(stage) + r * ROW_BYTES;
+        float hi[32], lo[32];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {  // 16-byte unit u of the row sits at unit (u ^ (row & 7)) - SWIZZLE_128B
+          float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+          if (in_act == SS_ACT_LRELU) {
+            x.x = x.x > 0.f ? x.x : x.x * in_slope;
+            x.y = x.y > 0.f ? x.y : x.y * in_slope;
+            x.z = x.z > 0.f ? x.z : x.z * in_slope;
+            x.w = x.w > 0.f ? x.w : x.w * in_slope;
+          }
+          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = tf32_rn(x.x - hi[4 * u + 0]);
+          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
+          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
+          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
+        }
+        mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
+        tc_fence_after();
+        tmem_st32(lane_base + slot * A_SLOT_COLS, hi);
+        tmem_st32(lane_base + slot * A_SLOT_COLS + KCHUNK, lo);
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tafull0 + 8 * slot);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)C::tmem_cols);
+  }
+}
+
+template <int BN, int STAGES>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& tmBl, TcArgs a, int in_act,
+           float in_slope, int group, cudaStream_t st) {
+  using C = Cfg<BN, STAGES>;
+  a.n_tiles = (a.Cout + BN - 1) / BN;
+  a.m_tiles = (a.S_out + BM - 1) / BM;
+  const int64_t tiles = (int64_t)a.B * a.m_tiles * a.n_tiles;
+  SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_ts: too many tiles");
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_ts_kernel<BN, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, C::smem_bytes);
+    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_ts: smem opt-in");
+    attr_set = true;
+  }
+  const int sms = sm_count();
+  SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3_ts: no CUDA device");
+  const int grid = (int)(tiles < sms ? tiles : sms);
+  conv1d_tf32_ts_kernel<BN, STAGES><<<grid, NTHREADS, C::smem_bytes, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
+  SS_CHECK_LAUNCH("ss_conv1d_tf32x3_ts");
+  return SS_OK;
+}
+
+}  // namespace
+
+extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream) {
+  SS_REQUIRE(p && p->x && p->w_hi && p->w_lo && (p->y || p->y_act || p->accum), SS_ERR_INVALID,
+             "ss_conv1d_tf32x3_ts: null pointer");
+  SS_REQUIRE(p->B > 0 && p->S_in > 0 && p->S_out > 0 && p->Cin > 0 && p->Cout > 0 && p->k > 0 && p->dilation > 0,
+             SS_ERR_INVALID, "ss_conv1d_tf32x3_ts: bad shape B=%d S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d", p->B,
+             p->S_in, p->S_out, p->Cin, p->Cout, p->k, p->dilation);
+  SS_REQUIRE(p->Cin % 4 == 0 && p->Cout % 4 == 0, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_ts: Cin (%d) and Cout (%d) must be multiples of 4", p->Cin, p->Cout);
+  SS_REQUIRE(p->x_row_stride % 4 == 0 && p->x_batch_stride % 4 == 0 && p->y_row_stride % 4 == 0 &&
+                 p->y_batch_stride % 4 == 0 && p->y_offset % 4 == 0 && p->y_batch_elems % 4 == 0,
+             SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_ts: strides/offsets must be multiples of 4 elements");
+  SS_REQUIRE(ss::aligned16(p->x) && ss::aligned16(p->w_hi) && ss::aligned16(p->w_lo) && ss::aligned16(p->y) &&
+                 ss::aligned16(p->y_act) && ss::aligned16(p->bias) && ss::aligned16(p->residual) && ss::aligned16(p->accum),
+             SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_ts: pointers must be 16-byte aligned");
+  SS_REQUIRE(p->in_act == SS_ACT_NONE || p->in_act == SS_ACT_LRELU, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_ts: in_act must be none or lrelu");
+
+  const int bn = p->Cout > 64 ? 128 : p->Cout > 32 ? 64 : 32;
+  CUtensorMap tmA, tmBh, tmBl;
+  int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
+                       (uint64_t)p->x_row_stride * 4, (uint64_t)p->x_batch_stride * 4, KCHUNK, BM);
+  if (rc != SS_OK) return rc;
+  rc = make_map_3d(&tmBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->w_hi, (uint64_t)p->Cin, (uint64_t)p->Cout, (uint64_t)p->k,
+                   (uint64_t)p->Cin * 4, (uint64_t)p->Cout * p->Cin * 4, KCHUNK, (uint32_t)bn);
+  if (rc != SS_OK) return rc;
+  rc = make_map_3d(&tmBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->w_lo, (uint64_t)p->Cin, (uint64_t)p->Cout, (uint64_t)p->k,
+                   (uint64_t)p->Cin * 4, (uint64_t)p->Cout * p->Cin * 4, KCHUNK, (uint32_t)bn);
+  if (rc != SS_OK) return rc;
+
+  TcArgs a;
+  a.bias = p->bias; a.residual = p->residual; a.lens = p->lens; a.y = p->y;
+  a.y_act = static_cast<__nv_bfloat16*>(p->y_act); a.accum = p->accum;
+  a.y_batch_stride = p->y_batch_stride; a.y_row_stride = p->y_row_stride; a.y_offset = p->y_offset;
+  a.y_batch_elems = p->y_batch_elems;
+  a.B = p->B; a.S_out = p->S_out; a.Cin = p->Cin; a.Cout = p->Cout; a.k = p->k; a.dilation = p->dilation; a.pad = p->pad;
+  a.m_tiles = a.n_tiles = 0;
+  a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
+  a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int group = p->k_group > 0 ? p->k_group : 4;
+  switch (bn) {
+    case 128: return launch<128, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
+    case 64: return launch<64, 6>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
+    default: return launch<32, 8>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
+  }
+}

@@ -105,6 +105,7 @@ def add_position(x, pe):
 
 fp32_backend = "tf32x3"  # "tf32x3": 3xTF32 tcgen05 kernel (default); "ffma": the FP32-pipe kernel
 tf32_k_group = 0         # 0 = library default (accumulator restart every 4 chunks = 128 channels)
+tf32_variant = "ss"      # "ss": split operands in shared memory; "ts": A operand in tensor memory
 
 
 def tf32_round(t):
@@ -161,7 +162,7 @@ def pack_conv_transpose(weight, stride):
 
 def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y_batch_stride, y_row_stride,
                y_offset, y_batch_elems, dilation, pad, in_act, in_slope, act, slope, act2, slope2, accum_scale,
-               accum_init, flops):
+               accum_init, flops, variant=None):
     hi, lo = W.tf32
     p = _lib.Conv1dTf32Params(
         x=x.data_ptr(), x_batch_stride=S_in * W.cin, x_row_stride=W.cin, w_hi=hi.data_ptr(), w_lo=lo.data_ptr(),
@@ -172,7 +173,8 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         B=B, S_in=S_in, S_out=S_out, Cin=W.cin, Cout=W.cout, k=W.k, dilation=dilation, pad=pad, in_act=in_act,
         in_slope=in_slope, act=act, slope=slope, act2=act2 or 0, slope2=slope2, accum_scale=accum_scale,
         accum_init=int(accum_init), k_group=tf32_k_group)
-    fn = lambda: _lib.lib().ss_conv1d_tf32x3(C.byref(p), _stream())  # noqa: E731
+    entry = _lib.lib().ss_conv1d_tf32x3_ts if (variant or tf32_variant) == "ts" else _lib.lib().ss_conv1d_tf32x3
+    fn = lambda: entry(C.byref(p), _stream())  # noqa: E731
     check(conv_timer.run(flops, fn, _tag("tf32x3", p)) if conv_timer is not None else fn())
 
 
@@ -193,8 +195,10 @@ def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.
     if write_y:
         y = out if out is not None else torch.empty((B, S, Cout), dtype=torch.float32, device=x.device)
         _chk(y, torch.float32, "out")
-    if (backend or fp32_backend) == "tf32x3":
-        _tf32_call(x, w, bias, residual, lens, y, None, accum, B=B, S_in=S, S_out=S, y_batch_stride=S * Cout,
+    be = backend or fp32_backend
+    if be.startswith("tf32x3"):
+        _tf32_call(x, w, bias, residual, lens, y, None, accum, variant=be[7:] or None, B=B, S_in=S, S_out=S,
+                   y_batch_stride=S * Cout,
                    y_row_stride=Cout, y_offset=0, y_batch_elems=S * Cout, dilation=dilation, pad=pad, in_act=in_act,
                    in_slope=in_slope, act=act, slope=slope, act2=None, slope2=0.0, accum_scale=accum_scale,
                    accum_init=accum_init, flops=2.0 * B * S * Cout * k * Cin)
@@ -221,8 +225,10 @@ def conv_transpose1d(x, w, bias, *, cout, stride, pad, in_act=ACT_NONE, in_slope
     T_out = (S - 1) * stride - 2 * pad + k_full
     S_out = (T_out - 1 + pad) // stride + 1
     y = torch.empty((B, T_out, cout), dtype=torch.float32, device=x.device)
-    if (backend or fp32_backend) == "tf32x3":
-        _tf32_call(x, w, bias, None, None, y, None, None, B=B, S_in=S, S_out=S_out, y_batch_stride=T_out * cout,
+    be = backend or fp32_backend
+    if be.startswith("tf32x3"):
+        _tf32_call(x, w, bias, None, None, y, None, None, variant=be[7:] or None, B=B, S_in=S, S_out=S_out,
+                   y_batch_stride=T_out * cout,
                    y_row_stride=stride * cout, y_offset=-pad * cout, y_batch_elems=T_out * cout, dilation=1,
                    pad=taps - 1, in_act=in_act, in_slope=in_slope, act=ACT_NONE, slope=0.0, act2=None, slope2=0.0,
                    accum_scale=0.0, accum_init=False, flops=2.0 * B * T_out * cout * taps * Cin)

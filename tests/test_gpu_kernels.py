@@ -53,7 +53,7 @@ def lrelu(x, s):
     (1, 1, 256, 512, 1, 1),      # single row (feature_wise_affine)
     (2, 5, 256, 256, 3, 1),      # sequence shorter than the kernel's halo
 ])
-@pytest.mark.parametrize("backend", ["ffma", "tf32x3"])
+@pytest.mark.parametrize("backend", ["ffma", "tf32x3_ss", "tf32x3_ts"])
 def test_conv1d_matches_torch(ops, backend, B, S, Cin, Cout, k, dil):
     """Both fp32-accurate kernels: the FP32-pipe one and the 3xTF32 tcgen05 one."""
     x, w, b = rnd(B, S, Cin, seed=1), rnd(Cout, Cin, k, seed=2, scale=1 / math.sqrt(Cin * k)), rnd(Cout, seed=3)
@@ -73,18 +73,19 @@ def test_tf32x3_is_at_least_as_accurate_as_fp32_fma(ops):
     ref = F.conv1d(x.transpose(1, 2).double(), w.double(), None, padding=1).transpose(1, 2)
     W = pack(w)
     e = {}
-    for backend in ("ffma", "tf32x3"):
+    for backend in ("ffma", "tf32x3_ss", "tf32x3_ts"):
         y = ops.conv1d(x.to(DEV), W, None, pad=1, backend=backend).cpu().double()
         e[backend] = ((y - ref).pow(2).mean().sqrt().item(), (y - ref).abs().max().item())
     import os
     d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
     if os.path.isdir(d):
         with open(os.path.join(d, "parity_report.txt"), "a") as f:
-            f.write(f"conv K=3072 error vs fp64 (rms, max): ffma {e['ffma']}, tf32x3 {e['tf32x3']}\n")
-    assert e["tf32x3"][0] <= 1.5 * e["ffma"][0] and e["tf32x3"][1] <= 1e-5
+            f.write(f"conv K=3072 error vs fp64 (rms, max): {e}\n")
+    for be in ("tf32x3_ss", "tf32x3_ts"):
+        assert e[be][0] <= 1.5 * e["ffma"][0] and e[be][1] <= 1e-5, be
 
 
-@pytest.mark.parametrize("backend", ["ffma", "tf32x3"])
+@pytest.mark.parametrize("backend", ["ffma", "tf32x3_ss", "tf32x3_ts"])
 def test_conv1d_epilogues(ops, backend, monkeypatch):
     monkeypatch.setattr(ops, "fp32_backend", backend)
     B, S, Cin, Cout, k = 3, 77, 64, 128, 3
@@ -121,7 +122,7 @@ def test_conv_transpose_phase_form(ops, Cin, Cout, k, u, S):
     x, w, b = rnd(B, S, Cin, seed=8), rnd(Cin, Cout, k, seed=9, scale=1 / math.sqrt(Cin * k / u)), rnd(Cout, seed=10)
     pad = (k - u) // 2
     ref = F.conv_transpose1d(lrelu(x, 0.1).transpose(1, 2), w, b, stride=u, padding=pad).transpose(1, 2)
-    for backend in ("ffma", "tf32x3"):
+    for backend in ("ffma", "tf32x3_ss", "tf32x3_ts"):
         y = ops.conv_transpose1d(x.to(DEV), ops.pack_conv_transpose(w.to(DEV), u), b.repeat(u).to(DEV), cout=Cout,
                                  stride=u, pad=pad, in_act=ops.ACT_LRELU, in_slope=0.1, backend=backend)
         assert y.shape == ref.shape
