@@ -196,15 +196,23 @@ def length_regulate(x, durations, max_len=None):
 
 
 def variance_adaptor(sd, mc, x, src_mask, gammas, betas, p_control=1.0, e_control=1.0, d_control=1.0,
-                     d_targets=None, max_len=None):
+                     d_targets=None, max_len=None, p_targets=None, e_targets=None):
     """model/modules.py:105-165, phoneme-level pitch/energy (all shipped configs)."""
     va = "variance_adaptor"
     log_d = variance_predictor(sd, va + ".duration_predictor", x, src_mask, gammas, betas)
-    pitch = variance_predictor(sd, va + ".pitch_predictor", x, src_mask) * p_control
-    pitch_idx = bucketize(pitch, sd[va + ".pitch_bins"])
+    pitch = variance_predictor(sd, va + ".pitch_predictor", x, src_mask)
+    if p_targets is not None:  # modules.py:85-86: embedding from the target, prediction returned unscaled
+        pitch_idx = bucketize(p_targets.to(pitch.dtype), sd[va + ".pitch_bins"])
+    else:
+        pitch = pitch * p_control
+        pitch_idx = bucketize(pitch, sd[va + ".pitch_bins"])
     x = x + sd[va + ".pitch_embedding.weight"][pitch_idx]
-    energy = variance_predictor(sd, va + ".energy_predictor", x, src_mask) * e_control
-    energy_idx = bucketize(energy, sd[va + ".energy_bins"])
+    energy = variance_predictor(sd, va + ".energy_predictor", x, src_mask)
+    if e_targets is not None:
+        energy_idx = bucketize(e_targets.to(energy.dtype), sd[va + ".energy_bins"])
+    else:
+        energy = energy * e_control
+        energy_idx = bucketize(energy, sd[va + ".energy_bins"])
     x = x + sd[va + ".energy_embedding.weight"][energy_idx]
     if d_targets is not None:
         d_rounded = d_targets
@@ -246,7 +254,7 @@ def postnet(sd, mel):
 
 
 def fastspeech2_forward(sd, mc, batch, p_control=1.0, e_control=1.0, d_control=1.0, dtype=torch.float32,
-                        intermediates=False):
+                        intermediates=False, p_targets=None, e_targets=None, d_targets=None):
     """model/fastspeech2.py:44-120 (inference: no targets).  Returns the 10-tuple, or a dict."""
     sd = _SD(sd, dtype)
     texts, src_lens = batch["texts"], batch["src_lens"]
@@ -257,8 +265,11 @@ def fastspeech2_forward(sd, mc, batch, p_control=1.0, e_control=1.0, d_control=1
     enc = enc_plain = encoder(sd, mc, texts, src_mask, gammas, betas)
     if "speaker_emb.weight" in sd and mc["multi_speaker"]:
         enc = enc + sd["speaker_emb.weight"][batch["speakers"]][:, None, :]  # pads included (fastspeech2.py:74-77)
-    va = variance_adaptor(sd, mc, enc, src_mask, gammas, betas, p_control, e_control, d_control)
-    mel_mask = mask_from_lengths(va["mel_len"])
+    va = variance_adaptor(sd, mc, enc, src_mask, gammas, betas, p_control, e_control, d_control, d_targets=d_targets,
+                          max_len=batch["max_mel_len"] if d_targets is not None else None, p_targets=p_targets,
+                          e_targets=e_targets)
+    # teacher forcing keeps the reference mel's mask (fastspeech2.py:62-66); otherwise it is rebuilt from mel_len
+    mel_mask = ref_mask if d_targets is not None else mask_from_lengths(va["mel_len"])
     dec, mel_mask = decoder(sd, mc, va["x"], mel_mask, gammas, betas)
     mel = F.linear(dec, sd["mel_linear.weight"], sd["mel_linear.bias"])
     post = postnet(sd, mel) + mel

@@ -99,6 +99,25 @@ def save_compact(name):
           f"T={out[0].shape[1]} frames={int(out[9].sum())}")
 
 
+def save_teacher_forced():
+    """Teacher-forced / fine-control call (p, e, d targets given) on the real reference."""
+    ds = "BC2013"
+    batch, tg = S.make_teacher_forced_batch()
+    d = tempfile.mkdtemp()
+    C.write_preprocessed_dir(d, ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    model = rh.build_fastspeech2(pc, mc, S.fastspeech2_state_dict(mc, ds, seed=FS2_SEED))
+    with torch.no_grad(), rh.quiet():
+        out = model(batch["speakers"], batch["texts"], batch["src_lens"], batch["max_src_len"], batch["mels"],
+                    batch["mel_lens"], batch["max_mel_len"], p_targets=tg["p_targets"], e_targets=tg["e_targets"],
+                    d_targets=tg["d_targets"])
+    names = ["mel", "postnet_mel", "pitch", "energy", "log_d", "d_rounded", "src_masks", "mel_masks", "src_lens",
+             "mel_lens"]
+    path = os.path.join(GOLDEN, "tiny_tf.npz")
+    np.savez_compressed(path, **{n: o.numpy() for n, o in zip(names, out)})
+    print(f"tiny_tf -> {path} ({os.path.getsize(path) / 1024:.0f} KiB) mel_lens={out[9].tolist()} dtype={out[9].dtype}")
+
+
 def save_hifigan_small():
     h = C.hifigan_config()
     gen = rh.build_generator(h, S.hifigan_state_dict(h, seed=VOC_SEED))
@@ -151,6 +170,7 @@ def main():
         "tiny": lambda: save_full("tiny", "tiny"),
         "tiny_ms": lambda: save_full("tiny_ms", "tiny_ms"),
         "tiny_ctl": lambda: save_full("tiny", "tiny_ctl", controls=(1.2, 0.8, 1.3)),
+        "tiny_tf": save_teacher_forced,
         "cfg1": lambda: save_compact("cfg1"),
     }
     if args.large:

@@ -72,8 +72,6 @@ class FastSpeech2(nn.Module, ParamCache):
         if mels is None or mel_lens is None:
             # the reference dereferences mel_masks / mask unconditionally (fastspeech2.py:79, modules.py:384)
             raise AttributeError("a reference mel (mels, mel_lens, max_mel_len) is mandatory at inference")
-        if p_targets is not None or e_targets is not None:
-            raise NotImplementedError("p_targets / e_targets are training inputs")
         nb = True
         speakers = torch.as_tensor(speakers).to(dev, torch.int64, non_blocking=nb).contiguous()
         texts = torch.as_tensor(texts).to(dev, torch.int64, non_blocking=nb).contiguous()
@@ -85,23 +83,32 @@ class FastSpeech2(nn.Module, ParamCache):
         src_lens32 = _as_lens(src_lens_in, dev)
         ref_lens32 = _as_lens(torch.as_tensor(mel_lens), dev)
 
+        if p_targets is not None:
+            p_targets = torch.as_tensor(p_targets).to(dev, torch.float32, non_blocking=nb)
+        if e_targets is not None:
+            e_targets = torch.as_tensor(e_targets).to(dev, torch.float32, non_blocking=nb)
+        if d_targets is not None:
+            d_targets = torch.as_tensor(d_targets).to(dev, non_blocking=nb)
         src_masks = ops.length_mask(src_lens32, max_src_len)
         gammas, betas = self.reference_encoder(mels, max_mel_len, None, lens=ref_lens32)
         x = self.encoder(texts, None, gammas, betas, lens=src_lens32)
         if self.speaker_emb is not None:
             x = ops.add_speaker(x, speakers, self.speaker_emb.weight)  # pads included (fastspeech2.py:74-77)
 
+        ref_masks = ops.length_mask(ref_lens32, max_mel_len) if d_targets is not None else None
         (x, p_pred, e_pred, log_d, d_rounded, mel_lens_out, mel_masks, extra) = self.variance_adaptor(
-            x, src_masks, None, max_mel_len, p_targets, e_targets, d_targets, p_control, e_control, d_control,
+            x, src_masks, ref_masks, max_mel_len, p_targets, e_targets, d_targets, p_control, e_control, d_control,
             gammas, betas, src_lens=src_lens32, decoder_pe=lambda T: self.decoder._pe(T, self.decoder.d_model),
             return_extra=True, inplace=True)
-        if d_targets is not None:
-            raise NotImplementedError("teacher-forced durations go through LengthRegulator directly (SURVEY 8f-3)")
         T = extra["T"]
-        # decoder key mask = mask from mel_len cropped to the expanded length (Models.py:154-162)
-        dec_lens = torch.clamp(mel_lens_out, max=T) if mel_masks.shape[1] != T else mel_lens_out
-        if mel_masks.shape[1] != T:
-            mel_masks = ops.length_mask(dec_lens, T)
+        if d_targets is not None:
+            # teacher forcing: the decoder mask is the reference mel's mask (fastspeech2.py:62-66, modules.py:133-135)
+            dec_lens = torch.clamp(ref_lens32, max=T)
+        else:
+            # decoder key mask = mask from mel_len cropped to the expanded length (Models.py:154-162)
+            dec_lens = torch.clamp(mel_lens_out, max=T) if mel_masks.shape[1] != T else mel_lens_out
+            if mel_masks.shape[1] != T:
+                mel_masks = ops.length_mask(dec_lens, T)
         if self.precision == "bf16":
             # Decoder, mel_linear and PostNet on the tensor cores (bf16 operands, fp32 accumulation and
             # fp32 residual stream).  Everything before this point decides integers and stays fp32.

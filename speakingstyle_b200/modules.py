@@ -144,22 +144,34 @@ class VarianceAdaptor(nn.Module):
     def forward(self, x, src_mask, mel_mask=None, max_len=None, pitch_target=None, energy_target=None,
                 duration_target=None, p_control=1.0, e_control=1.0, d_control=1.0, gammas=None, betas=None,
                 src_lens=None, decoder_pe=None, return_extra=False, inplace=False):
-        if pitch_target is not None or energy_target is not None:
-            raise NotImplementedError("pitch/energy targets are training inputs; inference path only")
         lens = src_lens if src_lens is not None else lens_from_mask(src_mask)
         log_d = self.duration_predictor(x, src_mask, gammas, betas, lens=lens)
         if not inplace:
             x = x.clone()  # the reference leaves its input untouched; the embedding adds below are in place
+        # With a target the embedding comes from the target and the prediction is returned unscaled
+        # (modules.py:85-86, 96-97); without, from control * prediction (88-91, 99-102).
         pitch = self.pitch_predictor(x, src_mask, lens=lens)
-        pitch_idx = ops.bucket_embed_add(pitch, p_control, self.pitch_bins, self.pitch_embedding.weight, x,
-                                         want_idx=return_extra)
+        if pitch_target is not None:
+            pitch_idx = ops.bucket_embed_add(pitch_target.to(torch.float32).contiguous().clone(), 1.0, self.pitch_bins,
+                                             self.pitch_embedding.weight, x, want_idx=return_extra)
+        else:
+            pitch_idx = ops.bucket_embed_add(pitch, p_control, self.pitch_bins, self.pitch_embedding.weight, x,
+                                             want_idx=return_extra)
         energy = self.energy_predictor(x, src_mask, lens=lens)
-        energy_idx = ops.bucket_embed_add(energy, e_control, self.energy_bins, self.energy_embedding.weight, x,
-                                          want_idx=return_extra)
+        if energy_target is not None:
+            energy_idx = ops.bucket_embed_add(energy_target.to(torch.float32).contiguous().clone(), 1.0,
+                                              self.energy_bins, self.energy_embedding.weight, x, want_idx=return_extra)
+        else:
+            energy_idx = ops.bucket_embed_add(energy, e_control, self.energy_bins, self.energy_embedding.weight, x,
+                                              want_idx=return_extra)
         if duration_target is not None:
+            # teacher forcing (modules.py:133-135): expand by the given durations to max_len; mel_mask is the caller's
             d_rounded = duration_target
-            out, mel_len = self.length_regulator(x, duration_target, max_len, pe=decoder_pe)
-            extra = None
+            T = int(max_len) if max_len is not None else None
+            pe = decoder_pe(T) if (callable(decoder_pe) and T is not None) else (None if callable(decoder_pe) else decoder_pe)
+            out, mel_len = self.length_regulator(x, duration_target, max_len, pe=pe)
+            extra = {"mel2phone": None, "pitch_idx": pitch_idx, "energy_idx": energy_idx, "T": out.shape[1],
+                     "mel_len_expand": mel_len, "pe_added": pe is not None}
         else:
             d_rounded, ends, lens2 = ops.duration_scan(log_d, d_control)
             lens_host = lens2.cpu()  # one host read (the reference does B*L of them, modules.py:193)

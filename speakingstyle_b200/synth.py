@@ -246,3 +246,24 @@ def make_workload(name, seed=1):
     ds, b, sl, rl, fixed, voc = WORKLOADS[name]
     batch = make_batch(b, sl, rl, n_speakers=C.N_SPEAKERS[ds], seed=seed, fixed_ref_len=fixed)
     return ds, batch, voc
+
+
+def make_teacher_forced_batch(batch=3, seed=7, n_mel=80):
+    """Batch + (p_targets, e_targets, d_targets) as the training / fine-control callers pass them
+    (train.py:86, notebooks/control.ipynb): integer durations whose sum is the reference mel's length,
+    pitch / energy targets in the normalised range of the bins."""
+    r = _Rng(seed)
+    src_lens = r.randint(5, 13, (batch,))
+    L = int(src_lens.max())
+    valid = torch.arange(L)[None, :] < src_lens[:, None]
+    d_targets = r.randint(0, 10, (batch, L)) * valid
+    d_targets[:, 0] += 1  # every utterance at least one frame
+    mel_lens = d_targets.sum(dim=1)
+    Tr = int(mel_lens.max())
+    texts = r.randint(1, C.N_SRC_VOCAB, (batch, L)) * valid
+    mels = r.normal((batch, Tr, n_mel)) * (torch.arange(Tr)[None, :, None] < mel_lens[:, None, None])
+    p_targets = r.normal((batch, L), std=2.0) * valid
+    e_targets = r.normal((batch, L), std=2.0) * valid
+    b = {"speakers": torch.zeros(batch, dtype=torch.int64), "texts": texts, "src_lens": src_lens, "max_src_len": L,
+         "mels": mels, "mel_lens": mel_lens, "max_mel_len": Tr}
+    return b, {"p_targets": p_targets, "e_targets": e_targets, "d_targets": d_targets}

@@ -333,3 +333,22 @@ def test_sharded_run_matches_oracle_per_shard():
             assert torch.equal(a[uid]["d_rounded"], b[uid]["d_rounded"])
             assert int(a[uid]["mel_len"]) == int(b[uid]["mel_len"])
             assert maxabs(a[uid]["postnet_mel"], b[uid]["postnet_mel"]) <= TOL
+
+
+def test_teacher_forced_path_vs_golden(golden):
+    """p_targets / e_targets / d_targets: embeddings from the targets, predictions returned
+    unscaled, LengthRegulator expands by the given integer durations to max_mel_len, decoder mask = the
+    reference mel's mask, mel_lens int64 from the regulator."""
+    g = golden("tiny_tf")
+    model, mc, sd = get_models("BC2013")
+    batch, tg = S.make_teacher_forced_batch()
+    out = model(batch["speakers"], batch["texts"], batch["src_lens"], batch["max_src_len"], batch["mels"],
+                batch["mel_lens"], batch["max_mel_len"], p_targets=tg["p_targets"], e_targets=tg["e_targets"],
+                d_targets=tg["d_targets"])
+    names = ["mel", "postnet_mel", "pitch", "energy", "log_d", "d_rounded", "src_masks", "mel_masks", "src_lens", "mel_lens"]
+    for n, o in zip(names, out):
+        if o.dtype.is_floating_point:
+            assert o.shape == g[n].shape and maxabs(o, g[n]) <= TOL, n
+        else:
+            assert np.array_equal(o.cpu().numpy(), g[n]), n
+    assert out[9].dtype == torch.int64 and out[5].dtype == torch.int64

@@ -163,3 +163,19 @@ def test_oracle_vs_live_reference():
     mel = torch.randn(1, 80, 12, generator=torch.Generator().manual_seed(3))
     with torch.no_grad():
         assert (gen(mel) - O.hifigan_forward(S.fold_weight_norm(vsd), h, mel)).abs().max().item() <= 2e-5
+
+
+def test_teacher_forced_oracle_matches_golden(golden):
+    """p/e/d targets given (the training / fine-control call)."""
+    g = golden("tiny_tf")
+    mc = C.model_config("BC2013")
+    sd = S.fastspeech2_state_dict(mc, "BC2013")
+    batch, tg = S.make_teacher_forced_batch()
+    with torch.no_grad():
+        out = O.fastspeech2_forward(sd, mc, batch, **tg)
+    names = ["mel", "postnet_mel", "pitch", "energy", "log_d", "d_rounded", "src_masks", "mel_masks", "src_lens", "mel_lens"]
+    for n, o in zip(names, out):
+        if o.dtype.is_floating_point:
+            np.testing.assert_allclose(o.numpy(), g[n], atol=2e-5, rtol=0, err_msg=n)
+        else:
+            assert np.array_equal(o.numpy(), g[n]) and o.numpy().dtype == g[n].dtype, n
