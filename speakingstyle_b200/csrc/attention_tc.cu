@@ -312,12 +312,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
 }  // namespace
 
+int ss_attention_tc128_launch(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, void* stream);
+
 extern "C" int ss_attention_tc(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, int dk,
                                void* stream) {
   SS_REQUIRE(qkv && ctx, SS_ERR_INVALID, "ss_attention_tc: null pointer");
   SS_REQUIRE(B > 0 && S > 0 && H > 0 && B <= 65535 && H <= 65535, SS_ERR_INVALID, "ss_attention_tc: bad shape");
-  SS_REQUIRE(dk == DK, SS_ERR_UNSUPPORTED, "ss_attention_tc: dk=%d (this kernel is specialised for dk=32)", dk);
+  SS_REQUIRE(dk == DK || dk == 128, SS_ERR_UNSUPPORTED, "ss_attention_tc: dk=%d (kernels exist for dk=32 and dk=128)", dk);
   SS_REQUIRE(ss::aligned16(qkv) && ss::aligned16(ctx), SS_ERR_ALIGNMENT, "ss_attention_tc: 16-byte alignment");
+  if (dk == 128) return ss_attention_tc128_launch(qkv, lens, ctx, B, S, H, stream);
   const int D = H * DK;
   CUtensorMap tmQ, tmKV, tmV;
   int rc = make_map_3d(&tmQ, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, qkv, (uint64_t)3 * D, (uint64_t)S, (uint64_t)B,

@@ -344,7 +344,7 @@ def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pr
 
 
 def attention(qkv, lens, n_head, backend=None):
-    """Fused masked-softmax attention.  backend "tc" = ss_attention_tc (tcgen05, head size 32), "simt" =
+    """Fused masked-softmax attention.  backend "tc" = ss_attention_tc (tcgen05, head sizes 32 / 128), "simt" =
     ss_attention_f32; default: tensor cores whenever the head size allows and ops.fp32_backend is "tf32x3"."""
     _chk(qkv, torch.float32, "qkv"); _chk(lens, torch.int32, "lens")
     B, S, D3 = qkv.shape
@@ -352,7 +352,7 @@ def attention(qkv, lens, n_head, backend=None):
     dk = D // n_head
     ctx = torch.empty((B, S, D), dtype=torch.float32, device=qkv.device)
     if backend is None:
-        backend = "tc" if (dk == 32 and fp32_backend == "tf32x3") else "simt"
+        backend = "tc" if (dk in (32, 128) and fp32_backend == "tf32x3") else "simt"
     fn = _lib.lib().ss_attention_tc if backend == "tc" else _lib.lib().ss_attention_f32
     check(fn(_ptr(qkv), _ptr(lens), _ptr(ctx), B, S, n_head, dk, _stream()))
     return ctx

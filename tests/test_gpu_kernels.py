@@ -156,11 +156,12 @@ def test_layernorm_variants(ops, C):
 
 @pytest.mark.parametrize("H,dk,S,lens", [(2, 128, 150, [150, 64, 1]), (8, 32, 203, [203, 129, 65]),
                                           (8, 32, 800, [800, 513, 64, 1]), (3, 32, 127, [127, 128 - 64, 5]),
-                                          (2, 128, 30, [30, 7, 12]), (4, 64, 70, [70, 70, 3])])
+                                          (2, 128, 30, [30, 7, 12]), (4, 64, 70, [70, 70, 3]),
+                                          (2, 128, 696, [696, 400, 33])])
 @pytest.mark.parametrize("backend", ["simt", "tc"])
 def test_attention_matches_oracle_math(ops, backend, H, dk, S, lens):
-    if backend == "tc" and dk != 32:
-        pytest.skip("the tcgen05 attention kernel is specialised for head size 32")
+    if backend == "tc" and dk not in (32, 128):
+        pytest.skip("the tcgen05 attention kernels cover head sizes 32 and 128")
     B, D = len(lens), H * dk
     qkv = rnd(B, S, 3 * D, seed=18)
     lens_t = torch.tensor(lens, dtype=torch.int32)
