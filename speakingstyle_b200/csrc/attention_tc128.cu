@@ -2,15 +2,20 @@
 // of 128), fp32-accurate (3xTF32 for both GEMMs, fp32 softmax and output accumulation).
 //
 // Same scheme as attention_tc.cu (head size 32) with the layout changes the larger head forces:
-//   * Q hi / lo (2 x 64 KB) cannot stay in shared memory next to K, V and P, so the split warps put them
-//     in TENSOR MEMORY once per CTA (tcgen05.st, thread = query row) and S = Q.K^T uses the TS form of
-//     tcgen05.mma (A from TMEM) - 256 of the 512 TMEM columns;
+//   * Q hi / lo (2 x 64 KB) cannot stay in shared memory next to K, V and P, so they are put in TENSOR
+//     MEMORY once per CTA (tcgen05.st, thread = query row) and S = Q.K^T uses the TS form of tcgen05.mma
+//     (A from TMEM) - 256 of the 512 TMEM columns;
 //   * keys come in 32-key tiles: K [32 x 128] is four K-major [32 x 32] chunk tiles, V [32 x 128] is
-//     transposed on chip into V^T [128 x 32] (thread = head dim), P [128 x 32] is one swizzle chunk;
-//   * O_j = P_j.V_j is a full N = 128 accumulator (single buffer) that the softmax warps fold into 128
-//     fp32 registers per row each tile (o = o*alpha + O_j).
-// TMEM: S0,S1 (2 x 32) | O (128) | Q_hi (128) | Q_lo (128) = 448 columns.  Shared memory: 2 stages x 80 KB
-// (K hi/lo, V as loaded, V^T hi/lo) + P hi/lo 32 KB; the Q staging area aliases the stages.
+//     transposed on chip into V^T [128 x 32], P [128 x 32] is one swizzle chunk (double-buffered);
+//   * O_j = P_j.V_j is a full N = 128 accumulator (single TMEM buffer) that the softmax warps fold into
+//     fp32 registers each tile (o = o*alpha_j + O_j).  EIGHT softmax warps: warps w and w+4 own the same
+//     32 query rows; both read the whole S row (same running max), but each exponentiates / writes half
+//     of the P row and folds half of the O columns, keeping a partial row sum that is merged at the end.
+//   * softmax(j) is issued BEFORE fold(j-1), so it overlaps P.V of the previous tile on the tensor pipe.
+// Rings (2 deep each): K hi/lo (freed by S_j), V as loaded (freed by the transpose), V^T hi/lo (freed by
+// P.V_j) - so no load waits for a whole tile to retire.
+// TMEM: S0,S1 (2 x 32) | O (128) | Q_hi (128) | Q_lo (128) = 448 columns.  Shared memory 224 KB: K 2x32,
+// V 2x16, V^T 2x32, P 2x32 KB; the Q staging area (64 KB) aliases the K ring.
 #include "tc_common.cuh"
 
 namespace {
@@ -19,18 +24,23 @@ using namespace sstc;
 
 constexpr int DK = 128, NCH = DK / 32;   // head size, 32-wide chunks of it
 constexpr int BQ = 128, BKV = 32;
-constexpr int NTHREADS = 320;
+constexpr int N_SOFTMAX_WARPS = 8, N_XF_WARPS = 2;
+constexpr int NTHREADS = 32 * (2 + N_SOFTMAX_WARPS + N_XF_WARPS);  // 384: three warps per scheduler -> 168 registers
 constexpr int CH_BYTES = BKV * 128;            // one [32 keys x 32 dims] chunk tile: 4 KB
 constexpr int KV_BYTES = NCH * CH_BYTES;       // 16 KB
-constexpr int STAGE_BYTES = 5 * KV_BYTES;      // K_hi, K_lo, V_raw, V^T_hi, V^T_lo
 constexpr int P_BYTES = BQ * 128;              // 16 KB
-constexpr int SMEM_DATA = 2 * STAGE_BYTES + 2 * P_BYTES;  // 160 + 32 KB
-constexpr int N_BARS = 2 + 6 + 4 + 2 + 2;
+constexpr int OFF_K = 0;                       // [2][K_hi 16 | K_lo 16]
+constexpr int OFF_VR = OFF_K + 4 * KV_BYTES;   // [2][V as loaded 16]
+constexpr int OFF_VT = OFF_VR + 2 * KV_BYTES;  // [2][V^T_hi 16 | V^T_lo 16]
+constexpr int OFF_P = OFF_VT + 4 * KV_BYTES;   // [2][P_hi 16 | P_lo 16]
+constexpr int SMEM_DATA = OFF_P + 4 * P_BYTES; // 224 KB
+constexpr int N_BARS = 24;
 constexpr int SMEM_BYTES = SMEM_DATA + N_BARS * 8 + 16 + 1024;
 constexpr int COL_S = 0, COL_O = 2 * BKV, COL_QH = COL_O + DK, COL_QL = COL_QH + DK;
 constexpr int TMEM_COLS = 512;
 static_assert(COL_QL + DK <= TMEM_COLS, "TMEM budget");
-static_assert(NCH * BQ * 128 <= 2 * STAGE_BYTES, "Q staging must fit in the stage area");
+static_assert(NCH * BQ * 128 <= 4 * KV_BYTES, "Q staging must fit in the K ring");
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
@@ -84,13 +94,12 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
-  constexpr int OFF_PH = 2 * STAGE_BYTES, OFF_PL = OFF_PH + P_BYTES;
   const uint32_t bars = smem0 + SMEM_DATA;
-  const uint32_t q_full = bars, q_tm = bars + 8;
-  const uint32_t kv_full0 = bars + 16, kv_xf0 = bars + 32, kv_empty0 = bars + 48;
-  const uint32_t s_full0 = bars + 64, s_empty0 = bars + 80;
-  const uint32_t p_full = bars + 96, p_empty = bars + 104;
-  const uint32_t o_full = bars + 112, o_empty = bars + 120;
+  // two-deep rings: index with + 8 * slot
+  const uint32_t k_full0 = bars + 0, k_xf0 = bars + 16, k_empty0 = bars + 32;
+  const uint32_t v_full0 = bars + 48, vr_empty0 = bars + 64, vt_full0 = bars + 80, vt_empty0 = bars + 96;
+  const uint32_t s_full0 = bars + 112, s_empty0 = bars + 128, p_full0 = bars + 144;
+  const uint32_t o_full = bars + 160, o_empty = bars + 168, q_full = bars + 176, q_tm = bars + 184;
   const uint32_t tslot = bars + N_BARS * 8;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + SMEM_DATA + N_BARS * 8);
 
@@ -100,19 +109,22 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     prefetch_tmap(&tmQ);
     prefetch_tmap(&tmK);
     prefetch_tmap(&tmV);
-    mbar_init(q_full, 1);
-    mbar_init(q_tm, 4);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(kv_full0 + 8 * s, 1);
-      mbar_init(kv_xf0 + 8 * s, 4);
-      mbar_init(kv_empty0 + 8 * s, 1);
+      mbar_init(k_full0 + 8 * s, 1);
+      mbar_init(k_xf0 + 8 * s, N_XF_WARPS);
+      mbar_init(k_empty0 + 8 * s, 1);
+      mbar_init(v_full0 + 8 * s, 1);
+      mbar_init(vr_empty0 + 8 * s, N_XF_WARPS);
+      mbar_init(vt_full0 + 8 * s, N_XF_WARPS);
+      mbar_init(vt_empty0 + 8 * s, 1);
       mbar_init(s_full0 + 8 * s, 1);
-      mbar_init(s_empty0 + 8 * s, 4);
+      mbar_init(s_empty0 + 8 * s, N_SOFTMAX_WARPS);
+      mbar_init(p_full0 + 8 * s, N_SOFTMAX_WARPS);
     }
-    mbar_init(p_full, 4);
-    mbar_init(p_empty, 1);
     mbar_init(o_full, 1);
-    mbar_init(o_empty, 4);
+    mbar_init(o_empty, N_SOFTMAX_WARPS);
+    mbar_init(q_full, 1);
+    mbar_init(q_tm, N_SOFTMAX_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tslot, TMEM_COLS);
@@ -125,18 +137,22 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     // ================= TMA producer =================
     if (lane == 0) {
       mbar_expect_tx(q_full, NCH * BQ * 128);
-      for (int c = 0; c < NCH; ++c)  // Q staging [chunk][128 rows x 128 B] over the (still unused) stage area
-        tma_load_3d(smem0 + c * (BQ * 128), &tmQ, q_full, h * DK + c * 32, q0, b);
-      mbar_wait(q_tm, 0);  // Q now lives in TMEM: the staging area may be overwritten
+      for (int c = 0; c < NCH; ++c)  // Q staging [chunk][128 rows x 128 B] over the (still unused) K ring
+        tma_load_3d(smem0 + OFF_K + c * (BQ * 128), &tmQ, q_full, h * DK + c * 32, q0, b);
       for (int j = 0; j < NT; ++j) {
         const int s = j & 1;
-        mbar_wait(kv_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
-        mbar_expect_tx(kv_full0 + 8 * s, 2 * KV_BYTES);
-        const uint32_t st = smem0 + s * STAGE_BYTES;
-        for (int c = 0; c < NCH; ++c) {
-          tma_load_3d(st + c * CH_BYTES, &tmK, kv_full0 + 8 * s, D + h * DK + c * 32, j * BKV, b);                    // K chunk
-          tma_load_3d(st + 2 * KV_BYTES + c * CH_BYTES, &tmV, kv_full0 + 8 * s, 2 * D + h * DK + c * 32, j * BKV, b);  // V chunk
-        }
+        const uint32_t ph = ((j >> 1) & 1) ^ 1;
+        mbar_wait(vr_empty0 + 8 * s, ph);
+        mbar_expect_tx(v_full0 + 8 * s, KV_BYTES);
+        for (int c = 0; c < NCH; ++c)
+          tma_load_3d(smem0 + OFF_VR + s * KV_BYTES + c * CH_BYTES, &tmV, v_full0 + 8 * s, 2 * D + h * DK + c * 32,
+                      j * BKV, b);
+        if (j == 0) mbar_wait(q_tm, 0);  // Q now lives in TMEM: its staging area may be overwritten
+        mbar_wait(k_empty0 + 8 * s, ph);
+        mbar_expect_tx(k_full0 + 8 * s, KV_BYTES);
+        for (int c = 0; c < NCH; ++c)
+          tma_load_3d(smem0 + OFF_K + s * 2 * KV_BYTES + c * CH_BYTES, &tmK, k_full0 + 8 * s, D + h * DK + c * 32,
+                      j * BKV, b);
       }
     }
   } else if (warp == 1) {
@@ -147,10 +163,10 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const uint32_t qh = tmem_base + COL_QH, ql = tmem_base + COL_QL;
       auto issue_s = [&](int j) {
         const int s = j & 1;
-        mbar_wait(kv_xf0 + 8 * s, (j >> 1) & 1);
+        mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
         mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t kh = smem0 + s * STAGE_BYTES, kl = kh + KV_BYTES;
+        const uint32_t kh = smem0 + OFF_K + s * 2 * KV_BYTES, kl = kh + KV_BYTES;
         const uint32_t d = tmem_base + COL_S + s * BKV;
 #pragma unroll
         for (int ks = 0; ks < DK / 8; ++ks) {  // 16 steps of 8 head dims
@@ -160,6 +176,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           umma_tf32_ts(d, qh + ks * 8, make_desc(kh + ko), idesc_s, 1u);
         }
         umma_commit(s_full0 + 8 * s);
+        umma_commit(k_empty0 + 8 * s);
       };
       mbar_wait(q_tm, 0);
       tc_fence_after();
@@ -167,46 +184,70 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       for (int j = 0; j < NT; ++j) {
         if (j + 1 < NT) issue_s(j + 1);
         const int s = j & 1;
-        mbar_wait(p_full, j & 1);
+        mbar_wait(vt_full0 + 8 * s, (j >> 1) & 1);
+        mbar_wait(p_full0 + 8 * s, (j >> 1) & 1);
         mbar_wait(o_empty, (j & 1) ^ 1);
         tc_fence_after();
-        const uint32_t vh = smem0 + s * STAGE_BYTES + 3 * KV_BYTES, vl = vh + KV_BYTES;  // V^T hi / lo [128 x 32]
+        const uint32_t vh = smem0 + OFF_VT + s * 2 * KV_BYTES, vl = vh + KV_BYTES;  // V^T hi / lo [128 x 32]
+        const uint32_t ph = smem0 + OFF_P + s * 2 * P_BYTES, pl = ph + P_BYTES;
         const uint32_t d = tmem_base + COL_O;
 #pragma unroll
         for (int kk = 0; kk < BKV / 8; ++kk) {  // 4 steps of 8 keys
           const uint32_t o = kk * 32;
-          umma_tf32(d, make_desc(smem0 + OFF_PL + o), make_desc(vh + o), idesc_o, kk != 0);
-          umma_tf32(d, make_desc(smem0 + OFF_PH + o), make_desc(vl + o), idesc_o, 1u);
-          umma_tf32(d, make_desc(smem0 + OFF_PH + o), make_desc(vh + o), idesc_o, 1u);
+          umma_tf32(d, make_desc(pl + o), make_desc(vh + o), idesc_o, kk != 0);
+          umma_tf32(d, make_desc(ph + o), make_desc(vl + o), idesc_o, 1u);
+          umma_tf32(d, make_desc(ph + o), make_desc(vh + o), idesc_o, 1u);
         }
         umma_commit(o_full);
-        umma_commit(p_empty);
-        umma_commit(kv_empty0 + 8 * s);
+        umma_commit(vt_empty0 + 8 * s);
       }
     }
-  } else if (warp < 6) {
-    // ================= softmax + output accumulation (thread = query row) =================
+  } else if (warp < 2 + N_SOFTMAX_WARPS) {
+    // ================= softmax + output accumulation =================
+    // thread = query row (lane group = warp % 4); half = which 16 keys of P / 64 columns of O it owns
     const int lg = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int r = lg * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
-    float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-    const float scale_log2 = 1.4426950408889634f / temperature;
-    float o[DK];
-#pragma unroll
-    for (int i = 0; i < DK; ++i) o[i] = 0.f;
-    uint8_t* ph_row = smem_al + OFF_PH + r * 128;
-    uint8_t* pl_row = smem_al + OFF_PL + r * 128;
     const int sw = r & 7;
+    {  // Q: shared staging (swizzled chunk tiles) -> registers -> TMEM hi / lo; this half does two of the chunks
+      mbar_wait(q_full, 0);
+#pragma unroll 1
+      for (int c = 2 * half; c < 2 * half + 2; ++c) {
+        const uint8_t* row = smem_al + OFF_K + c * (BQ * 128) + r * 128;
+        float hi[32], lo[32];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = tf32_rn(x.x - hi[4 * u + 0]);
+          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
+          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
+          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
+        }
+        tmem_st32(lane_base + COL_QH + c * 32, hi);
+        tmem_st32(lane_base + COL_QL + c * 32, lo);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(q_tm);
+    }
 
-    auto fold_o = [&](int jj) {  // o = o*alpha + O_jj
+    float m = -INFINITY, l = 0.f, alpha_fold = 1.f;
+    const float scale_log2 = 1.4426950408889634f / temperature;
+    float o[DK / 2];
+#pragma unroll
+    for (int i = 0; i < DK / 2; ++i) o[i] = 0.f;
+
+    auto fold_o = [&](int jj, float alpha) {  // o = o*alpha + O_jj (this half's 64 columns)
       mbar_wait(o_full, jj & 1);
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) {
+      for (int c = 0; c < 2; ++c) {
         float v[32];
-        tmem_ld32(lane_base + COL_O + c * 32, v);
+        tmem_ld32(lane_base + COL_O + half * 64 + c * 32, v);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = fmaf(o[c * 32 + i], alpha_prev, v[i]);
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = fmaf(o[c * 32 + i], alpha, v[i]);
       }
       tc_fence_before();
       __syncwarp();
@@ -215,7 +256,6 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 
     for (int j = 0; j < NT; ++j) {
       const int sb = j & 1;
-      if (j > 0) fold_o(j - 1);
       mbar_wait(s_full0 + 8 * sb, (j >> 1) & 1);
       tc_fence_after();
       float s0[32];
@@ -226,109 +266,115 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 
       const int kbase = j * BKV;
       float mx = -INFINITY;
+      if (kbase + BKV <= len) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        s0[i] = (kbase + i < len) ? s0[i] * scale_log2 : -INFINITY;
-        mx = fmaxf(mx, s0[i]);
+        for (int i = 0; i < 32; ++i) {
+          s0[i] *= scale_log2;
+          mx = fmaxf(mx, s0[i]);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          s0[i] = (kbase + i < len) ? s0[i] * scale_log2 : -INFINITY;
+          mx = fmaxf(mx, s0[i]);
+        }
       }
       const float m_new = fmaxf(m, mx);  // finite: every tile holds at least one valid key
       const float alpha = exp2f(m - m_new);
+      m = m_new;
+      // this half's 16 keys: exponentiate, sum, write P hi / lo (units 4*half .. 4*half+3 of the swizzled row)
+      uint8_t* ph_row = smem_al + OFF_P + sb * 2 * P_BYTES + r * 128;
+      uint8_t* pl_row = ph_row + P_BYTES;
       float sum = 0.f;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        s0[i] = exp2f(s0[i] - m_new);
-        sum += s0[i];
-      }
-      l = l * alpha + sum;
-      m = m_new;
-      alpha_prev = alpha;
-
-      mbar_wait(p_empty, (j & 1) ^ 1);  // P.V of the previous tile has finished reading P
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
+      for (int uu = 0; uu < 4; ++uu) {
+        const int u = 4 * half + uu;
+        float4 a;  // the s0 index has to be a compile-time constant (registers): select on half
+        a.x = exp2f((half ? s0[16 + 4 * uu + 0] : s0[4 * uu + 0]) - m_new);
+        a.y = exp2f((half ? s0[16 + 4 * uu + 1] : s0[4 * uu + 1]) - m_new);
+        a.z = exp2f((half ? s0[16 + 4 * uu + 2] : s0[4 * uu + 2]) - m_new);
+        a.w = exp2f((half ? s0[16 + 4 * uu + 3] : s0[4 * uu + 3]) - m_new);
+        sum += (a.x + a.y) + (a.z + a.w);
         const int pu = (u ^ sw) * 16;
-        const float4 a = make_float4(s0[4 * u], s0[4 * u + 1], s0[4 * u + 2], s0[4 * u + 3]);
         const float4 ah = make_float4(tf32_rn(a.x), tf32_rn(a.y), tf32_rn(a.z), tf32_rn(a.w));
         *reinterpret_cast<float4*>(ph_row + pu) = ah;
         *reinterpret_cast<float4*>(pl_row + pu) =
             make_float4(tf32_rn(a.x - ah.x), tf32_rn(a.y - ah.y), tf32_rn(a.z - ah.z), tf32_rn(a.w - ah.w));
       }
+      l = l * alpha + sum;
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
+      if (lane == 0) mbar_arrive(p_full0 + 8 * sb);  // buffer sb was last read by P.V_{j-2}: retired before fold(j-2)
+
+      if (j > 0) fold_o(j - 1, alpha_fold);
+      alpha_fold = alpha;
     }
-    fold_o(NT - 1);
+    fold_o(NT - 1, alpha_fold);
+
+    // merge the two halves' row sums through shared memory (all MMAs have retired: P is free)
+    float* lbuf = reinterpret_cast<float*>(smem_al + OFF_P);
+    lbuf[half * BQ + r] = l;
+    asm volatile("bar.sync 1, %0;" ::"n"(N_SOFTMAX_WARPS * 32) : "memory");
+    l += lbuf[(half ^ 1) * BQ + r];
     const int q = q0 + r;
     if (q < S) {
       const float inv = q < len ? 1.0f / l : 0.f;  // padded query rows are written as zeros
-      float4* orow = reinterpret_cast<float4*>(out + (int64_t)q * D);
+      float4* orow = reinterpret_cast<float4*>(out + (int64_t)q * D + half * 64);
 #pragma unroll
-      for (int c = 0; c < DK / 4; ++c)
+      for (int c = 0; c < DK / 8; ++c)
         orow[c] = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
     }
   } else {
-    // ================= operand split / transpose (warps 6..9) =================
-    const int lg = warp & 3;
-    const int r = lg * 32 + lane;         // Q: this thread's query row; V: this thread's head dim
-    const int tt = (warp - 6) * 32 + lane;  // linear id for element-wise work
-    const int sw = r & 7;
-    {  // Q: shared staging (swizzled chunk tiles) -> registers -> TMEM hi / lo, thread = row
-      mbar_wait(q_full, 0);
-      const uint32_t tq = tmem_base + ((uint32_t)(lg * 32) << 16);
-#pragma unroll 1
-      for (int c = 0; c < NCH; ++c) {
-        const uint8_t* row = smem_al + c * (BQ * 128) + r * 128;
-        float hi[32], lo[32];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
-          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = tf32_rn(x.x - hi[4 * u + 0]);
-          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
-          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
-          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
-        }
-        tmem_st32(tq + COL_QH + c * 32, hi);
-        tmem_st32(tq + COL_QL + c * 32, lo);
-      }
-      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(q_tm);
-    }
+    // ================= K split / V transpose (2 warps, 64 threads) =================
+    const int tt = (warp - 2 - N_SOFTMAX_WARPS) * 32 + lane;  // 0..63
     for (int j = 0; j < NT; ++j) {
       const int s = j & 1;
-      mbar_wait(kv_full0 + 8 * s, (j >> 1) & 1);
-      uint8_t* st = smem_al + s * STAGE_BYTES;
+      const uint32_t ph = (j >> 1) & 1;
       {  // K: element-wise split, hi in place, lo next to it
-        float4* hi = reinterpret_cast<float4*>(st);
-        float4* lo = reinterpret_cast<float4*>(st + KV_BYTES);
-#pragma unroll
-        for (int i = 0; i < KV_BYTES / 16 / 128; ++i) {
-          const int idx = tt + i * 128;
+        mbar_wait(k_full0 + 8 * s, ph);
+        float4* hi = reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES);
+        float4* lo = reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES);
+#pragma unroll 4
+        for (int i = 0; i < KV_BYTES / 16 / (N_XF_WARPS * 32); ++i) {
+          const int idx = tt + i * (N_XF_WARPS * 32);
           const float4 x = hi[idx];
           const float4 hv = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
           hi[idx] = hv;
           lo[idx] = make_float4(tf32_rn(x.x - hv.x), tf32_rn(x.y - hv.y), tf32_rn(x.z - hv.z), tf32_rn(x.w - hv.w));
         }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(k_xf0 + 8 * s);
       }
       {  // V [32 keys x 128 dims] (chunked [c][key][32]) -> V^T hi / lo [128 dims x 32 keys], swizzled rows
-        const float* vraw = reinterpret_cast<const float*>(st + 2 * KV_BYTES) + (r >> 5) * (CH_BYTES / 4) + (r & 31);
-        uint8_t* th = st + 3 * KV_BYTES + r * 128;
-        uint8_t* tl = st + 4 * KV_BYTES + r * 128;
+        mbar_wait(v_full0 + 8 * s, ph);
+        mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-2} has retired
+        const float* vr = reinterpret_cast<const float*>(smem_al + OFF_VR + s * KV_BYTES);
+#pragma unroll 1
+        for (int dd = 0; dd < DK / (N_XF_WARPS * 32); ++dd) {
+          const int d = tt + dd * (N_XF_WARPS * 32);  // head dim = V^T row
+          const float* vraw = vr + (d >> 5) * (CH_BYTES / 4) + (d & 31);
+          uint8_t* th = smem_al + OFF_VT + s * 2 * KV_BYTES + d * 128;
+          uint8_t* tl = th + KV_BYTES;
+          const int swd = d & 7;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {  // keys 4u .. 4u+3
-          const float x0 = vraw[(4 * u + 0) * 32], x1 = vraw[(4 * u + 1) * 32];
-          const float x2 = vraw[(4 * u + 2) * 32], x3 = vraw[(4 * u + 3) * 32];
-          const float4 hv = make_float4(tf32_rn(x0), tf32_rn(x1), tf32_rn(x2), tf32_rn(x3));
-          const int pu = (u ^ sw) << 4;
-          *reinterpret_cast<float4*>(th + pu) = hv;
-          *reinterpret_cast<float4*>(tl + pu) =
-              make_float4(tf32_rn(x0 - hv.x), tf32_rn(x1 - hv.y), tf32_rn(x2 - hv.z), tf32_rn(x3 - hv.w));
+          for (int u = 0; u < 8; ++u) {  // keys 4u .. 4u+3
+            const float x0 = vraw[(4 * u + 0) * 32], x1 = vraw[(4 * u + 1) * 32];
+            const float x2 = vraw[(4 * u + 2) * 32], x3 = vraw[(4 * u + 3) * 32];
+            const float4 hv = make_float4(tf32_rn(x0), tf32_rn(x1), tf32_rn(x2), tf32_rn(x3));
+            const int pu = (u ^ swd) << 4;
+            *reinterpret_cast<float4*>(th + pu) = hv;
+            *reinterpret_cast<float4*>(tl + pu) =
+                make_float4(tf32_rn(x0 - hv.x), tf32_rn(x1 - hv.y), tf32_rn(x2 - hv.z), tf32_rn(x3 - hv.w));
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(vr_empty0 + 8 * s);
+          mbar_arrive(vt_full0 + 8 * s);
         }
       }
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(kv_xf0 + 8 * s);
     }
   }
 
