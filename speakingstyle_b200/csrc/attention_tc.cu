@@ -3,20 +3,22 @@
 // accumulation in TMEM; softmax statistics, probabilities and the output accumulator are fp32.
 //
 // One CTA = 128 queries of one head of one utterance; keys/values stream through in 64-key tiles up to
-// the utterance's valid length.  Roles (320 threads):
-//   warp 0      TMA: Q once, then K_j / V_j tiles into a 2-stage ring (rows outside [0,S) zero-filled)
+// the utterance's valid length.  Roles (384 threads = three warps per scheduler, 168 registers each):
+//   warp 0      TMA: Q once, then V_j / K_j tiles into two-deep rings (rows outside [0,S) zero-filled)
 //   warp 1      one thread issues  S_j = Q.K_j^T  (12 MMAs, N = 64) and  O_j = P_j.V_j  (24 MMAs, N = 32);
-//               S_{j+1} is issued before O_j so it overlaps the softmax of tile j
-//   warps 2-5   softmax: thread = query row.  tcgen05.ld S_j -> scale by log2(e)/sqrt(dk) -> mask keys >= len
-//               -> online max/sum in the base-2 domain -> P_j = 2^(t - m) (MUFU.EX2), split into TF32
-//               hi/lo and written straight into the 128-byte-swizzled K-major layout the MMA reads;
-//               then  o = o*alpha_j + O_j  in registers once O_j lands (fp32 round-to-nearest adds, so the
-//               truncating TMEM accumulation never runs longer than one tile)
-//   warps 6-9   split Q, K_j, V_j into TF32 hi/lo in shared memory (element-wise, layout-agnostic)
+//               S_{j+1} is issued before O_j so it overlaps the softmax of tile j.  The kernel is bound by
+//               this thread's issue rate (36 small MMAs per tile), hence the one-add descriptor forms.
+//   warps 2-9   softmax: thread = query row, warps w and w+4 share the rows.  Both read the whole S_j row
+//               (same running max, base-2 domain); each exponentiates its own 32 keys (MUFU.EX2), splits
+//               them into TF32 hi/lo straight into the 128-byte-swizzled K-major P chunk the MMA reads,
+//               keeps a partial row sum, and folds its 16 columns of O_{j-1} in registers
+//               (o = o*alpha + O, fp32 round-to-nearest, so the truncating TMEM accumulation never runs
+//               longer than one tile).  The fold comes AFTER P_j is handed over, off the critical path.
+//   warps 10-11 split Q, K_j into TF32 hi/lo in shared memory and transpose V_j while splitting it:
 // V arrives [keys x 32] (head dims contiguous) but the MMA wants its B operand K-major, i.e. V^T with the
-// keys contiguous: the split warps transpose the 8 KB tile while they split it (conflict-free: a lane
-// reads one head dim of four consecutive keys and writes one 16-byte unit of the swizzled V^T row).
-// The [S x S] score matrix never leaves the SM.
+// keys contiguous (conflict-free: a lane reads one head dim of four consecutive keys and writes one
+// 16-byte unit of the swizzled V^T row).  Rings: K hi/lo freed by S_j, V as loaded freed by the transpose,
+// V^T hi/lo freed by P.V_j.  The [S x S] score matrix never leaves the SM.
 #include "tc_common.cuh"
 
 namespace {
@@ -26,14 +28,20 @@ using namespace sstc;
 constexpr int DK = 32;            // head size = one 128-byte row of fp32
 constexpr int BQ = 128;           // queries per CTA = TMEM lanes
 constexpr int BKV = 64;           // keys per tile
-constexpr int NTHREADS = 320;
+constexpr int N_SOFTMAX_WARPS = 8, N_XF_WARPS = 2, XF_THREADS = N_XF_WARPS * 32;
+constexpr int NTHREADS = 32 * (2 + N_SOFTMAX_WARPS + N_XF_WARPS);
 constexpr int Q_BYTES = BQ * 128;      // 16 KB
 constexpr int KV_BYTES = BKV * 128;    // 8 KB
-constexpr int STAGE_BYTES = 5 * KV_BYTES;  // K_hi, K_lo, V (as loaded, unswizzled), V^T_hi, V^T_lo
-constexpr int P_BYTES = 2 * Q_BYTES;   // 2 chunks of 32 keys x 128 rows
-constexpr int SMEM_DATA = 2 * Q_BYTES + 2 * STAGE_BYTES + 2 * P_BYTES;  // 32 + 80 + 64 KB
-constexpr int N_BARS = 2 + 6 + 4 + 2 + 4;
+constexpr int OFF_QH = 0, OFF_QL = Q_BYTES;
+constexpr int OFF_K = 2 * Q_BYTES;              // [2][K_hi 8 | K_lo 8]
+constexpr int OFF_VR = OFF_K + 4 * KV_BYTES;    // [2][V as loaded (unswizzled) 8]
+constexpr int OFF_VT = OFF_VR + 2 * KV_BYTES;   // [2][V^T_hi 8 | V^T_lo 8]
+constexpr int OFF_PH = OFF_VT + 4 * KV_BYTES;   // P_hi: 2 chunks of 32 keys x 128 rows
+constexpr int OFF_PL = OFF_PH + 2 * Q_BYTES;
+constexpr int SMEM_DATA = OFF_PL + 2 * Q_BYTES;  // 32 + 80 + 64 KB
+constexpr int N_BARS = 28;
 constexpr int SMEM_BYTES = SMEM_DATA + N_BARS * 8 + 16 + 1024;
+constexpr int COL_S = 0, COL_O = 2 * BKV;
 constexpr int TMEM_COLS = 256;  // S0,S1: 2 x 64; O0,O1: 2 x 32
 
 __device__ __forceinline__ float tf32_rn(float x) {
@@ -41,12 +49,26 @@ __device__ __forceinline__ float tf32_rn(float x) {
 }
 
 __device__ __forceinline__ void split_tile(float4* hi, float4* lo, int n_vec, int tt) {
-  for (int idx = tt; idx < n_vec; idx += 128) {
+#pragma unroll 4
+  for (int idx = tt; idx < n_vec; idx += XF_THREADS) {
     const float4 x = hi[idx];
     const float4 h = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
     hi[idx] = h;
     lo[idx] = make_float4(tf32_rn(x.x - h.x), tf32_rn(x.y - h.y), tf32_rn(x.z - h.z), tf32_rn(x.w - h.w));
   }
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -69,14 +91,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
-  constexpr int OFF_QH = 0, OFF_QL = Q_BYTES, OFF_ST = 2 * Q_BYTES, OFF_PH = OFF_ST + 2 * STAGE_BYTES,
-                OFF_PL = OFF_PH + P_BYTES;
   const uint32_t bars = smem0 + SMEM_DATA;
-  const uint32_t q_full = bars, q_xf = bars + 8;
-  const uint32_t kv_full0 = bars + 16, kv_xf0 = bars + 32, kv_empty0 = bars + 48;
-  const uint32_t s_full0 = bars + 64, s_empty0 = bars + 80;
-  const uint32_t p_full = bars + 96, p_empty = bars + 104;
-  const uint32_t o_full0 = bars + 112, o_empty0 = bars + 128;
+  // two-deep rings: index with + 8 * slot
+  const uint32_t k_full0 = bars + 0, k_xf0 = bars + 16, k_empty0 = bars + 32;
+  const uint32_t v_full0 = bars + 48, vr_empty0 = bars + 64, vt_full0 = bars + 80, vt_empty0 = bars + 96;
+  const uint32_t s_full0 = bars + 112, s_empty0 = bars + 128, o_full0 = bars + 144, o_empty0 = bars + 160;
+  const uint32_t p_full = bars + 176, p_empty = bars + 184, q_full = bars + 192, q_xf = bars + 200;
   const uint32_t tslot = bars + N_BARS * 8;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + SMEM_DATA + N_BARS * 8);
 
@@ -86,19 +106,23 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     prefetch_tmap(&tmQ);
     prefetch_tmap(&tmKV);
     prefetch_tmap(&tmV);
-    mbar_init(q_full, 1);
-    mbar_init(q_xf, 4);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(kv_full0 + 8 * s, 1);
-      mbar_init(kv_xf0 + 8 * s, 4);
-      mbar_init(kv_empty0 + 8 * s, 1);
+      mbar_init(k_full0 + 8 * s, 1);
+      mbar_init(k_xf0 + 8 * s, N_XF_WARPS);
+      mbar_init(k_empty0 + 8 * s, 1);
+      mbar_init(v_full0 + 8 * s, 1);
+      mbar_init(vr_empty0 + 8 * s, N_XF_WARPS);
+      mbar_init(vt_full0 + 8 * s, N_XF_WARPS);
+      mbar_init(vt_empty0 + 8 * s, 1);
       mbar_init(s_full0 + 8 * s, 1);
-      mbar_init(s_empty0 + 8 * s, 4);
+      mbar_init(s_empty0 + 8 * s, N_SOFTMAX_WARPS);
       mbar_init(o_full0 + 8 * s, 1);
-      mbar_init(o_empty0 + 8 * s, 4);
+      mbar_init(o_empty0 + 8 * s, N_SOFTMAX_WARPS);
     }
-    mbar_init(p_full, 4);
+    mbar_init(p_full, N_SOFTMAX_WARPS);
     mbar_init(p_empty, 1);
+    mbar_init(q_full, 1);
+    mbar_init(q_xf, N_XF_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tslot, TMEM_COLS);
@@ -114,11 +138,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tma_load_3d(smem0 + OFF_QH, &tmQ, q_full, h * DK, q0, b);
       for (int j = 0; j < NT; ++j) {
         const int s = j & 1;
-        mbar_wait(kv_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
-        mbar_expect_tx(kv_full0 + 8 * s, 2 * KV_BYTES);
-        const uint32_t st = smem0 + OFF_ST + s * STAGE_BYTES;
-        tma_load_3d(st, &tmKV, kv_full0 + 8 * s, D + h * DK, j * BKV, b);                    // K_j -> K_hi slot
-        tma_load_3d(st + 2 * KV_BYTES, &tmV, kv_full0 + 8 * s, 2 * D + h * DK, j * BKV, b);   // V_j, unswizzled
+        const uint32_t ph = ((j >> 1) & 1) ^ 1;
+        mbar_wait(vr_empty0 + 8 * s, ph);
+        mbar_expect_tx(v_full0 + 8 * s, KV_BYTES);
+        tma_load_3d(smem0 + OFF_VR + s * KV_BYTES, &tmV, v_full0 + 8 * s, 2 * D + h * DK, j * BKV, b);  // V_j, unswizzled
+        mbar_wait(k_empty0 + 8 * s, ph);
+        mbar_expect_tx(k_full0 + 8 * s, KV_BYTES);
+        tma_load_3d(smem0 + OFF_K + s * 2 * KV_BYTES, &tmKV, k_full0 + 8 * s, D + h * DK, j * BKV, b);  // K_j -> K_hi slot
       }
     }
   } else if (warp == 1) {
@@ -126,150 +152,155 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (lane == 0) {
       const uint32_t idesc_s = make_idesc(2u, BKV);               // tf32, N = 64, A and B K-major
       const uint32_t idesc_o = make_idesc(2u, DK);                // tf32, N = 32, B = V^T K-major
-      const uint32_t qh = smem0 + OFF_QH, ql = smem0 + OFF_QL;
+      const uint32_t qh = desc_lo(smem0 + OFF_QH), ql = desc_lo(smem0 + OFF_QL);
+      const uint32_t ph = desc_lo(smem0 + OFF_PH), pl = desc_lo(smem0 + OFF_PL);
       auto issue_s = [&](int j) {
         const int s = j & 1;
-        mbar_wait(kv_xf0 + 8 * s, (j >> 1) & 1);
+        mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
         mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t kh = smem0 + OFF_ST + s * STAGE_BYTES, kl = kh + KV_BYTES;
-        const uint32_t d = tmem_base + s * BKV;
+        const uint32_t kh = desc_lo(smem0 + OFF_K + s * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
+        const uint32_t d = tmem_base + COL_S + s * BKV;
 #pragma unroll
-        for (int kk = 0; kk < DK / 8; ++kk) {
-          const uint32_t o = kk * 32;
-          umma_tf32(d, make_desc(ql + o), make_desc(kh + o), idesc_s, kk != 0);
-          umma_tf32(d, make_desc(qh + o), make_desc(kl + o), idesc_s, 1u);
-          umma_tf32(d, make_desc(qh + o), make_desc(kh + o), idesc_s, 1u);
+        for (int kk = 0; kk < DK / 8; ++kk) {  // 8 head dims = 32 bytes of each operand row per instruction
+          const uint32_t o = kk * 2;
+          umma_tf32_w(d, ql + o, kh + o, idesc_s, kk != 0);
+          umma_tf32_w(d, qh + o, kl + o, idesc_s, 1u);
+          umma_tf32_w(d, qh + o, kh + o, idesc_s, 1u);
         }
         umma_commit(s_full0 + 8 * s);
+        umma_commit(k_empty0 + 8 * s);
       };
       mbar_wait(q_xf, 0);
       issue_s(0);
       for (int j = 0; j < NT; ++j) {
         if (j + 1 < NT) issue_s(j + 1);
         const int s = j & 1;
+        mbar_wait(vt_full0 + 8 * s, (j >> 1) & 1);
         mbar_wait(p_full, j & 1);
         mbar_wait(o_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t vh = smem0 + OFF_ST + s * STAGE_BYTES + 3 * KV_BYTES, vl = vh + KV_BYTES;  // V^T hi / lo
-        const uint32_t d = tmem_base + 2 * BKV + s * DK;
+        const uint32_t vh = desc_lo(smem0 + OFF_VT + s * 2 * KV_BYTES), vl = vh + (KV_BYTES >> 4);  // V^T hi / lo
+        const uint32_t d = tmem_base + COL_O + s * DK;
 #pragma unroll
         for (int ks = 0; ks < BKV / 8; ++ks) {  // 8 keys per instruction
-          const uint32_t pa = (ks >> 2) * Q_BYTES + (ks & 3) * 32;  // chunk of 32 keys, then 32 bytes per step
-          const uint32_t vb = (ks >> 2) * (DK * 128) + (ks & 3) * 32;  // V^T: 32 rows x 128 B per 32-key chunk
-          umma_tf32(d, make_desc(smem0 + OFF_PL + pa), make_desc(vh + vb), idesc_o, ks != 0);
-          umma_tf32(d, make_desc(smem0 + OFF_PH + pa), make_desc(vl + vb), idesc_o, 1u);
-          umma_tf32(d, make_desc(smem0 + OFF_PH + pa), make_desc(vh + vb), idesc_o, 1u);
+          const uint32_t pa = ((ks >> 2) * Q_BYTES + (ks & 3) * 32) >> 4;     // chunk of 32 keys, then 32 bytes per step
+          const uint32_t vb = ((ks >> 2) * (DK * 128) + (ks & 3) * 32) >> 4;  // V^T: 32 rows x 128 B per 32-key chunk
+          umma_tf32_w(d, pl + pa, vh + vb, idesc_o, ks != 0);
+          umma_tf32_w(d, ph + pa, vl + vb, idesc_o, 1u);
+          umma_tf32_w(d, ph + pa, vh + vb, idesc_o, 1u);
         }
         umma_commit(o_full0 + 8 * s);
         umma_commit(p_empty);
-        umma_commit(kv_empty0 + 8 * s);
+        umma_commit(vt_empty0 + 8 * s);
       }
     }
-  } else if (warp < 6) {
-    // ================= softmax + output accumulation (thread = query row) =================
+  } else if (warp < 2 + N_SOFTMAX_WARPS) {
+    // ================= softmax + output accumulation =================
+    // thread = query row (lane group = warp % 4); half = which 32 keys of the tile / 16 columns of O it owns
     const int lg = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int r = lg * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
-    float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
+    float m = -INFINITY, l = 0.f, alpha_fold = 1.f;
     const float scale_log2 = 1.4426950408889634f / temperature;
-    float o[DK];
+    float o[DK / 2];
 #pragma unroll
-    for (int i = 0; i < DK; ++i) o[i] = 0.f;
-    uint8_t* ph_row = smem_al + OFF_PH + r * 128;
-    uint8_t* pl_row = smem_al + OFF_PL + r * 128;
+    for (int i = 0; i < DK / 2; ++i) o[i] = 0.f;
+    uint8_t* ph_row = smem_al + OFF_PH + half * Q_BYTES + r * 128;  // this half's 32-key chunk of P
+    uint8_t* pl_row = smem_al + OFF_PL + half * Q_BYTES + r * 128;
     const int sw = r & 7;
+
+    auto fold_o = [&](int jj, float alpha) {  // o = o*alpha + O_jj (this half's 16 columns)
+      const int ob = jj & 1;
+      mbar_wait(o_full0 + 8 * ob, (jj >> 1) & 1);
+      tc_fence_after();
+      float v[16];
+      tmem_ld16(lane_base + COL_O + ob * DK + half * 16, v);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_empty0 + 8 * ob);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o[i] = fmaf(o[i], alpha, v[i]);
+    };
 
     for (int j = 0; j < NT; ++j) {
       const int sb = j & 1;
-      if (j > 0) {  // fold in O_{j-1} (its P.V ran while we were busy with S_j's predecessor)
-        const int ob = (j - 1) & 1;
-        mbar_wait(o_full0 + 8 * ob, ((j - 1) >> 1) & 1);
-        tc_fence_after();
-        float v[32];
-        tmem_ld32(lane_base + 2 * BKV + ob * DK, v);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(o_empty0 + 8 * ob);
-#pragma unroll
-        for (int i = 0; i < DK; ++i) o[i] = fmaf(o[i], alpha_prev, v[i]);
-      }
       mbar_wait(s_full0 + 8 * sb, (j >> 1) & 1);
       tc_fence_after();
-      float s0[32], s1[32];
-      tmem_ld32(lane_base + sb * BKV, s0);
-      tmem_ld32(lane_base + sb * BKV + 32, s1);
+      float sa[32], sc[32];  // sa = this half's 32 keys, sc = the other half's (needed for the row max only)
+      tmem_ld32(lane_base + COL_S + sb * BKV + half * 32, sa);
+      tmem_ld32(lane_base + COL_S + sb * BKV + (half ^ 1) * 32, sc);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(s_empty0 + 8 * sb);
 
       // softmax in the base-2 domain: t = s * log2(e)/sqrt(dk); p = 2^(t - m).  One FMUL and one MUFU.EX2 per
-      // score (the four softmax warps are the busiest part of this kernel; libm expf and a true division
-      // cost ~10x more issue slots).  Relative error of p <= ~3e-7, far inside the kernel's 1e-6 class.
+      // score; relative error of p <= ~3e-7, far inside the kernel's 1e-6 class.
       const int kbase = j * BKV;
       float mx = -INFINITY;
+      if (kbase + BKV <= len) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        s0[i] = (kbase + i < len) ? s0[i] * scale_log2 : -INFINITY;
-        s1[i] = (kbase + 32 + i < len) ? s1[i] * scale_log2 : -INFINITY;
-        mx = fmaxf(mx, fmaxf(s0[i], s1[i]));
+        for (int i = 0; i < 32; ++i) {
+          sa[i] *= scale_log2;
+          mx = fmaxf(mx, fmaxf(sa[i], sc[i] * scale_log2));
+        }
+      } else {
+        const int ka = kbase + half * 32, kc = kbase + (half ^ 1) * 32;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          sa[i] = (ka + i < len) ? sa[i] * scale_log2 : -INFINITY;
+          const float c = (kc + i < len) ? sc[i] * scale_log2 : -INFINITY;
+          mx = fmaxf(mx, fmaxf(sa[i], c));
+        }
       }
       const float m_new = fmaxf(m, mx);  // finite: every tile holds at least one valid key
       const float alpha = exp2f(m - m_new);
+      m = m_new;
       float sum = 0.f;
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        s0[i] = exp2f(s0[i] - m_new);
-        s1[i] = exp2f(s1[i] - m_new);
-        sum += s0[i] + s1[i];
+        sa[i] = exp2f(sa[i] - m_new);
+        sum += sa[i];
       }
       l = l * alpha + sum;
-      m = m_new;
-      alpha_prev = alpha;
 
       mbar_wait(p_empty, (j & 1) ^ 1);  // P.V of the previous tile has finished reading P
 #pragma unroll
       for (int u = 0; u < 8; ++u) {  // 16-byte unit u of this row lives at unit (u ^ (row & 7)) - SWIZZLE_128B
         const int pu = (u ^ sw) * 16;
-        const float4 a = make_float4(s0[4 * u], s0[4 * u + 1], s0[4 * u + 2], s0[4 * u + 3]);
-        const float4 c = make_float4(s1[4 * u], s1[4 * u + 1], s1[4 * u + 2], s1[4 * u + 3]);
+        const float4 a = make_float4(sa[4 * u], sa[4 * u + 1], sa[4 * u + 2], sa[4 * u + 3]);
         const float4 ah = make_float4(tf32_rn(a.x), tf32_rn(a.y), tf32_rn(a.z), tf32_rn(a.w));
-        const float4 ch = make_float4(tf32_rn(c.x), tf32_rn(c.y), tf32_rn(c.z), tf32_rn(c.w));
         *reinterpret_cast<float4*>(ph_row + pu) = ah;
-        *reinterpret_cast<float4*>(ph_row + Q_BYTES + pu) = ch;
         *reinterpret_cast<float4*>(pl_row + pu) =
             make_float4(tf32_rn(a.x - ah.x), tf32_rn(a.y - ah.y), tf32_rn(a.z - ah.z), tf32_rn(a.w - ah.w));
-        *reinterpret_cast<float4*>(pl_row + Q_BYTES + pu) =
-            make_float4(tf32_rn(c.x - ch.x), tf32_rn(c.y - ch.y), tf32_rn(c.z - ch.z), tf32_rn(c.w - ch.w));
       }
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
+
+      if (j > 0) fold_o(j - 1, alpha_fold);  // O_{j-1} landed together with p_empty
+      alpha_fold = alpha;
     }
-    {  // last tile's O
-      const int ob = (NT - 1) & 1;
-      mbar_wait(o_full0 + 8 * ob, ((NT - 1) >> 1) & 1);
-      tc_fence_after();
-      float v[32];
-      tmem_ld32(lane_base + 2 * BKV + ob * DK, v);
-#pragma unroll
-      for (int i = 0; i < DK; ++i) o[i] = fmaf(o[i], alpha_prev, v[i]);
-    }
+    fold_o(NT - 1, alpha_fold);
+
+    // merge the two halves' row sums through shared memory (all MMAs have retired: P is free)
+    float* lbuf = reinterpret_cast<float*>(smem_al + OFF_PH);
+    lbuf[half * BQ + r] = l;
+    asm volatile("bar.sync 1, %0;" ::"n"(N_SOFTMAX_WARPS * 32) : "memory");
+    l += lbuf[(half ^ 1) * BQ + r];
     const int q = q0 + r;
     if (q < S) {
       const float inv = q < len ? 1.0f / l : 0.f;  // padded query rows are written as zeros
-      float4* orow = reinterpret_cast<float4*>(out + (int64_t)q * D);
+      float4* orow = reinterpret_cast<float4*>(out + (int64_t)q * D + half * 16);
 #pragma unroll
-      for (int c = 0; c < DK / 4; ++c)
+      for (int c = 0; c < DK / 8; ++c)
         orow[c] = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
-#ifdef ATT_DEBUG
-      orow[0] = make_float4(l, m, o[0], o[1]);
-      orow[1] = make_float4(inv, alpha_prev, (float)NT, (float)len);
-#endif
     }
   } else {
-    // ================= operand split (warps 6..9) =================
-    const int tt = (warp - 6) * 32 + lane;
+    // ================= operand split / transpose (2 warps) =================
+    const int w = warp - 2 - N_SOFTMAX_WARPS;
+    const int tt = w * 32 + lane;
     mbar_wait(q_full, 0);
     split_tile(reinterpret_cast<float4*>(smem_al + OFF_QH), reinterpret_cast<float4*>(smem_al + OFF_QL), Q_BYTES / 16, tt);
     fence_proxy_async();
@@ -277,27 +308,38 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (lane == 0) mbar_arrive(q_xf);
     for (int j = 0; j < NT; ++j) {
       const int s = j & 1;
-      mbar_wait(kv_full0 + 8 * s, (j >> 1) & 1);
-      uint8_t* st = smem_al + OFF_ST + s * STAGE_BYTES;
-      split_tile(reinterpret_cast<float4*>(st), reinterpret_cast<float4*>(st + KV_BYTES), KV_BYTES / 16, tt);
+      const uint32_t ph = (j >> 1) & 1;
+      mbar_wait(k_full0 + 8 * s, ph);
+      split_tile(reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES),
+                 reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES), KV_BYTES / 16, tt);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(k_xf0 + 8 * s);
+
+      mbar_wait(v_full0 + 8 * s, ph);
+      mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-2} has retired
       {  // V [64 keys x 32 dims] -> V^T hi / lo [32 dims x 64 keys], K-major, 128-byte swizzle
-        const float* vraw = reinterpret_cast<const float*>(st + 2 * KV_BYTES);
-        const int d = lane, w = warp - 6;
+        const float* vraw = reinterpret_cast<const float*>(smem_al + OFF_VR + s * KV_BYTES);
+        uint8_t* vt = smem_al + OFF_VT + s * 2 * KV_BYTES;
+        const int d = lane;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int kq = w + 4 * i;  // quad of keys 4*kq .. 4*kq+3
+        for (int i = 0; i < 16 / N_XF_WARPS; ++i) {
+          const int kq = w + N_XF_WARPS * i;  // quad of keys 4*kq .. 4*kq+3
           const float x0 = vraw[(4 * kq + 0) * DK + d], x1 = vraw[(4 * kq + 1) * DK + d];
           const float x2 = vraw[(4 * kq + 2) * DK + d], x3 = vraw[(4 * kq + 3) * DK + d];
           const float4 hv = make_float4(tf32_rn(x0), tf32_rn(x1), tf32_rn(x2), tf32_rn(x3));
           const int off = (kq >> 3) * (DK * 128) + d * 128 + (((kq & 7) ^ (d & 7)) << 4);
-          *reinterpret_cast<float4*>(st + 3 * KV_BYTES + off) = hv;
-          *reinterpret_cast<float4*>(st + 4 * KV_BYTES + off) =
+          *reinterpret_cast<float4*>(vt + off) = hv;
+          *reinterpret_cast<float4*>(vt + KV_BYTES + off) =
               make_float4(tf32_rn(x0 - hv.x), tf32_rn(x1 - hv.y), tf32_rn(x2 - hv.z), tf32_rn(x3 - hv.w));
         }
       }
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive(kv_xf0 + 8 * s);
+      if (lane == 0) {
+        mbar_arrive(vr_empty0 + 8 * s);
+        mbar_arrive(vt_full0 + 8 * s);
+      }
     }
   }
 

@@ -166,14 +166,14 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
         mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t kh = smem0 + OFF_K + s * 2 * KV_BYTES, kl = kh + KV_BYTES;
+        const uint32_t kh = desc_lo(smem0 + OFF_K + s * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
         const uint32_t d = tmem_base + COL_S + s * BKV;
 #pragma unroll
         for (int ks = 0; ks < DK / 8; ++ks) {  // 16 steps of 8 head dims
-          const uint32_t ko = (ks >> 2) * CH_BYTES + (ks & 3) * 32;
-          umma_tf32_ts(d, ql + ks * 8, make_desc(kh + ko), idesc_s, ks != 0);
-          umma_tf32_ts(d, qh + ks * 8, make_desc(kl + ko), idesc_s, 1u);
-          umma_tf32_ts(d, qh + ks * 8, make_desc(kh + ko), idesc_s, 1u);
+          const uint32_t ko = ((ks >> 2) * CH_BYTES + (ks & 3) * 32) >> 4;
+          umma_tf32_ts_w(d, ql + ks * 8, kh + ko, idesc_s, ks != 0);
+          umma_tf32_ts_w(d, qh + ks * 8, kl + ko, idesc_s, 1u);
+          umma_tf32_ts_w(d, qh + ks * 8, kh + ko, idesc_s, 1u);
         }
         umma_commit(s_full0 + 8 * s);
         umma_commit(k_empty0 + 8 * s);
@@ -188,15 +188,15 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         mbar_wait(p_full0 + 8 * s, (j >> 1) & 1);
         mbar_wait(o_empty, (j & 1) ^ 1);
         tc_fence_after();
-        const uint32_t vh = smem0 + OFF_VT + s * 2 * KV_BYTES, vl = vh + KV_BYTES;  // V^T hi / lo [128 x 32]
-        const uint32_t ph = smem0 + OFF_P + s * 2 * P_BYTES, pl = ph + P_BYTES;
+        const uint32_t vh = desc_lo(smem0 + OFF_VT + s * 2 * KV_BYTES), vl = vh + (KV_BYTES >> 4);  // V^T hi / lo
+        const uint32_t ph = desc_lo(smem0 + OFF_P + s * 2 * P_BYTES), pl = ph + (P_BYTES >> 4);
         const uint32_t d = tmem_base + COL_O;
 #pragma unroll
-        for (int kk = 0; kk < BKV / 8; ++kk) {  // 4 steps of 8 keys
-          const uint32_t o = kk * 32;
-          umma_tf32(d, make_desc(pl + o), make_desc(vh + o), idesc_o, kk != 0);
-          umma_tf32(d, make_desc(ph + o), make_desc(vl + o), idesc_o, 1u);
-          umma_tf32(d, make_desc(ph + o), make_desc(vh + o), idesc_o, 1u);
+        for (int kk = 0; kk < BKV / 8; ++kk) {  // 4 steps of 8 keys (32 bytes of each operand row)
+          const uint32_t o = kk * 2;
+          umma_tf32_w(d, pl + o, vh + o, idesc_o, kk != 0);
+          umma_tf32_w(d, ph + o, vl + o, idesc_o, 1u);
+          umma_tf32_w(d, ph + o, vh + o, idesc_o, 1u);
         }
         umma_commit(o_full);
         umma_commit(vt_empty0 + 8 * s);

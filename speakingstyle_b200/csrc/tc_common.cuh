@@ -110,6 +110,40 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t
       "l"(da), "l"(db), "r"(idesc), "r"(accum)
       : "memory");
 }
+// Low-word forms for issue-bound kernels (many small MMAs from one thread): the descriptor's high word is
+// the constant 0x40004040 (SBO = 64, version 1, SWIZZLE_128B) and the low word is start>>4 | 1<<16, so an
+// operand that sits `off` bytes further on is just  lo + (off >> 4)  - one add instead of the shift / mask /
+// or chain per MMA that make_desc() costs on the (serial, high-latency) uniform datapath.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16); }
+__device__ __forceinline__ void umma_tf32_w(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b32 hi;\n\t"
+      ".reg .b64 da, db;\n\t"
+      "mov.u32 hi, 0x40004040;\n\t"
+      "mov.b64 da, {%1, hi};\n\t"
+      "mov.b64 db, {%2, hi};\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b32 hi;\n\t"
+      ".reg .b64 db;\n\t"
+      "mov.u32 hi, 0x40004040;\n\t"
+      "mov.b64 db, {%2, hi};\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], db, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "r"(tmem_a), "r"(b_lo), "r"(idesc), "r"(accum)
+      : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
