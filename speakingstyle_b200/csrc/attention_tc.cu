@@ -48,13 +48,21 @@ __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
 
+// n_vec is a multiple of 8 * XF_THREADS.  All loads of a batch come first: with the in-place stores in between,
+// every load would otherwise be serialised behind the previous store (aliasing) on a warp with no ILP to spare.
 __device__ __forceinline__ void split_tile(float4* hi, float4* lo, int n_vec, int tt) {
-#pragma unroll 4
-  for (int idx = tt; idx < n_vec; idx += XF_THREADS) {
-    const float4 x = hi[idx];
-    const float4 h = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
-    hi[idx] = h;
-    lo[idx] = make_float4(tf32_rn(x.x - h.x), tf32_rn(x.y - h.y), tf32_rn(x.z - h.z), tf32_rn(x.w - h.w));
+#pragma unroll 1
+  for (int base = tt; base < n_vec; base += 8 * XF_THREADS) {
+    float4 x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = hi[base + i * XF_THREADS];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 h = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
+      hi[base + i * XF_THREADS] = h;
+      lo[base + i * XF_THREADS] =
+          make_float4(tf32_rn(x[i].x - h.x), tf32_rn(x[i].y - h.y), tf32_rn(x[i].z - h.z), tf32_rn(x[i].w - h.w));
+    }
   }
 }
 
@@ -133,7 +141,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   if (warp == 0) {
     // ================= TMA producer =================
-    if (lane == 0) {
+    if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
       mbar_expect_tx(q_full, Q_BYTES);
       tma_load_3d(smem0 + OFF_QH, &tmQ, q_full, h * DK, q0, b);
       for (int j = 0; j < NT; ++j) {
@@ -149,7 +157,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
       const uint32_t idesc_s = make_idesc(2u, BKV);               // tf32, N = 64, A and B K-major
       const uint32_t idesc_o = make_idesc(2u, DK);                // tf32, N = 32, B = V^T K-major
       const uint32_t qh = desc_lo(smem0 + OFF_QH), ql = desc_lo(smem0 + OFF_QL);
@@ -238,12 +246,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       // softmax in the base-2 domain: t = s * log2(e)/sqrt(dk); p = 2^(t - m).  One FMUL and one MUFU.EX2 per
       // score; relative error of p <= ~3e-7, far inside the kernel's 1e-6 class.
       const int kbase = j * BKV;
-      float mx = -INFINITY;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the warp has little else to overlap
       if (kbase + BKV <= len) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           sa[i] *= scale_log2;
-          mx = fmaxf(mx, fmaxf(sa[i], sc[i] * scale_log2));
+          mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(sa[i], sc[i] * scale_log2));
         }
       } else {
         const int ka = kbase + half * 32, kc = kbase + (half ^ 1) * 32;
@@ -251,19 +259,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int i = 0; i < 32; ++i) {
           sa[i] = (ka + i < len) ? sa[i] * scale_log2 : -INFINITY;
           const float c = (kc + i < len) ? sc[i] * scale_log2 : -INFINITY;
-          mx = fmaxf(mx, fmaxf(sa[i], c));
+          mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(sa[i], c));
         }
       }
-      const float m_new = fmaxf(m, mx);  // finite: every tile holds at least one valid key
-      const float alpha = exp2f(m - m_new);
+      const float m_new = fmaxf(fmaxf(m, mx4[0]), fmaxf(fmaxf(mx4[1], mx4[2]), mx4[3]));  // finite: >= 1 valid key per tile
+      const float alpha = ex2_approx(m - m_new);
       m = m_new;
-      float sum = 0.f;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        sa[i] = exp2f(sa[i] - m_new);
-        sum += sa[i];
+        sa[i] = ex2_approx(sa[i] - m_new);
+        sum4[i & 3] += sa[i];
       }
-      l = l * alpha + sum;
+      l = l * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
 
       mbar_wait(p_empty, (j & 1) ^ 1);  // P.V of the previous tile has finished reading P
 #pragma unroll
@@ -322,11 +330,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const float* vraw = reinterpret_cast<const float*>(smem_al + OFF_VR + s * KV_BYTES);
         uint8_t* vt = smem_al + OFF_VT + s * 2 * KV_BYTES;
         const int d = lane;
+        float xv[16 / N_XF_WARPS][4];
+#pragma unroll
+        for (int i = 0; i < 16 / N_XF_WARPS; ++i)  // all loads first (the stores below could alias them)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) xv[i][e] = vraw[(4 * (w + N_XF_WARPS * i) + e) * DK + d];
 #pragma unroll
         for (int i = 0; i < 16 / N_XF_WARPS; ++i) {
           const int kq = w + N_XF_WARPS * i;  // quad of keys 4*kq .. 4*kq+3
-          const float x0 = vraw[(4 * kq + 0) * DK + d], x1 = vraw[(4 * kq + 1) * DK + d];
-          const float x2 = vraw[(4 * kq + 2) * DK + d], x3 = vraw[(4 * kq + 3) * DK + d];
+          const float x0 = xv[i][0], x1 = xv[i][1], x2 = xv[i][2], x3 = xv[i][3];
           const float4 hv = make_float4(tf32_rn(x0), tf32_rn(x1), tf32_rn(x2), tf32_rn(x3));
           const int off = (kq >> 3) * (DK * 128) + d * 128 + (((kq & 7) ^ (d & 7)) << 4);
           *reinterpret_cast<float4*>(vt + off) = hv;

@@ -42,19 +42,19 @@ static_assert(COL_QL + DK <= TMEM_COLS, "TMEM budget");
 static_assert(NCH * BQ * 128 <= 4 * KV_BYTES, "Q staging must fit in the K ring");
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
+// Debug build (-DSS_ATT_TRACE, scripts/attn_trace.py): CTA (0,0,0) stamps clock64() at the pipeline hand-overs.
+#ifdef SS_ATT_TRACE
+__device__ long long g_att_trace[16 * 64];
+#define ATT_TRACE(ev, j)                                                                   \
+  do {                                                                                     \
+    if ((blockIdx.x | blockIdx.y | blockIdx.z) == 0 && (j) < 64) g_att_trace[(ev) * 64 + (j)] = clock64(); \
+  } while (0)
+#else
+#define ATT_TRACE(ev, j)
+#endif
+
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
-}
-
-__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "r"(tmem_a), "l"(db), "r"(idesc), "r"(accum)
-      : "memory");
 }
 
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
@@ -135,7 +135,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 
   if (warp == 0) {
     // ================= TMA producer =================
-    if (lane == 0) {
+    if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
       mbar_expect_tx(q_full, NCH * BQ * 128);
       for (int c = 0; c < NCH; ++c)  // Q staging [chunk][128 rows x 128 B] over the (still unused) K ring
         tma_load_3d(smem0 + OFF_K + c * (BQ * 128), &tmQ, q_full, h * DK + c * 32, q0, b);
@@ -143,12 +143,14 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const int s = j & 1;
         const uint32_t ph = ((j >> 1) & 1) ^ 1;
         mbar_wait(vr_empty0 + 8 * s, ph);
+        ATT_TRACE(0, j);
         mbar_expect_tx(v_full0 + 8 * s, KV_BYTES);
         for (int c = 0; c < NCH; ++c)
           tma_load_3d(smem0 + OFF_VR + s * KV_BYTES + c * CH_BYTES, &tmV, v_full0 + 8 * s, 2 * D + h * DK + c * 32,
                       j * BKV, b);
         if (j == 0) mbar_wait(q_tm, 0);  // Q now lives in TMEM: its staging area may be overwritten
         mbar_wait(k_empty0 + 8 * s, ph);
+        ATT_TRACE(1, j);
         mbar_expect_tx(k_full0 + 8 * s, KV_BYTES);
         for (int c = 0; c < NCH; ++c)
           tma_load_3d(smem0 + OFF_K + s * 2 * KV_BYTES + c * CH_BYTES, &tmK, k_full0 + 8 * s, D + h * DK + c * 32,
@@ -157,7 +159,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc_s = make_idesc(2u, BKV);  // N = 32 keys
       const uint32_t idesc_o = make_idesc(2u, DK);   // N = 128 head dims
       const uint32_t qh = tmem_base + COL_QH, ql = tmem_base + COL_QL;
@@ -166,6 +168,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
         mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
+        ATT_TRACE(6, j);
         const uint32_t kh = desc_lo(smem0 + OFF_K + s * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
         const uint32_t d = tmem_base + COL_S + s * BKV;
 #pragma unroll
@@ -177,6 +180,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         }
         umma_commit(s_full0 + 8 * s);
         umma_commit(k_empty0 + 8 * s);
+        ATT_TRACE(7, j);
       };
       mbar_wait(q_tm, 0);
       tc_fence_after();
@@ -188,6 +192,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         mbar_wait(p_full0 + 8 * s, (j >> 1) & 1);
         mbar_wait(o_empty, (j & 1) ^ 1);
         tc_fence_after();
+        ATT_TRACE(8, j);
         const uint32_t vh = desc_lo(smem0 + OFF_VT + s * 2 * KV_BYTES), vl = vh + (KV_BYTES >> 4);  // V^T hi / lo
         const uint32_t ph = desc_lo(smem0 + OFF_P + s * 2 * P_BYTES), pl = ph + (P_BYTES >> 4);
         const uint32_t d = tmem_base + COL_O;
@@ -200,6 +205,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         }
         umma_commit(o_full);
         umma_commit(vt_empty0 + 8 * s);
+        ATT_TRACE(9, j);
       }
     }
   } else if (warp < 2 + N_SOFTMAX_WARPS) {
@@ -242,6 +248,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     auto fold_o = [&](int jj, float alpha) {  // o = o*alpha + O_jj (this half's 64 columns)
       mbar_wait(o_full, jj & 1);
       tc_fence_after();
+      if (warp == 2 && lane == 0) ATT_TRACE(12, jj);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         float v[32];
@@ -252,12 +259,14 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(o_empty);
+      if (warp == 2 && lane == 0) ATT_TRACE(13, jj);
     };
 
     for (int j = 0; j < NT; ++j) {
       const int sb = j & 1;
       mbar_wait(s_full0 + 8 * sb, (j >> 1) & 1);
       tc_fence_after();
+      if (warp == 2 && lane == 0) ATT_TRACE(10, j);
       float s0[32];
       tmem_ld32(lane_base + COL_S + sb * BKV, s0);
       tc_fence_before();
@@ -265,45 +274,46 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       if (lane == 0) mbar_arrive(s_empty0 + 8 * sb);
 
       const int kbase = j * BKV;
-      float mx = -INFINITY;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the warp has little else to overlap
       if (kbase + BKV <= len) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           s0[i] *= scale_log2;
-          mx = fmaxf(mx, s0[i]);
+          mx4[i & 3] = fmaxf(mx4[i & 3], s0[i]);
         }
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           s0[i] = (kbase + i < len) ? s0[i] * scale_log2 : -INFINITY;
-          mx = fmaxf(mx, s0[i]);
+          mx4[i & 3] = fmaxf(mx4[i & 3], s0[i]);
         }
       }
-      const float m_new = fmaxf(m, mx);  // finite: every tile holds at least one valid key
-      const float alpha = exp2f(m - m_new);
+      const float m_new = fmaxf(fmaxf(m, mx4[0]), fmaxf(fmaxf(mx4[1], mx4[2]), mx4[3]));  // finite: >= 1 valid key per tile
+      const float alpha = ex2_approx(m - m_new);
       m = m_new;
       // this half's 16 keys: exponentiate, sum, write P hi / lo (units 4*half .. 4*half+3 of the swizzled row)
       uint8_t* ph_row = smem_al + OFF_P + sb * 2 * P_BYTES + r * 128;
       uint8_t* pl_row = ph_row + P_BYTES;
-      float sum = 0.f;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int uu = 0; uu < 4; ++uu) {
         const int u = 4 * half + uu;
         float4 a;  // the s0 index has to be a compile-time constant (registers): select on half
-        a.x = exp2f((half ? s0[16 + 4 * uu + 0] : s0[4 * uu + 0]) - m_new);
-        a.y = exp2f((half ? s0[16 + 4 * uu + 1] : s0[4 * uu + 1]) - m_new);
-        a.z = exp2f((half ? s0[16 + 4 * uu + 2] : s0[4 * uu + 2]) - m_new);
-        a.w = exp2f((half ? s0[16 + 4 * uu + 3] : s0[4 * uu + 3]) - m_new);
-        sum += (a.x + a.y) + (a.z + a.w);
+        a.x = ex2_approx((half ? s0[16 + 4 * uu + 0] : s0[4 * uu + 0]) - m_new);
+        a.y = ex2_approx((half ? s0[16 + 4 * uu + 1] : s0[4 * uu + 1]) - m_new);
+        a.z = ex2_approx((half ? s0[16 + 4 * uu + 2] : s0[4 * uu + 2]) - m_new);
+        a.w = ex2_approx((half ? s0[16 + 4 * uu + 3] : s0[4 * uu + 3]) - m_new);
+        sum4[uu] = (a.x + a.y) + (a.z + a.w);
         const int pu = (u ^ sw) * 16;
         const float4 ah = make_float4(tf32_rn(a.x), tf32_rn(a.y), tf32_rn(a.z), tf32_rn(a.w));
         *reinterpret_cast<float4*>(ph_row + pu) = ah;
         *reinterpret_cast<float4*>(pl_row + pu) =
             make_float4(tf32_rn(a.x - ah.x), tf32_rn(a.y - ah.y), tf32_rn(a.z - ah.z), tf32_rn(a.w - ah.w));
       }
-      l = l * alpha + sum;
+      l = l * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
       fence_proxy_async();
       __syncwarp();
+      if (warp == 2 && lane == 0) ATT_TRACE(11, j);
       if (lane == 0) mbar_arrive(p_full0 + 8 * sb);  // buffer sb was last read by P.V_{j-2}: retired before fold(j-2)
 
       if (j > 0) fold_o(j - 1, alpha_fold);
@@ -332,23 +342,33 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const uint32_t ph = (j >> 1) & 1;
       {  // K: element-wise split, hi in place, lo next to it
         mbar_wait(k_full0 + 8 * s, ph);
+        if (tt == 0) ATT_TRACE(2, j);
         float4* hi = reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES);
         float4* lo = reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES);
-#pragma unroll 4
-        for (int i = 0; i < KV_BYTES / 16 / (N_XF_WARPS * 32); ++i) {
-          const int idx = tt + i * (N_XF_WARPS * 32);
-          const float4 x = hi[idx];
-          const float4 hv = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
-          hi[idx] = hv;
-          lo[idx] = make_float4(tf32_rn(x.x - hv.x), tf32_rn(x.y - hv.y), tf32_rn(x.z - hv.z), tf32_rn(x.w - hv.w));
+        constexpr int NV = KV_BYTES / 16 / (N_XF_WARPS * 32);  // 16 vectors per thread, in batches of 8:
+#pragma unroll 1
+        for (int i0 = 0; i0 < NV; i0 += 8) {  // all loads of a batch first - in-place stores would otherwise
+          float4 x[8];                        // serialise every load behind the previous store (aliasing)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) x[i] = hi[tt + (i0 + i) * (N_XF_WARPS * 32)];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int idx = tt + (i0 + i) * (N_XF_WARPS * 32);
+            const float4 hv = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
+            hi[idx] = hv;
+            lo[idx] = make_float4(tf32_rn(x[i].x - hv.x), tf32_rn(x[i].y - hv.y), tf32_rn(x[i].z - hv.z),
+                                  tf32_rn(x[i].w - hv.w));
+          }
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(k_xf0 + 8 * s);
+        if (tt == 0) ATT_TRACE(3, j);
       }
       {  // V [32 keys x 128 dims] (chunked [c][key][32]) -> V^T hi / lo [128 dims x 32 keys], swizzled rows
         mbar_wait(v_full0 + 8 * s, ph);
         mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-2} has retired
+        if (tt == 0) ATT_TRACE(4, j);
         const float* vr = reinterpret_cast<const float*>(smem_al + OFF_VR + s * KV_BYTES);
 #pragma unroll 1
         for (int dd = 0; dd < DK / (N_XF_WARPS * 32); ++dd) {
@@ -357,10 +377,12 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           uint8_t* th = smem_al + OFF_VT + s * 2 * KV_BYTES + d * 128;
           uint8_t* tl = th + KV_BYTES;
           const int swd = d & 7;
+          float xv[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) xv[k] = vraw[k * 32];  // all 32 keys of this head dim first
 #pragma unroll
           for (int u = 0; u < 8; ++u) {  // keys 4u .. 4u+3
-            const float x0 = vraw[(4 * u + 0) * 32], x1 = vraw[(4 * u + 1) * 32];
-            const float x2 = vraw[(4 * u + 2) * 32], x3 = vraw[(4 * u + 3) * 32];
+            const float x0 = xv[4 * u + 0], x1 = xv[4 * u + 1], x2 = xv[4 * u + 2], x3 = xv[4 * u + 3];
             const float4 hv = make_float4(tf32_rn(x0), tf32_rn(x1), tf32_rn(x2), tf32_rn(x3));
             const int pu = (u ^ swd) << 4;
             *reinterpret_cast<float4*>(th + pu) = hv;
@@ -374,6 +396,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           mbar_arrive(vr_empty0 + 8 * s);
           mbar_arrive(vt_full0 + 8 * s);
         }
+        if (tt == 0) ATT_TRACE(5, j);
       }
     }
   }
@@ -388,6 +411,12 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 }
 
 }  // namespace
+
+#ifdef SS_ATT_TRACE
+extern "C" __attribute__((visibility("default"))) int ss_debug_att_trace(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_att_trace, sizeof(long long) * 16 * 64);
+}
+#endif
 
 // dispatched from ss_attention_tc (attention_tc.cu) for dk == 128
 int ss_attention_tc128_launch(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, void* stream) {

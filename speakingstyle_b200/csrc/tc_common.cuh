@@ -33,6 +33,19 @@ struct TcArgs {
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// true in exactly one lane of a fully converged warp (elect.sync); ptxas knows a region guarded by it runs
+// single-threaded, which `lane == 0` does not tell it
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
@@ -109,6 +122,12 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t
       "}" ::"r"(tmem_d),
       "l"(da), "l"(db), "r"(idesc), "r"(accum)
       : "memory");
+}
+// 2^x on the special-function unit (one MUFU.EX2; x <= 0 here, -inf -> 0, denormal results flush to 0)
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 // Low-word forms for issue-bound kernels (many small MMAs from one thread): the descriptor's high word is
 // the constant 0x40004040 (SBO = 64, version 1, SWIZZLE_128B) and the low word is start>>4 | 1<<16, so an
