@@ -171,8 +171,9 @@ typedef struct {
   float slope2;
   float accum_scale;
   int32_t accum_init;
-  int32_t k_group;         /* 32-channel chunks per accumulator restart (0 = default 4): tcgen05 accumulates with
-                              truncation, so partial sums are re-added in registers every k_group*4 MMAs */
+  int32_t k_group;         /* 32-channel chunks per accumulator restart (0 = default 8): tcgen05 accumulates with
+                              truncation, so partial sums are re-added in registers every k_group*4 MMAs.  8 keeps
+                              rms / max error below the FP32-pipe kernel's (scripts/tf32_group_error.py) */
 } ss_conv1d_tf32_params;
 SS_API int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream);
 /* Same contract; the split activations are kept in tensor memory (tcgen05.st) and the MMAs take their A

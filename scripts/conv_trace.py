@@ -1,0 +1,34 @@
+"""Debug: per-K-chunk clock64() timeline of the 3xTF32 conv kernels (CTA 0).  Rebuilds with -DSS_CONV_TRACE on
+the GPU box.  Usage: python scripts/conv_trace.py [ss|ts]"""
+import ctypes, math, os, sys
+os.environ["SS_NVCC_EXTRA"] = "-DSS_CONV_TRACE"
+sys.path.insert(0, ".")
+from speakingstyle_b200 import build
+build.build(force=True)
+import numpy as np, torch
+from speakingstyle_b200 import ops
+var = sys.argv[1] if len(sys.argv) > 1 else "ss"
+B, S, Cin, Cout, k = 64, 696, 256, 1024, 9
+x = torch.randn(B, S, Cin, device="cuda:0")
+W = ops.pack_conv(torch.randn(Cout, Cin, k, device="cuda:0") / math.sqrt(Cin * k))
+bias = torch.randn(Cout, device="cuda:0")
+for _ in range(3):
+    ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var)
+torch.cuda.synchronize()
+a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+a.record(); ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var); b.record(); torch.cuda.synchronize()
+print(f"{var}: {a.elapsed_time(b):.3f} ms (trace build)")
+buf = np.zeros(8 * 256, dtype=np.int64)
+dll = ctypes.CDLL(build.LIB_PATH)
+fn = getattr(dll, f"ss_debug_conv_{var}_trace")
+assert fn(buf.ctypes.data_as(ctypes.c_void_p)) == 0
+t = buf.reshape(8, 256)
+t0 = t[0, 0]
+names = ["tma", "full", "xf<", "mma>", "mma<", "st?", "st>", "epi<"]
+print("chunk " + " ".join(f"{n:>7s}" for n in names))
+for i in list(range(0, 12)) + list(range(100, 124)):
+    print(f"{i:5d} " + " ".join(f"{int(t[e, i] - t0):7d}" if t[e, i] else "      -" for e in range(8)))
+d = np.diff(t[4, 80:240])
+print("MMA issue period per chunk (clk): mean %.0f median %.0f" % (d.mean(), np.median(d)))
+print("tma->full latency: median %.0f" % np.median((t[1] - t[0])[80:240]))
+print("full->xf<: median %.0f" % np.median((t[2] - t[1])[80:240]))

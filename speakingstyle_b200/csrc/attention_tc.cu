@@ -44,6 +44,17 @@ constexpr int SMEM_BYTES = SMEM_DATA + N_BARS * 8 + 16 + 1024;
 constexpr int COL_S = 0, COL_O = 2 * BKV;
 constexpr int TMEM_COLS = 256;  // S0,S1: 2 x 64; O0,O1: 2 x 32
 
+// Debug build (-DSS_ATT_TRACE, scripts/attn_trace.py): CTA (0,0,0) stamps clock64() at the pipeline hand-overs.
+#ifdef SS_ATT_TRACE
+__device__ long long g_att32_trace[16 * 64];
+#define ATT_TRACE(ev, j)                                                                   \
+  do {                                                                                     \
+    if ((blockIdx.x | blockIdx.y | blockIdx.z) == 0 && (j) < 64) g_att32_trace[(ev) * 64 + (j)] = clock64(); \
+  } while (0)
+#else
+#define ATT_TRACE(ev, j)
+#endif
+
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
@@ -148,9 +159,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const int s = j & 1;
         const uint32_t ph = ((j >> 1) & 1) ^ 1;
         mbar_wait(vr_empty0 + 8 * s, ph);
+        ATT_TRACE(0, j);
         mbar_expect_tx(v_full0 + 8 * s, KV_BYTES);
         tma_load_3d(smem0 + OFF_VR + s * KV_BYTES, &tmV, v_full0 + 8 * s, 2 * D + h * DK, j * BKV, b);  // V_j, unswizzled
         mbar_wait(k_empty0 + 8 * s, ph);
+        ATT_TRACE(1, j);
         mbar_expect_tx(k_full0 + 8 * s, KV_BYTES);
         tma_load_3d(smem0 + OFF_K + s * 2 * KV_BYTES, &tmKV, k_full0 + 8 * s, D + h * DK, j * BKV, b);  // K_j -> K_hi slot
       }
@@ -167,6 +180,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
         mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
+        ATT_TRACE(6, j);
         const uint32_t kh = desc_lo(smem0 + OFF_K + s * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
         const uint32_t d = tmem_base + COL_S + s * BKV;
 #pragma unroll
@@ -178,6 +192,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         umma_commit(s_full0 + 8 * s);
         umma_commit(k_empty0 + 8 * s);
+        ATT_TRACE(7, j);
       };
       mbar_wait(q_xf, 0);
       issue_s(0);
@@ -188,6 +203,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_wait(p_full, j & 1);
         mbar_wait(o_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
+        ATT_TRACE(8, j);
         const uint32_t vh = desc_lo(smem0 + OFF_VT + s * 2 * KV_BYTES), vl = vh + (KV_BYTES >> 4);  // V^T hi / lo
         const uint32_t d = tmem_base + COL_O + s * DK;
 #pragma unroll
@@ -201,6 +217,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         umma_commit(o_full0 + 8 * s);
         umma_commit(p_empty);
         umma_commit(vt_empty0 + 8 * s);
+        ATT_TRACE(9, j);
       }
     }
   } else if (warp < 2 + N_SOFTMAX_WARPS) {
@@ -223,6 +240,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const int ob = jj & 1;
       mbar_wait(o_full0 + 8 * ob, (jj >> 1) & 1);
       tc_fence_after();
+      if (warp == 2 && lane == 0) ATT_TRACE(12, jj);
       float v[16];
       tmem_ld16(lane_base + COL_O + ob * DK + half * 16, v);
       tc_fence_before();
@@ -230,12 +248,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (lane == 0) mbar_arrive(o_empty0 + 8 * ob);
 #pragma unroll
       for (int i = 0; i < 16; ++i) o[i] = fmaf(o[i], alpha, v[i]);
+      if (warp == 2 && lane == 0) ATT_TRACE(13, jj);
     };
 
     for (int j = 0; j < NT; ++j) {
       const int sb = j & 1;
       mbar_wait(s_full0 + 8 * sb, (j >> 1) & 1);
       tc_fence_after();
+      if (warp == 2 && lane == 0) ATT_TRACE(10, j);
       float sa[32], sc[32];  // sa = this half's 32 keys, sc = the other half's (needed for the row max only)
       tmem_ld32(lane_base + COL_S + sb * BKV + half * 32, sa);
       tmem_ld32(lane_base + COL_S + sb * BKV + (half ^ 1) * 32, sc);
@@ -273,6 +293,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       l = l * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
 
+      if (warp == 2 && lane == 0) ATT_TRACE(14, j);  // exponentials done, waiting for the P buffer
       mbar_wait(p_empty, (j & 1) ^ 1);  // P.V of the previous tile has finished reading P
 #pragma unroll
       for (int u = 0; u < 8; ++u) {  // 16-byte unit u of this row lives at unit (u ^ (row & 7)) - SWIZZLE_128B
@@ -286,6 +307,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
+      if (warp == 2 && lane == 0) ATT_TRACE(11, j);
 
       if (j > 0) fold_o(j - 1, alpha_fold);  // O_{j-1} landed together with p_empty
       alpha_fold = alpha;
@@ -318,14 +340,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const int s = j & 1;
       const uint32_t ph = (j >> 1) & 1;
       mbar_wait(k_full0 + 8 * s, ph);
+      if (tt == 0) ATT_TRACE(2, j);
       split_tile(reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES),
                  reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES), KV_BYTES / 16, tt);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(k_xf0 + 8 * s);
+      if (tt == 0) ATT_TRACE(3, j);
 
       mbar_wait(v_full0 + 8 * s, ph);
       mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-2} has retired
+      if (tt == 0) ATT_TRACE(4, j);
       {  // V [64 keys x 32 dims] -> V^T hi / lo [32 dims x 64 keys], K-major, 128-byte swizzle
         const float* vraw = reinterpret_cast<const float*>(smem_al + OFF_VR + s * KV_BYTES);
         uint8_t* vt = smem_al + OFF_VT + s * 2 * KV_BYTES;
@@ -352,6 +377,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_arrive(vr_empty0 + 8 * s);
         mbar_arrive(vt_full0 + 8 * s);
       }
+      if (tt == 0) ATT_TRACE(5, j);
     }
   }
 
@@ -365,6 +391,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 }
 
 }  // namespace
+
+#ifdef SS_ATT_TRACE
+extern "C" __attribute__((visibility("default"))) int ss_debug_att32_trace(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_att32_trace, sizeof(long long) * 16 * 64);
+}
+#endif
 
 int ss_attention_tc128_launch(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, void* stream);
 

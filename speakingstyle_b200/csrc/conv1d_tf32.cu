@@ -45,6 +45,17 @@ struct Cfg {
   static constexpr int smem_bytes = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16 + 1024;
 };
 
+// Debug build (-DSS_CONV_TRACE, scripts/conv_trace.py): CTA 0 stamps clock64() per K-chunk at the hand-overs.
+#ifdef SS_CONV_TRACE
+__device__ long long g_conv_ss_trace[8 * 256];
+#define CONV_TRACE(ev, i)                                                              \
+  do {                                                                                 \
+    if (blockIdx.x == 0 && (i) < 256) g_conv_ss_trace[(ev) * 256 + (i)] = clock64();           \
+  } while (0)
+#else
+#define CONV_TRACE(ev, i)
+#endif
+
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
@@ -103,6 +114,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
       int stage = 0;
       uint32_t phase = 0;
+      [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int nt = tile % p.n_tiles;
         const int rest = tile / p.n_tiles;
@@ -113,6 +125,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           const int j = it / nchunk;
           const int c0 = (it - j * nchunk) * KCHUNK;
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
+          CONV_TRACE(0, gi); ++gi;
           mbar_expect_tx(full0 + 8 * stage, C::tx_bytes);
           tma_load_3d(smem0 + off_a(stage), &tmA, full0 + 8 * stage, c0, t0 + j * p.dilation - p.pad, b);
           tma_load_3d(smem0 + off_bh(stage), &tmBh, full0 + 8 * stage, c0, n0, j);
@@ -129,6 +142,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       uint32_t phase = 0;
       int local = 0;   // tiles done by this CTA -> correction buffer / phase
       int gcount = 0;  // K-groups done by this CTA -> main buffer / phase
+      [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
         const int cs = local & 1;
         mbar_wait(cempty0 + 8 * cs, ((local >> 1) & 1) ^ 1);
@@ -142,6 +156,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           for (int it = it0; it < it1; ++it) {
             mbar_wait(xf0 + 8 * stage, phase);  // hi / lo written (implies the TMA data has landed)
             tc_fence_after();
+            CONV_TRACE(3, gi);
             const uint32_t a_hi = smem0 + off_a(stage), a_lo = smem0 + off_alo(stage);
             const uint32_t b_hi = smem0 + off_bh(stage), b_lo = smem0 + off_bl(stage);
 #pragma unroll
@@ -152,6 +167,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
               umma_tf32(d_tmem, make_desc(a_hi + o), make_desc(b_hi + o), idesc, ((it - it0) | kk) != 0);
             }
             umma_commit(empty0 + 8 * stage);
+            CONV_TRACE(4, gi); ++gi;
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           umma_commit(tfull0 + 8 * as);  // this group's partial sum is complete
@@ -173,7 +189,22 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       float acc[BN];
 #pragma unroll
       for (int i = 0; i < BN; ++i) acc[i] = 0.f;
+      const int cs = local & 1;
       for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
+        if (it0 + group >= KT) {  // last group: correction terms first (same summation order as the TS kernel)
+          mbar_wait(cfull0 + 8 * cs, (local >> 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(lane_base + (2 + cs) * BN + c0, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(cempty0 + 8 * cs);
+        }
         const int as = gcount & 1;
         mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
         tc_fence_after();
@@ -188,30 +219,25 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
       }
-      const int cs = local & 1;
-      mbar_wait(cfull0 + 8 * cs, (local >> 1) & 1);
-      tc_fence_after();
       const int len = p.lens ? p.lens[b] : 0x7fffffff;
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {
         float v[32];
-        tmem_ld32(lane_base + (2 + cs) * BN + c0, v);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] += acc[c0 + i];
+        for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(cempty0 + 8 * cs);
     }
   } else {
     // ================= operand split (warps 6..9) =================
     const int tt = (warp - 6) * 32 + lane;  // 0..127
     int stage = 0;
     uint32_t phase = 0;
+    [[maybe_unused]] int gi = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       for (int it = 0; it < KT; ++it) {
         mbar_wait(full0 + 8 * stage, phase);
+        if (threadIdx.x == 192) CONV_TRACE(1, gi);
         float4* a = reinterpret_cast<float4*>(smem_al + off_a(stage));
         float4* alo = reinterpret_cast<float4*>(smem_al + off_alo(stage));
 #pragma unroll
@@ -231,6 +257,8 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         fence_proxy_async();  // make these generic-proxy writes visible to tcgen05.mma
         __syncwarp();
         if (lane == 0) mbar_arrive(xf0 + 8 * stage);
+        if (threadIdx.x == 192) CONV_TRACE(2, gi);
+        ++gi;
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -269,6 +297,12 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
 }
 
 }  // namespace
+
+#ifdef SS_CONV_TRACE
+extern "C" __attribute__((visibility("default"))) int ss_debug_conv_ss_trace(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_conv_ss_trace, sizeof(long long) * 8 * 256);
+}
+#endif
 
 extern "C" int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream) {
   SS_REQUIRE(p && p->x && p->w_hi && p->w_lo && (p->y || p->y_act || p->accum), SS_ERR_INVALID,
@@ -309,7 +343,7 @@ extern "C" int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream) {
   a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int group = p->k_group > 0 ? p->k_group : 4;  // chunks (of 32 channels) per main-accumulator restart
+  const int group = p->k_group > 0 ? p->k_group : 8;  // chunks (of 32 channels) per main-accumulator restart
   switch (bn) {
     case 128: return launch<128, 3>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
     case 64: return launch<64, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);

@@ -35,6 +35,17 @@ struct Cfg {
   static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
 };
 
+// Debug build (-DSS_CONV_TRACE, scripts/conv_trace.py): CTA 0 stamps clock64() per K-chunk at the hand-overs.
+#ifdef SS_CONV_TRACE
+__device__ long long g_conv_ts_trace[8 * 256];
+#define CONV_TRACE(ev, i)                                                              \
+  do {                                                                                 \
+    if (blockIdx.x == 0 && (i) < 256) g_conv_ts_trace[(ev) * 256 + (i)] = clock64();           \
+  } while (0)
+#else
+#define CONV_TRACE(ev, i)
+#endif
+
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
@@ -122,6 +133,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
       int stage = 0;
       uint32_t phase = 0;
+      [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int nt = tile % p.n_tiles;
         const int rest = tile / p.n_tiles;
@@ -132,6 +144,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const int j = it / nchunk;
           const int c0 = (it - j * nchunk) * KCHUNK;
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
+          CONV_TRACE(0, gi); ++gi;
           mbar_expect_tx(full0 + 8 * stage, C::stage_bytes);
           tma_load_3d(smem0 + off_a(stage), &tmA, full0 + 8 * stage, c0, t0 + j * p.dilation - p.pad, b);
           tma_load_3d(smem0 + off_bh(stage), &tmBh, full0 + 8 * stage, c0, n0, j);
@@ -147,6 +160,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       int stage = 0, slot = 0;
       uint32_t phase = 0, sphase = 0;
       int local = 0, gcount = 0;
+      [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
         mbar_wait(cempty, (local & 1) ^ 1);  // the epilogue has drained the correction accumulator
         const uint32_t c_tmem = tmem_base + 2 * BN;
@@ -159,6 +173,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           for (int it = it0; it < it1; ++it) {
             mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of this chunk are in TMEM (so its TMA has landed too)
             tc_fence_after();
+            CONV_TRACE(3, gi);
             const uint32_t a_hi = tmem_base + C::a_col0 + slot * A_SLOT_COLS, a_lo = a_hi + KCHUNK;
             const uint32_t b_hi = smem0 + off_bh(stage), b_lo = smem0 + off_bl(stage);
 #pragma unroll
@@ -169,6 +184,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             }
             umma_commit(empty0 + 8 * stage);    // smem stage free (x was consumed by the split warps earlier)
             umma_commit(taempty0 + 8 * slot);   // TMEM A slot free
+            CONV_TRACE(4, gi); ++gi;
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
             if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
           }
@@ -192,6 +208,23 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 #pragma unroll
       for (int i = 0; i < BN; ++i) acc[i] = 0.f;
       for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
+        if (it0 + group >= KT) {
+          // Last group: its MMAs and the correction terms finish together.  Take the (single-buffered) correction
+          // accumulator first and hand it back at once - the next tile's MMAs wait for it, and with a short
+          // reduction (k = 1 layers: 8 chunks) anything slower would stall the tensor pipe between tiles.
+          mbar_wait(cfull, local & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(lane_base + 2 * BN + c0, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(cempty);
+        }
         const int as = gcount & 1;
         mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
         tc_fence_after();
@@ -205,21 +238,14 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
+        if (threadIdx.x == 64) CONV_TRACE(7, local * KT + min(it0 + group, KT) - 1);  // stamped at the group's last chunk
       }
-      mbar_wait(cfull, local & 1);
-      tc_fence_after();
       const int len = p.lens ? p.lens[b] : 0x7fffffff;
 #pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
         float v[32];
-        tmem_ld32(lane_base + 2 * BN + c0, v);
-        if (c0 + 32 >= BN) {  // last read of the correction accumulator: hand it back before the stores
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(cempty);
-        }
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] += acc[c0 + i];
+        for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
     }
@@ -231,9 +257,11 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int sw = r & 7;
     int stage = 0, slot = 0;
     uint32_t phase = 0, sphase = 0;
+    [[maybe_unused]] int gi = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       for (int it = 0; it < KT; ++it) {
         mbar_wait(full0 + 8 * stage, phase);
+        if (threadIdx.x == 192) CONV_TRACE(1, gi);
         const uint8_t* row = smem_al + off_a(stage) + r * ROW_BYTES;
         float hi[32], lo[32];
 #pragma unroll
@@ -250,14 +278,18 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
           hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
         }
+        if (threadIdx.x == 192) CONV_TRACE(5, gi);
         mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
         tc_fence_after();
+        if (threadIdx.x == 192) CONV_TRACE(6, gi);
         tmem_st32(lane_base + slot * A_SLOT_COLS, hi);
         tmem_st32(lane_base + slot * A_SLOT_COLS + KCHUNK, lo);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tafull0 + 8 * slot);
+        if (threadIdx.x == 192) CONV_TRACE(2, gi);
+        ++gi;
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
         if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
       }
@@ -298,6 +330,12 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
 
 }  // namespace
 
+#ifdef SS_CONV_TRACE
+extern "C" __attribute__((visibility("default"))) int ss_debug_conv_ts_trace(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_conv_ts_trace, sizeof(long long) * 8 * 256);
+}
+#endif
+
 extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream) {
   SS_REQUIRE(p && p->x && p->w_hi && p->w_lo && (p->y || p->y_act || p->accum), SS_ERR_INVALID,
              "ss_conv1d_tf32x3_ts: null pointer");
@@ -337,7 +375,7 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int group = p->k_group > 0 ? p->k_group : 4;
+  const int group = p->k_group > 0 ? p->k_group : 8;
   switch (bn) {
     case 128: return launch<128, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
     case 64: return launch<64, 6>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);

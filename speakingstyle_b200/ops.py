@@ -5,6 +5,7 @@ device pointers and enqueues ONE library call on torch's current stream.  Nothin
 computes with torch operators.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -104,8 +105,9 @@ def add_position(x, pe):
 
 
 fp32_backend = "tf32x3"  # "tf32x3": 3xTF32 tcgen05 kernel (default); "ffma": the FP32-pipe kernel
-tf32_k_group = 0         # 0 = library default (accumulator restart every 4 chunks = 128 channels)
-tf32_variant = "ss"      # "ss": split operands in shared memory; "ts": A operand in tensor memory
+# experiment knobs (environment overrides are for A/B timing only; the defaults are what the tests pin)
+tf32_k_group = int(os.environ.get("SS_TF32_KGROUP", "0"))  # 0 = library default (accumulator restart every 8 chunks)
+tf32_variant = os.environ.get("SS_TF32_VARIANT", "ts")     # "ts": A operand in tensor memory; "ss": in shared memory
 
 
 def tf32_round(t):
