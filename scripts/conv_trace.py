@@ -7,8 +7,10 @@ from speakingstyle_b200 import build
 build.build(force=True)
 import numpy as np, torch
 from speakingstyle_b200 import ops
-var = sys.argv[1] if len(sys.argv) > 1 else "ss"
+var = sys.argv[1] if len(sys.argv) > 1 else "ts"
 B, S, Cin, Cout, k = 64, 696, 256, 1024, 9
+if len(sys.argv) > 2:
+    Cin, Cout, k = (int(v) for v in sys.argv[2:5])
 x = torch.randn(B, S, Cin, device="cuda:0")
 W = ops.pack_conv(torch.randn(Cout, Cin, k, device="cuda:0") / math.sqrt(Cin * k))
 bias = torch.randn(Cout, device="cuda:0")
@@ -26,9 +28,11 @@ t = buf.reshape(8, 256)
 t0 = t[0, 0]
 names = ["tma", "full", "xf<", "mma>", "mma<", "st?", "st>", "epi<"]
 print("chunk " + " ".join(f"{n:>7s}" for n in names))
-for i in list(range(0, 12)) + list(range(100, 124)):
+NCH = int(os.environ.get("TRACE_ROWS", "124"))
+for i in list(range(0, 12)) + list(range(NCH - 24, NCH)):
     print(f"{i:5d} " + " ".join(f"{int(t[e, i] - t0):7d}" if t[e, i] else "      -" for e in range(8)))
-d = np.diff(t[4, 80:240])
+hi = min(240, int((t[4] != 0).sum()))
+d = np.diff(t[4, 8:hi])
 print("MMA issue period per chunk (clk): mean %.0f median %.0f" % (d.mean(), np.median(d)))
-print("tma->full latency: median %.0f" % np.median((t[1] - t[0])[80:240]))
-print("full->xf<: median %.0f" % np.median((t[2] - t[1])[80:240]))
+print("tma->full latency: median %.0f" % np.median((t[1] - t[0])[8:hi]))
+print("full->xf<: median %.0f" % np.median((t[2] - t[1])[8:hi]))

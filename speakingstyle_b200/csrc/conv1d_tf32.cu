@@ -220,12 +220,16 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
       }
       const int len = p.lens ? p.lens[b] : 0x7fffffff;
+      const bool lean = drain_is_lean(p);  // warp-uniform
 #pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
-        drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+        if (lean)
+          drain_block_lean(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+        else
+          drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
     }
   } else {

@@ -326,6 +326,61 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
   }
 }
 
+// Lean variant for the fp32 kernels' common case (fp32 y, optional bias / fp32 residual / row mask, activation
+// none / relu / leaky-relu; no running mean, no bf16 copy, no tanh).  The 3xTF32 kernels keep the whole output
+// row in registers, so their column-block loop must be unrolled and this body is instantiated BN/32 times:
+// it has to be small (one warp per scheduler runs it - the general drain_block above, four times over, spills
+// out of the instruction cache and took ~4.5k cycles per block) and its eight row steps are straight-line
+// with all residual loads in flight before the first is used.
+__device__ __forceinline__ bool drain_is_lean(const TcArgs& p) {
+  return p.y != nullptr && p.y_dtype == SS_F32 && p.accum == nullptr && p.y_act == nullptr && p.act != SS_ACT_TANH &&
+         (p.residual == nullptr || p.residual_dtype == SS_F32);
+}
+__device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane,
+                                                 int b, int mt, int n_blk, int len) {
+  const int col = (lane & 7) * 4;
+  const int rsub = lane >> 3;
+  float* my = stg + lane * STG_PITCH;
+  __syncwarp();  // the previous block has been fully read back
+#pragma unroll
+  for (int q = 0; q < 8; ++q)
+    *reinterpret_cast<float4*>(my + q * 4) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+  __syncwarp();
+  const int n = n_blk + col;
+  if (n >= p.Cout) return;
+  float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+  const float neg = p.act == SS_ACT_NONE ? 1.f : p.act == SS_ACT_RELU ? 0.f : p.slope;  // x > 0 ? x : x * neg
+  const int t_first = mt * BM + lg * 32 + rsub;
+  const float* src = stg + rsub * STG_PITCH + col;
+  const float* res = static_cast<const float*>(p.residual);
+  float* y = static_cast<float*>(p.y) + (int64_t)b * p.y_batch_stride;
+  if (res) res += (int64_t)b * p.y_batch_stride;
+  int64_t off[8];
+  bool ok[8];
+  float4 r[8];
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int t = t_first + it * 4;
+    off[it] = p.y_offset + (int64_t)t * p.y_row_stride + n;
+    ok[it] = t < p.S_out && off[it] >= 0 && off[it] < p.y_batch_elems;
+    r[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (res && ok[it]) r[it] = __ldg(reinterpret_cast<const float4*>(res + off[it]));
+  }
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    float4 f = *reinterpret_cast<const float4*>(src + it * 4 * STG_PITCH);
+    f.x += bias4.x; f.y += bias4.y; f.z += bias4.z; f.w += bias4.w;
+    f.x = f.x > 0.f ? f.x : f.x * neg;
+    f.y = f.y > 0.f ? f.y : f.y * neg;
+    f.z = f.z > 0.f ? f.z : f.z * neg;
+    f.w = f.w > 0.f ? f.w : f.w * neg;
+    f.x += r[it].x; f.y += r[it].y; f.z += r[it].z; f.w += r[it].w;
+    if (t_first + it * 4 >= len) f = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ok[it]) *reinterpret_cast<float4*>(y + off[it]) = f;
+  }
+}
+
 // G epilogue warps share one TMEM lane group; warp `sub` of the group takes every G-th 32-column block.
 template <int BN, int G = 1>
 __device__ __forceinline__ void drain_tile(const TcArgs& p, uint32_t taddr, float* stg, int lg, int lane, int b, int mt,
