@@ -20,17 +20,18 @@ torch.cuda.synchronize()
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 a.record(); ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var); b.record(); torch.cuda.synchronize()
 print(f"{var}: {a.elapsed_time(b):.3f} ms (trace build)")
-buf = np.zeros(8 * 256, dtype=np.int64)
+NEV = 12 if var == "ts" else 8
+buf = np.zeros(NEV * 256, dtype=np.int64)
 dll = ctypes.CDLL(build.LIB_PATH)
 fn = getattr(dll, f"ss_debug_conv_{var}_trace")
 assert fn(buf.ctypes.data_as(ctypes.c_void_p)) == 0
-t = buf.reshape(8, 256)
+t = buf.reshape(NEV, 256)
 t0 = t[0, 0]
-names = ["tma", "full", "xf<", "mma>", "mma<", "st?", "st>", "epi<"]
+names = ["tma", "full", "xf<", "mma>", "mma<", "st?", "st>", "epi<", "m:cemp", "m:temp", "e:cfull", "e:cemp"][:NEV]
 print("chunk " + " ".join(f"{n:>7s}" for n in names))
 NCH = int(os.environ.get("TRACE_ROWS", "124"))
 for i in list(range(0, 12)) + list(range(NCH - 24, NCH)):
-    print(f"{i:5d} " + " ".join(f"{int(t[e, i] - t0):7d}" if t[e, i] else "      -" for e in range(8)))
+    print(f"{i:5d} " + " ".join(f"{int(t[e, i] - t0):7d}" if t[e, i] else "      -" for e in range(NEV)))
 hi = min(240, int((t[4] != 0).sum()))
 d = np.diff(t[4, 8:hi])
 print("MMA issue period per chunk (clk): mean %.0f median %.0f" % (d.mean(), np.median(d)))

@@ -219,7 +219,14 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
       }
-      const int len = p.lens ? p.lens[b] : 0x7fffffff;
+      int b_t = b, t_tile0 = mt * BM;
+      bool straddle = false;
+      if (p.flat) {  // un-flatten the tile's first row once; most tiles lie inside one utterance
+        b_t = t_tile0 / p.S_out;
+        t_tile0 -= b_t * p.S_out;
+        straddle = t_tile0 + BM > p.S_out;
+      }
+      const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
       const bool lean = drain_is_lean(p);  // warp-uniform
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
@@ -227,7 +234,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+          drain_block_lean(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
         else
           drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }

@@ -37,7 +37,7 @@ struct Cfg {
 
 // Debug build (-DSS_CONV_TRACE, scripts/conv_trace.py): CTA 0 stamps clock64() per K-chunk at the hand-overs.
 #ifdef SS_CONV_TRACE
-__device__ long long g_conv_ts_trace[8 * 256];
+__device__ long long g_conv_ts_trace[12 * 256];
 #define CONV_TRACE(ev, i)                                                              \
   do {                                                                                 \
     if (blockIdx.x == 0 && (i) < 256) g_conv_ts_trace[(ev) * 256 + (i)] = clock64();           \
@@ -100,7 +100,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
   const int KT = p.k * nchunk;
-  const int num_tiles = p.B * p.m_tiles * p.n_tiles;
+  const int num_tiles = (p.flat ? 1 : p.B) * p.m_tiles * p.n_tiles;  // flat: m_tiles spans all utterances
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -163,11 +163,13 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
         mbar_wait(cempty, (local & 1) ^ 1);  // the epilogue has drained the correction accumulator
+        CONV_TRACE(8, gi);
         const uint32_t c_tmem = tmem_base + 2 * BN;
         for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
           const int as = gcount & 1;
           mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);
           tc_fence_after();
+          CONV_TRACE(9, gi);
           const uint32_t d_tmem = tmem_base + as * BN;
           const int it1 = min(it0 + group, KT);
           for (int it = it0; it < it1; ++it) {
@@ -214,6 +216,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           // reduction (k = 1 layers: 8 chunks) anything slower would stall the tensor pipe between tiles.
           mbar_wait(cfull, local & 1);
           tc_fence_after();
+          if (threadIdx.x == 64) CONV_TRACE(10, local * KT + KT - 1);
 #pragma unroll
           for (int c0 = 0; c0 < BN; c0 += 32) {
             float v[32];
@@ -224,6 +227,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(cempty);
+          if (threadIdx.x == 64) CONV_TRACE(11, local * KT + KT - 1);
         }
         const int as = gcount & 1;
         mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
@@ -240,7 +244,14 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
         if (threadIdx.x == 64) CONV_TRACE(7, local * KT + min(it0 + group, KT) - 1);  // stamped at the group's last chunk
       }
-      const int len = p.lens ? p.lens[b] : 0x7fffffff;
+      int b_t = b, t_tile0 = mt * BM;
+      bool straddle = false;
+      if (p.flat) {  // un-flatten the tile's first row once; most tiles lie inside one utterance
+        b_t = t_tile0 / p.S_out;
+        t_tile0 -= b_t * p.S_out;
+        straddle = t_tile0 + BM > p.S_out;
+      }
+      const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
       const bool lean = drain_is_lean(p);  // warp-uniform
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
@@ -248,7 +259,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+          drain_block_lean(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
         else
           drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
@@ -263,10 +274,25 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint32_t phase = 0, sphase = 0;
     [[maybe_unused]] int gi = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      // flat tiling: frame index of this row inside its own utterance, and whether any row of the tile (with its
+      // halo) can reach across an utterance end - only then do taps have to be checked row by row
+      int t_row = 0;
+      bool edge_tile = false;
+      if (p.flat) {
+        const int R0 = ((tile / p.n_tiles) % p.m_tiles) * BM;
+        const int t0 = R0 % p.S_in;
+        t_row = t0 + r;
+        if (t_row >= p.S_in) t_row %= p.S_in;
+        edge_tile = t0 - p.pad < 0 || t0 + BM - 1 + (p.k - 1) * p.dilation - p.pad >= p.S_in;
+      }
+      int t_src = t_row - p.pad, cleft = nchunk;  // source frame of this row for the current tap
       for (int it = 0; it < KT; ++it) {
         mbar_wait(full0 + 8 * stage, phase);
         if (threadIdx.x == 192) CONV_TRACE(1, gi);
         const uint8_t* row = smem_al + off_a(stage) + r * ROW_BYTES;
+        // flat tiling: a tap that leaves this row's utterance must read the zero padding, not the neighbour's frames
+        const bool outside = edge_tile && (t_src < 0 || t_src >= p.S_in);
+        if (--cleft == 0) { cleft = nchunk; t_src += p.dilation; }
         float hi[32], lo[32];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {  // 16-byte unit u of the row sits at unit (u ^ (row & 7)) - SWIZZLE_128B
@@ -281,6 +307,13 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
           hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
           hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
+        }
+        if (edge_tile && __any_sync(0xffffffffu, outside)) {  // warp-uniform branch: skipped in interior tiles
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            hi[i] = outside ? 0.f : hi[i];
+            lo[i] = outside ? 0.f : lo[i];
+          }
         }
         if (threadIdx.x == 192) CONV_TRACE(5, gi);
         mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
@@ -314,8 +347,8 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
            float in_slope, int group, cudaStream_t st) {
   using C = Cfg<BN, STAGES>;
   a.n_tiles = (a.Cout + BN - 1) / BN;
-  a.m_tiles = (a.S_out + BM - 1) / BM;
-  const int64_t tiles = (int64_t)a.B * a.m_tiles * a.n_tiles;
+  a.m_tiles = a.flat ? (int)(((int64_t)a.B * a.S_out + BM - 1) / BM) : (a.S_out + BM - 1) / BM;
+  const int64_t tiles = (int64_t)(a.flat ? 1 : a.B) * a.m_tiles * a.n_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_ts: too many tiles");
   static bool attr_set = false;
   if (!attr_set) {
@@ -336,7 +369,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
 
 #ifdef SS_CONV_TRACE
 extern "C" __attribute__((visibility("default"))) int ss_debug_conv_ts_trace(long long* host) {
-  return (int)cudaMemcpyFromSymbol(host, g_conv_ts_trace, sizeof(long long) * 8 * 256);
+  return (int)cudaMemcpyFromSymbol(host, g_conv_ts_trace, sizeof(long long) * 12 * 256);
 }
 #endif
 
@@ -358,9 +391,17 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
              "ss_conv1d_tf32x3_ts: in_act must be none or lrelu");
 
   const int bn = p->Cout > 64 ? 128 : p->Cout > 32 ? 64 : 32;
+  // Flat tiling (see TcArgs::flat): stride-1 same-length layer, batch-contiguous input, lean epilogue, and a
+  // sequence length that would otherwise leave a partly empty last tile in every utterance.
+  const bool flat = p->B > 1 && p->S_in == p->S_out && p->S_out % BM != 0 &&
+                    p->x_batch_stride == (int64_t)p->S_in * p->x_row_stride && (int64_t)p->B * p->S_in < (1ll << 30) &&
+                    p->y != nullptr && p->accum == nullptr && p->y_act == nullptr && p->act != SS_ACT_TANH;
   CUtensorMap tmA, tmBh, tmBl;
-  int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
-                       (uint64_t)p->x_row_stride * 4, (uint64_t)p->x_batch_stride * 4, KCHUNK, BM);
+  int rc = flat ? make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin,
+                              (uint64_t)p->B * (uint64_t)p->S_in, 1, (uint64_t)p->x_row_stride * 4,
+                              (uint64_t)p->B * (uint64_t)p->x_batch_stride * 4, KCHUNK, BM)
+                : make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in,
+                              (uint64_t)p->B, (uint64_t)p->x_row_stride * 4, (uint64_t)p->x_batch_stride * 4, KCHUNK, BM);
   if (rc != SS_OK) return rc;
   rc = make_map_3d(&tmBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->w_hi, (uint64_t)p->Cin, (uint64_t)p->Cout, (uint64_t)p->k,
                    (uint64_t)p->Cin * 4, (uint64_t)p->Cout * p->Cin * 4, KCHUNK, (uint32_t)bn);
@@ -378,6 +419,7 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   a.m_tiles = a.n_tiles = 0;
   a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
+  a.flat = flat ? 1 : 0; a.S_in = p->S_in;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int group = p->k_group > 0 ? p->k_group : 8;
   switch (bn) {

@@ -28,6 +28,12 @@ struct TcArgs {
   int32_t m_tiles, n_tiles;
   int32_t act, act2, y_dtype, residual_dtype, accum_init;
   float slope, slope2, accum_scale;
+  // "flat" tiling (3xTF32 TS kernel, stride-1 same-length layers with batch-contiguous x): the B*S rows of all
+  // utterances are tiled as ONE sequence, so no 128-row tile is padded at every utterance end (S = 696 wastes
+  // 9 % of each M = 128 MMA otherwise).  m_tiles then counts tiles of the flattened sequence; rows whose tap
+  // falls outside their own utterance are zeroed by the operand-split warps, and the epilogue maps each
+  // flattened row back to (utterance, frame).
+  int32_t flat = 0, S_in = 0;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -336,8 +342,10 @@ __device__ __forceinline__ bool drain_is_lean(const TcArgs& p) {
   return p.y != nullptr && p.y_dtype == SS_F32 && p.accum == nullptr && p.y_act == nullptr && p.act != SS_ACT_TANH &&
          (p.residual == nullptr || p.residual_dtype == SS_F32);
 }
+// (b, t_tile0) = utterance and frame of the tile's first row; straddle = the tile runs past the end of utterance b
+// (flat tiling only), in which case rows are un-flattened one by one and the row mask is looked up per row.
 __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane,
-                                                 int b, int mt, int n_blk, int len) {
+                                                 int b, int t_tile0, bool straddle, int n_blk, int len) {
   const int col = (lane & 7) * 4;
   const int rsub = lane >> 3;
   float* my = stg + lane * STG_PITCH;
@@ -351,33 +359,41 @@ __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&
   float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
   if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + n));
   const float neg = p.act == SS_ACT_NONE ? 1.f : p.act == SS_ACT_RELU ? 0.f : p.slope;  // x > 0 ? x : x * neg
-  const int t_first = mt * BM + lg * 32 + rsub;
   const float* src = stg + rsub * STG_PITCH + col;
   const float* res = static_cast<const float*>(p.residual);
-  float* y = static_cast<float*>(p.y) + (int64_t)b * p.y_batch_stride;
-  if (res) res += (int64_t)b * p.y_batch_stride;
-  int64_t off[8];
-  bool ok[8];
-  float4 r[8];
+  float* y = static_cast<float*>(p.y);
+  int t = t_tile0 + lg * 32 + rsub, bb = b;  // first row of this lane
+  // two half-loops of four rows (register budget: the caller holds a whole output row); the residual loads of a
+  // half are all in flight before the first is used
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    int64_t off[4];
+    bool ok[4], keep[4];
+    float4 r[4];
 #pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int t = t_first + it * 4;
-    off[it] = p.y_offset + (int64_t)t * p.y_row_stride + n;
-    ok[it] = t < p.S_out && off[it] >= 0 && off[it] < p.y_batch_elems;
-    r[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (res && ok[it]) r[it] = __ldg(reinterpret_cast<const float4*>(res + off[it]));
-  }
+    for (int u = 0; u < 4; ++u) {
+      if (straddle)
+        while (t >= p.S_out) { t -= p.S_out; ++bb; }
+      off[u] = p.y_offset + (int64_t)t * p.y_row_stride + n;
+      ok[u] = bb < p.B && t < p.S_out && off[u] >= 0 && off[u] < p.y_batch_elems;
+      off[u] += (int64_t)bb * p.y_batch_stride;
+      keep[u] = t < (straddle ? (p.lens && ok[u] ? __ldg(p.lens + bb) : 0x7fffffff) : len);
+      r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (res && ok[u]) r[u] = __ldg(reinterpret_cast<const float4*>(res + off[u]));
+      t += 4;
+    }
 #pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    float4 f = *reinterpret_cast<const float4*>(src + it * 4 * STG_PITCH);
-    f.x += bias4.x; f.y += bias4.y; f.z += bias4.z; f.w += bias4.w;
-    f.x = f.x > 0.f ? f.x : f.x * neg;
-    f.y = f.y > 0.f ? f.y : f.y * neg;
-    f.z = f.z > 0.f ? f.z : f.z * neg;
-    f.w = f.w > 0.f ? f.w : f.w * neg;
-    f.x += r[it].x; f.y += r[it].y; f.z += r[it].z; f.w += r[it].w;
-    if (t_first + it * 4 >= len) f = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (ok[it]) *reinterpret_cast<float4*>(y + off[it]) = f;
+    for (int u = 0; u < 4; ++u) {
+      float4 f = *reinterpret_cast<const float4*>(src + (half * 4 + u) * 4 * STG_PITCH);
+      f.x += bias4.x; f.y += bias4.y; f.z += bias4.z; f.w += bias4.w;
+      f.x = f.x > 0.f ? f.x : f.x * neg;
+      f.y = f.y > 0.f ? f.y : f.y * neg;
+      f.z = f.z > 0.f ? f.z : f.z * neg;
+      f.w = f.w > 0.f ? f.w : f.w * neg;
+      f.x += r[u].x; f.y += r[u].y; f.z += r[u].z; f.w += r[u].w;
+      if (!keep[u]) f = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok[u]) *reinterpret_cast<float4*>(y + off[u]) = f;
+    }
   }
 }
 
