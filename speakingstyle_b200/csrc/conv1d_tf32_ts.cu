@@ -206,6 +206,29 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int rest = tile / p.n_tiles;
       const int mt = rest % p.m_tiles;
       const int b = rest / p.m_tiles;
+      int b_t = b, t_tile0 = mt * BM;
+      bool straddle = false;
+      if (p.flat) {  // un-flatten the tile's first row once; most tiles lie inside one utterance
+        b_t = t_tile0 / p.S_out;
+        t_tile0 -= b_t * p.S_out;
+        straddle = t_tile0 + BM > p.S_out;
+      }
+      const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
+      const bool lean = drain_is_lean(p);  // warp-uniform
+      if (lean && p.residual) {
+        // Pull this tile's residual rows into L2 now, while the MMAs run: the drain below keeps only four 16-byte
+        // loads per lane in flight, which from HBM (~1 us) capped the whole kernel at ~1.2 TB/s of residual reads.
+        int t = t_tile0 + lg * 32 + lane, bb = b_t;
+        if (straddle)
+          while (t >= p.S_out) { t -= p.S_out; ++bb; }
+        const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + nt * BN;
+        if (bb < p.B && t < p.S_out && off >= 0 && off < p.y_batch_elems) {
+          const float* rp = static_cast<const float*>(p.residual) + (int64_t)bb * p.y_batch_stride + off;
+          const int ncol = min(BN, p.Cout - nt * BN);
+          for (int c = 0; c < ncol; c += 32)  // one 128-byte line per step
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + c));
+        }
+      }
       float acc[BN];
 #pragma unroll
       for (int i = 0; i < BN; ++i) acc[i] = 0.f;
@@ -244,15 +267,6 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
         if (threadIdx.x == 64) CONV_TRACE(7, local * KT + min(it0 + group, KT) - 1);  // stamped at the group's last chunk
       }
-      int b_t = b, t_tile0 = mt * BM;
-      bool straddle = false;
-      if (p.flat) {  // un-flatten the tile's first row once; most tiles lie inside one utterance
-        b_t = t_tile0 / p.S_out;
-        t_tile0 -= b_t * p.S_out;
-        straddle = t_tile0 + BM > p.S_out;
-      }
-      const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
-      const bool lean = drain_is_lean(p);  // warp-uniform
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
         float v[32];
