@@ -14,11 +14,15 @@ if len(sys.argv) > 2:
 x = torch.randn(B, S, Cin, device="cuda:0")
 W = ops.pack_conv(torch.randn(Cout, Cin, k, device="cuda:0") / math.sqrt(Cin * k))
 bias = torch.randn(Cout, device="cuda:0")
+cold = os.environ.get("TRACE_COLD", "0") == "1"
+res = torch.randn(B, S, Cout, device="cuda:0") if os.environ.get("TRACE_RES", "0") == "1" else None
 for _ in range(3):
-    ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var)
+    ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var, residual=res)
+if cold:  # evict x / residual / weights from L2 before the traced launch
+    junk = torch.empty(512 << 20, dtype=torch.uint8, device="cuda:0"); junk.zero_(); junk.add_(1)
 torch.cuda.synchronize()
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-a.record(); ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var); b.record(); torch.cuda.synchronize()
+a.record(); ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var, residual=res); b.record(); torch.cuda.synchronize()
 print(f"{var}: {a.elapsed_time(b):.3f} ms (trace build)")
 NEV = 12 if var == "ts" else 8
 buf = np.zeros(NEV * 256, dtype=np.int64)
