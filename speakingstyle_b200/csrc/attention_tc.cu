@@ -3,22 +3,26 @@
 // accumulation in TMEM; softmax statistics, probabilities and the output accumulator are fp32.
 //
 // One CTA = 128 queries of one head of one utterance; keys/values stream through in 64-key tiles up to
-// the utterance's valid length.  Roles (384 threads = three warps per scheduler, 168 registers each):
-//   warp 0      TMA: Q once, then V_j / K_j tiles into two-deep rings (rows outside [0,S) zero-filled)
-//   warp 1      one thread issues  S_j = Q.K_j^T  (12 MMAs, N = 64) and  O_j = P_j.V_j  (24 MMAs, N = 32);
-//               S_{j+1} is issued before O_j so it overlaps the softmax of tile j.  The kernel is bound by
-//               this thread's issue rate (36 small MMAs per tile), hence the one-add descriptor forms.
-//   warps 2-9   softmax: thread = query row, warps w and w+4 share the rows.  Both read the whole S_j row
-//               (same running max, base-2 domain); each exponentiates its own 32 keys (MUFU.EX2), splits
-//               them into TF32 hi/lo straight into the 128-byte-swizzled K-major P chunk the MMA reads,
-//               keeps a partial row sum, and folds its 16 columns of O_{j-1} in registers
-//               (o = o*alpha + O, fp32 round-to-nearest, so the truncating TMEM accumulation never runs
-//               longer than one tile).  The fold comes AFTER P_j is handed over, off the critical path.
-//   warps 10-11 split Q, K_j into TF32 hi/lo in shared memory and transpose V_j while splitting it:
-// V arrives [keys x 32] (head dims contiguous) but the MMA wants its B operand K-major, i.e. V^T with the
-// keys contiguous (conflict-free: a lane reads one head dim of four consecutive keys and writes one
-// 16-byte unit of the swizzled V^T row).  Rings: K hi/lo freed by S_j, V as loaded freed by the transpose,
-// V^T hi/lo freed by P.V_j.  The [S x S] score matrix never leaves the SM.
+// the utterance's valid length.  The A operands of both GEMMs live in TENSOR MEMORY: with N = 64 / 32 the
+// MMAs are small, and re-reading a 4 KB Q or P slice from shared memory for each of them (the first
+// version) held them at ~45 cycles apiece where the tensor pipe needs 32 / 16.
+// Roles (384 threads = three warps per scheduler, 168 registers each):
+//   warp 0      TMA: Q once, then V_j / K_j tiles into four-deep rings (rows outside [0,S) zero-filled)
+//   warp 1      one elected thread issues  S_j = Q.K_j^T  (12 MMAs, N = 64, A = Q hi/lo in TMEM) and
+//               O_j = P_j.V_j  (24 MMAs, N = 32, A = P_j hi/lo in TMEM); S_{j+1} goes before O_j
+//   warps 2-9   softmax: thread = query row, warps w and w+4 share the rows.  First they split this CTA's
+//               Q rows into TMEM.  Per tile both read the whole S_j row (same running max, base-2 domain);
+//               each exponentiates its own 32 keys (MUFU.EX2), tcgen05.st's them as TF32 hi/lo into the
+//               P buffer (double-buffered), keeps a partial row sum, and folds its 16 columns of O_{j-1}
+//               in registers (o = o*alpha + O, fp32 round-to-nearest, so the truncating TMEM accumulation
+//               never runs longer than one tile) - after P_j is handed over, off the critical path.
+//   warps 10-11 split K_j into TF32 hi/lo in shared memory and transpose V_j while splitting it: V arrives
+//               [keys x 32] but the MMA wants its B operand K-major, i.e. V^T with the keys contiguous
+//               (conflict-free: a lane reads one head dim of four consecutive keys and writes one 16-byte
+//               unit of the swizzled V^T row).
+// Rings: K hi/lo freed by S_j, V as loaded freed by the transpose, V^T hi/lo freed by P.V_j.
+// TMEM (512 columns): S x2 (128) | O x2 (64) | Q hi, lo (64) | P hi, lo x2 (256).
+// The [S x S] score matrix never leaves the SM.
 #include "tc_common.cuh"
 
 namespace {
@@ -28,21 +32,22 @@ using namespace sstc;
 constexpr int DK = 32;            // head size = one 128-byte row of fp32
 constexpr int BQ = 128;           // queries per CTA = TMEM lanes
 constexpr int BKV = 64;           // keys per tile
+constexpr int NS = 4;             // ring depth
 constexpr int N_SOFTMAX_WARPS = 8, N_XF_WARPS = 2, XF_THREADS = N_XF_WARPS * 32;
 constexpr int NTHREADS = 32 * (2 + N_SOFTMAX_WARPS + N_XF_WARPS);
 constexpr int Q_BYTES = BQ * 128;      // 16 KB
 constexpr int KV_BYTES = BKV * 128;    // 8 KB
-constexpr int OFF_QH = 0, OFF_QL = Q_BYTES;
-constexpr int OFF_K = 2 * Q_BYTES;              // [2][K_hi 8 | K_lo 8]
-constexpr int OFF_VR = OFF_K + 4 * KV_BYTES;    // [2][V as loaded (unswizzled) 8]
-constexpr int OFF_VT = OFF_VR + 2 * KV_BYTES;   // [2][V^T_hi 8 | V^T_lo 8]
-constexpr int OFF_PH = OFF_VT + 4 * KV_BYTES;   // P_hi: 2 chunks of 32 keys x 128 rows
-constexpr int OFF_PL = OFF_PH + 2 * Q_BYTES;
-constexpr int SMEM_DATA = OFF_PL + 2 * Q_BYTES;  // 32 + 80 + 64 KB
-constexpr int N_BARS = 28;
+constexpr int OFF_Q = 0;                             // Q as loaded (read once by the softmax warps)
+constexpr int OFF_K = Q_BYTES;                       // [NS][K_hi 8 | K_lo 8]
+constexpr int OFF_VR = OFF_K + NS * 2 * KV_BYTES;    // [NS][V as loaded (unswizzled) 8]
+constexpr int OFF_VT = OFF_VR + NS * KV_BYTES;       // [NS][V^T_hi 8 | V^T_lo 8]
+constexpr int SMEM_DATA = OFF_VT + NS * 2 * KV_BYTES;  // 16 + 160 KB
+constexpr int N_BARS = 7 * NS + 12;
 constexpr int SMEM_BYTES = SMEM_DATA + N_BARS * 8 + 16 + 1024;
-constexpr int COL_S = 0, COL_O = 2 * BKV;
-constexpr int TMEM_COLS = 256;  // S0,S1: 2 x 64; O0,O1: 2 x 32
+constexpr int COL_S = 0, COL_O = 2 * BKV, COL_QH = COL_O + 2 * DK, COL_QL = COL_QH + DK, COL_P = COL_QL + DK;
+constexpr int TMEM_COLS = 512;
+static_assert(COL_P + 2 * 2 * BKV <= TMEM_COLS, "TMEM budget");
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 // Debug build (-DSS_ATT_TRACE, scripts/attn_trace.py): CTA (0,0,0) stamps clock64() at the pipeline hand-overs.
 #ifdef SS_ATT_TRACE
@@ -90,6 +95,22 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15])),
+      "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])), "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])),
+      "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+      "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
+      "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+
 __global__ void __launch_bounds__(NTHREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                     const __grid_constant__ CUtensorMap tmV, const int32_t* __restrict__ lens, float* __restrict__ ctx, int S, int H, float temperature) {
@@ -111,11 +132,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
   const uint32_t bars = smem0 + SMEM_DATA;
-  // two-deep rings: index with + 8 * slot
-  const uint32_t k_full0 = bars + 0, k_xf0 = bars + 16, k_empty0 = bars + 32;
-  const uint32_t v_full0 = bars + 48, vr_empty0 = bars + 64, vt_full0 = bars + 80, vt_empty0 = bars + 96;
-  const uint32_t s_full0 = bars + 112, s_empty0 = bars + 128, o_full0 = bars + 144, o_empty0 = bars + 160;
-  const uint32_t p_full = bars + 176, p_empty = bars + 184, q_full = bars + 192, q_xf = bars + 200;
+  // NS-deep rings: index with + 8 * slot
+  const uint32_t k_full0 = bars, k_xf0 = k_full0 + 8 * NS, k_empty0 = k_xf0 + 8 * NS;
+  const uint32_t v_full0 = k_empty0 + 8 * NS, vr_empty0 = v_full0 + 8 * NS, vt_full0 = vr_empty0 + 8 * NS,
+                 vt_empty0 = vt_full0 + 8 * NS;
+  // two-deep: S, O, P buffers
+  const uint32_t s_full0 = vt_empty0 + 8 * NS, s_empty0 = s_full0 + 16, o_full0 = s_empty0 + 16, o_empty0 = o_full0 + 16,
+                 p_full0 = o_empty0 + 16, q_full = p_full0 + 16, q_tm = q_full + 8;
   const uint32_t tslot = bars + N_BARS * 8;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + SMEM_DATA + N_BARS * 8);
 
@@ -125,7 +148,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     prefetch_tmap(&tmQ);
     prefetch_tmap(&tmKV);
     prefetch_tmap(&tmV);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < NS; ++s) {
       mbar_init(k_full0 + 8 * s, 1);
       mbar_init(k_xf0 + 8 * s, N_XF_WARPS);
       mbar_init(k_empty0 + 8 * s, 1);
@@ -133,15 +156,16 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       mbar_init(vr_empty0 + 8 * s, N_XF_WARPS);
       mbar_init(vt_full0 + 8 * s, N_XF_WARPS);
       mbar_init(vt_empty0 + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(s_full0 + 8 * s, 1);
       mbar_init(s_empty0 + 8 * s, N_SOFTMAX_WARPS);
       mbar_init(o_full0 + 8 * s, 1);
       mbar_init(o_empty0 + 8 * s, N_SOFTMAX_WARPS);
+      mbar_init(p_full0 + 8 * s, N_SOFTMAX_WARPS);
     }
-    mbar_init(p_full, N_SOFTMAX_WARPS);
-    mbar_init(p_empty, 1);
     mbar_init(q_full, 1);
-    mbar_init(q_xf, N_XF_WARPS);
+    mbar_init(q_tm, N_SOFTMAX_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tslot, TMEM_COLS);
@@ -154,10 +178,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // ================= TMA producer =================
     if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
       mbar_expect_tx(q_full, Q_BYTES);
-      tma_load_3d(smem0 + OFF_QH, &tmQ, q_full, h * DK, q0, b);
+      tma_load_3d(smem0 + OFF_Q, &tmQ, q_full, h * DK, q0, b);
+      int s = 0;
+      uint32_t ph = 1;  // "empty" parity of a fresh barrier
       for (int j = 0; j < NT; ++j) {
-        const int s = j & 1;
-        const uint32_t ph = ((j >> 1) & 1) ^ 1;
         mbar_wait(vr_empty0 + 8 * s, ph);
         ATT_TRACE(0, j);
         mbar_expect_tx(v_full0 + 8 * s, KV_BYTES);
@@ -166,56 +190,55 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         ATT_TRACE(1, j);
         mbar_expect_tx(k_full0 + 8 * s, KV_BYTES);
         tma_load_3d(smem0 + OFF_K + s * 2 * KV_BYTES, &tmKV, k_full0 + 8 * s, D + h * DK, j * BKV, b);  // K_j -> K_hi slot
+        if (++s == NS) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (elect_one()) {  // elect.sync, not lane == 0: lets ptxas issue TMA / MMA without a per-instruction elect loop
-      const uint32_t idesc_s = make_idesc(2u, BKV);               // tf32, N = 64, A and B K-major
+      const uint32_t idesc_s = make_idesc(2u, BKV);               // tf32, N = 64, B = K K-major
       const uint32_t idesc_o = make_idesc(2u, DK);                // tf32, N = 32, B = V^T K-major
-      const uint32_t qh = desc_lo(smem0 + OFF_QH), ql = desc_lo(smem0 + OFF_QL);
-      const uint32_t ph = desc_lo(smem0 + OFF_PH), pl = desc_lo(smem0 + OFF_PL);
+      const uint32_t qh = tmem_base + COL_QH, ql = tmem_base + COL_QL;
       auto issue_s = [&](int j) {
-        const int s = j & 1;
-        mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
-        mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
+        const int s = j % NS, sb = j & 1;
+        mbar_wait(k_xf0 + 8 * s, (j / NS) & 1);
+        mbar_wait(s_empty0 + 8 * sb, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
         ATT_TRACE(6, j);
         const uint32_t kh = desc_lo(smem0 + OFF_K + s * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
-        const uint32_t d = tmem_base + COL_S + s * BKV;
+        const uint32_t d = tmem_base + COL_S + sb * BKV;
 #pragma unroll
-        for (int kk = 0; kk < DK / 8; ++kk) {  // 8 head dims = 32 bytes of each operand row per instruction
-          const uint32_t o = kk * 2;
-          umma_tf32_w(d, ql + o, kh + o, idesc_s, kk != 0);
-          umma_tf32_w(d, qh + o, kl + o, idesc_s, 1u);
-          umma_tf32_w(d, qh + o, kh + o, idesc_s, 1u);
+        for (int kk = 0; kk < DK / 8; ++kk) {  // 8 head dims per instruction: 8 TMEM columns of Q, 32 bytes of each K row
+          umma_tf32_ts_w(d, ql + kk * 8, kh + kk * 2, idesc_s, kk != 0);
+          umma_tf32_ts_w(d, qh + kk * 8, kl + kk * 2, idesc_s, 1u);
+          umma_tf32_ts_w(d, qh + kk * 8, kh + kk * 2, idesc_s, 1u);
         }
-        umma_commit(s_full0 + 8 * s);
+        umma_commit(s_full0 + 8 * sb);
         umma_commit(k_empty0 + 8 * s);
         ATT_TRACE(7, j);
       };
-      mbar_wait(q_xf, 0);
+      mbar_wait(q_tm, 0);
+      tc_fence_after();
       issue_s(0);
       for (int j = 0; j < NT; ++j) {
         if (j + 1 < NT) issue_s(j + 1);
-        const int s = j & 1;
-        mbar_wait(vt_full0 + 8 * s, (j >> 1) & 1);
-        mbar_wait(p_full, j & 1);
-        mbar_wait(o_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
+        const int s = j % NS, pb = j & 1;
+        mbar_wait(vt_full0 + 8 * s, (j / NS) & 1);
+        mbar_wait(p_full0 + 8 * pb, (j >> 1) & 1);
+        mbar_wait(o_empty0 + 8 * pb, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
         ATT_TRACE(8, j);
         const uint32_t vh = desc_lo(smem0 + OFF_VT + s * 2 * KV_BYTES), vl = vh + (KV_BYTES >> 4);  // V^T hi / lo
-        const uint32_t d = tmem_base + COL_O + s * DK;
+        const uint32_t ph = tmem_base + COL_P + pb * 2 * BKV, pl = ph + BKV;
+        const uint32_t d = tmem_base + COL_O + pb * DK;
 #pragma unroll
-        for (int ks = 0; ks < BKV / 8; ++ks) {  // 8 keys per instruction
-          const uint32_t pa = ((ks >> 2) * Q_BYTES + (ks & 3) * 32) >> 4;     // chunk of 32 keys, then 32 bytes per step
+        for (int ks = 0; ks < BKV / 8; ++ks) {  // 8 keys per instruction: 8 TMEM columns of P, 32 bytes of each V^T row
           const uint32_t vb = ((ks >> 2) * (DK * 128) + (ks & 3) * 32) >> 4;  // V^T: 32 rows x 128 B per 32-key chunk
-          umma_tf32_w(d, pl + pa, vh + vb, idesc_o, ks != 0);
-          umma_tf32_w(d, ph + pa, vl + vb, idesc_o, 1u);
-          umma_tf32_w(d, ph + pa, vh + vb, idesc_o, 1u);
+          umma_tf32_ts_w(d, pl + ks * 8, vh + vb, idesc_o, ks != 0);
+          umma_tf32_ts_w(d, ph + ks * 8, vl + vb, idesc_o, 1u);
+          umma_tf32_ts_w(d, ph + ks * 8, vh + vb, idesc_o, 1u);
         }
-        umma_commit(o_full0 + 8 * s);
-        umma_commit(p_empty);
+        umma_commit(o_full0 + 8 * pb);
         umma_commit(vt_empty0 + 8 * s);
         ATT_TRACE(9, j);
       }
@@ -227,14 +250,31 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int half = (warp - 2) >> 2;
     const int r = lg * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
+    {  // Q row: shared staging (one swizzled 128-byte row) -> TMEM; half 0 stores hi, half 1 stores lo
+      mbar_wait(q_full, 0);
+      const uint8_t* row = smem_al + OFF_Q + r * 128;
+      const int sw = r & 7;
+      float qv[32];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+        const float4 hq = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
+        qv[4 * u + 0] = half ? tf32_rn(x.x - hq.x) : hq.x;
+        qv[4 * u + 1] = half ? tf32_rn(x.y - hq.y) : hq.y;
+        qv[4 * u + 2] = half ? tf32_rn(x.z - hq.z) : hq.z;
+        qv[4 * u + 3] = half ? tf32_rn(x.w - hq.w) : hq.w;
+      }
+      tmem_st32(lane_base + (half ? COL_QL : COL_QH), qv);
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(q_tm);
+    }
     float m = -INFINITY, l = 0.f, alpha_fold = 1.f;
     const float scale_log2 = 1.4426950408889634f / temperature;
     float o[DK / 2];
 #pragma unroll
     for (int i = 0; i < DK / 2; ++i) o[i] = 0.f;
-    uint8_t* ph_row = smem_al + OFF_PH + half * Q_BYTES + r * 128;  // this half's 32-key chunk of P
-    uint8_t* pl_row = smem_al + OFF_PL + half * Q_BYTES + r * 128;
-    const int sw = r & 7;
 
     auto fold_o = [&](int jj, float alpha) {  // o = o*alpha + O_jj (this half's 16 columns)
       const int ob = jj & 1;
@@ -292,30 +332,30 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         sum4[i & 3] += sa[i];
       }
       l = l * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
+      if (warp == 2 && lane == 0) ATT_TRACE(14, j);
 
-      if (warp == 2 && lane == 0) ATT_TRACE(14, j);  // exponentials done, waiting for the P buffer
-      mbar_wait(p_empty, (j & 1) ^ 1);  // P.V of the previous tile has finished reading P
+      // P_j (this half's 32 keys) -> TMEM as TF32 hi / lo.  Buffer j & 1 was last read by P.V_{j-2}, which had
+      // retired before fold(j-2) returned in the previous iteration.
+      const uint32_t pcol = lane_base + COL_P + sb * 2 * BKV + half * 32;
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {  // 16-byte unit u of this row lives at unit (u ^ (row & 7)) - SWIZZLE_128B
-        const int pu = (u ^ sw) * 16;
-        const float4 a = make_float4(sa[4 * u], sa[4 * u + 1], sa[4 * u + 2], sa[4 * u + 3]);
-        const float4 ah = make_float4(tf32_rn(a.x), tf32_rn(a.y), tf32_rn(a.z), tf32_rn(a.w));
-        *reinterpret_cast<float4*>(ph_row + pu) = ah;
-        *reinterpret_cast<float4*>(pl_row + pu) =
-            make_float4(tf32_rn(a.x - ah.x), tf32_rn(a.y - ah.y), tf32_rn(a.z - ah.z), tf32_rn(a.w - ah.w));
-      }
-      fence_proxy_async();
+      for (int i = 0; i < 32; ++i) sc[i] = tf32_rn(sa[i]);
+      tmem_st32(pcol, sc);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) sa[i] = tf32_rn(sa[i] - sc[i]);
+      tmem_st32(pcol + BKV, sa);
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
+      if (lane == 0) mbar_arrive(p_full0 + 8 * sb);
       if (warp == 2 && lane == 0) ATT_TRACE(11, j);
 
-      if (j > 0) fold_o(j - 1, alpha_fold);  // O_{j-1} landed together with p_empty
+      if (j > 0) fold_o(j - 1, alpha_fold);
       alpha_fold = alpha;
     }
     fold_o(NT - 1, alpha_fold);
 
-    // merge the two halves' row sums through shared memory (all MMAs have retired: P is free)
-    float* lbuf = reinterpret_cast<float*>(smem_al + OFF_PH);
+    // merge the two halves' row sums through shared memory (all loads have landed and been consumed: Q staging is free)
+    float* lbuf = reinterpret_cast<float*>(smem_al + OFF_Q);
     lbuf[half * BQ + r] = l;
     asm volatile("bar.sync 1, %0;" ::"n"(N_SOFTMAX_WARPS * 32) : "memory");
     l += lbuf[(half ^ 1) * BQ + r];
@@ -331,14 +371,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // ================= operand split / transpose (2 warps) =================
     const int w = warp - 2 - N_SOFTMAX_WARPS;
     const int tt = w * 32 + lane;
-    mbar_wait(q_full, 0);
-    split_tile(reinterpret_cast<float4*>(smem_al + OFF_QH), reinterpret_cast<float4*>(smem_al + OFF_QL), Q_BYTES / 16, tt);
-    fence_proxy_async();
-    __syncwarp();
-    if (lane == 0) mbar_arrive(q_xf);
+    int s = 0;
+    uint32_t ph = 0;
     for (int j = 0; j < NT; ++j) {
-      const int s = j & 1;
-      const uint32_t ph = (j >> 1) & 1;
       mbar_wait(k_full0 + 8 * s, ph);
       if (tt == 0) ATT_TRACE(2, j);
       split_tile(reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES),
@@ -349,7 +384,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (tt == 0) ATT_TRACE(3, j);
 
       mbar_wait(v_full0 + 8 * s, ph);
-      mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-2} has retired
+      mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-NS} has retired
       if (tt == 0) ATT_TRACE(4, j);
       {  // V [64 keys x 32 dims] -> V^T hi / lo [32 dims x 64 keys], K-major, 128-byte swizzle
         const float* vraw = reinterpret_cast<const float*>(smem_al + OFF_VR + s * KV_BYTES);
@@ -378,6 +413,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_arrive(vt_full0 + 8 * s);
       }
       if (tt == 0) ATT_TRACE(5, j);
+      if (++s == NS) { s = 0; ph ^= 1; }
     }
   }
 
