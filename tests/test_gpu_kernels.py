@@ -113,6 +113,36 @@ def test_conv1d_epilogues(ops, backend, monkeypatch):
     assert (acc.cpu() - want).abs().max().item() <= 2e-5
 
 
+@pytest.mark.parametrize("B,S,Cin,Cout,k,dil", [
+    (7, 50, 64, 128, 9, 1),     # several utterances inside one 128-row tile; halo wider than the gaps
+    (5, 129, 256, 256, 1, 1),   # one row past a tile: every tile straddles
+    (3, 300, 64, 80, 11, 5),    # dilated taps reaching 25 frames across an utterance end; Cout not a tile multiple
+    (64, 119, 256, 256, 3, 1),  # the encoder's shape
+    (9, 1, 256, 256, 1, 1),     # S = 1
+])
+def test_conv1d_flat_tiling_across_utterances(ops, B, S, Cin, Cout, k, dil):
+    """The default 3xTF32 kernel tiles stride-1 same-length layers over the flattened B*S rows:
+    taps must not leak across utterance ends, and bias / relu / residual / row mask must land on the right
+    (utterance, frame) of tiles that straddle.  Checked against torch per utterance and against the kernel's own
+    per-utterance tiling (one launch per utterance)."""
+    x, w, b = rnd(B, S, Cin, seed=61), rnd(Cout, Cin, k, seed=62, scale=1 / math.sqrt(Cin * k)), rnd(Cout, seed=63)
+    res = rnd(B, S, Cout, seed=64)
+    lens = torch.tensor([(S * (i + 1)) // B if i % 2 else S for i in range(B)], dtype=torch.int32)
+    pad = (k - 1) // 2 * dil
+    conv = F.conv1d(x.transpose(1, 2).double(), w.double(), b.double(), padding=pad, dilation=dil).transpose(1, 2)
+    keep = (torch.arange(S)[None, :] < lens[:, None])[..., None]
+    want = (F.relu(conv) + res.double()) * keep
+    W = pack(w)
+    y = ops.conv1d(x.to(DEV), W, b.to(DEV), k=k, dilation=dil, pad=pad, act=ops.ACT_RELU, residual=res.to(DEV),
+                   lens=lens.to(DEV), backend="tf32x3_ts")
+    assert (y.cpu().double() - want).abs().max().item() <= 2e-5
+    # one launch per utterance (B = 1 turns flat tiling off): per-utterance tiling must agree to the last bit
+    y2 = torch.cat([ops.conv1d(x[i:i + 1].to(DEV), W, b.to(DEV), k=k, dilation=dil, pad=pad, act=ops.ACT_RELU,
+                               residual=res[i:i + 1].to(DEV), lens=lens[i:i + 1].to(DEV), backend="tf32x3_ts")
+                    for i in range(B)])
+    assert torch.equal(y, y2)
+
+
 @pytest.mark.parametrize("Cin,Cout,k,u,S", [(512, 256, 16, 8, 13), (128, 64, 4, 2, 50), (64, 32, 4, 2, 129)])
 def test_conv_transpose_phase_form(ops, Cin, Cout, k, u, S):
     from speakingstyle_b200 import configs as C
