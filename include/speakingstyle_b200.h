@@ -327,6 +327,17 @@ SS_API int ss_add_speaker(float* x, const int64_t* ids, const float* table, int 
 SS_API int ss_hifigan_post(const float* x, const float* w, const float* bias, float* wave, int16_t* pcm,
                            float pcm_scale, float in_slope, int B, int T, int C, int k, void* stream);
 
+/* Ragged PCM epilogue: what utils/model.py:105-113 (x32768, astype int16, trim each wave to
+ * mel_len*hop) and utils/tools.py:222-230 do on the host after a full fp32 D2H.  Same head as ss_hifigan_post,
+ * but utterance b writes only its first n_samples[b] samples (clamped to [0,T]), contiguously from
+ * pcm[out_offset[b]]; samples past an utterance's end are neither computed nor written.  n_samples [B] int32 and
+ * out_offset [B] int64 are device arrays.  pcm may be device memory or page-locked host memory (under unified
+ * addressing its host pointer is also its device pointer): then the trimmed int16 samples are the only bytes that
+ * cross PCIe and no separate copy is needed - synchronise the stream before reading them on the host. */
+SS_API int ss_hifigan_post_trim(const float* x, const float* w, const float* bias, const int32_t* n_samples,
+                                const int64_t* out_offset, int16_t* pcm, float pcm_scale, float in_slope, int B, int T,
+                                int C, int k, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

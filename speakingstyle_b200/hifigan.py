@@ -138,7 +138,17 @@ class Generator(nn.Module, ParamCache):
         pk["post"] = wp[0].t().contiguous().reshape(-1)
         return pk
 
-    def _forward_bf16(self, x, pcm):
+    def _post(self, xs, pk, pcm, pcm_out):
+        """Output head.  pcm_out = (n_samples [B] int32 dev, out_offset [B] int64 dev, flat int16 buffer): ragged PCM
+        straight into that buffer (ss_hifigan_post_trim) instead of the padded float wave."""
+        if pcm_out is not None:
+            return ops.hifigan_post_trim(xs, pk["post"], self.conv_post.bias, *pcm_out, k=7, in_slope=0.01)
+        wave, pcm16 = ops.hifigan_post(xs, pk["post"], self.conv_post.bias, k=7, in_slope=0.01, want_wave=True,
+                                       want_pcm=pcm)
+        wave = wave.unsqueeze(1)
+        return (wave, pcm16) if pcm else wave
+
+    def _forward_bf16(self, x, pcm, pcm_out=None):
         """Tensor-core path.  Convolution operands are bf16; the residual stream of every ResBlock and
         the stage mean stay fp32.  Each epilogue also emits the leaky-ReLU'd bf16 copy that the next
         convolution consumes (the activation cannot sit between TMA and the MMA)."""
@@ -170,15 +180,14 @@ class Generator(nn.Module, ParamCache):
                                             want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0),
                                             act2=L if feeds_ups else None, slope2=LRELU_SLOPE)[1]
             xa = nxt
-        wave, pcm16 = ops.hifigan_post(xs, pk["post"], self.conv_post.bias, k=7, in_slope=0.01, want_wave=True,
-                                       want_pcm=pcm)
-        wave = wave.unsqueeze(1)
-        return (wave, pcm16) if pcm else wave
+        return self._post(xs, pk, pcm, pcm_out)
 
     @torch.no_grad()
-    def forward(self, x, channels_last=False, pcm=False):
+    def forward(self, x, channels_last=False, pcm=False, pcm_out=None):
         """x: mel [B,80,T] (reference layout) or [B,T,80] with channels_last=True.
-        Returns wave [B,1,256*T] float32; with pcm=True returns (wave, int16 [B,256*T])."""
+        Returns wave [B,1,256*T] float32; with pcm=True returns (wave, int16 [B,256*T]).
+        pcm_out = (n_samples [B] int32, out_offset [B] int64, flat int16 buffer - device or pinned host): the ragged
+        PCM epilogue of SURVEY 8(f1); returns that buffer and produces no padded wave."""
         if not x.is_cuda:
             raise RuntimeError("speakingstyle_b200 Generator needs CUDA tensors; there is no CPU fallback")
         h = self.h
@@ -187,7 +196,7 @@ class Generator(nn.Module, ParamCache):
             x = x.transpose(1, 2)
         x = x.to(torch.float32).contiguous()
         if self.precision == "bf16":
-            return self._forward_bf16(x, pcm)
+            return self._forward_bf16(x, pcm, pcm_out)
         x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3)
         nk = self.num_kernels
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
@@ -215,7 +224,4 @@ class Generator(nn.Module, ParamCache):
                                    in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, write_y=False,
                                    accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0))
             x = xs
-        wave, pcm16 = ops.hifigan_post(x, pk["post"], self.conv_post.bias, k=7, in_slope=0.01, want_wave=True,
-                                       want_pcm=pcm)
-        wave = wave.unsqueeze(1)
-        return (wave, pcm16) if pcm else wave
+        return self._post(x, pk, pcm, pcm_out)

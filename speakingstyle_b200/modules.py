@@ -167,6 +167,7 @@ class VarianceAdaptor(nn.Module):
         if duration_target is not None:
             # teacher forcing (modules.py:133-135): expand by the given durations to max_len; mel_mask is the caller's
             d_rounded = duration_target
+            self.last_mel_len_host = None
             T = int(max_len) if max_len is not None else None
             pe = decoder_pe(T) if (callable(decoder_pe) and T is not None) else (None if callable(decoder_pe) else decoder_pe)
             out, mel_len = self.length_regulator(x, duration_target, max_len, pe=pe)
@@ -181,6 +182,7 @@ class VarianceAdaptor(nn.Module):
             out, m2p = res if return_extra else (res, None)
             mel_len = lens2[1]  # int32, from the float sum (modules.py:143)
             mel_mask = ops.length_mask(mel_len, int(lens_host[1].max()))
+            self.last_mel_len_host = lens_host[1]  # already on the host: lets the wave epilogue trim without a second sync
             extra = {"mel2phone": m2p, "pitch_idx": pitch_idx, "energy_idx": energy_idx, "T": T,
                      "mel_len_expand": lens2[0]}
         ret = (out, pitch, energy, log_d, d_rounded, mel_len, mel_mask)

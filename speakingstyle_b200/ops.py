@@ -443,3 +443,17 @@ def hifigan_post(x, w, bias, *, k, in_slope=0.01, want_wave=True, want_pcm=False
     check(_lib.lib().ss_hifigan_post(_ptr(x), _ptr(w), _ptr(bias), _ptr(wave), _ptr(pcm), float(pcm_scale),
                                      float(in_slope), B, T, Cc, k, _stream()))
     return wave, pcm
+
+
+def hifigan_post_trim(x, w, bias, n_samples, out_offset, pcm_out, *, k, in_slope=0.01, pcm_scale=32768.0):
+    """Ragged PCM epilogue (ss_hifigan_post_trim): utterance b's first n_samples[b] int16 samples go to
+    pcm_out[out_offset[b]:].  n_samples [B] int32 / out_offset [B] int64 on the device; pcm_out is a flat int16
+    tensor on the device or in page-locked host memory (written by the kernel over PCIe, no separate copy)."""
+    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w")
+    _chk(n_samples, torch.int32, "n_samples"); _chk(out_offset, torch.int64, "out_offset")
+    if pcm_out.dtype != torch.int16 or not pcm_out.is_contiguous() or not (pcm_out.is_cuda or pcm_out.is_pinned()):
+        raise _lib.SSError("hifigan_post_trim: pcm_out must be a contiguous int16 tensor on the device or in pinned host memory")
+    B, T, Cc = x.shape
+    check(_lib.lib().ss_hifigan_post_trim(_ptr(x), _ptr(w), _ptr(bias), _ptr(n_samples), _ptr(out_offset),
+                                          pcm_out.data_ptr(), float(pcm_scale), float(in_slope), B, T, Cc, k, _stream()))
+    return pcm_out

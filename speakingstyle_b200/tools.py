@@ -24,19 +24,43 @@ def get_vocoder(h=None, device="cuda", state_dict=None, precision="fp32"):
 
 
 @torch.no_grad()
+def _ragged_pcm(vocoder, mels, n_samples, channels_last):
+    """Runs the vocoder with the ragged PCM epilogue writing into pinned host memory; returns one int16 numpy view
+    per utterance (no padded wave, no separate D2H copy - the kernel's stores are what crosses PCIe)."""
+    T = mels.shape[1] if channels_last else mels.shape[2]
+    hop = 1
+    for u in vocoder.h["upsample_rates"]:
+        hop *= u
+    n = [max(0, min(int(v), T * hop)) for v in n_samples]
+    offs = [0]
+    for v in n:
+        offs.append(offs[-1] + v)
+    host = torch.empty(max(offs[-1], 1), dtype=torch.int16, pin_memory=True)  # cached pinned allocator: cheap after the first call
+    dev = mels.device
+    n_dev = torch.tensor(n, dtype=torch.int32).to(dev, non_blocking=True)
+    o_dev = torch.tensor(offs[:-1], dtype=torch.int64).to(dev, non_blocking=True)
+    vocoder(mels, channels_last=channels_last, pcm_out=(n_dev, o_dev, host))
+    torch.cuda.current_stream(dev).synchronize()
+    flat = host.numpy()
+    return [flat[offs[i]:offs[i + 1]] for i in range(len(n))]
+
+
 def vocoder_infer(mels, vocoder, model_config=None, preprocess_config=None, lengths=None):
     """utils/model.py:97-115: mels [B,80,T] -> list of int16 numpy arrays trimmed to ``lengths``.
-    The scaling and the int16 truncation happen in the output kernel; only int16 crosses PCIe."""
+    The x32768 scaling, the int16 truncation and the trim happen in the output kernel, which writes each
+    utterance's valid samples straight into pinned host memory; with lengths=None the whole padded
+    waves are returned, as the reference does."""
     scale = 32768.0
     if preprocess_config is not None:
         scale = float(preprocess_config["preprocessing"]["audio"]["max_wav_value"])
     if scale != 32768.0:
         raise NotImplementedError("max_wav_value other than 32768 is not wired into the PCM epilogue")
-    _, pcm = vocoder(mels, pcm=True)
-    wavs = [w for w in pcm.cpu().numpy()]
-    if lengths is not None:
-        wavs = [w[: int(n)] for w, n in zip(wavs, lengths)]
-    return wavs
+    B, T = mels.shape[0], mels.shape[2]
+    hop = 1
+    for u in vocoder.h["upsample_rates"]:
+        hop *= u
+    n = [T * hop] * B if lengths is None else [int(v) for v in lengths]
+    return _ragged_pcm(vocoder, mels, n, channels_last=False)
 
 
 @torch.no_grad()
@@ -48,7 +72,8 @@ def synthesize_batch(model, vocoder, batch, p_control=1.0, e_control=1.0, d_cont
                 d_control=d_control)
     wavs = None
     if vocoder is not None:
-        lengths = (out[9] * hop_length).cpu().tolist()
-        _, pcm = vocoder(out[1], channels_last=True, pcm=True)
-        wavs = [w[:n] for w, n in zip(pcm.cpu().numpy(), lengths)]
+        mel_len = getattr(model.variance_adaptor, "last_mel_len_host", None)  # read once inside forward()
+        if mel_len is None or len(mel_len) != out[9].shape[0]:
+            mel_len = out[9].cpu()
+        wavs = _ragged_pcm(vocoder, out[1], [int(v) * hop_length for v in mel_len.tolist()], channels_last=True)
     return out, wavs

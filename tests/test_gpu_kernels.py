@@ -331,6 +331,37 @@ def test_hifigan_post_and_pcm(ops):
     assert np.array_equal(pcm.cpu().numpy().reshape(-1), want)
 
 
+@pytest.mark.parametrize("where", ["device", "pinned_host"])
+def test_hifigan_post_trim_writes_ragged_pcm(ops, where):
+    """each utterance's first n_samples int16 samples, back to back, and nothing else - into device
+    memory or straight into page-locked host memory.  Bit-exact against the padded PCM epilogue."""
+    B, T, C, k = 5, 1000, 32, 7
+    x = rnd(B, T, C, seed=47).to(DEV)
+    w, b = rnd(1, C, k, seed=48, scale=0.4)[0].t().contiguous().reshape(-1).to(DEV), torch.tensor([0.05]).to(DEV)
+    _, pcm = ops.hifigan_post(x, w, b, k=k, want_pcm=True)
+    n = [1000, 0, 257, 999, 1]          # full, empty, one past a CTA tile, ...
+    slack = [3, 0, 5, 0, 2]             # gaps between utterances must stay untouched
+    offs, pos = [], 0
+    for ni, sl in zip(n, slack):
+        offs.append(pos)
+        pos += ni + sl
+    buf = torch.full((pos + 7,), -12345, dtype=torch.int16)
+    buf = buf.to(DEV) if where == "device" else buf.pin_memory()
+    out = ops.hifigan_post_trim(x, w, b, torch.tensor(n, dtype=torch.int32, device=DEV),
+                                torch.tensor(offs, dtype=torch.int64, device=DEV), buf, k=k)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    want = np.full(pos + 7, -12345, dtype=np.int16)
+    for i in range(B):
+        want[offs[i]:offs[i] + n[i]] = pcm[i, :n[i]].cpu().numpy()
+    assert np.array_equal(got, want)
+    # n_samples beyond T is clamped
+    big = torch.zeros(T + 4, dtype=torch.int16, device=DEV)
+    ops.hifigan_post_trim(x[:1], w, b, torch.tensor([T + 100], dtype=torch.int32, device=DEV),
+                          torch.zeros(1, dtype=torch.int64, device=DEV), big, k=k)
+    assert torch.equal(big[:T], pcm[0]) and int(big[T:].abs().sum()) == 0
+
+
 def test_errors_cross_the_abi_as_exceptions(ops):
     from speakingstyle_b200._lib import SSError
 

@@ -191,6 +191,34 @@ def test_hifigan_small_vs_golden_and_stages(golden):
     assert maxabs(gen(mel3.to(DEV)), ref) <= 1e-4
 
 
+def test_vocoder_infer_and_synthesize_batch_return_trimmed_int16(golden):
+    """utils/model.py:97-115 / utils/tools.py:222-230 through the ragged PCM epilogue: same samples as
+    the padded int16 path, trimmed per utterance, delivered in pinned host memory."""
+    from speakingstyle_b200 import tools
+    g = golden("hifigan_small")
+    gen, h, vsd = get_vocoder()
+    mel = torch.from_numpy(g["mel"]).to(DEV)
+    _, pcm = gen(mel, pcm=True)
+    pcm = pcm.cpu().numpy()
+    lengths = [pcm.shape[1] - 300, 256 * 3 + 1]
+    wavs = tools.vocoder_infer(mel, gen, lengths=lengths)
+    assert [w.dtype for w in wavs] == [np.int16] * 2 and [len(w) for w in wavs] == lengths
+    for i, w in enumerate(wavs):
+        assert np.array_equal(w, pcm[i, :lengths[i]])
+        assert np.abs(w.astype(np.int32) - g["wave_int16"][i, :lengths[i]].astype(np.int32)).max() <= 4
+    full = tools.vocoder_infer(mel, gen)  # lengths=None: whole padded waves, as the reference returns them
+    assert all(np.array_equal(full[i], pcm[i]) for i in range(2))
+    # end to end: FastSpeech2 -> Generator, waves trimmed to mel_len * hop
+    ds, batch, _ = S.make_workload("tiny")
+    model = get_models(ds)[0]
+    out, waves = tools.synthesize_batch(model, gen, batch)
+    mel_lens = out[9].cpu().tolist()
+    assert [len(w) for w in waves] == [m * 256 for m in mel_lens]
+    _, pcm2 = gen(out[1], channels_last=True, pcm=True)
+    for i, w in enumerate(waves):
+        assert np.array_equal(w, pcm2[i, :mel_lens[i] * 256].cpu().numpy())
+
+
 def test_modules_standalone_api():
     """The sub-modules keep the reference's own signatures."""
     import speakingstyle_b200 as ss
