@@ -338,6 +338,21 @@ SS_API int ss_hifigan_post_trim(const float* x, const float* w, const float* bia
                                 const int64_t* out_offset, int16_t* pcm, float pcm_scale, float in_slope, int B, int T,
                                 int C, int k, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Reference-mel front-end: audio/stft.py:51-81 (STFT.transform), :160-178 (TacotronSTFT.mel_spectrogram),
+ * audio/audio_processing.py:85-91 (dynamic_range_compression).  The two contractions are ss_conv1d_tf32x3_ts calls
+ * (Fourier basis as a k = n_fft/hop convolution over hop-sized rows; mel filterbank as a k = 1 layer); these are the
+ * steps around them.
+ * ------------------------------------------------------------------------------------------ */
+/* out[b, i] = y[b, reflect(i - half)] for i < n_out <= T + 2*half   (F.pad(mode="reflect"), stft.py:59-64) */
+SS_API int ss_reflect_pad(const float* y, float* out, int B, int T, int half, int n_out, void* stream);
+/* spec [rows, spec_stride] = [re(n_bins) | im(n_bins) | pad] -> mag [rows, mag_stride] = sqrt(re^2+im^2), zero in the
+ * padding columns (stft.py:76-79); energy [rows] = ||mag||_2 (stft.py:176), may be NULL */
+SS_API int ss_stft_magnitude(const float* spec, float* mag, float* energy, int64_t rows, int n_bins, int spec_stride,
+                             int mag_stride, void* stream);
+/* x[i] = log(max(x[i], clip))  in place (audio_processing.py:85-91, C = 1) */
+SS_API int ss_log_clamp(float* x, int64_t n, float clip, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -157,6 +157,28 @@ def save_length_regulator():
     print("length_regulator.npz written")
 
 
+def save_mel_frontend():
+    """wave -> log-mel through the reference's own TacotronSTFT (audio/stft.py) - librosa's filterbank replaced by
+    the restatement in oracle/mel_oracle.py (librosa is not installed: filterbank values unpinned, the rest pinned)."""
+    st = rh.load_audio()
+    t = st.TacotronSTFT(1024, 256, 1024, 80, 22050, 0.0, 8000.0)
+    g = torch.Generator().manual_seed(505)
+    n = torch.arange(9000, dtype=torch.float32)
+    tone = 0.4 * torch.sin(2 * np.pi * 440.0 * n / 22050) + 0.2 * torch.sin(2 * np.pi * 3000.0 * n / 22050)
+    y = torch.stack([tone + 0.05 * torch.randn(9000, generator=g), (torch.rand(9000, generator=g) * 2 - 1) * 0.9,
+                     torch.cat([torch.zeros(4500), 0.5 * torch.randn(4500, generator=g).clamp(-1.9, 1.9)])]).clamp(-1, 1)
+    y_odd = y[:2, :4099].contiguous()
+    with torch.no_grad():
+        mel, en = t.mel_spectrogram(y)
+        mel_o, en_o = t.mel_spectrogram(y_odd)
+    fb = t.stft_fn.forward_basis
+    path = os.path.join(GOLDEN, "mel_frontend.npz")
+    np.savez_compressed(path, y=y.numpy(), mel=mel.numpy(), energy=en.numpy(), y_odd=y_odd.numpy(), mel_odd=mel_o.numpy(),
+                        energy_odd=en_o.numpy(), mel_basis=t.mel_basis.numpy(), forward_basis_s=fb[::19, 0, ::7].numpy(),
+                        forward_basis_abs=np.float64(fb.double().abs().sum().item()))
+    print(f"mel_frontend -> {path} ({os.path.getsize(path) / 1024:.0f} KiB) mel {tuple(mel.shape)}")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--large", action="store_true")
@@ -171,6 +193,7 @@ def main():
         "tiny_ms": lambda: save_full("tiny_ms", "tiny_ms"),
         "tiny_ctl": lambda: save_full("tiny", "tiny_ctl", controls=(1.2, 0.8, 1.3)),
         "tiny_tf": save_teacher_forced,
+        "mel_frontend": save_mel_frontend,
         "cfg1": lambda: save_compact("cfg1"),
     }
     if args.large:

@@ -52,6 +52,44 @@ def _install_stubs():
         mpl.pylab = stub("matplotlib.pylab")
 
 
+def load_audio():
+    """The reference's audio.stft module (STFT, TacotronSTFT) with stand-ins for the librosa symbols it imports at
+    module level (audio/stft.py:5-6; librosa is not installed here): pad_center / tiny are one-liners, and
+    filters.mel is the restatement in oracle/mel_oracle.py - so the filterbank VALUES are unpinned, everything
+    else (reflect pad, Fourier-basis convolution, magnitude, log compression, energy) is the reference's own code."""
+    if "audio" in _loaded:
+        return _loaded["audio"]
+    if not available():
+        raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
+    import numpy as np
+    from oracle import mel_oracle
+
+    def pad_center(data, size, axis=-1, **kw):
+        n = data.shape[axis]
+        lpad = int((size - n) // 2)
+        lengths = [(0, 0)] * data.ndim
+        lengths[axis] = (lpad, int(size - n - lpad))
+        return np.pad(data, lengths, **kw)
+
+    try:
+        import librosa  # noqa: F401
+    except ImportError:
+        lib = types.ModuleType("librosa")
+        util = types.ModuleType("librosa.util")
+        util.pad_center, util.tiny = pad_center, (lambda x: np.finfo(np.float32).tiny)
+        filters = types.ModuleType("librosa.filters")
+        filters.mel = lambda sr, n_fft, n_mels=128, fmin=0.0, fmax=None: mel_oracle.slaney_mel(sr, n_fft, n_mels, fmin, fmax)
+        lib.util, lib.filters = util, filters
+        sys.modules.update({"librosa": lib, "librosa.util": util, "librosa.filters": filters})
+    if REFERENCE_ROOT not in sys.path:
+        sys.path.insert(0, REFERENCE_ROOT)
+    import torch.cuda
+    with contextlib.redirect_stdout(io.StringIO()):
+        import audio.stft as ref_stft
+    _loaded["audio"] = ref_stft
+    return ref_stft
+
+
 _loaded = {}
 
 

@@ -7,6 +7,7 @@ include/speakingstyle_b200.h (libspeakingstyle_b200.so, loaded with ctypes).  Py
 device memory, streams and torch.distributed only.  There is no CPU or eager fallback: importing
 the model classes works anywhere, running them needs the built library and a CUDA device.
 """
+from .audio import STFT, TacotronSTFT, get_mel_from_wav  # noqa: F401
 from .configs import AttrDict, hifigan_config, model_config, preprocess_config  # noqa: F401
 from .fastspeech2 import FastSpeech2  # noqa: F401
 from .hifigan import Generator, ResBlock  # noqa: F401

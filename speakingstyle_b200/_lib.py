@@ -84,6 +84,9 @@ _SIGNATURES = {
     "ss_mean_pool": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_add_speaker": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_hifigan_post": (C.c_int, [vp, vp, vp, vp, vp, f32, f32, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_reflect_pad": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_stft_magnitude": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_log_clamp": (C.c_int, [vp, C.c_int64, f32, vp]),
     "ss_hifigan_post_trim": (C.c_int, [vp, vp, vp, vp, vp, vp, f32, f32, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
 }
 

@@ -182,9 +182,10 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
 
 def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.0, in_act=ACT_NONE, in_slope=0.0,
            residual=None, lens=None, out=None, accum=None, accum_scale=1.0, accum_init=False, write_y=True,
-           backend=None):
+           backend=None, s_out=None):
     """fp32-accurate convolution: x [B,S,Cin] f32, w a ConvW -> y [B,S,Cout] f32.
-    backend (default ops.fp32_backend): "tf32x3" = ss_conv1d_tf32x3, "ffma" = ss_conv1d_f32."""
+    backend (default ops.fp32_backend): "tf32x3" = ss_conv1d_tf32x3, "ffma" = ss_conv1d_f32.
+    s_out: output length when it is not S (a "valid" convolution: pad=0, s_out = S - (k-1)*dilation); 3xTF32 only."""
     _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias")
     _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
     B, S, Cin = x.shape
@@ -193,17 +194,20 @@ def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.
     if w.cin != Cin or (k is not None and k != w.k):
         raise _lib.SSError(f"conv1d: weight is [k={w.k}, Cout={w.cout}, Cin={w.cin}] but x has Cin={Cin}, k={k}")
     k, Cout = w.k, w.cout
+    So = S if s_out is None else int(s_out)
+    be = backend or fp32_backend
+    if So != S and (not be.startswith("tf32x3") or So < 1):
+        raise _lib.SSError(f"conv1d: s_out={So} needs the 3xTF32 backend and s_out >= 1")
     y = None
     if write_y:
-        y = out if out is not None else torch.empty((B, S, Cout), dtype=torch.float32, device=x.device)
+        y = out if out is not None else torch.empty((B, So, Cout), dtype=torch.float32, device=x.device)
         _chk(y, torch.float32, "out")
-    be = backend or fp32_backend
     if be.startswith("tf32x3"):
-        _tf32_call(x, w, bias, residual, lens, y, None, accum, variant=be[7:] or None, B=B, S_in=S, S_out=S,
-                   y_batch_stride=S * Cout,
-                   y_row_stride=Cout, y_offset=0, y_batch_elems=S * Cout, dilation=dilation, pad=pad, in_act=in_act,
+        _tf32_call(x, w, bias, residual, lens, y, None, accum, variant=be[7:] or None, B=B, S_in=S, S_out=So,
+                   y_batch_stride=So * Cout,
+                   y_row_stride=Cout, y_offset=0, y_batch_elems=So * Cout, dilation=dilation, pad=pad, in_act=in_act,
                    in_slope=in_slope, act=act, slope=slope, act2=None, slope2=0.0, accum_scale=accum_scale,
-                   accum_init=accum_init, flops=2.0 * B * S * Cout * k * Cin)
+                   accum_init=accum_init, flops=2.0 * B * So * Cout * k * Cin)
         return y
     w = w.ffma
     p = _lib.Conv1dF32Params(
@@ -457,3 +461,30 @@ def hifigan_post_trim(x, w, bias, n_samples, out_offset, pcm_out, *, k, in_slope
     check(_lib.lib().ss_hifigan_post_trim(_ptr(x), _ptr(w), _ptr(bias), _ptr(n_samples), _ptr(out_offset),
                                           pcm_out.data_ptr(), float(pcm_scale), float(in_slope), B, T, Cc, k, _stream()))
     return pcm_out
+
+
+def reflect_pad(y, half, n_out):
+    """ss_reflect_pad: y [B,T] f32 -> [B,n_out], out[b,i] = y[b, reflect(i - half)] (F.pad mode="reflect")."""
+    _chk(y, torch.float32, "y")
+    B, T = y.shape
+    out = torch.empty((B, n_out), dtype=torch.float32, device=y.device)
+    check(_lib.lib().ss_reflect_pad(_ptr(y), _ptr(out), B, T, int(half), int(n_out), _stream()))
+    return out
+
+
+def stft_magnitude(spec, n_bins, want_energy=True):
+    """ss_stft_magnitude: spec [B,F,>=2*n_bins] (re | im | pad) -> (mag [B,F,ceil4(n_bins)] zero-padded, energy [B,F])."""
+    _chk(spec, torch.float32, "spec")
+    B, F, W = spec.shape
+    ms = (n_bins + 3) // 4 * 4
+    mag = torch.empty((B, F, ms), dtype=torch.float32, device=spec.device)
+    energy = torch.empty((B, F), dtype=torch.float32, device=spec.device) if want_energy else None
+    check(_lib.lib().ss_stft_magnitude(_ptr(spec), _ptr(mag), _ptr(energy), B * F, int(n_bins), W, ms, _stream()))
+    return mag, energy
+
+
+def log_clamp_(x, clip=1e-5):
+    """ss_log_clamp: x = log(max(x, clip)) in place."""
+    _chk(x, torch.float32, "x")
+    check(_lib.lib().ss_log_clamp(_ptr(x), x.numel(), float(clip), _stream()))
+    return x
