@@ -179,6 +179,9 @@ SS_API int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream);
 /* Same contract; the split activations are kept in tensor memory (tcgen05.st) and the MMAs take their A
  * operand from there, which removes the shared-memory re-reads that bound the variant above. */
 SS_API int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream);
+/* Same contract; two CTAs of a cluster compute one 256 x 128 tile with tcgen05 cta_group::2, each holding half
+ * of the weight tile, which halves the shared-memory traffic per SM (layers with Cout <= 64 go to the kernel above). */
+SS_API int ss_conv1d_tf32x3_ts2(const ss_conv1d_tf32_params* p, void* stream);
 
 /* out = bf16(act(x)) element-wise over n elements (n % 8 == 0): the entry into the bf16 path. */
 SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream);

@@ -1,7 +1,7 @@
 """Debug: per-K-chunk clock64() timeline of the 3xTF32 conv kernels (CTA 0).  Rebuilds with -DSS_CONV_TRACE on
 the GPU box.  Usage: python scripts/conv_trace.py [ss|ts]"""
 import ctypes, math, os, sys
-os.environ["SS_NVCC_EXTRA"] = "-DSS_CONV_TRACE"
+os.environ["SS_NVCC_EXTRA"] = "-DSS_CONV_TRACE -DSS_CONV2_TRACE"
 sys.path.insert(0, ".")
 from speakingstyle_b200 import build
 build.build(force=True)
@@ -24,7 +24,7 @@ torch.cuda.synchronize()
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 a.record(); ops.conv1d(x, W, bias, pad=k // 2, act=ops.ACT_RELU, backend="tf32x3_" + var, residual=res); b.record(); torch.cuda.synchronize()
 print(f"{var}: {a.elapsed_time(b):.3f} ms (trace build)")
-NEV = 12 if var == "ts" else 8
+NEV = 12 if var in ("ts", "ts2") else 8
 buf = np.zeros(NEV * 256, dtype=np.int64)
 dll = ctypes.CDLL(build.LIB_PATH)
 fn = getattr(dll, f"ss_debug_conv_{var}_trace")

@@ -175,7 +175,9 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         B=B, S_in=S_in, S_out=S_out, Cin=W.cin, Cout=W.cout, k=W.k, dilation=dilation, pad=pad, in_act=in_act,
         in_slope=in_slope, act=act, slope=slope, act2=act2 or 0, slope2=slope2, accum_scale=accum_scale,
         accum_init=int(accum_init), k_group=tf32_k_group)
-    entry = _lib.lib().ss_conv1d_tf32x3_ts if (variant or tf32_variant) == "ts" else _lib.lib().ss_conv1d_tf32x3
+    v = variant or tf32_variant
+    entry = {"ts": _lib.lib().ss_conv1d_tf32x3_ts, "ts2": _lib.lib().ss_conv1d_tf32x3_ts2,
+             "ss": _lib.lib().ss_conv1d_tf32x3}[v]
     fn = lambda: entry(C.byref(p), _stream())  # noqa: E731
     check(conv_timer.run(flops, fn, _tag("tf32x3", p)) if conv_timer is not None else fn())
 
