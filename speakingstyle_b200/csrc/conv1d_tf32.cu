@@ -277,7 +277,7 @@ conv1d_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           }
           const float4 h = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
           a[idx] = h;
-          alo[idx] = make_float4(tf32_rn(x.x - h.x), tf32_rn(x.y - h.y), tf32_rn(x.z - h.z), tf32_rn(x.w - h.w));
+          alo[idx] = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);  // truncated to TF32 by the MMA
         }
         fence_proxy_async();  // make these generic-proxy writes visible to tcgen05.mma
         __syncwarp();

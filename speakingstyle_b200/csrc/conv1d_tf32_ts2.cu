@@ -68,7 +68,7 @@ __device__ __forceinline__ void mbar_arrive_cta(uint32_t bar, uint32_t cta) {
       "{\n\t"
       ".reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t"
       "}" ::"r"(bar),
       "r"(cta)
       : "memory");
@@ -78,7 +78,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
       "{\n\t"
       ".reg .pred p;\n\t"
       "WAIT_LOOP_C:\n\t"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
       "@p bra WAIT_DONE_C;\n\t"
       "bra WAIT_LOOP_C;\n\t"
       "WAIT_DONE_C:\n\t"
@@ -370,10 +370,10 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             x.z = x.z > 0.f ? x.z : x.z * in_slope;
             x.w = x.w > 0.f ? x.w : x.w * in_slope;
           }
-          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = tf32_rn(x.x - hi[4 * u + 0]);
-          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
-          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
-          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
+          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = x.x - hi[4 * u + 0];  // truncated to TF32 by the MMA (see conv1d_tf32_ts.cu)
+          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = x.y - hi[4 * u + 1];  // truncated to TF32 by the MMA (see conv1d_tf32_ts.cu)
+          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = x.z - hi[4 * u + 2];  // truncated to TF32 by the MMA (see conv1d_tf32_ts.cu)
+          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = x.w - hi[4 * u + 3];  // truncated to TF32 by the MMA (see conv1d_tf32_ts.cu)
         }
         if (edge_tile && __any_sync(0xffffffffu, outside)) {  // warp-uniform branch: skipped in interior tiles
 #pragma unroll

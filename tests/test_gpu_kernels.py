@@ -143,6 +143,21 @@ def test_conv1d_flat_tiling_across_utterances(ops, B, S, Cin, Cout, k, dil):
     assert torch.equal(y, y2)
 
 
+@pytest.mark.parametrize("B,S,Cin,Cout,k,dil", [(3, 150, 256, 1024, 9, 1), (7, 50, 64, 128, 9, 1), (2, 300, 64, 80, 11, 5),
+                                                 (5, 257, 256, 256, 1, 1), (1, 700, 128, 384, 3, 1), (2, 37, 80, 64, 3, 1)])
+def test_cta_pair_conv_is_bit_identical_to_single_cta(ops, B, S, Cin, Cout, k, dil):
+    """The cta_group::2 form (two CTAs per 256 x 128 tile, DESIGN.md 3.1) does the same sums in the same order."""
+    x, w, b = rnd(B, S, Cin, seed=71), rnd(Cout, Cin, k, seed=72, scale=1 / math.sqrt(Cin * k)), rnd(Cout, seed=73)
+    res = rnd(B, S, Cout, seed=74)
+    lens = torch.tensor([max(1, S - 13 * i) for i in range(B)], dtype=torch.int32)
+    pad = (k - 1) // 2 * dil
+    W = pack(w)
+    kw = dict(k=k, dilation=dil, pad=pad, act=ops.ACT_LRELU, slope=0.1, residual=res.to(DEV), lens=lens.to(DEV))
+    y1 = ops.conv1d(x.to(DEV), W, b.to(DEV), backend="tf32x3_ts", **kw)
+    y2 = ops.conv1d(x.to(DEV), W, b.to(DEV), backend="tf32x3_ts2", **kw)
+    assert torch.equal(y1, y2)
+
+
 @pytest.mark.parametrize("Cin,Cout,k,u,S", [(512, 256, 16, 8, 13), (128, 64, 4, 2, 50), (64, 32, 4, 2, 129)])
 def test_conv_transpose_phase_form(ops, Cin, Cout, k, u, S):
     from speakingstyle_b200 import configs as C
