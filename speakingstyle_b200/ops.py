@@ -107,7 +107,10 @@ def add_position(x, pe):
 fp32_backend = "tf32x3"  # "tf32x3": 3xTF32 tcgen05 kernel (default); "ffma": the FP32-pipe kernel
 # experiment knobs (environment overrides are for A/B timing only; the defaults are what the tests pin)
 tf32_k_group = int(os.environ.get("SS_TF32_KGROUP", "0"))  # 0 = library default (accumulator restart every 8 chunks)
-tf32_variant = os.environ.get("SS_TF32_VARIANT", "ts")     # "ts": A operand in tensor memory; "ss": in shared memory
+# "auto": A operand in tensor memory - the CTA-pair kernel ("ts2") for long reductions, the single-CTA one ("ts") for
+# short ones (they are bit-identical; the pair form is ~3 % faster from 16 chunks up and slower on k = 1, K = 256 layers);
+# "ss": split operands in shared memory (the first version, kept as a cross-check)
+tf32_variant = os.environ.get("SS_TF32_VARIANT", "auto")
 
 
 def tf32_round(t):
@@ -176,6 +179,8 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         in_slope=in_slope, act=act, slope=slope, act2=act2 or 0, slope2=slope2, accum_scale=accum_scale,
         accum_init=int(accum_init), k_group=tf32_k_group)
     v = variant or tf32_variant
+    if v == "auto":
+        v = "ts2" if W.k * ((W.cin + 31) // 32) >= 16 else "ts"
     entry = {"ts": _lib.lib().ss_conv1d_tf32x3_ts, "ts2": _lib.lib().ss_conv1d_tf32x3_ts2,
              "ss": _lib.lib().ss_conv1d_tf32x3}[v]
     fn = lambda: entry(C.byref(p), _stream())  # noqa: E731
