@@ -144,7 +144,8 @@ def test_conv1d_flat_tiling_across_utterances(ops, B, S, Cin, Cout, k, dil):
 
 
 @pytest.mark.parametrize("B,S,Cin,Cout,k,dil", [(3, 150, 256, 1024, 9, 1), (7, 50, 64, 128, 9, 1), (2, 300, 64, 80, 11, 5),
-                                                 (5, 257, 256, 256, 1, 1), (1, 700, 128, 384, 3, 1), (2, 37, 80, 64, 3, 1)])
+                                                 (5, 257, 256, 256, 1, 1), (1, 700, 128, 384, 3, 1), (2, 37, 80, 64, 3, 1),
+                                                 (2, 37, 80, 1024, 3, 1), (1, 1, 256, 512, 1, 1), (4, 256, 64, 128, 5, 1)])
 def test_cta_pair_conv_is_bit_identical_to_single_cta(ops, B, S, Cin, Cout, k, dil):
     """The cta_group::2 form (two CTAs per 256 x 128 tile, DESIGN.md 3.1) does the same sums in the same order."""
     x, w, b = rnd(B, S, Cin, seed=71), rnd(Cout, Cin, k, seed=72, scale=1 / math.sqrt(Cin * k)), rnd(Cout, seed=73)
