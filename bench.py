@@ -400,9 +400,9 @@ def main():
                                  f"{w / (ms * 1e-3) / 1e12:8.1f} TFLOP/s  {tag}\n")
             sys.stderr.write(f"step {dev_ms / args.steps:.3f} ms, convs {conv_ms / args.steps:.3f} ms\n")
         ach = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
-        roof = {"kernel": "conv1d_tf32_ts_kernel (3xTF32 tcgen05) + conv1d_tc_kernel (bf16 tcgen05): all conv/linear launches"
+        roof = {"kernel": "conv1d_tf32_ts2 / _ts kernels (3xTF32 tcgen05) + conv1d_tc_kernel (bf16 tcgen05): all conv/linear launches"
                 if args.precision == "bf16" else
-                "conv1d_tf32_ts_kernel (3xTF32 tcgen05 implicit-GEMM conv/linear, A operand in TMEM, fp32-accurate)",
+                "conv1d_tf32_ts2_kernel (CTA pair) / conv1d_tf32_ts_kernel: 3xTF32 tcgen05 implicit-GEMM conv/linear, A operand in TMEM, fp32-accurate",
                 "bound": "tensor", "achieved": ach,
                 "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tflops_sustained"], "traffic": None,
                 "launches": calls, "avg_launch_ms": conv_ms / max(calls, 1), "share_of_step": conv_ms / dev_ms,
@@ -410,8 +410,8 @@ def main():
                 "note": "achieved = algorithmic FLOPs of ALL conv/linear launches / their CUDA-event time; frac divides "
                         "by the measured bf16 peak as the contract asks.  A 3xTF32 kernel issues 3 TF32 MMAs per "
                         "algorithmic MAC and the TF32 pipe retires 2048 MAC/clk/SM (half of bf16), so its own ceiling "
-                        "at the SM clock sampled during the run is 148*2048*2*f/3; ncu (profiles/r1d_ncu_hot_kernels.txt) "
-                        "shows the tensor pipe active 80 % of elapsed cycles on the FFN conv"}
+                        "at the SM clock sampled during the run is 148*2048*2*f/3; ncu (profiles/r1e_ncu_hot_kernels.txt) "
+                        "shows the tensor pipe active 86 % of elapsed cycles on the FFN conv"}
         if args.precision == "fp32" and clocks.get("sm_mhz"):
             ceil = 148 * 2048 * 2 * clocks["sm_mhz"] * 1e6 / 3.0 / 1e12
             roof["tf32x3_ceiling_at_sampled_clock"] = ceil
