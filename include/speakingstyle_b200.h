@@ -318,6 +318,14 @@ SS_API int ss_length_mask(const int32_t* lens, uint8_t* mask, int B, int T, void
 /* out[b,:] = (1/S) * sum_t x[b,t,:]   over the PADDED length S (model/modules.py:398). */
 SS_API int ss_mean_pool(const float* x, float* out, int B, int S, int C, void* stream);
 
+/* Batch-invariant mode (opt-in, deviates from the reference by design - see DESIGN.md):
+ * out[b,:] = (1/n_b) * sum_{t<n_b} x[b,t,:], n_b = clamp(lens[b], 1, S): the mean over the utterance's own frames,
+ * so that the style vector does not depend on how far the batch was padded. */
+SS_API int ss_mean_pool_lens(const float* x, const int32_t* lens, float* out, int B, int S, int C, void* stream);
+/* x[b,t,:] = 0 for t >= lens[b] (in place): closes the padding leaks the reference leaves open after the speaker /
+ * pitch / energy embedding adds (fastspeech2.py:74-77, modules.py:126,131). */
+SS_API int ss_mask_rows(float* x, const int32_t* lens, int B, int S, int C, void* stream);
+
 /* x[b,l,:] += table[ids[b],:] for every l, padding included (model/fastspeech2.py:74-77). */
 SS_API int ss_add_speaker(float* x, const int64_t* ids, const float* table, int B, int L, int C, int n_speakers,
                           void* stream);

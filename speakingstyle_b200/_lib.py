@@ -83,6 +83,8 @@ _SIGNATURES = {
     "ss_length_regulate_noalloc": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_length_mask": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
     "ss_mean_pool": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_mean_pool_lens": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_mask_rows": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_add_speaker": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_hifigan_post": (C.c_int, [vp, vp, vp, vp, vp, f32, f32, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_reflect_pad": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),

@@ -204,15 +204,17 @@ __global__ void length_mask_kernel(const int32_t* __restrict__ lens, uint8_t* __
 }
 
 // one CTA per (batch, 128-channel slab); threads = 32 channel-quads x 8 row groups
-__global__ void __launch_bounds__(256) mean_pool_kernel(const float* __restrict__ x, float* __restrict__ out, int S,
-                                                        int C) {
+__global__ void __launch_bounds__(256) mean_pool_kernel(const float* __restrict__ x, float* __restrict__ out, int S_all,
+                                                        int C, const int32_t* __restrict__ lens) {
   __shared__ float4 part[8][32];
   const int b = blockIdx.y;
+  // lens given (batch-invariant mode): mean over the utterance's own frames; otherwise over the padded length
+  const int S = lens ? min(max(lens[b], 1), S_all) : S_all;
   const int cq = blockIdx.x * 32 + (threadIdx.x & 31);  // float4 column
   const int g = threadIdx.x >> 5;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (cq < C / 4) {
-    const float4* xp = reinterpret_cast<const float4*>(x + (int64_t)b * S * C) + cq;
+    const float4* xp = reinterpret_cast<const float4*>(x + (int64_t)b * S_all * C) + cq;
     for (int t = g; t < S; t += 8) {
       const float4 a = __ldg(xp + (int64_t)t * (C / 4));
       s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
@@ -228,6 +230,16 @@ __global__ void __launch_bounds__(256) mean_pool_kernel(const float* __restrict_
     const float inv = 1.0f / (float)S;
     reinterpret_cast<float4*>(out + (int64_t)b * C)[cq] = make_float4(s.x * inv, s.y * inv, s.z * inv, s.w * inv);
   }
+}
+
+// x[b, t, :] = 0 for t >= lens[b]: one warp per row, only padded rows are touched
+__global__ void mask_rows_kernel(float* __restrict__ x, const int32_t* __restrict__ lens, int B, int S, int C) {
+  const int64_t row = (int64_t)blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
+  if (row >= (int64_t)B * S) return;
+  const int b = (int)(row / S), t = (int)(row - (int64_t)b * S);
+  if (t < lens[b]) return;
+  float4* xr = reinterpret_cast<float4*>(x + row * C);
+  for (int c = threadIdx.x & 31; c < C / 4; c += 32) xr[c] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 __global__ void add_speaker_kernel(float* __restrict__ x, const int64_t* __restrict__ ids,
@@ -369,8 +381,23 @@ int ss_length_mask(const int32_t* lens, uint8_t* mask, int B, int T, void* strea
 int ss_mean_pool(const float* x, float* out, int B, int S, int C, void* stream) {
   SS_REQUIRE(x && out && B > 0 && S > 0 && C > 0 && C % 4 == 0, SS_ERR_INVALID, "ss_mean_pool: bad argument");
   dim3 grid((C / 4 + 31) / 32, B);
-  mean_pool_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, out, S, C);
+  mean_pool_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, out, S, C, nullptr);
   SS_CHECK_LAUNCH("ss_mean_pool");
+  return SS_OK;
+}
+
+int ss_mean_pool_lens(const float* x, const int32_t* lens, float* out, int B, int S, int C, void* stream) {
+  SS_REQUIRE(x && lens && out && B > 0 && S > 0 && C > 0 && C % 4 == 0, SS_ERR_INVALID, "ss_mean_pool_lens: bad argument");
+  dim3 grid((C / 4 + 31) / 32, B);
+  mean_pool_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, out, S, C, lens);
+  SS_CHECK_LAUNCH("ss_mean_pool_lens");
+  return SS_OK;
+}
+
+int ss_mask_rows(float* x, const int32_t* lens, int B, int S, int C, void* stream) {
+  SS_REQUIRE(x && lens && B > 0 && S > 0 && C > 0 && C % 4 == 0, SS_ERR_INVALID, "ss_mask_rows: bad argument");
+  mask_rows_kernel<<<row_grid((int64_t)B * S), 256, 0, (cudaStream_t)stream>>>(x, lens, B, S, C);
+  SS_CHECK_LAUNCH("ss_mask_rows");
   return SS_OK;
 }
 

@@ -15,7 +15,7 @@ from .transformer import Decoder, Dense, Encoder, ParamCache, PostNet, pack_conv
 class FastSpeech2(nn.Module, ParamCache):
     """model/fastspeech2.py:13-120."""
 
-    def __init__(self, preprocess_config, model_config, precision="fp32"):
+    def __init__(self, preprocess_config, model_config, precision="fp32", batch_invariant=False):
         super().__init__()
         self.model_config = model_config
         # "fp32": every kernel accumulates in fp32 FMA (mel max-abs <= 1e-3 vs the reference);
@@ -39,6 +39,23 @@ class FastSpeech2(nn.Module, ParamCache):
         for p in self.parameters():
             p.requires_grad_(False)
         self.eval()
+        self.set_batch_invariant(batch_invariant)
+
+    def set_batch_invariant(self, flag=True):
+        """Opt-in mode in which an utterance's outputs do not depend on what it was batched with.
+        The reference leaks padding in six places: the reference encoder's conv stack is not masked between
+        layers, the second convolution of its FFT blocks ([3, 3] kernels) reads the first one's output at padded
+        frames, and its style vector is a mean over the PADDED length (modules.py:366-371, 353, 398); the speaker,
+        pitch and energy embeddings are added at padded tokens (fastspeech2.py:74-77, modules.py:126, 131) and the
+        predictors' two convolutions are not masked in between; mel_linear's bias sits in the padded frames that
+        the PostNet convolves over.  This mode zeroes the pads at each of those points and averages over the valid
+        frames.  It DEVIATES from the reference by design (the parity tests run with it off); with it on, running
+        an utterance alone or in any batch gives the same integers and the same mel, bit for bit."""
+        self.batch_invariant = bool(flag)
+        for m in self.modules():
+            if m is not self:
+                m.batch_invariant = bool(flag)
+        return self
 
     def _pack(self):
         return {"mel_w": pack_conv(self.mel_linear.weight)}
@@ -94,6 +111,8 @@ class FastSpeech2(nn.Module, ParamCache):
         x = self.encoder(texts, None, gammas, betas, lens=src_lens32)
         if self.speaker_emb is not None:
             x = ops.add_speaker(x, speakers, self.speaker_emb.weight)  # pads included (fastspeech2.py:74-77)
+            if self.batch_invariant:
+                ops.mask_rows_(x, src_lens32)
 
         ref_masks = ops.length_mask(ref_lens32, max_mel_len) if d_targets is not None else None
         (x, p_pred, e_pred, log_d, d_rounded, mel_lens_out, mel_masks, extra) = self.variance_adaptor(
@@ -109,17 +128,18 @@ class FastSpeech2(nn.Module, ParamCache):
             dec_lens = torch.clamp(mel_lens_out, max=T) if mel_masks.shape[1] != T else mel_lens_out
             if mel_masks.shape[1] != T:
                 mel_masks = ops.length_mask(dec_lens, T)
+        inv_lens = dec_lens if self.batch_invariant else None  # zero the padded mel frames (mel_linear's bias)
         if self.precision == "bf16":
             # Decoder, mel_linear and PostNet on the tensor cores (bf16 operands, fp32 accumulation and
             # fp32 residual stream).  Everything before this point decides integers and stays fp32.
             (x, xb), _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True, precision="bf16",
                                       return_bf16=True)
-            mel, melb = ops.conv1d_tc(xb, self.packed()["mel_w"], self.mel_linear.bias, act2=ops.ACT_NONE)
-            postnet_mel = self.postnet(mel, residual=mel, precision="bf16", xb=melb)
+            mel, melb = ops.conv1d_tc(xb, self.packed()["mel_w"], self.mel_linear.bias, act2=ops.ACT_NONE, lens=inv_lens)
+            postnet_mel = self.postnet(mel, residual=mel, precision="bf16", xb=melb, lens=inv_lens)
         else:
             x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True)
-            mel = ops.conv1d(x, self.packed()["mel_w"], self.mel_linear.bias)
-            postnet_mel = self.postnet(mel, residual=mel)
+            mel = ops.conv1d(x, self.packed()["mel_w"], self.mel_linear.bias, lens=inv_lens)
+            postnet_mel = self.postnet(mel, residual=mel, lens=inv_lens)
         out = (mel, postnet_mel, p_pred, e_pred, log_d, d_rounded, src_masks, mel_masks, src_lens_in, mel_lens_out)
         if return_extra:
             extra.update(gammas=gammas, betas=betas)

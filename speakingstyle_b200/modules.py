@@ -82,7 +82,10 @@ class VariancePredictor(nn.Module, ParamCache):
         k = self.kernel
         h = ops.conv1d(encoder_output, pk["w1"], cl.conv1d_1.conv.bias, k=k, pad=cl.conv1d_1.padding,
                        act=ops.ACT_RELU)
-        h = ops.layernorm(h, cl.layer_norm_1.weight, cl.layer_norm_1.bias, out=h)  # no mask between the convs
+        # the reference has no mask between the convs; batch-invariant mode zeroes the pads so that the second
+        # convolution's halo at an utterance end reads zeros whatever the batch was padded to
+        h = ops.layernorm(h, cl.layer_norm_1.weight, cl.layer_norm_1.bias, out=h,
+                          lens=lens if getattr(self, "batch_invariant", False) else None)
         h = ops.conv1d(h, pk["w2"], cl.conv1d_2.conv.bias, k=k, pad=cl.conv1d_2.padding, act=ops.ACT_RELU)
         return ops.predictor_head(h, cl.layer_norm_2.weight, cl.layer_norm_2.bias, pk["lin_w"],
                                   self.linear_layer.bias, film=film_args(self.film, gammas, betas), lens=lens)
@@ -157,6 +160,9 @@ class VarianceAdaptor(nn.Module):
         else:
             pitch_idx = ops.bucket_embed_add(pitch, p_control, self.pitch_bins, self.pitch_embedding.weight, x,
                                              want_idx=return_extra)
+        binv = getattr(self, "batch_invariant", False)
+        if binv:
+            ops.mask_rows_(x, lens)  # the pitch embedding was added at the pads too (modules.py:126)
         energy = self.energy_predictor(x, src_mask, lens=lens)
         if energy_target is not None:
             energy_idx = ops.bucket_embed_add(energy_target.to(torch.float32).contiguous().clone(), 1.0,
@@ -164,6 +170,8 @@ class VarianceAdaptor(nn.Module):
         else:
             energy_idx = ops.bucket_embed_add(energy, e_control, self.energy_bins, self.energy_embedding.weight, x,
                                               want_idx=return_extra)
+        if binv:
+            ops.mask_rows_(x, lens)  # ... and the energy embedding (modules.py:131)
         if duration_target is not None:
             # teacher forcing (modules.py:133-135): expand by the given durations to max_len; mel_mask is the caller's
             d_rounded = duration_target
@@ -238,13 +246,17 @@ class ReferenceEncoder(nn.Module, ParamCache, _PositionTable):
         for i, seq in enumerate(self.layer_stack):
             x = ops.conv1d(x, pk["convs"][i], seq[0].conv.bias, k=k, pad=(k - 1) // 2, act=ops.ACT_RELU)
             last = i == n - 1
-            # no mask between the conv layers (modules.py:366-371); mask + position add after the last
-            x = ops.layernorm(x, seq[1].weight, seq[1].bias, lens=lens if last else None,
+            # no mask between the conv layers (modules.py:366-371); mask + position add after the last.
+            # Batch-invariant mode masks after every layer (the padded frames' bias would otherwise leak into
+            # the last valid frames through the next layer's halo).
+            binv = getattr(self, "batch_invariant", False)
+            x = ops.layernorm(x, seq[1].weight, seq[1].bias, lens=lens if (last or binv) else None,
                               pe=self._pe(Tr, self.filter_size) if last else None, out=x)
         x = ops.conv1d(x, pk["lin"], None)
         for blk in self.fftb_stack:
             x, _ = blk(x, lens=lens)
-        pooled = ops.mean_pool(x)  # mean over the PADDED length (modules.py:398)
+        # mean over the PADDED length (modules.py:398); batch-invariant mode: over the utterance's own frames
+        pooled = ops.mean_pool(x, lens=lens if getattr(self, "batch_invariant", False) else None)
         gb = ops.conv1d(pooled.unsqueeze(0), pk["affine"], None, backend="ffma")[0]  # [B, 2d]: one tiny GEMV
         d = self.d_model
         gammas = gb[:, :d].unsqueeze(1)

@@ -431,12 +431,24 @@ def length_mask(lens, T):
     return mask
 
 
-def mean_pool(x):
-    _chk(x, torch.float32, "x")
+def mean_pool(x, lens=None):
+    """Mean over the padded length (the reference, modules.py:398); with lens: over each utterance's own frames."""
+    _chk(x, torch.float32, "x"); _chk(lens, torch.int32, "lens")
     B, S, Cc = x.shape
     out = torch.empty((B, Cc), dtype=torch.float32, device=x.device)
-    check(_lib.lib().ss_mean_pool(_ptr(x), _ptr(out), B, S, Cc, _stream()))
+    if lens is None:
+        check(_lib.lib().ss_mean_pool(_ptr(x), _ptr(out), B, S, Cc, _stream()))
+    else:
+        check(_lib.lib().ss_mean_pool_lens(_ptr(x), _ptr(lens), _ptr(out), B, S, Cc, _stream()))
     return out
+
+
+def mask_rows_(x, lens):
+    """x[b, t, :] = 0 for t >= lens[b], in place (batch-invariant mode)."""
+    _chk(x, torch.float32, "x"); _chk(lens, torch.int32, "lens")
+    B, S, Cc = x.shape
+    check(_lib.lib().ss_mask_rows(_ptr(x), _ptr(lens), B, S, Cc, _stream()))
+    return x
 
 
 def add_speaker(x, ids, table):

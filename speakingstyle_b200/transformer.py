@@ -139,12 +139,15 @@ class PositionwiseFeedForward(nn.Module, ParamCache):
         pk = self.packed()
         k1, k2 = self.kernel_size
         ln = self.layer_norm
+        # Batch-invariant mode: when w_2 has a halo (the reference encoder's [3, 3] kernels) it reads w_1's output at
+        # padded frames, which a lone utterance would see as zero padding - mask the intermediate there.
+        hl = lens if (getattr(self, "batch_invariant", False) and k2 > 1) else None
         if xb is not None:  # tensor-core path: the 1024-channel intermediate only ever exists in bf16
-            h, _ = ops.conv1d_tc(xb, pk["w1"], self.w_1.bias, pad=(k1 - 1) // 2, act=ops.ACT_RELU,
+            h, _ = ops.conv1d_tc(xb, pk["w1"], self.w_1.bias, pad=(k1 - 1) // 2, act=ops.ACT_RELU, lens=hl,
                                  out_dtype=torch.bfloat16)
             y, _ = ops.conv1d_tc(h, pk["w2"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x)
             return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y, want_bf16=True)
-        h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU)
+        h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU, lens=hl)
         y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x)
         return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y)
 
@@ -300,9 +303,10 @@ class PostNet(nn.Module, ParamCache):
             out.append((pack_conv(w), b.contiguous()))
         return out
 
-    def forward(self, x, residual=None, precision="fp32", xb=None):
+    def forward(self, x, residual=None, precision="fp32", xb=None, lens=None):
         """x [B,T,n_mel] -> postnet(x) (+ residual fused into the last convolution if given).
-        precision="bf16": tensor-core convolutions, bf16 activations between layers (xb = bf16 copy of x)."""
+        precision="bf16": tensor-core convolutions, bf16 activations between layers (xb = bf16 copy of x).
+        lens (batch-invariant mode): rows >= lens[b] are zeroed after every layer."""
         pk = self.packed()
         k = self.kernel_size
         n = len(pk)
@@ -311,11 +315,11 @@ class PostNet(nn.Module, ParamCache):
             for i, (wtc, b) in enumerate(pk):
                 last = i == n - 1
                 h, _ = ops.conv1d_tc(h, wtc, b, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
-                                     residual=residual if last else None,
+                                     residual=residual if last else None, lens=lens,
                                      out_dtype=torch.float32 if last else torch.bfloat16)
             return h
         for i, (w, b) in enumerate(pk):
             last = i == n - 1
             x = ops.conv1d(x, w, b, k=k, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
-                           residual=residual if last else None)
+                           residual=residual if last else None, lens=lens)
         return x

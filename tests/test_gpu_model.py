@@ -219,6 +219,42 @@ def test_vocoder_infer_and_synthesize_batch_return_trimmed_int16(golden):
         assert np.array_equal(w, pcm2[i, :mel_lens[i] * 256].cpu().numpy())
 
 
+@pytest.mark.parametrize("name", ["tiny", "tiny_ms"])
+def test_batch_invariant_mode_is_independent_of_batch_composition(name):
+    """SURVEY 8 (f4), opt-in: with the padding leaks closed, an utterance synthesised alone and inside a batch gives
+    the same integers and the same mel, bit for bit - and the mode is off by default (reference behaviour, which
+    test_outputs_depend_on_batch_composition_like_the_reference pins)."""
+    import speakingstyle_b200 as ss
+
+    ds, batch, voc = S.make_workload(name)
+    d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    model = ss.get_model(pc, mc, DEV, S.fastspeech2_state_dict(mc, ds))
+    assert model.batch_invariant is False
+    model.set_batch_invariant(True)
+    out = run(model, batch)
+    B = batch["texts"].shape[0]
+    for i in range(B):
+        L, Tr = int(batch["src_lens"][i]), int(batch["mel_lens"][i])
+        one = {"speakers": batch["speakers"][i:i + 1], "texts": batch["texts"][i:i + 1, :L].contiguous(),
+               "src_lens": batch["src_lens"][i:i + 1], "max_src_len": L,
+               "mels": batch["mels"][i:i + 1, :Tr].contiguous(), "mel_lens": batch["mel_lens"][i:i + 1],
+               "max_mel_len": Tr}
+        o1 = run(model, one)
+        n = int(o1[9][0])
+        assert n == int(out[9][i])                                            # mel_len
+        assert torch.equal(o1[5][0, :L], out[5][i, :L])                       # d_rounded
+        for k in (2, 3, 4):                                                   # pitch, energy, log-duration
+            assert torch.equal(o1[k][0, :L], out[k][i, :L]), k
+        for k in (0, 1):                                                      # mel, postnet mel
+            assert torch.equal(o1[k][0, :n], out[k][i, :n]), k
+            assert float(out[k][i, n:].abs().sum()) == 0.0                    # pads are zeros in this mode
+    # and it does change something: the default mode differs on the shorter utterances
+    model.set_batch_invariant(False)
+    ref = run(model, batch)
+    assert not torch.equal(ref[1], out[1])
+
+
 def test_modules_standalone_api():
     """The sub-modules keep the reference's own signatures."""
     import speakingstyle_b200 as ss
