@@ -255,6 +255,45 @@ def test_batch_invariant_mode_is_independent_of_batch_composition(name):
     assert not torch.equal(ref[1], out[1])
 
 
+def test_reference_sweep_cfg4_sharded_matches_oracle():
+    """BASELINE configs[3] at reduced size: ReferenceEncoder alone over length-bucketed mels (bucket width 64,
+    batch <= 64), planned for 2 ranks, every shard checked against the oracle on the same shard (results depend
+    on the shard's padding, so the plan is part of the contract)."""
+    from speakingstyle_b200 import shard as SH
+
+    model, mc, sd = get_models("BC2013")
+    g = torch.Generator().manual_seed(404)
+    n = 90
+    lens = torch.randint(100, 1001, (n,), generator=g).tolist()
+    mels = [torch.randn(t, 80, generator=g) for t in lens]
+    plan = SH.plan_shards([0] * n, lens, max_batch=64, bucket_width=64, n_ranks=2, vocoder=False, text=False)
+    assert sorted(u for s_ in plan.shards for u in s_.utterances) == list(range(n))
+    texts = [torch.ones(1, dtype=torch.int64)] * n
+
+    def gpu(batch):
+        ga, be, pooled = model.reference_encoder(batch["mels"].to(DEV), batch["max_mel_len"], None,
+                                                 lens=batch["mel_lens"].to(DEV, torch.int32), return_pooled=True)
+        return {"gammas": ga[:, 0].cpu(), "betas": be[:, 0].cpu(), "pooled": pooled.cpu()}
+
+    def cpu(batch):
+        with torch.no_grad():
+            ga, be, pooled = O.reference_encoder(sd, mc, batch["mels"], O.mask_from_lengths(batch["mel_lens"],
+                                                                                           batch["max_mel_len"]),
+                                                 return_pooled=True)
+        return {"gammas": ga[:, 0], "betas": be[:, 0], "pooled": pooled}
+
+    worst = 0.0
+    for rank in range(2):
+        got = SH.run_rank(plan, rank, gpu, [0] * n, texts, mels)
+        want = SH.run_rank(plan, rank, cpu, [0] * n, texts, mels)
+        assert sorted(got) == sorted(want) and len(got) > 0
+        for uid in got:
+            for k in ("gammas", "betas", "pooled"):
+                worst = max(worst, maxabs(got[uid][k], want[uid][k]))
+    _report(f"cfg4-style sweep ({n} mels, {len(plan.shards)} shards, 2 ranks): max-abs {worst:.2e}")
+    assert worst <= 2e-4
+
+
 def test_modules_standalone_api():
     """The sub-modules keep the reference's own signatures."""
     import speakingstyle_b200 as ss
