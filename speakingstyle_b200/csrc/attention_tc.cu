@@ -255,9 +255,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint8_t* row = smem_al + OFF_Q + r * 128;
       const int sw = r & 7;
       float qv[32];
+      const float qs = 1.4426950408889634f / temperature;  // log2(e)/sqrt(dk) folded into Q: S comes out in the base-2 domain
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
-        const float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+        float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+        x.x *= qs; x.y *= qs; x.z *= qs; x.w *= qs;
         const float4 hq = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
         qv[4 * u + 0] = half ? tf32_rn(x.x - hq.x) : hq.x;
         qv[4 * u + 1] = half ? tf32_rn(x.y - hq.y) : hq.y;
@@ -271,7 +273,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (lane == 0) mbar_arrive(q_tm);
     }
     float m = -INFINITY, l = 0.f, alpha_fold = 1.f;
-    const float scale_log2 = 1.4426950408889634f / temperature;
     float o[DK / 2];
 #pragma unroll
     for (int i = 0; i < DK / 2; ++i) o[i] = 0.f;
@@ -297,28 +298,24 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tc_fence_after();
       if (warp == 2 && lane == 0) ATT_TRACE(10, j);
       float sa[32], sc[32];  // sa = this half's 32 keys, sc = the other half's (needed for the row max only)
-      tmem_ld32(lane_base + COL_S + sb * BKV + half * 32, sa);
-      tmem_ld32(lane_base + COL_S + sb * BKV + (half ^ 1) * 32, sc);
+      tmem_ld32x2(lane_base + COL_S + sb * BKV + half * 32, sa, lane_base + COL_S + sb * BKV + (half ^ 1) * 32, sc);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(s_empty0 + 8 * sb);
 
-      // softmax in the base-2 domain: t = s * log2(e)/sqrt(dk); p = 2^(t - m).  One FMUL and one MUFU.EX2 per
-      // score; relative error of p <= ~3e-7, far inside the kernel's 1e-6 class.
+      // softmax in the base-2 domain: S already carries log2(e)/sqrt(dk) (folded into Q); p = 2^(t - m), one
+      // MUFU.EX2 per score; relative error of p <= ~3e-7, far inside the kernel's 1e-6 class.
       const int kbase = j * BKV;
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the warp has little else to overlap
       if (kbase + BKV <= len) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          sa[i] *= scale_log2;
-          mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(sa[i], sc[i] * scale_log2));
-        }
+        for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(sa[i], sc[i]));
       } else {
         const int ka = kbase + half * 32, kc = kbase + (half ^ 1) * 32;
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          sa[i] = (ka + i < len) ? sa[i] * scale_log2 : -INFINITY;
-          const float c = (kc + i < len) ? sc[i] * scale_log2 : -INFINITY;
+          sa[i] = (ka + i < len) ? sa[i] : -INFINITY;
+          const float c = (kc + i < len) ? sc[i] : -INFINITY;
           mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(sa[i], c));
         }
       }

@@ -222,9 +222,11 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       for (int c = 2 * half; c < 2 * half + 2; ++c) {
         const uint8_t* row = smem_al + OFF_K + c * (BQ * 128) + r * 128;
         float hi[32], lo[32];
+        const float qs = 1.4426950408889634f / temperature;  // log2(e)/sqrt(dk) folded into Q
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-          const float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+          float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+          x.x *= qs; x.y *= qs; x.z *= qs; x.w *= qs;
           hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = tf32_rn(x.x - hi[4 * u + 0]);
           hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
           hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
@@ -240,7 +242,6 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     }
 
     float m = -INFINITY, l = 0.f, alpha_fold = 1.f;
-    const float scale_log2 = 1.4426950408889634f / temperature;
     float o[DK / 2];
 #pragma unroll
     for (int i = 0; i < DK / 2; ++i) o[i] = 0.f;
@@ -277,14 +278,11 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the warp has little else to overlap
       if (kbase + BKV <= len) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          s0[i] *= scale_log2;
-          mx4[i & 3] = fmaxf(mx4[i & 3], s0[i]);
-        }
+        for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], s0[i]);
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          s0[i] = (kbase + i < len) ? s0[i] * scale_log2 : -INFINITY;
+          s0[i] = (kbase + i < len) ? s0[i] : -INFINITY;
           mx4[i & 3] = fmaxf(mx4[i & 3], s0[i]);
         }
       }
