@@ -53,6 +53,7 @@ class WNConv(nn.Module):
             w = self.folded_weight().detach().clone()
             del self._parameters["weight_g"], self._parameters["weight_v"]
             self.weight = nn.Parameter(w, requires_grad=False)
+            ParamCache.epoch += 1  # Parameter objects replaced: cached source lists are stale
 
     def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
         has_plain = prefix + "weight" in state_dict

@@ -13,7 +13,14 @@ from . import _lib
 from ._lib import ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, check  # noqa: F401
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream():
+    """The current CUDA stream of the current device as a raw handle.  torch.cuda.current_stream() builds a Python
+    Stream object per call (~15 us, more than a small kernel runs); the raw getter is a plain C call."""
+    if _raw_stream is not None:
+        return C.c_void_p(_raw_stream(torch.cuda.current_device()))
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

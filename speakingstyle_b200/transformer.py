@@ -20,8 +20,17 @@ PAD = 0  # transformer/Constants.py:1
 class ParamCache:
     """Kernel-layout copies of parameters, rebuilt when a source parameter changes."""
 
+    epoch = 0  # bumped whenever some module replaces Parameter objects
+
     def packed(self):
-        srcs = [p for p in self.parameters(recurse=True)] + [b for b in self.buffers(recurse=True)]
+        # the walk over parameters / buffers is done once (it costs more host time than a small kernel runs); in-place
+        # updates (load_state_dict, .to()) are still seen through data_ptr / _version.  Code that REPLACES Parameter
+        # objects (remove_weight_norm) bumps ParamCache.epoch, which invalidates every cached list.
+        srcs = self.__dict__.get("_pack_srcs")
+        if srcs is None or self.__dict__.get("_pack_epoch") != ParamCache.epoch:
+            srcs = [p for p in self.parameters(recurse=True)] + [b for b in self.buffers(recurse=True)]
+            self.__dict__["_pack_srcs"] = srcs
+            self.__dict__["_pack_epoch"] = ParamCache.epoch
         key = tuple((t.data_ptr(), t._version) for t in srcs)
         if self.__dict__.get("_pack_key") != key:
             with torch.no_grad():
