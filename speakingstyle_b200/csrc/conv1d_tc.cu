@@ -212,12 +212,11 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, TcArgs a, cudaStream_
   a.m_tiles = (a.S_out + BM - 1) / BM;
   const int64_t tiles = (int64_t)a.B * ((a.m_tiles + C::MT - 1) / C::MT) * a.n_tiles;  // scheduling units
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tc: too many tiles");
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
+  static unsigned long long attr_mask = 0;  // per device
+  if (first_use_on_device(attr_mask)) {
     cudaError_t e = cudaFuncSetAttribute(conv1d_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C::smem_bytes);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tc: smem opt-in");
-    attr_set = true;
   }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tc: no CUDA device");

@@ -417,12 +417,11 @@ int launch2(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& 
   a.m_tiles = (int)((rows + 2 * BM - 1) / (2 * BM));  // pair tiles of 256 rows
   const int64_t tiles = (int64_t)(a.flat ? 1 : a.B) * a.m_tiles * a.n_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_ts2: too many tiles");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_mask = 0;  // per device
+  if (first_use_on_device(attr_mask)) {
     cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_ts2_kernel<BN2, STAGES2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C::smem_bytes);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_ts2: smem opt-in");
-    attr_set = true;
   }
   const int sms = sm_count();
   SS_REQUIRE(sms >= 2, SS_ERR_CUDA, "ss_conv1d_tf32x3_ts2: no CUDA device");

@@ -475,6 +475,17 @@ inline int make_map_3d(CUtensorMap* m, CUtensorMapDataType dt, const void* base,
   return SS_OK;
 }
 
+// true the first time it is called for the current device with this mask (kernel attributes such as the dynamic
+// shared-memory opt-in are per device; one process normally drives one GPU, but nothing here should assume it)
+inline bool first_use_on_device(unsigned long long& mask) {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess) return true;
+  const unsigned long long bit = 1ull << (d & 63);
+  if (mask & bit) return false;
+  mask |= bit;
+  return true;
+}
+
 inline int sm_count() {
   static int n = []() {
     int dev = 0, v = 0;
