@@ -344,6 +344,39 @@ def test_outputs_depend_on_batch_composition_like_the_reference():
     assert torch.equal(out[5].cpu(), ref[5]) and maxabs(out[1], ref[1]) <= TOL
 
 
+def _custom_batch(src_lens, mel_lens, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    B, L, Tr = len(src_lens), max(src_lens), max(mel_lens)
+    sl, ml = torch.tensor(src_lens), torch.tensor(mel_lens)
+    texts = torch.randint(1, C.N_SRC_VOCAB, (B, L), generator=g) * (torch.arange(L)[None, :] < sl[:, None])
+    mels = torch.randn(B, Tr, 80, generator=g) * (torch.arange(Tr)[None, :, None] < ml[:, None, None])
+    return {"speakers": torch.zeros(B, dtype=torch.int64), "texts": texts, "src_lens": sl, "max_src_len": L,
+            "mels": mels, "mel_lens": ml, "max_mel_len": Tr}
+
+
+@pytest.mark.parametrize("src_lens,mel_lens", [
+    ([1, 120, 37], [1, 400, 50]),      # one-token utterance with a one-frame reference next to long ones
+    ([170, 90], [300, 1000]),          # > 1000 output frames (on-the-fly position table, Models.py:154-162) and the
+                                       # longest reference the encoder's table covers
+    ([7], [1]),                        # batch of one
+])
+def test_edge_shapes_against_the_oracle(src_lens, mel_lens):
+    """Ragged and extreme shapes: every integer output exact, floats within the fp32 tolerance, against the oracle
+    (itself pinned to the reference by tests/test_oracle.py)."""
+    model, mc, sd = get_models("BC2013")
+    batch = _custom_batch(src_lens, mel_lens)
+    out = run(model, batch)
+    with torch.no_grad():
+        ref = O.fastspeech2_forward(sd, mc, batch)
+    assert out[0].shape == ref[0].shape
+    assert torch.equal(out[5].cpu(), ref[5])                                   # d_rounded
+    assert torch.equal(out[9].cpu().to(torch.int64), ref[9].to(torch.int64))   # mel_lens
+    assert torch.equal(out[6].cpu(), ref[6]) and torch.equal(out[7].cpu(), ref[7])
+    for k in (0, 1, 2, 3, 4):
+        assert maxabs(out[k], ref[k]) <= TOL, k
+    _report(f"edge shapes src={src_lens} ref={mel_lens}: T={out[0].shape[1]}, mel max-abs {maxabs(out[1], ref[1]):.2e}")
+
+
 # ---------------------------------------------------------------------------------------------
 # bf16 precision mode (tcgen05 convolutions): integers identical, floats within relative L2 1e-2
 # ---------------------------------------------------------------------------------------------
