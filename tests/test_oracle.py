@@ -165,6 +165,35 @@ def test_oracle_vs_live_reference():
         assert (gen(mel) - O.hifigan_forward(S.fold_weight_norm(vsd), h, mel)).abs().max().item() <= 2e-5
 
 
+@pytest.mark.skipif(not ref_harness.available(), reason="needs /root/reference (build container only)")
+def test_oracle_vs_live_reference_beyond_the_position_table():
+    """More than 1000 output frames: the reference's decoder builds its position table on the fly (Models.py:154-162)
+    and crops nothing; the oracle must follow it (the GPU test test_edge_shapes_against_the_oracle leans on this)."""
+    ds = "BC2013"
+    g = torch.Generator().manual_seed(3)
+    sl, ml = torch.tensor([170, 90]), torch.tensor([300, 1000])
+    L, Tr = 170, 1000
+    texts = torch.randint(1, C.N_SRC_VOCAB, (2, L), generator=g) * (torch.arange(L)[None, :] < sl[:, None])
+    mels = torch.randn(2, Tr, 80, generator=g) * (torch.arange(Tr)[None, :, None] < ml[:, None, None])
+    batch = {"speakers": torch.zeros(2, dtype=torch.int64), "texts": texts, "src_lens": sl, "max_src_len": L,
+             "mels": mels, "mel_lens": ml, "max_mel_len": Tr}
+    d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    sd = S.fastspeech2_state_dict(mc, ds)
+    model = ref_harness.build_fastspeech2(pc, mc, sd)
+    with torch.no_grad(), ref_harness.quiet():
+        ref = model(batch["speakers"], batch["texts"], batch["src_lens"], batch["max_src_len"], batch["mels"],
+                    batch["mel_lens"], batch["max_mel_len"])
+        mine = O.fastspeech2_forward(sd, mc, batch)
+    assert ref[0].shape[1] > 1000
+    for a, b in zip(ref, mine):
+        assert a.dtype == b.dtype and a.shape == b.shape
+        if a.dtype.is_floating_point:
+            assert (a - b).abs().max().item() <= 5e-5
+        else:
+            assert torch.equal(a, b)
+
+
 def test_teacher_forced_oracle_matches_golden(golden):
     """p/e/d targets given (the training / fine-control call)."""
     g = golden("tiny_tf")
