@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libspeakingstyle_b200.so")
+# SS_LIB_PATH: A/B timing of two builds of the same ABI on one box (debug only; the default is the in-tree build)
+LIB_PATH = os.environ.get("SS_LIB_PATH") or os.path.join(_HERE, "lib", "libspeakingstyle_b200.so")
 
 vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 

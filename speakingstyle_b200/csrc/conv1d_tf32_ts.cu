@@ -18,7 +18,14 @@ namespace {
 using namespace sstc;
 
 constexpr int KCHUNK = 32;  // fp32 elements per 128-byte swizzle row
-constexpr int NTHREADS = 320;
+// Split warps: four (one per TMEM lane group) for BN = 128; eight for the narrow tiles, where the split (~650 cycles
+// per chunk whatever N is) - not the N = 64 / 32 MMAs (384 / 192 cycles) - sets the pace: warps w and w+4 share a lane
+// group and each splits half of the row's 32 channels.  (At BN = 128 the epilogue's 128-float row caps the kernel at
+// three warps per scheduler.)
+template <int BN>
+constexpr int xf_warps() { return BN <= 64 ? 8 : 4; }
+template <int BN>
+constexpr int n_threads() { return 32 * (6 + xf_warps<BN>()); }
 constexpr int A_SLOTS = 2;
 constexpr int A_SLOT_COLS = 2 * KCHUNK;  // hi | lo
 
@@ -82,8 +89,19 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) 
       : "memory");
 }
 
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+
 template <int BN, int STAGES>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __launch_bounds__(n_threads<BN>(), 1)
 conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                       const __grid_constant__ CUtensorMap tmBl, const TcArgs p, const int in_act, const float in_slope,
                       const int group) {
@@ -116,7 +134,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       mbar_init(empty0 + 8 * s, 1);
     }
     for (int t = 0; t < A_SLOTS; ++t) {
-      mbar_init(tafull0 + 8 * t, 4);  // one arrival per split warp
+      mbar_init(tafull0 + 8 * t, xf_warps<BN>());  // one arrival per split warp
       mbar_init(taempty0 + 8 * t, 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -219,7 +237,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         straddle = t_tile0 + BM > p.S_out;
       }
       const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
-      const bool lean = drain_is_lean(p);  // warp-uniform
+      const bool lean = drain_is_lean<(BN <= 64)>(p);  // warp-uniform
       if (lean && p.residual) {
         // Pull this tile's residual rows into L2 now, while the MMAs run: the drain below keeps only four 16-byte
         // loads per lane in flight, which from HBM (~1 us) capped the whole kernel at ~1.2 TB/s of residual reads.
@@ -278,7 +296,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
+          drain_block_lean<(BN <= 64)>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
         else
           drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
@@ -286,6 +304,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   } else {
     // ================= operand split (warps 6..9): thread = row, shared memory -> registers -> TMEM =========
     const int lg = warp & 3;  // TMEM lane group this warp may write
+    const int xhalf = (warp - 6) >> 2;  // which half of the row's channels (eight split warps only)
     const int r = lg * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16) + C::a_col0;
     const int sw = r & 7;
@@ -312,9 +331,11 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         // flat tiling: a tap that leaves this row's utterance must read the zero padding, not the neighbour's frames
         const bool outside = edge_tile && (t_src < 0 || t_src >= p.S_in);
         if (--cleft == 0) { cleft = nchunk; t_src += p.dilation; }
-        float hi[32], lo[32];
+        constexpr int NU = 32 / xf_warps<BN>();  // 16-byte units of the row this warp splits: 8 (whole row) or 4 (half)
+        float hi[4 * NU], lo[4 * NU];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {  // 16-byte unit u of the row sits at unit (u ^ (row & 7)) - SWIZZLE_128B
+        for (int uu = 0; uu < NU; ++uu) {  // 16-byte unit u of the row sits at unit (u ^ (row & 7)) - SWIZZLE_128B
+          const int u = xhalf * NU + uu;
           float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
           if (in_act == SS_ACT_LRELU) {
             x.x = x.x > 0.f ? x.x : x.x * in_slope;
@@ -322,14 +343,14 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             x.z = x.z > 0.f ? x.z : x.z * in_slope;
             x.w = x.w > 0.f ? x.w : x.w * in_slope;
           }
-          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = LO_RN(x.x - hi[4 * u + 0]);
-          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = LO_RN(x.y - hi[4 * u + 1]);
-          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = LO_RN(x.z - hi[4 * u + 2]);
-          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = LO_RN(x.w - hi[4 * u + 3]);
+          hi[4 * uu + 0] = tf32_rn(x.x); lo[4 * uu + 0] = LO_RN(x.x - hi[4 * uu + 0]);
+          hi[4 * uu + 1] = tf32_rn(x.y); lo[4 * uu + 1] = LO_RN(x.y - hi[4 * uu + 1]);
+          hi[4 * uu + 2] = tf32_rn(x.z); lo[4 * uu + 2] = LO_RN(x.z - hi[4 * uu + 2]);
+          hi[4 * uu + 3] = tf32_rn(x.w); lo[4 * uu + 3] = LO_RN(x.w - hi[4 * uu + 3]);
         }
         if (edge_tile && __any_sync(0xffffffffu, outside)) {  // warp-uniform branch: skipped in interior tiles
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
+          for (int i = 0; i < 4 * NU; ++i) {
             hi[i] = outside ? 0.f : hi[i];
             lo[i] = outside ? 0.f : lo[i];
           }
@@ -338,8 +359,13 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
         tc_fence_after();
         if (threadIdx.x == 192) CONV_TRACE(6, gi);
-        tmem_st32(lane_base + slot * A_SLOT_COLS, hi);
-        tmem_st32(lane_base + slot * A_SLOT_COLS + KCHUNK, lo);
+        if constexpr (NU == 8) {
+          tmem_st32(lane_base + slot * A_SLOT_COLS, hi);
+          tmem_st32(lane_base + slot * A_SLOT_COLS + KCHUNK, lo);
+        } else {
+          tmem_st16(lane_base + slot * A_SLOT_COLS + xhalf * 16, hi);
+          tmem_st16(lane_base + slot * A_SLOT_COLS + KCHUNK + xhalf * 16, lo);
+        }
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncwarp();
@@ -378,7 +404,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3_ts: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  conv1d_tf32_ts_kernel<BN, STAGES><<<grid, NTHREADS, C::smem_bytes, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
+  conv1d_tf32_ts_kernel<BN, STAGES><<<grid, n_threads<BN>(), C::smem_bytes, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
   SS_CHECK_LAUNCH("ss_conv1d_tf32x3_ts");
   return SS_OK;
 }
@@ -413,7 +439,8 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   // sequence length that would otherwise leave a partly empty last tile in every utterance.
   const bool flat = p->B > 1 && p->S_in == p->S_out && p->S_out % BM != 0 &&
                     p->x_batch_stride == (int64_t)p->S_in * p->x_row_stride && (int64_t)p->B * p->S_in < (1ll << 30) &&
-                    p->y != nullptr && p->accum == nullptr && p->y_act == nullptr && p->act != SS_ACT_TANH;
+                    (p->accum == nullptr ? p->y != nullptr : p->Cout <= 64) && p->y_act == nullptr &&
+                    p->act != SS_ACT_TANH;  // = the conditions of the lean epilogue, the only one that un-flattens rows
   CUtensorMap tmA, tmBh, tmBl;
   int rc = flat ? make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin,
                               (uint64_t)p->B * (uint64_t)p->S_in, 1, (uint64_t)p->x_row_stride * 4,

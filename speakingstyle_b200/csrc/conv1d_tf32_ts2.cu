@@ -267,7 +267,7 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         straddle = t_tile0 + BM > p.S_out;
       }
       const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
-      const bool lean = drain_is_lean(p);  // warp-uniform
+      const bool lean = drain_is_lean<(BN <= 64)>(p);  // warp-uniform
       if (lean && p.residual) {
         // Pull this tile's residual rows into L2 now, while the MMAs run: the drain below keeps only four 16-byte
         // loads per lane in flight, which from HBM (~1 us) capped the whole kernel at ~1.2 TB/s of residual reads.
@@ -326,7 +326,7 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
+          drain_block_lean<(BN <= 64)>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
         else
           drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }

@@ -361,18 +361,23 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
   }
 }
 
-// Lean variant for the fp32 kernels' common case (fp32 y, optional bias / fp32 residual / row mask, activation
-// none / relu / leaky-relu; no running mean, no bf16 copy, no tanh).  The 3xTF32 kernels keep the whole output
+// Lean variant for the fp32 kernels' common case (fp32 y and / or running mean, optional bias / fp32 residual / row
+// mask, activation none / relu / leaky-relu; no bf16 copy, no tanh).  The 3xTF32 kernels keep the whole output
 // row in registers, so their column-block loop must be unrolled and this body is instantiated BN/32 times:
 // it has to be small (one warp per scheduler runs it - the general drain_block above, four times over, spills
 // out of the instruction cache and took ~4.5k cycles per block) and its eight row steps are straight-line
 // with all residual loads in flight before the first is used.
+// WITH_ACCUM: the running-mean form is compiled in only for the narrow tiles (BN <= 64, the HiFi-GAN stages that use
+// it); at BN = 128 the epilogue already holds a 128-float row and the extra live values would spill.
+template <bool WITH_ACCUM>
 __device__ __forceinline__ bool drain_is_lean(const TcArgs& p) {
-  return p.y != nullptr && p.y_dtype == SS_F32 && p.accum == nullptr && p.y_act == nullptr && p.act != SS_ACT_TANH &&
+  return (p.y != nullptr || (WITH_ACCUM && p.accum != nullptr)) && (WITH_ACCUM || p.accum == nullptr) &&
+         p.y_dtype == SS_F32 && p.y_act == nullptr && p.act != SS_ACT_TANH &&
          (p.residual == nullptr || p.residual_dtype == SS_F32);
 }
 // (b, t_tile0) = utterance and frame of the tile's first row; straddle = the tile runs past the end of utterance b
 // (flat tiling only), in which case rows are un-flattened one by one and the row mask is looked up per row.
+template <bool WITH_ACCUM>
 __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane,
                                                  int b, int t_tile0, bool straddle, int n_blk, int len) {
   const int col = (lane & 7) * 4;
@@ -410,6 +415,34 @@ __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&
       r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (res && ok[u]) r[u] = __ldg(reinterpret_cast<const float4*>(res + off[u]));
       t += 4;
+    }
+    if (WITH_ACCUM && p.accum) {  // running mean (HiFi-GAN MRF): accum = scale*v (first branch) or accum += scale*v
+      const bool rd = !p.accum_init;
+      float4 a[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rd && ok[u]) a[u] = *reinterpret_cast<const float4*>(p.accum + off[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float4 f = *reinterpret_cast<const float4*>(src + (half * 4 + u) * 4 * STG_PITCH);
+        f.x += bias4.x; f.y += bias4.y; f.z += bias4.z; f.w += bias4.w;
+        f.x = f.x > 0.f ? f.x : f.x * neg;
+        f.y = f.y > 0.f ? f.y : f.y * neg;
+        f.z = f.z > 0.f ? f.z : f.z * neg;
+        f.w = f.w > 0.f ? f.w : f.w * neg;
+        f.x += r[u].x; f.y += r[u].y; f.z += r[u].z; f.w += r[u].w;
+        if (!keep[u]) f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!ok[u]) continue;
+        if (y) *reinterpret_cast<float4*>(y + off[u]) = f;
+        f.x = fmaf(p.accum_scale, f.x, a[u].x);
+        f.y = fmaf(p.accum_scale, f.y, a[u].y);
+        f.z = fmaf(p.accum_scale, f.z, a[u].z);
+        f.w = fmaf(p.accum_scale, f.w, a[u].w);
+        *reinterpret_cast<float4*>(p.accum + off[u]) = f;
+      }
+      continue;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
