@@ -1,10 +1,12 @@
 // 3xTF32 implicit-GEMM convolution as a CTA PAIR (tcgen05 cta_group::2): two CTAs of a 2-CTA cluster compute one
 // M = 256 x N = 128 tile.  Same mathematics, accuracy measures and epilogue as conv1d_tf32_ts.cu; what changes is
 // who holds the weights.  With one CTA per tile every SM streams the whole [128 x 32] W_hi / W_lo chunk through its
-// own shared memory (48 KB of MMA reads + 32 KB of TMA fill per chunk, 112 KB with the activations) and the
-// 128 B/clk shared-memory pipe, not the tensor pipe, sets the pace (894 cycles per chunk against 768).  In the
-// pair form each SM holds HALF of the weight tile (64 of the 128 output channels): the M = 256 MMA reads the two
-// halves from the two SMs, so per SM it is 24 KB of reads + 16 KB of fill (72 KB per chunk in all).
+// own shared memory (48 KB of MMA reads + 32 KB of TMA fill per chunk, 112 KB with the activations = 875 cycles of
+// the 128 B/clk shared-memory pipe against 768 cycles of tensor time).  In the pair form each SM holds HALF of the
+// weight tile (64 of the 128 output channels): the M = 256 MMA reads the two halves from the two SMs, so per SM it
+// is 24 KB of reads + 16 KB of fill (72 KB per chunk in all).  Measured: bit-identical results, ~4 % faster on long
+// reductions (282 vs 271 TFLOP/s on 1024->1024 k3), slower on 8-chunk tiles where the cluster-wide hand-overs
+// weigh more - ops.py picks it from 16 chunks up (DESIGN.md 3.1 has the whole story, including what it disproved).
 //   * CTA r of the pair owns rows [128 r, 128 r + 128) of the tile: its own activation slab by TMA, its own split
 //     warps writing hi / lo into its own TMEM, its own accumulators (same TMEM columns in both SMs), its own
 //     epilogue.  It loads weight rows [64 r, 64 r + 64).
