@@ -60,6 +60,9 @@ __device__ long long g_att32_trace[16 * 64];
 #define ATT_TRACE(ev, j)
 #endif
 
+// Only hi is rounded here; lo = x - hi goes to the MMA as is - the tensor core truncates an fp32 operand to TF32
+// itself, and lo only carries bits 12-22 of x (same finding as in conv1d_tf32_ts.cu: error unchanged, fewer ALU ops
+// on the split / softmax warps that pace these kernels).
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
@@ -77,7 +80,7 @@ __device__ __forceinline__ void split_tile(float4* hi, float4* lo, int n_vec, in
       const float4 h = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
       hi[base + i * XF_THREADS] = h;
       lo[base + i * XF_THREADS] =
-          make_float4(tf32_rn(x[i].x - h.x), tf32_rn(x[i].y - h.y), tf32_rn(x[i].z - h.z), tf32_rn(x[i].w - h.w));
+          make_float4((x[i].x - h.x), (x[i].y - h.y), (x[i].z - h.z), (x[i].w - h.w));
     }
   }
 }
@@ -261,10 +264,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
         x.x *= qs; x.y *= qs; x.z *= qs; x.w *= qs;
         const float4 hq = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
-        qv[4 * u + 0] = half ? tf32_rn(x.x - hq.x) : hq.x;
-        qv[4 * u + 1] = half ? tf32_rn(x.y - hq.y) : hq.y;
-        qv[4 * u + 2] = half ? tf32_rn(x.z - hq.z) : hq.z;
-        qv[4 * u + 3] = half ? tf32_rn(x.w - hq.w) : hq.w;
+        qv[4 * u + 0] = half ? (x.x - hq.x) : hq.x;
+        qv[4 * u + 1] = half ? (x.y - hq.y) : hq.y;
+        qv[4 * u + 2] = half ? (x.z - hq.z) : hq.z;
+        qv[4 * u + 3] = half ? (x.w - hq.w) : hq.w;
       }
       tmem_st32(lane_base + (half ? COL_QL : COL_QH), qv);
       asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -338,7 +341,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int i = 0; i < 32; ++i) sc[i] = tf32_rn(sa[i]);
       tmem_st32(pcol, sc);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) sa[i] = tf32_rn(sa[i] - sc[i]);
+      for (int i = 0; i < 32; ++i) sa[i] = (sa[i] - sc[i]);
       tmem_st32(pcol + BKV, sa);
       asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
       tc_fence_before();
@@ -400,7 +403,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           const int off = (kq >> 3) * (DK * 128) + d * 128 + (((kq & 7) ^ (d & 7)) << 4);
           *reinterpret_cast<float4*>(vt + off) = hv;
           *reinterpret_cast<float4*>(vt + KV_BYTES + off) =
-              make_float4(tf32_rn(x0 - hv.x), tf32_rn(x1 - hv.y), tf32_rn(x2 - hv.z), tf32_rn(x3 - hv.w));
+              make_float4((x0 - hv.x), (x1 - hv.y), (x2 - hv.z), (x3 - hv.w));
         }
       }
       fence_proxy_async();

@@ -6,16 +6,18 @@
 //     MEMORY once per CTA (tcgen05.st, thread = query row) and S = Q.K^T uses the TS form of tcgen05.mma
 //     (A from TMEM) - 256 of the 512 TMEM columns;
 //   * keys come in 32-key tiles: K [32 x 128] is four K-major [32 x 32] chunk tiles, V [32 x 128] is
-//     transposed on chip into V^T [128 x 32], P [128 x 32] is one swizzle chunk (double-buffered);
+//     transposed on chip into V^T [128 x 32]; P [128 x 32] goes to TMEM too (tcgen05.st by the softmax warps, TS-form
+//     P.V), which leaves shared memory for a three-deep K ring;
 //   * O_j = P_j.V_j is a full N = 128 accumulator (single TMEM buffer) that the softmax warps fold into
 //     fp32 registers each tile (o = o*alpha_j + O_j).  EIGHT softmax warps: warps w and w+4 own the same
 //     32 query rows; both read the whole S row (same running max), but each exponentiates / writes half
 //     of the P row and folds half of the O columns, keeping a partial row sum that is merged at the end.
-//   * softmax(j) is issued BEFORE fold(j-1), so it overlaps P.V of the previous tile on the tensor pipe.
-// Rings (2 deep each): K hi/lo (freed by S_j), V as loaded (freed by the transpose), V^T hi/lo (freed by
-// P.V_j) - so no load waits for a whole tile to retire.
-// TMEM: S0,S1 (2 x 32) | O (128) | Q_hi (128) | Q_lo (128) = 448 columns.  Shared memory 224 KB: K 2x32,
-// V 2x16, V^T 2x32, P 2x32 KB; the Q staging area (64 KB) aliases the K ring.
+//   * the exponentials of tile j are computed BEFORE fold(j-1), so they overlap P.V of the previous tile on the
+//     tensor pipe; P_j itself is stored after the fold (the single P buffer is free once P.V_{j-1} has retired).
+// Rings: K hi/lo three deep (freed by S_j: the loop "S_j retires -> K_{j+3} lands -> split -> S_{j+3}" was the
+// critical one with two stages), V as loaded (freed by the transpose) and V^T hi/lo (freed by P.V_j) two deep.
+// TMEM: S0,S1 (2 x 32) | O (128) | Q_hi (128) | Q_lo (128) | P hi, lo (64) = 512 columns.  Shared memory 192 KB:
+// K 3x32, V 2x16, V^T 2x32 KB; the Q staging area (64 KB) aliases the K ring.
 #include "tc_common.cuh"
 
 namespace {
@@ -28,18 +30,17 @@ constexpr int N_SOFTMAX_WARPS = 8, N_XF_WARPS = 2;
 constexpr int NTHREADS = 32 * (2 + N_SOFTMAX_WARPS + N_XF_WARPS);  // 384: three warps per scheduler -> 168 registers
 constexpr int CH_BYTES = BKV * 128;            // one [32 keys x 32 dims] chunk tile: 4 KB
 constexpr int KV_BYTES = NCH * CH_BYTES;       // 16 KB
-constexpr int P_BYTES = BQ * 128;              // 16 KB
-constexpr int OFF_K = 0;                       // [2][K_hi 16 | K_lo 16]
-constexpr int OFF_VR = OFF_K + 4 * KV_BYTES;   // [2][V as loaded 16]
+constexpr int NK = 3;                          // K ring depth (the loop S_j retires -> K_{j+NK} lands -> split -> S_{j+NK})
+constexpr int OFF_K = 0;                       // [NK][K_hi 16 | K_lo 16]
+constexpr int OFF_VR = OFF_K + NK * 2 * KV_BYTES;  // [2][V as loaded 16]
 constexpr int OFF_VT = OFF_VR + 2 * KV_BYTES;  // [2][V^T_hi 16 | V^T_lo 16]
-constexpr int OFF_P = OFF_VT + 4 * KV_BYTES;   // [2][P_hi 16 | P_lo 16]
-constexpr int SMEM_DATA = OFF_P + 4 * P_BYTES; // 224 KB
-constexpr int N_BARS = 24;
+constexpr int SMEM_DATA = OFF_VT + 4 * KV_BYTES;  // 192 KB
+constexpr int N_BARS = 3 * NK + 4 * 2 + 2 * 2 + 5;
 constexpr int SMEM_BYTES = SMEM_DATA + N_BARS * 8 + 16 + 1024;
-constexpr int COL_S = 0, COL_O = 2 * BKV, COL_QH = COL_O + DK, COL_QL = COL_QH + DK;
+constexpr int COL_S = 0, COL_O = 2 * BKV, COL_QH = COL_O + DK, COL_QL = COL_QH + DK, COL_P = COL_QL + DK;
 constexpr int TMEM_COLS = 512;
-static_assert(COL_QL + DK <= TMEM_COLS, "TMEM budget");
-static_assert(NCH * BQ * 128 <= 4 * KV_BYTES, "Q staging must fit in the K ring");
+static_assert(COL_P + 2 * BKV <= TMEM_COLS, "TMEM budget");
+static_assert(NCH * BQ * 128 <= NK * 2 * KV_BYTES, "Q staging must fit in the K ring");
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 // Debug build (-DSS_ATT_TRACE, scripts/attn_trace.py): CTA (0,0,0) stamps clock64() at the pipeline hand-overs.
@@ -53,6 +54,9 @@ __device__ long long g_att_trace[16 * 64];
 #define ATT_TRACE(ev, j)
 #endif
 
+// Only hi is rounded here; lo = x - hi goes to the MMA as is - the tensor core truncates an fp32 operand to TF32
+// itself, and lo only carries bits 12-22 of x (same finding as in conv1d_tf32_ts.cu: error unchanged, fewer ALU ops
+// on the split / softmax warps that pace these kernels).
 __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
@@ -70,6 +74,17 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) 
       "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
       "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
       "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
       : "memory");
 }
 
@@ -95,11 +110,11 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
   const uint32_t bars = smem0 + SMEM_DATA;
-  // two-deep rings: index with + 8 * slot
-  const uint32_t k_full0 = bars + 0, k_xf0 = bars + 16, k_empty0 = bars + 32;
-  const uint32_t v_full0 = bars + 48, vr_empty0 = bars + 64, vt_full0 = bars + 80, vt_empty0 = bars + 96;
-  const uint32_t s_full0 = bars + 112, s_empty0 = bars + 128, p_full0 = bars + 144;
-  const uint32_t o_full = bars + 160, o_empty = bars + 168, q_full = bars + 176, q_tm = bars + 184;
+  // rings: index with + 8 * slot (K: NK deep; V, V^T, S: two deep)
+  const uint32_t k_full0 = bars, k_xf0 = k_full0 + 8 * NK, k_empty0 = k_xf0 + 8 * NK;
+  const uint32_t v_full0 = k_empty0 + 8 * NK, vr_empty0 = v_full0 + 16, vt_full0 = vr_empty0 + 16, vt_empty0 = vt_full0 + 16;
+  const uint32_t s_full0 = vt_empty0 + 16, s_empty0 = s_full0 + 16;
+  const uint32_t p_full = s_empty0 + 16, o_full = p_full + 8, o_empty = o_full + 8, q_full = o_empty + 8, q_tm = q_full + 8;
   const uint32_t tslot = bars + N_BARS * 8;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + SMEM_DATA + N_BARS * 8);
 
@@ -109,18 +124,20 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     prefetch_tmap(&tmQ);
     prefetch_tmap(&tmK);
     prefetch_tmap(&tmV);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < NK; ++s) {
       mbar_init(k_full0 + 8 * s, 1);
       mbar_init(k_xf0 + 8 * s, N_XF_WARPS);
       mbar_init(k_empty0 + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(v_full0 + 8 * s, 1);
       mbar_init(vr_empty0 + 8 * s, N_XF_WARPS);
       mbar_init(vt_full0 + 8 * s, N_XF_WARPS);
       mbar_init(vt_empty0 + 8 * s, 1);
       mbar_init(s_full0 + 8 * s, 1);
       mbar_init(s_empty0 + 8 * s, N_SOFTMAX_WARPS);
-      mbar_init(p_full0 + 8 * s, N_SOFTMAX_WARPS);
     }
+    mbar_init(p_full, N_SOFTMAX_WARPS);
     mbar_init(o_full, 1);
     mbar_init(o_empty, N_SOFTMAX_WARPS);
     mbar_init(q_full, 1);
@@ -149,11 +166,12 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           tma_load_3d(smem0 + OFF_VR + s * KV_BYTES + c * CH_BYTES, &tmV, v_full0 + 8 * s, 2 * D + h * DK + c * 32,
                       j * BKV, b);
         if (j == 0) mbar_wait(q_tm, 0);  // Q now lives in TMEM: its staging area may be overwritten
-        mbar_wait(k_empty0 + 8 * s, ph);
+        const int ks = j % NK;
+        mbar_wait(k_empty0 + 8 * ks, ((j / NK) & 1) ^ 1);
         ATT_TRACE(1, j);
-        mbar_expect_tx(k_full0 + 8 * s, KV_BYTES);
+        mbar_expect_tx(k_full0 + 8 * ks, KV_BYTES);
         for (int c = 0; c < NCH; ++c)
-          tma_load_3d(smem0 + OFF_K + s * 2 * KV_BYTES + c * CH_BYTES, &tmK, k_full0 + 8 * s, D + h * DK + c * 32,
+          tma_load_3d(smem0 + OFF_K + ks * 2 * KV_BYTES + c * CH_BYTES, &tmK, k_full0 + 8 * ks, D + h * DK + c * 32,
                       j * BKV, b);
       }
     }
@@ -164,12 +182,12 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const uint32_t idesc_o = make_idesc(2u, DK);   // N = 128 head dims
       const uint32_t qh = tmem_base + COL_QH, ql = tmem_base + COL_QL;
       auto issue_s = [&](int j) {
-        const int s = j & 1;
-        mbar_wait(k_xf0 + 8 * s, (j >> 1) & 1);
+        const int s = j & 1, ks_ = j % NK;
+        mbar_wait(k_xf0 + 8 * ks_, (j / NK) & 1);
         mbar_wait(s_empty0 + 8 * s, ((j >> 1) & 1) ^ 1);
         tc_fence_after();
         ATT_TRACE(6, j);
-        const uint32_t kh = desc_lo(smem0 + OFF_K + s * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
+        const uint32_t kh = desc_lo(smem0 + OFF_K + ks_ * 2 * KV_BYTES), kl = kh + (KV_BYTES >> 4);
         const uint32_t d = tmem_base + COL_S + s * BKV;
 #pragma unroll
         for (int ks = 0; ks < DK / 8; ++ks) {  // 16 steps of 8 head dims
@@ -179,7 +197,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           umma_tf32_ts_w(d, qh + ks * 8, kh + ko, idesc_s, 1u);
         }
         umma_commit(s_full0 + 8 * s);
-        umma_commit(k_empty0 + 8 * s);
+        umma_commit(k_empty0 + 8 * ks_);
         ATT_TRACE(7, j);
       };
       mbar_wait(q_tm, 0);
@@ -189,19 +207,18 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         if (j + 1 < NT) issue_s(j + 1);
         const int s = j & 1;
         mbar_wait(vt_full0 + 8 * s, (j >> 1) & 1);
-        mbar_wait(p_full0 + 8 * s, (j >> 1) & 1);
+        mbar_wait(p_full, j & 1);
         mbar_wait(o_empty, (j & 1) ^ 1);
         tc_fence_after();
         ATT_TRACE(8, j);
         const uint32_t vh = desc_lo(smem0 + OFF_VT + s * 2 * KV_BYTES), vl = vh + (KV_BYTES >> 4);  // V^T hi / lo
-        const uint32_t ph = desc_lo(smem0 + OFF_P + s * 2 * P_BYTES), pl = ph + (P_BYTES >> 4);
+        const uint32_t ph = tmem_base + COL_P, pl = ph + BKV;                                       // P hi / lo in TMEM
         const uint32_t d = tmem_base + COL_O;
 #pragma unroll
-        for (int kk = 0; kk < BKV / 8; ++kk) {  // 4 steps of 8 keys (32 bytes of each operand row)
-          const uint32_t o = kk * 2;
-          umma_tf32_w(d, pl + o, vh + o, idesc_o, kk != 0);
-          umma_tf32_w(d, ph + o, vl + o, idesc_o, 1u);
-          umma_tf32_w(d, ph + o, vh + o, idesc_o, 1u);
+        for (int kk = 0; kk < BKV / 8; ++kk) {  // 4 steps of 8 keys: 8 TMEM columns of P, 32 bytes of each V^T row
+          umma_tf32_ts_w(d, pl + kk * 8, vh + kk * 2, idesc_o, kk != 0);
+          umma_tf32_ts_w(d, ph + kk * 8, vl + kk * 2, idesc_o, 1u);
+          umma_tf32_ts_w(d, ph + kk * 8, vh + kk * 2, idesc_o, 1u);
         }
         umma_commit(o_full);
         umma_commit(vt_empty0 + 8 * s);
@@ -227,10 +244,10 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         for (int u = 0; u < 8; ++u) {
           float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
           x.x *= qs; x.y *= qs; x.z *= qs; x.w *= qs;
-          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = tf32_rn(x.x - hi[4 * u + 0]);
-          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = tf32_rn(x.y - hi[4 * u + 1]);
-          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = tf32_rn(x.z - hi[4 * u + 2]);
-          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = tf32_rn(x.w - hi[4 * u + 3]);
+          hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = (x.x - hi[4 * u + 0]);
+          hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = (x.y - hi[4 * u + 1]);
+          hi[4 * u + 2] = tf32_rn(x.z); lo[4 * u + 2] = (x.z - hi[4 * u + 2]);
+          hi[4 * u + 3] = tf32_rn(x.w); lo[4 * u + 3] = (x.w - hi[4 * u + 3]);
         }
         tmem_st32(lane_base + COL_QH + c * 32, hi);
         tmem_st32(lane_base + COL_QL + c * 32, lo);
@@ -289,38 +306,39 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const float m_new = fmaxf(fmaxf(m, mx4[0]), fmaxf(fmaxf(mx4[1], mx4[2]), mx4[3]));  // finite: >= 1 valid key per tile
       const float alpha = ex2_approx(m - m_new);
       m = m_new;
-      // this half's 16 keys: exponentiate, sum, write P hi / lo (units 4*half .. 4*half+3 of the swizzled row)
-      uint8_t* ph_row = smem_al + OFF_P + sb * 2 * P_BYTES + r * 128;
-      uint8_t* pl_row = ph_row + P_BYTES;
+      // this half's 16 keys: exponentiate, sum, split into TF32 hi / lo
+      float pv_hi[16], pv_lo[16];
       float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int uu = 0; uu < 4; ++uu) {
-        const int u = 4 * half + uu;
         float4 a;  // the s0 index has to be a compile-time constant (registers): select on half
         a.x = ex2_approx((half ? s0[16 + 4 * uu + 0] : s0[4 * uu + 0]) - m_new);
         a.y = ex2_approx((half ? s0[16 + 4 * uu + 1] : s0[4 * uu + 1]) - m_new);
         a.z = ex2_approx((half ? s0[16 + 4 * uu + 2] : s0[4 * uu + 2]) - m_new);
         a.w = ex2_approx((half ? s0[16 + 4 * uu + 3] : s0[4 * uu + 3]) - m_new);
         sum4[uu] = (a.x + a.y) + (a.z + a.w);
-        const int pu = (u ^ sw) * 16;
-        const float4 ah = make_float4(tf32_rn(a.x), tf32_rn(a.y), tf32_rn(a.z), tf32_rn(a.w));
-        *reinterpret_cast<float4*>(ph_row + pu) = ah;
-        *reinterpret_cast<float4*>(pl_row + pu) =
-            make_float4(tf32_rn(a.x - ah.x), tf32_rn(a.y - ah.y), tf32_rn(a.z - ah.z), tf32_rn(a.w - ah.w));
+        pv_hi[4 * uu + 0] = tf32_rn(a.x); pv_lo[4 * uu + 0] = (a.x - pv_hi[4 * uu + 0]);
+        pv_hi[4 * uu + 1] = tf32_rn(a.y); pv_lo[4 * uu + 1] = (a.y - pv_hi[4 * uu + 1]);
+        pv_hi[4 * uu + 2] = tf32_rn(a.z); pv_lo[4 * uu + 2] = (a.z - pv_hi[4 * uu + 2]);
+        pv_hi[4 * uu + 3] = tf32_rn(a.w); pv_lo[4 * uu + 3] = (a.w - pv_hi[4 * uu + 3]);
       }
       l = l * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
-      fence_proxy_async();
-      __syncwarp();
-      if (warp == 2 && lane == 0) ATT_TRACE(11, j);
-      if (lane == 0) mbar_arrive(p_full0 + 8 * sb);  // buffer sb was last read by P.V_{j-2}: retired before fold(j-2)
-
+      // P lives in TMEM (single buffer): P.V_{j-1} must have retired before it is overwritten - that is the same
+      // event fold(j-1) waits for, so the fold comes first; S_{j+1} keeps the tensor pipe busy meanwhile
       if (j > 0) fold_o(j - 1, alpha_fold);
       alpha_fold = alpha;
+      tmem_st16(lane_base + COL_P + half * 16, pv_hi);
+      tmem_st16(lane_base + COL_P + BKV + half * 16, pv_lo);
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (warp == 2 && lane == 0) ATT_TRACE(11, j);
+      if (lane == 0) mbar_arrive(p_full);
     }
     fold_o(NT - 1, alpha_fold);
 
-    // merge the two halves' row sums through shared memory (all MMAs have retired: P is free)
-    float* lbuf = reinterpret_cast<float*>(smem_al + OFF_P);
+    // merge the two halves' row sums through shared memory (all MMAs have retired: the K ring is free)
+    float* lbuf = reinterpret_cast<float*>(smem_al + OFF_K);
     lbuf[half * BQ + r] = l;
     asm volatile("bar.sync 1, %0;" ::"n"(N_SOFTMAX_WARPS * 32) : "memory");
     l += lbuf[(half ^ 1) * BQ + r];
@@ -339,10 +357,11 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const int s = j & 1;
       const uint32_t ph = (j >> 1) & 1;
       {  // K: element-wise split, hi in place, lo next to it
-        mbar_wait(k_full0 + 8 * s, ph);
+        const int ks = j % NK;
+        mbar_wait(k_full0 + 8 * ks, (j / NK) & 1);
         if (tt == 0) ATT_TRACE(2, j);
-        float4* hi = reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES);
-        float4* lo = reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES);
+        float4* hi = reinterpret_cast<float4*>(smem_al + OFF_K + ks * 2 * KV_BYTES);
+        float4* lo = reinterpret_cast<float4*>(smem_al + OFF_K + ks * 2 * KV_BYTES + KV_BYTES);
         constexpr int NV = KV_BYTES / 16 / (N_XF_WARPS * 32);  // 16 vectors per thread, in batches of 8:
 #pragma unroll 1
         for (int i0 = 0; i0 < NV; i0 += 8) {  // all loads of a batch first - in-place stores would otherwise
@@ -354,13 +373,13 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             const int idx = tt + (i0 + i) * (N_XF_WARPS * 32);
             const float4 hv = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
             hi[idx] = hv;
-            lo[idx] = make_float4(tf32_rn(x[i].x - hv.x), tf32_rn(x[i].y - hv.y), tf32_rn(x[i].z - hv.z),
-                                  tf32_rn(x[i].w - hv.w));
+            lo[idx] = make_float4((x[i].x - hv.x), (x[i].y - hv.y), (x[i].z - hv.z),
+                                  (x[i].w - hv.w));
           }
         }
         fence_proxy_async();
         __syncwarp();
-        if (lane == 0) mbar_arrive(k_xf0 + 8 * s);
+        if (lane == 0) mbar_arrive(k_xf0 + 8 * ks);
         if (tt == 0) ATT_TRACE(3, j);
       }
       {  // V [32 keys x 128 dims] (chunked [c][key][32]) -> V^T hi / lo [128 dims x 32 keys], swizzled rows
@@ -385,7 +404,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             const int pu = (u ^ swd) << 4;
             *reinterpret_cast<float4*>(th + pu) = hv;
             *reinterpret_cast<float4*>(tl + pu) =
-                make_float4(tf32_rn(x0 - hv.x), tf32_rn(x1 - hv.y), tf32_rn(x2 - hv.z), tf32_rn(x3 - hv.w));
+                make_float4((x0 - hv.x), (x1 - hv.y), (x2 - hv.z), (x3 - hv.w));
           }
         }
         fence_proxy_async();
