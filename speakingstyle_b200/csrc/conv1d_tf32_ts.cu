@@ -8,9 +8,13 @@
 // Here the split warps read the TMA-landed fp32 tile ONCE (thread = row, un-swizzling the eight 16-byte
 // units of its row), split it in registers and store hi / lo with tcgen05.st into TMEM, from where the
 // MMAs take A for free; shared memory then only carries the TMA fill and the B (weight) reads.
+// Stride-1 same-length layers are tiled over the flattened B*S rows (TcArgs::flat); the common epilogue is the
+// lean straight-line one of tc_common.cuh; long reductions at BN = 128 go to the CTA-pair form
+// (conv1d_tf32_ts2.cu).  DESIGN.md 3.1 has the measurements behind each of these.
 //
 // TMEM columns (BN = 128): main accumulator x2 (256) | correction accumulator (128) | A hi/lo, 2 slots x
 // (32 + 32) columns (128) = 512.  Shared memory per stage: x tile 16 KB + W_hi + W_lo.
+// Warps: TMA, MMA, 4 epilogue, 4 split (8 split warps for the narrow tiles BN = 64 / 32).
 #include "tc_common.cuh"
 
 namespace {
