@@ -126,7 +126,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     prefetch_tmap(&tmV);
     for (int s = 0; s < NK; ++s) {
       mbar_init(k_full0 + 8 * s, 1);
-      mbar_init(k_xf0 + 8 * s, N_XF_WARPS);
+      mbar_init(k_xf0 + 8 * s, N_SOFTMAX_WARPS);
       mbar_init(k_empty0 + 8 * s, 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -257,6 +257,32 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       __syncwarp();
       if (lane == 0) mbar_arrive(q_tm);
     }
+    // K_j is split into TF32 hi / lo by these warps too (element-wise, 4 vectors per thread, two tiles ahead of its
+    // S_j): with the split on the two transpose warps as well, those paced the kernel (~2 k cycles per tile)
+    const int st_id = (warp - 2) * 32 + lane;  // 0..255
+    auto split_k = [&](int jj) {
+      if (jj >= NT) return;
+      const int ks = jj % NK;
+      mbar_wait(k_full0 + 8 * ks, (jj / NK) & 1);
+      if (st_id == 0) ATT_TRACE(2, jj);
+      float4* khi = reinterpret_cast<float4*>(smem_al + OFF_K + ks * 2 * KV_BYTES);
+      float4* klo = khi + KV_BYTES / 16;
+      float4 x[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) x[i] = khi[st_id + i * (N_SOFTMAX_WARPS * 32)];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 hv = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
+        khi[st_id + i * (N_SOFTMAX_WARPS * 32)] = hv;
+        klo[st_id + i * (N_SOFTMAX_WARPS * 32)] = make_float4(x[i].x - hv.x, x[i].y - hv.y, x[i].z - hv.z, x[i].w - hv.w);
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(k_xf0 + 8 * ks);
+      if (st_id == 0) ATT_TRACE(3, jj);
+    };
+    split_k(0);
+    split_k(1);
 
     float m = -INFINITY, l = 0.f, alpha_fold = 1.f;
     float o[DK / 2];
@@ -334,6 +360,7 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       __syncwarp();
       if (warp == 2 && lane == 0) ATT_TRACE(11, j);
       if (lane == 0) mbar_arrive(p_full);
+      split_k(j + 2);
     }
     fold_o(NT - 1, alpha_fold);
 
@@ -351,37 +378,11 @@ attention_tc128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         orow[c] = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
     }
   } else {
-    // ================= K split / V transpose (2 warps, 64 threads) =================
+    // ================= V transpose (2 warps, 64 threads) =================
     const int tt = (warp - 2 - N_SOFTMAX_WARPS) * 32 + lane;  // 0..63
     for (int j = 0; j < NT; ++j) {
       const int s = j & 1;
       const uint32_t ph = (j >> 1) & 1;
-      {  // K: element-wise split, hi in place, lo next to it
-        const int ks = j % NK;
-        mbar_wait(k_full0 + 8 * ks, (j / NK) & 1);
-        if (tt == 0) ATT_TRACE(2, j);
-        float4* hi = reinterpret_cast<float4*>(smem_al + OFF_K + ks * 2 * KV_BYTES);
-        float4* lo = reinterpret_cast<float4*>(smem_al + OFF_K + ks * 2 * KV_BYTES + KV_BYTES);
-        constexpr int NV = KV_BYTES / 16 / (N_XF_WARPS * 32);  // 16 vectors per thread, in batches of 8:
-#pragma unroll 1
-        for (int i0 = 0; i0 < NV; i0 += 8) {  // all loads of a batch first - in-place stores would otherwise
-          float4 x[8];                        // serialise every load behind the previous store (aliasing)
-#pragma unroll
-          for (int i = 0; i < 8; ++i) x[i] = hi[tt + (i0 + i) * (N_XF_WARPS * 32)];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int idx = tt + (i0 + i) * (N_XF_WARPS * 32);
-            const float4 hv = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
-            hi[idx] = hv;
-            lo[idx] = make_float4((x[i].x - hv.x), (x[i].y - hv.y), (x[i].z - hv.z),
-                                  (x[i].w - hv.w));
-          }
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(k_xf0 + 8 * ks);
-        if (tt == 0) ATT_TRACE(3, j);
-      }
       {  // V [32 keys x 128 dims] (chunked [c][key][32]) -> V^T hi / lo [128 dims x 32 keys], swizzled rows
         mbar_wait(v_full0 + 8 * s, ph);
         mbar_wait(vt_empty0 + 8 * s, ph ^ 1);  // P.V_{j-2} has retired
