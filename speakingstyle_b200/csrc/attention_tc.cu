@@ -9,7 +9,7 @@
 // Roles (384 threads = three warps per scheduler, 168 registers each):
 //   warp 0      TMA: Q once, then V_j / K_j tiles into four-deep rings (rows outside [0,S) zero-filled)
 //   warp 1      one elected thread issues  S_j = Q.K_j^T  (12 MMAs, N = 64, A = Q hi/lo in TMEM) and
-//               O_j = P_j.V_j  (24 MMAs, N = 32, A = P_j hi/lo in TMEM); S_{j+1} goes before O_j
+//               O_j = P_j.V_j  (24 MMAs, N = 32, A = P_j hi/lo in TMEM); S runs two tiles ahead of P.V
 //   warps 2-9   softmax: thread = query row, warps w and w+4 share the rows.  First they split this CTA's
 //               Q rows into TMEM.  Per tile both read the whole S_j row (same running max, base-2 domain);
 //               each exponentiates its own 32 keys (MUFU.EX2), tcgen05.st's them as TF32 hi/lo into the
@@ -222,9 +222,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       };
       mbar_wait(q_tm, 0);
       tc_fence_after();
+      // S runs TWO tiles ahead of P.V: S_{j+2} only needs the softmax warps to have READ S_j (its buffer), which
+      // happens ~1 k cycles before they hand over P_j - issued after P.V_j instead, it sat on the critical loop
+      // P_j -> P.V_j -> S_{j+2} -> softmax_{j+2} -> P_{j+2}
       issue_s(0);
+      if (NT > 1) issue_s(1);
       for (int j = 0; j < NT; ++j) {
-        if (j + 1 < NT) issue_s(j + 1);
+        if (j + 2 < NT) issue_s(j + 2);
         const int s = j % NS, pb = j & 1;
         mbar_wait(vt_full0 + 8 * s, (j / NS) & 1);
         mbar_wait(p_full0 + 8 * pb, (j >> 1) & 1);
