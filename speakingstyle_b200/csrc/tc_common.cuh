@@ -397,6 +397,10 @@ __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&
   const float* res = static_cast<const float*>(p.residual);
   float* y = static_cast<float*>(p.y);
   int t = t_tile0 + lg * 32 + rsub, bb = b;  // first row of this lane
+  // offsets are carried along incrementally (64-bit multiplies per row showed up in the profile of this loop)
+  const int64_t row4 = 4 * p.y_row_stride;
+  int64_t off_rel = p.y_offset + (int64_t)t * p.y_row_stride + n;  // inside the utterance's output window
+  int64_t base = (int64_t)bb * p.y_batch_stride;
   // two half-loops of four rows (register budget: the caller holds a whole output row); the residual loads of a
   // half are all in flight before the first is used
 #pragma unroll 1
@@ -407,14 +411,19 @@ __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       if (straddle)
-        while (t >= p.S_out) { t -= p.S_out; ++bb; }
-      off[u] = p.y_offset + (int64_t)t * p.y_row_stride + n;
-      ok[u] = bb < p.B && t < p.S_out && off[u] >= 0 && off[u] < p.y_batch_elems;
-      off[u] += (int64_t)bb * p.y_batch_stride;
+        while (t >= p.S_out) {
+          t -= p.S_out;
+          ++bb;
+          off_rel -= (int64_t)p.S_out * p.y_row_stride;
+          base += p.y_batch_stride;
+        }
+      ok[u] = bb < p.B && t < p.S_out && off_rel >= 0 && off_rel < p.y_batch_elems;
+      off[u] = base + off_rel;
       keep[u] = t < (straddle ? (p.lens && ok[u] ? __ldg(p.lens + bb) : 0x7fffffff) : len);
       r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (res && ok[u]) r[u] = __ldg(reinterpret_cast<const float4*>(res + off[u]));
       t += 4;
+      off_rel += row4;
     }
     if (WITH_ACCUM && p.accum) {  // running mean (HiFi-GAN MRF): accum = scale*v (first branch) or accum += scale*v
       const bool rd = !p.accum_init;
