@@ -37,11 +37,15 @@ template <int BN, int STAGES>
 struct Cfg {
   static constexpr int b_bytes = BN * ROW_BYTES;
   static constexpr int stage_bytes = A_BYTES + 2 * b_bytes;  // x (fp32), W_hi, W_lo
-  static constexpr int a_col0 = 3 * BN;                      // after main0, main1, corr
+  // BN = 96 is the short-reduction form: with a single accumulator restart group per tile, the one correction
+  // accumulator of the BN = 128 layout stalls the tensor pipe between tiles until the epilogue has drained it
+  // (~3.6 k cycles against a 7 k-cycle tile at K = 256); 4 x 96 + 128 columns fit a second one.
+  static constexpr int corr_bufs = BN == 96 ? 2 : 1;
+  static constexpr int a_col0 = (2 + corr_bufs) * BN;        // after main0, main1, corr (x corr_bufs)
   static constexpr int used_cols = a_col0 + A_SLOTS * A_SLOT_COLS;
   static constexpr int tmem_cols = used_cols <= 32 ? 32 : used_cols <= 64 ? 64 : used_cols <= 128 ? 128 : used_cols <= 256 ? 256 : 512;
   static_assert(used_cols <= 512, "TMEM budget");
-  static constexpr int n_bars = 2 * STAGES + 2 * A_SLOTS + 4 + 2;
+  static constexpr int n_bars = 2 * STAGES + 2 * A_SLOTS + 4 + 4;
   static constexpr int smem_bytes = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16 + 1024;
   static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
 };
@@ -120,7 +124,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const uint32_t bars = smem0 + STAGES * C::stage_bytes + STG_BYTES;
   const uint32_t full0 = bars, empty0 = full0 + 8 * STAGES, tafull0 = empty0 + 8 * STAGES,
                  taempty0 = tafull0 + 8 * A_SLOTS, tfull0 = taempty0 + 8 * A_SLOTS, tempty0 = tfull0 + 16,
-                 cfull = tempty0 + 16, cempty = cfull + 8, tslot = cempty + 8;
+                 cfull0 = tempty0 + 16, cempty0 = cfull0 + 16, tslot = cempty0 + 16;
   volatile uint32_t* tslot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + STG_BYTES + C::n_bars * 8);
 
@@ -145,8 +149,10 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       mbar_init(tfull0 + 8 * a, 1);
       mbar_init(tempty0 + 8 * a, 4);
     }
-    mbar_init(cfull, 1);
-    mbar_init(cempty, 4);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(cfull0 + 8 * a, 1);
+      mbar_init(cempty0 + 8 * a, 4);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tslot, (uint32_t)C::tmem_cols);
@@ -189,9 +195,11 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       int local = 0, gcount = 0;
       [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-        mbar_wait(cempty, (local & 1) ^ 1);  // the epilogue has drained the correction accumulator
+        const int cs = C::corr_bufs == 2 ? (local & 1) : 0;
+        const uint32_t cph = C::corr_bufs == 2 ? ((local >> 1) & 1) : (local & 1);
+        mbar_wait(cempty0 + 8 * cs, cph ^ 1);  // the epilogue has drained this correction accumulator
         CONV_TRACE(8, gi);
-        const uint32_t c_tmem = tmem_base + 2 * BN;
+        const uint32_t c_tmem = tmem_base + (2 + cs) * BN;
         for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
           const int as = gcount & 1;
           mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);
@@ -219,7 +227,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           }
           umma_commit(tfull0 + 8 * as);
         }
-        umma_commit(cfull);
+        umma_commit(cfull0 + 8 * cs);
       }
     }
   } else if (warp < 6) {
@@ -264,19 +272,21 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           // Last group: its MMAs and the correction terms finish together.  Take the (single-buffered) correction
           // accumulator first and hand it back at once - the next tile's MMAs wait for it, and with a short
           // reduction (k = 1 layers: 8 chunks) anything slower would stall the tensor pipe between tiles.
-          mbar_wait(cfull, local & 1);
+          const int cs = C::corr_bufs == 2 ? (local & 1) : 0;
+          const uint32_t cph = C::corr_bufs == 2 ? ((local >> 1) & 1) : (local & 1);
+          mbar_wait(cfull0 + 8 * cs, cph);
           tc_fence_after();
           if (threadIdx.x == 64) CONV_TRACE(10, local * KT + KT - 1);
 #pragma unroll
           for (int c0 = 0; c0 < BN; c0 += 32) {
             float v[32];
-            tmem_ld32(lane_base + 2 * BN + c0, v);
+            tmem_ld32(lane_base + (2 + cs) * BN + c0, v);
 #pragma unroll
             for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(cempty);
+          if (lane == 0) mbar_arrive(cempty0 + 8 * cs);
           if (threadIdx.x == 64) CONV_TRACE(11, local * KT + KT - 1);
         }
         const int as = gcount & 1;
@@ -438,7 +448,12 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   SS_REQUIRE(p->in_act == SS_ACT_NONE || p->in_act == SS_ACT_LRELU, SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_ts: in_act must be none or lrelu");
 
-  const int bn = p->Cout > 64 ? 128 : p->Cout > 32 ? 64 : 32;
+  const int group = p->k_group > 0 ? p->k_group : 8;
+  const int chunks = p->k * ((p->Cin + KCHUNK - 1) / KCHUNK);
+  // one restart group per tile (k = 1 layers with K <= 256): the 96-column form, whose correction accumulator is
+  // double-buffered, unless that would waste more than a quarter of the last column tile
+  const bool short_k = chunks <= group && p->Cout > 64 && ((p->Cout + 95) / 96) * 96 * 4 <= p->Cout * 5;
+  const int bn = short_k ? 96 : p->Cout > 64 ? 128 : p->Cout > 32 ? 64 : 32;
   // Flat tiling (see TcArgs::flat): stride-1 same-length layer, batch-contiguous input, lean epilogue, and a
   // sequence length that would otherwise leave a partly empty last tile in every utterance.
   const bool flat = p->B > 1 && p->S_in == p->S_out && p->S_out % BM != 0 &&
@@ -470,9 +485,9 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   a.flat = flat ? 1 : 0; a.S_in = p->S_in;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int group = p->k_group > 0 ? p->k_group : 8;
   switch (bn) {
     case 128: return launch<128, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
+    case 96: return launch<96, 5>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
     case 64: return launch<64, 6>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
     default: return launch<32, 8>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
   }
