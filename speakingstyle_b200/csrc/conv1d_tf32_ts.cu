@@ -450,9 +450,11 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
 
   const int group = p->k_group > 0 ? p->k_group : 8;
   const int chunks = p->k * ((p->Cin + KCHUNK - 1) / KCHUNK);
-  // one restart group per tile (k = 1 layers with K <= 256): the 96-column form, whose correction accumulator is
-  // double-buffered, unless that would waste more than a quarter of the last column tile
-  const bool short_k = chunks <= group && p->Cout > 64 && ((p->Cout + 95) / 96) * 96 * 4 <= p->Cout * 5;
+  // short reductions (under 16 chunks: the k = 1 layers with K <= 256, the 80-channel input layers): the 96-column
+  // form, whose correction accumulator is double-buffered, unless that would waste more than a quarter of the
+  // last column tile.  Per output column its steady state costs the same as the 128-column form (it is bound by
+  // the split, 650 cycles per chunk), and it has no stall between tiles.
+  const bool short_k = chunks < 16 && p->Cout > 64 && ((p->Cout + 95) / 96) * 96 * 4 <= p->Cout * 5;
   const int bn = short_k ? 96 : p->Cout > 64 ? 128 : p->Cout > 32 ? 64 : 32;
   // Flat tiling (see TcArgs::flat): stride-1 same-length layer, batch-contiguous input, lean epilogue, and a
   // sequence length that would otherwise leave a partly empty last tile in every utterance.
