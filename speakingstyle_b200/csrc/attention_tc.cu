@@ -67,21 +67,20 @@ __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
 
-// n_vec is a multiple of 8 * XF_THREADS.  All loads of a batch come first: with the in-place stores in between,
-// every load would otherwise be serialised behind the previous store (aliasing) on a warp with no ILP to spare.
-__device__ __forceinline__ void split_tile(float4* hi, float4* lo, int n_vec, int tt) {
-#pragma unroll 1
-  for (int base = tt; base < n_vec; base += 8 * XF_THREADS) {
-    float4 x[8];
+// All loads of a batch come first: with the in-place stores in between, every load would otherwise be serialised
+// behind the previous store (aliasing) on a warp with no ILP to spare.
+template <int N_VEC>
+__device__ __forceinline__ void split_tile(float4* hi, float4* lo, int tt) {
+  constexpr int PER = N_VEC / XF_THREADS;  // vectors per thread
+  static_assert(N_VEC % XF_THREADS == 0 && PER >= 1 && PER <= 8, "split_tile batch");
+  float4 x[PER];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x[i] = hi[base + i * XF_THREADS];
+  for (int i = 0; i < PER; ++i) x[i] = hi[tt + i * XF_THREADS];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float4 h = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
-      hi[base + i * XF_THREADS] = h;
-      lo[base + i * XF_THREADS] =
-          make_float4((x[i].x - h.x), (x[i].y - h.y), (x[i].z - h.z), (x[i].w - h.w));
-    }
+  for (int i = 0; i < PER; ++i) {
+    const float4 h = make_float4(tf32_rn(x[i].x), tf32_rn(x[i].y), tf32_rn(x[i].z), tf32_rn(x[i].w));
+    hi[tt + i * XF_THREADS] = h;
+    lo[tt + i * XF_THREADS] = make_float4((x[i].x - h.x), (x[i].y - h.y), (x[i].z - h.z), (x[i].w - h.w));
   }
 }
 
@@ -380,8 +379,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     for (int j = 0; j < NT; ++j) {
       mbar_wait(k_full0 + 8 * s, ph);
       if (tt == 0) ATT_TRACE(2, j);
-      split_tile(reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES),
-                 reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES), KV_BYTES / 16, tt);
+      split_tile<KV_BYTES / 16>(reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES),
+                                reinterpret_cast<float4*>(smem_al + OFF_K + s * 2 * KV_BYTES + KV_BYTES), tt);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(k_xf0 + 8 * s);
