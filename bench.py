@@ -400,25 +400,38 @@ def main():
                                  f"{w / (ms * 1e-3) / 1e12:8.1f} TFLOP/s  {tag}\n")
             sys.stderr.write(f"step {dev_ms / args.steps:.3f} ms, convs {conv_ms / args.steps:.3f} ms\n")
         ach = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
-        roof = {"kernel": "conv1d_tf32_ts2 / _ts kernels (3xTF32 tcgen05) + conv1d_tc_kernel (bf16 tcgen05): all conv/linear launches"
-                if args.precision == "bf16" else
-                "conv1d_tf32_ts2_kernel (CTA pair) / conv1d_tf32_ts_kernel: 3xTF32 tcgen05 implicit-GEMM conv/linear, A operand in TMEM, fp32-accurate",
-                "bound": "tensor", "achieved": ach,
-                "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tflops_sustained"], "traffic": None,
-                "launches": calls, "avg_launch_ms": conv_ms / max(calls, 1), "share_of_step": conv_ms / dev_ms,
+        roof_all = {"kernel": "all conv / linear launches of the step (3xTF32 tcgen05 kernels"
+                              + (" + bf16 tcgen05 kernel)" if args.precision == "bf16" else ")"),
+                    "bound": "tensor", "achieved": ach, "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
+                    "frac": ach / pk["tflops_sustained"], "launches": calls, "avg_launch_ms": conv_ms / max(calls, 1),
+                    "share_of_step": conv_ms / dev_ms}
+        # the dominant kernel = the launch shape with the largest share of the step (per-launch figures, as the
+        # contract asks: algorithmic FLOPs of one launch / its average CUDA-event duration inside the timed region)
+        tag, (c, ms, w) = next(iter(timer.by_tag().items()))
+        d_ach = w / (ms * 1e-3) / 1e12
+        roof = {"kernel": ("conv1d_tf32_ts2_kernel (CTA-pair 3xTF32 tcgen05 implicit-GEMM conv, A operand in TMEM, "
+                           "fp32-accurate)" if tag.startswith("tf32x3") else "conv1d_tc_kernel (bf16 tcgen05 implicit-GEMM conv)"),
+                "shape": tag, "bound": "tensor", "achieved": d_ach, "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
+                "frac": d_ach / pk["tflops_sustained"], "traffic": None, "launches": c, "avg_launch_ms": ms / max(c, 1),
+                "flops_per_launch": w / max(c, 1), "share_of_step": ms / dev_ms,
                 "peak_source": pk["source"] + " bf16 dense (sustained)",
-                "note": "achieved = algorithmic FLOPs of ALL conv/linear launches / their CUDA-event time; frac divides "
-                        "by the measured bf16 peak as the contract asks.  A 3xTF32 kernel issues 3 TF32 MMAs per "
-                        "algorithmic MAC and the TF32 pipe retires 2048 MAC/clk/SM (half of bf16), so its own ceiling "
+                "note": "frac divides by the measured bf16 peak as the contract asks.  A 3xTF32 kernel issues 3 TF32 MMAs "
+                        "per algorithmic MAC and the TF32 pipe retires 2048 MAC/clk/SM (half of bf16), so its own ceiling "
                         "at the SM clock sampled during the run is 148*2048*2*f/3; ncu (profiles/r1e_ncu_hot_kernels.txt) "
-                        "shows the tensor pipe active 86 % of elapsed cycles on the FFN conv"}
-        if args.precision == "fp32" and clocks.get("sm_mhz"):
+                        "shows the tensor pipe active 86 % of elapsed cycles on this kernel and shape"}
+        if tag.startswith("tf32x3") and clocks.get("sm_mhz"):
             ceil = 148 * 2048 * 2 * clocks["sm_mhz"] * 1e6 / 3.0 / 1e12
             roof["tf32x3_ceiling_at_sampled_clock"] = ceil
-            roof["frac_of_3xtf32_ceiling"] = ach / ceil
-        try:
+            roof["frac_of_3xtf32_ceiling"] = d_ach / ceil
+            roof_all["frac_of_3xtf32_ceiling"] = ach / ceil
+        try:  # DRAM bytes of one launch of the same shape from the committed ncu --set full capture
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-            roof["traffic_example"] = {k: v for k, v in tj.items() if k.startswith("conv1d_tf32")}
+            shape_key = " ".join(t for t in tag.split() if t.split("=")[0] in ("B", "S", "Cin", "Cout", "k"))
+            for k_, v_ in tj.items():
+                if k_.startswith("conv1d_tf32_ts2") and k_.endswith(shape_key):
+                    roof["traffic"] = v_["bytes"]
+                    roof["algorithmic_bytes"] = v_["algorithmic_bytes"]
+                    roof["traffic_source"] = v_["source"]
         except Exception:
             pass
         line = {
@@ -435,6 +448,7 @@ def main():
                     "ms_per_step": e2e_ms_max / args.steps, "audio_seconds_per_s": e2e_value * HOP / SR},
             "gpu_launches": launches,
             "roofline": roof,
+            "roofline_all_convs": roof_all,
         }
         try:
             line["roofline_length_regulator"] = lr_roofline(dev, pk)
