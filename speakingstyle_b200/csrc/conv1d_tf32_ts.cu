@@ -46,7 +46,10 @@ struct Cfg {
   static constexpr int tmem_cols = used_cols <= 32 ? 32 : used_cols <= 64 ? 64 : used_cols <= 128 ? 128 : used_cols <= 256 ? 256 : 512;
   static_assert(used_cols <= 512, "TMEM budget");
   static constexpr int n_bars = 2 * STAGES + 2 * A_SLOTS + 4 + 4;
-  static constexpr int smem_bytes = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16 + 1024;
+  // the 96-column form stages a whole output row per epilogue thread (drain_tile_lean_wide)
+  static constexpr int stg_pitch = BN == 96 ? BN + 4 : STG_PITCH;
+  static constexpr int stg_bytes = 4 * 32 * stg_pitch * 4;
+  static constexpr int smem_bytes = STAGES * stage_bytes + stg_bytes + n_bars * 8 + 16 + 1024;
   static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
 };
 
@@ -121,12 +124,12 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   auto off_bh = [](int s) { return s * C::stage_bytes + A_BYTES; };
   auto off_bl = [](int s) { return s * C::stage_bytes + A_BYTES + C::b_bytes; };
   float* stg_all = reinterpret_cast<float*>(smem_al + STAGES * C::stage_bytes);
-  const uint32_t bars = smem0 + STAGES * C::stage_bytes + STG_BYTES;
+  const uint32_t bars = smem0 + STAGES * C::stage_bytes + C::stg_bytes;
   const uint32_t full0 = bars, empty0 = full0 + 8 * STAGES, tafull0 = empty0 + 8 * STAGES,
                  taempty0 = tafull0 + 8 * A_SLOTS, tfull0 = taempty0 + 8 * A_SLOTS, tempty0 = tfull0 + 16,
                  cfull0 = tempty0 + 16, cempty0 = cfull0 + 16, tslot = cempty0 + 16;
   volatile uint32_t* tslot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + STG_BYTES + C::n_bars * 8);
+      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + C::stg_bytes + C::n_bars * 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
@@ -233,7 +236,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   } else if (warp < 6) {
     // ================= epilogue (warps 2..5) =================
     const int lg = warp & 3;
-    float* stg = stg_all + lg * 32 * STG_PITCH;
+    float* stg = stg_all + lg * 32 * C::stg_pitch;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
     int local = 0, gcount = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
@@ -303,6 +306,12 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty0 + 8 * as);
         if (threadIdx.x == 64) CONV_TRACE(7, local * KT + min(it0 + group, KT) - 1);  // stamped at the group's last chunk
+      }
+      if constexpr (BN == 96) {
+        if (lean) {
+          drain_tile_lean_wide<BN / 32>(p, acc, stg, lg, lane, b_t, t_tile0, straddle, nt * BN, len);
+          continue;
+        }
       }
 #pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
@@ -489,7 +498,7 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (bn) {
     case 128: return launch<128, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
-    case 96: return launch<96, 5>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
+    case 96: return launch<96, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
     case 64: return launch<64, 6>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
     default: return launch<32, 8>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);
   }

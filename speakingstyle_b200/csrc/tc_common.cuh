@@ -468,6 +468,83 @@ __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&
   }
 }
 
+// Whole-row form of the lean drain for tiles whose row fits a per-warp staging tile (BN = 96): the thread's
+// BN-float row goes to shared memory in one go - the accumulator registers are dead afterwards - and the row
+// bookkeeping (utterance, frame, mask, offset) is done once per row quad for all column blocks instead of once per
+// block; two warp syncs per tile instead of two per block.  With cold operands this epilogue, not the main loop,
+// paces the short-reduction layers.
+template <int NB>  // column blocks of 32
+__device__ __forceinline__ void drain_tile_lean_wide(const TcArgs& p, const float (&acc)[NB * 32], float* stg, int lg,
+                                                     int lane, int b, int t_tile0, bool straddle, int n0, int len) {
+  constexpr int PW = NB * 32 + 4;  // pitch in floats: +4 keeps the float4 writes and reads conflict-free
+  const int col = (lane & 7) * 4;
+  const int rsub = lane >> 3;
+  float* my = stg + lane * PW;
+  __syncwarp();  // the previous tile has been fully read back
+#pragma unroll
+  for (int q = 0; q < NB * 8; ++q)
+    *reinterpret_cast<float4*>(my + q * 4) = make_float4(acc[q * 4], acc[q * 4 + 1], acc[q * 4 + 2], acc[q * 4 + 3]);
+  __syncwarp();
+  float4 bias4[NB];
+  bool colok[NB];
+#pragma unroll
+  for (int k = 0; k < NB; ++k) {
+    const int n = n0 + k * 32 + col;
+    colok[k] = n < p.Cout;
+    bias4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.bias && colok[k]) bias4[k] = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+  }
+  const float neg = p.act == SS_ACT_NONE ? 1.f : p.act == SS_ACT_RELU ? 0.f : p.slope;  // x > 0 ? x : x * neg
+  const float* src = stg + rsub * PW + col;
+  const float* res = static_cast<const float*>(p.residual);
+  float* y = static_cast<float*>(p.y);
+  int t = t_tile0 + lg * 32 + rsub, bb = b;  // first row of this lane
+  const int64_t row4 = 4 * p.y_row_stride;
+  int64_t off_rel = p.y_offset + (int64_t)t * p.y_row_stride + n0 + col;
+  int64_t base = (int64_t)bb * p.y_batch_stride;
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    int64_t off[4];
+    bool ok[4], keep[4];
+    float4 r[4][NB];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (straddle)
+        while (t >= p.S_out) {
+          t -= p.S_out;
+          ++bb;
+          off_rel -= (int64_t)p.S_out * p.y_row_stride;
+          base += p.y_batch_stride;
+        }
+      ok[u] = bb < p.B && t < p.S_out && off_rel >= 0 && off_rel < p.y_batch_elems;
+      off[u] = base + off_rel;
+      keep[u] = t < (straddle ? (p.lens && ok[u] ? __ldg(p.lens + bb) : 0x7fffffff) : len);
+#pragma unroll
+      for (int k = 0; k < NB; ++k) {
+        r[u][k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (res && ok[u] && colok[k]) r[u][k] = __ldg(reinterpret_cast<const float4*>(res + off[u] + k * 32));
+      }
+      t += 4;
+      off_rel += row4;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int k = 0; k < NB; ++k) {
+        float4 f = *reinterpret_cast<const float4*>(src + (half * 4 + u) * 4 * PW + k * 32);
+        f.x += bias4[k].x; f.y += bias4[k].y; f.z += bias4[k].z; f.w += bias4[k].w;
+        f.x = f.x > 0.f ? f.x : f.x * neg;
+        f.y = f.y > 0.f ? f.y : f.y * neg;
+        f.z = f.z > 0.f ? f.z : f.z * neg;
+        f.w = f.w > 0.f ? f.w : f.w * neg;
+        f.x += r[u][k].x; f.y += r[u][k].y; f.z += r[u][k].z; f.w += r[u][k].w;
+        if (!keep[u]) f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok[u] && colok[k]) *reinterpret_cast<float4*>(y + off[u] + k * 32) = f;
+      }
+    }
+  }
+}
+
 // G epilogue warps share one TMEM lane group; warp `sub` of the group takes every G-th 32-column block.
 template <int BN, int G = 1>
 __device__ __forceinline__ void drain_tile(const TcArgs& p, uint32_t taddr, float* stg, int lg, int lane, int b, int mt,
