@@ -8,7 +8,7 @@ build.build(force=True)
 import numpy as np, torch
 from speakingstyle_b200 import ops
 var = sys.argv[1] if len(sys.argv) > 1 else "ts"
-B, S, Cin, Cout, k = 64, 696, 256, 1024, 9
+B, S, Cin, Cout, k = int(os.environ.get("TRACE_B", "64")), int(os.environ.get("TRACE_S", "696")), 256, 1024, 9
 if len(sys.argv) > 2:
     Cin, Cout, k = (int(v) for v in sys.argv[2:5])
 x = torch.randn(B, S, Cin, device="cuda:0")

@@ -42,28 +42,36 @@ def _chk(t, dtype, name):
 class KernelTimer:
     """Optional per-call CUDA-event timing of one kernel family, used by bench.py to measure the
     dominant kernel's average launch duration inside the timed region (events are recorded on the
-    stream the kernel is launched on).  Costs two event records per call while installed."""
+    stream the kernel is launched on).  Costs two event records per call while installed.
+    ``ctx`` is whatever the caller sets before a group of launches (bench.py: the index of the batch being
+    processed); it is stored with every record so the caller can attribute launches afterwards."""
 
     def __init__(self):
-        self.records = []  # (start_event, end_event, work)
+        self.records = []  # (start_event, end_event, work, tag, ctx, meta)
+        self.ctx = None
 
-    def run(self, work, fn, tag=None):
+    def run(self, work, fn, tag=None, meta=None):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         status = fn()
         b.record()
-        self.records.append((a, b, work, tag))
+        self.records.append((a, b, work, tag, self.ctx, meta))
         return status
 
     def summary(self):
         """(calls, total_ms, total_work) - call after a synchronize."""
-        ms = sum(a.elapsed_time(b) for a, b, _, _ in self.records)
-        return len(self.records), ms, sum(w for _, _, w, _ in self.records)
+        ms = sum(r[0].elapsed_time(r[1]) for r in self.records)
+        return len(self.records), ms, sum(r[2] for r in self.records)
+
+    def rows(self):
+        """[(ms, work, tag, ctx, meta)] per launch - call after a synchronize.
+        meta = (kind, B, S_in, Cin, Cout, k, dilation) of the convolution."""
+        return [(a.elapsed_time(b), w, tag, ctx, meta) for a, b, w, tag, ctx, meta in self.records]
 
     def by_tag(self):
         """{tag: (calls, ms, work)} sorted by time, for the per-shape breakdown bench.py can print."""
         agg = {}
-        for a, b, w, tag in self.records:
+        for a, b, w, tag, _, _ in self.records:
             c, ms, ww = agg.get(tag, (0, 0.0, 0.0))
             agg[tag] = (c + 1, ms + a.elapsed_time(b), ww + w)
         return dict(sorted(agg.items(), key=lambda kv: -kv[1][1]))
@@ -76,9 +84,13 @@ def _tag(kind, p):
     return f"{kind} B={p.B} S={p.S_in} Cin={p.Cin} Cout={p.Cout} k={p.k} dil={p.dilation}"
 
 
+def _meta(kind, p):
+    return (kind, int(p.B), int(p.S_in), int(p.Cin), int(p.Cout), int(p.k), int(p.dilation))
+
+
 def _run_conv(p, flops):
     fn = lambda: _lib.lib().ss_conv1d_f32(C.byref(p), _stream())  # noqa: E731
-    check(conv_timer.run(flops, fn, _tag("f32", p)) if conv_timer is not None else fn())
+    check(conv_timer.run(flops, fn, _tag("f32", p), _meta("f32", p)) if conv_timer is not None else fn())
 
 
 def launch_count():
@@ -191,7 +203,7 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
     entry = {"ts": _lib.lib().ss_conv1d_tf32x3_ts, "ts2": _lib.lib().ss_conv1d_tf32x3_ts2,
              "ss": _lib.lib().ss_conv1d_tf32x3}[v]
     fn = lambda: entry(C.byref(p), _stream())  # noqa: E731
-    check(conv_timer.run(flops, fn, _tag("tf32x3", p)) if conv_timer is not None else fn())
+    check(conv_timer.run(flops, fn, _tag("tf32x3", p), _meta("tf32x3", p)) if conv_timer is not None else fn())
 
 
 def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.0, in_act=ACT_NONE, in_slope=0.0,
@@ -283,7 +295,7 @@ def pack_conv_tc(weight):
 
 def _tc_call(p, flops):
     fn = lambda: _lib.lib().ss_conv1d_tc(C.byref(p), _stream())  # noqa: E731
-    check(conv_timer.run(flops, fn, _tag("tc", p)) if conv_timer is not None else fn())
+    check(conv_timer.run(flops, fn, _tag("tc", p), _meta("tc", p)) if conv_timer is not None else fn())
 
 
 def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, residual=None, lens=None,

@@ -267,3 +267,53 @@ def make_teacher_forced_batch(batch=3, seed=7, n_mel=80):
     b = {"speakers": torch.zeros(batch, dtype=torch.int64), "texts": texts, "src_lens": src_lens, "max_src_len": L,
          "mels": mels, "mel_lens": mel_lens, "max_mel_len": Tr}
     return b, {"p_targets": p_targets, "e_targets": e_targets, "d_targets": d_targets}
+
+
+# ---------------------------------------------------------------------------------------------
+# synthetic corpora for the sharded sweeps (BASELINE configs[3] and [4])
+# ---------------------------------------------------------------------------------------------
+CORPORA = {
+    # name: (dataset, utterances, src_len_range or None (reference encoder only), ref_len_range, max_batch,
+    #        bucket_width, vocoder)
+    "cfg4": ("BC2013", 10000, None, (100, 1000), 64, 64, False),
+    "cfg5": ("BC2013", 2048, (40, 110), (200, 1000), 32, 16, True),
+}
+
+
+class Corpus:
+    """Lengths of every utterance (cheap, drawn at once) and lazily drawn payloads: utterance ``i`` has its own
+    generator seeded with (seed, i), so any process can materialise any subset - a rank only ever builds the
+    utterances of its own shards - and gets the same tensors as any other process."""
+
+    def __init__(self, name, seed=1, n=None):
+        ds, n_all, sl, rl, max_batch, width, voc = CORPORA[name]
+        self.name, self.dataset, self.vocoder, self.text = name, ds, voc, sl is not None
+        self.max_batch, self.bucket_width, self.seed = max_batch, width, int(seed)
+        self.n = n_all if n is None else min(int(n), n_all)
+        r = _Rng(seed)
+        self.src_lens = (r.randint(sl[0], sl[1] + 1, (n_all,)) if sl is not None else torch.ones(n_all, dtype=torch.int64))
+        self.ref_lens = r.randint(rl[0], rl[1] + 1, (n_all,))
+        self.speakers = r.randint(0, C.N_SPEAKERS[ds], (n_all,))
+        self.src_lens, self.ref_lens, self.speakers = self.src_lens[: self.n], self.ref_lens[: self.n], self.speakers[: self.n]
+
+    def plan(self, n_ranks):
+        from . import shard as SH
+
+        return SH.plan_shards(self.src_lens.tolist() if self.text else None, self.ref_lens.tolist(),
+                              max_batch=self.max_batch, bucket_width=self.bucket_width, n_ranks=n_ranks,
+                              vocoder=self.vocoder, text=self.text)
+
+    def utterance(self, i, n_mel=80):
+        """(text [src_len] i64, mel [ref_len, 80] f32) of utterance i."""
+        r = _Rng(self.seed * 1000003 + 7919 * (int(i) + 1))
+        text = r.randint(1, C.N_SRC_VOCAB, (int(self.src_lens[i]),)) if self.text else torch.ones(1, dtype=torch.int64)
+        return text, r.normal((int(self.ref_lens[i]), n_mel))
+
+    def shard_batch(self, shard):
+        """One shard collated in the reference's batch layout (dataset.py:198-217)."""
+        from . import shard as SH
+
+        texts, mels = {}, {}
+        for i in shard.utterances:
+            texts[i], mels[i] = self.utterance(i)
+        return SH.make_shard_batch(shard, self.speakers, texts, mels)
