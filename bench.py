@@ -301,15 +301,15 @@ class Runner:
                     t.to("cpu")
                     d2h += t.numel() * 4
             return None, d2h, None
-        if e2e and self.gen is not None:
-            # public API (tools.synthesize_batch): H2D inside forward(), the ragged PCM epilogue writes the trimmed
-            # int16 waves straight into pinned host memory (it synchronises the stream before returning them)
-            o, waves = self.ss.synthesize_batch(self.model, self.gen, b)
-            d2h = 2 * sum(len(x) for x in waves)
+        if self.gen is not None:
+            # public API (tools.synthesize_batch), the reference's synthesize.py:128-150 + vocoder_infer: waves trimmed to
+            # mel_len * hop.  e2e: H2D inside forward(), the ragged PCM epilogue writes the int16 waves straight into
+            # pinned host memory (it synchronises the stream before returning them).  Device-resident: same call, the
+            # trimmed int16 waves stay in HBM.
+            o, waves = self.ss.synthesize_batch(self.model, self.gen, b, device_out=not e2e)
+            d2h = 2 * sum(len(x) for x in waves) if e2e else 0
         else:
             o = call(self.model, b)  # with host inputs the H2D of the pinned tensors happens inside forward()
-            if self.gen is not None:
-                self.gen(o[1], channels_last=True, pcm=True)
             d2h = 0
         if e2e:
             o[1].to("cpu")

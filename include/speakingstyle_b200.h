@@ -137,6 +137,7 @@ typedef struct {
   int32_t y_dtype, residual_dtype; /* SS_F32 / SS_BF16 */
   float accum_scale;
   int32_t accum_init;
+  const int32_t* rows;     /* [B] or NULL - ragged schedule, see ss_conv1d_tf32_params */
 } ss_conv1d_tc_params;
 SS_API int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream);
 
@@ -174,6 +175,12 @@ typedef struct {
   int32_t k_group;         /* 32-channel chunks per accumulator restart (0 = default 8): tcgen05 accumulates with
                               truncation, so partial sums are re-added in registers every k_group*4 MMAs.  8 keeps
                               rms / max error below the FP32-pipe kernel's (scripts/tf32_group_error.py) */
+  const int32_t* rows;     /* [B] or NULL.  Ragged schedule: only output rows t < rows[b] of utterance b are wanted
+                              (clamped to [0, S_out]); whole 128-row tiles past that are neither computed nor
+                              written - their output memory keeps whatever it held.  For callers that know which
+                              frames can still reach a result: the decoder layers whose padded frames the next
+                              LayerNorm zeroes without reading them, and the vocoder when its wave is trimmed to
+                              mel_len*hop (rows[b] = (mel_len[b] + halo)*up covers the receptive field).  B <= 1024. */
 } ss_conv1d_tf32_params;
 SS_API int ss_conv1d_tf32x3(const ss_conv1d_tf32_params* p, void* stream);
 /* Same contract; the split activations are kept in tensor memory (tcgen05.st) and the MMAs take their A
@@ -182,6 +189,15 @@ SS_API int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream);
 /* Same contract; two CTAs of a cluster compute one 256 x 128 tile with tcgen05 cta_group::2, each holding half
  * of the weight tile, which halves the shared-memory traffic per SM (layers with Cout <= 64 go to the kernel above). */
 SS_API int ss_conv1d_tf32x3_ts2(const ss_conv1d_tf32_params* p, void* stream);
+
+/* Same contract, for the NARROW layers (HiFi-GAN's 64- and 32-channel MRF stages, hifigan/models.py:96-103): the
+ * activations of a 128-row tile are fetched once as a panel of 128 + (k-1)*dilation rows (tap j of row r is panel row
+ * r + j*dilation) and the weights of all taps stay in shared memory when they fit, instead of one TMA fetch of both per
+ * (tap, chunk) step - those layers were bound by L2 -> shared-memory traffic, not by the tensor pipe.  Bit-identical to
+ * ss_conv1d_tf32x3_ts.  Takes: S_in == S_out, k >= 2, Cin in {32, 64}, Cout <= 64, 128 + (k-1)*dilation <= 256
+ * (ss_conv1d_tf32x3_panel_supported() returns 1); anything else is SS_ERR_UNSUPPORTED. */
+SS_API int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stream);
+SS_API int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p);
 
 /* out = bf16(act(x)) element-wise over n elements (n % 8 == 0): the entry into the bf16 path. */
 SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream);

@@ -196,24 +196,30 @@ def length_regulate(x, durations, max_len=None):
 
 
 def variance_adaptor(sd, mc, x, src_mask, gammas, betas, p_control=1.0, e_control=1.0, d_control=1.0,
-                     d_targets=None, max_len=None, p_targets=None, e_targets=None):
-    """model/modules.py:105-165, phoneme-level pitch/energy (all shipped configs)."""
+                     d_targets=None, max_len=None, p_targets=None, e_targets=None, mel_mask=None,
+                     levels=("phoneme_level", "phoneme_level")):
+    """model/modules.py:105-165.  ``levels`` = (pitch, energy) feature level of the preprocess config: phoneme_level
+    predictors run on the token sequence before the LengthRegulator (modules.py:121-131), frame_level ones on the
+    expanded sequence after it, masked with mel_mask (modules.py:146-155)."""
     va = "variance_adaptor"
     log_d = variance_predictor(sd, va + ".duration_predictor", x, src_mask, gammas, betas)
-    pitch = variance_predictor(sd, va + ".pitch_predictor", x, src_mask)
-    if p_targets is not None:  # modules.py:85-86: embedding from the target, prediction returned unscaled
-        pitch_idx = bucketize(p_targets.to(pitch.dtype), sd[va + ".pitch_bins"])
-    else:
-        pitch = pitch * p_control
-        pitch_idx = bucketize(pitch, sd[va + ".pitch_bins"])
-    x = x + sd[va + ".pitch_embedding.weight"][pitch_idx]
-    energy = variance_predictor(sd, va + ".energy_predictor", x, src_mask)
-    if e_targets is not None:
-        energy_idx = bucketize(e_targets.to(energy.dtype), sd[va + ".energy_bins"])
-    else:
-        energy = energy * e_control
-        energy_idx = bucketize(energy, sd[va + ".energy_bins"])
-    x = x + sd[va + ".energy_embedding.weight"][energy_idx]
+    res = {}
+
+    def embed(which, x, mask, target, control):
+        pred = variance_predictor(sd, f"{va}.{which}_predictor", x, mask)
+        if target is not None:  # modules.py:85-86: embedding from the target, prediction returned unscaled
+            idx = bucketize(target.to(pred.dtype), sd[f"{va}.{which}_bins"])
+        else:
+            pred = pred * control
+            idx = bucketize(pred, sd[f"{va}.{which}_bins"])
+        res[which], res[which + "_idx"] = pred, idx
+        return x + sd[f"{va}.{which}_embedding.weight"][idx]
+
+    if levels[0] == "phoneme_level":
+        x = embed("pitch", x, src_mask, p_targets, p_control)
+    if levels[1] == "phoneme_level":
+        x = embed("energy", x, src_mask, e_targets, e_control)
+    x_pre_lr = x
     if d_targets is not None:
         d_rounded = d_targets
         out, mel_len, mel2phone = length_regulate(x, d_targets, max_len)
@@ -221,10 +227,15 @@ def variance_adaptor(sd, mc, x, src_mask, gammas, betas, p_control=1.0, e_contro
         d_rounded = round_durations(log_d, d_control)
         out, _, mel2phone = length_regulate(x, d_rounded, None)
         mel_len = d_rounded.sum(-1).int()  # int32, from the float sum (modules.py:143)
+        mel_mask = mask_from_lengths(mel_len)
+    if levels[0] == "frame_level":
+        out = embed("pitch", out, mel_mask, p_targets, p_control)
+    if levels[1] == "frame_level":
+        out = embed("energy", out, mel_mask, e_targets, e_control)
     return {
-        "x": out, "pitch": pitch, "energy": energy, "log_d": log_d, "d_rounded": d_rounded,
-        "mel_len": mel_len, "mel2phone": mel2phone, "pitch_idx": pitch_idx, "energy_idx": energy_idx,
-        "x_pre_lr": x,
+        "x": out, "pitch": res["pitch"], "energy": res["energy"], "log_d": log_d, "d_rounded": d_rounded,
+        "mel_len": mel_len, "mel2phone": mel2phone, "pitch_idx": res["pitch_idx"], "energy_idx": res["energy_idx"],
+        "x_pre_lr": x_pre_lr, "mel_mask": mel_mask,
     }
 
 
@@ -254,7 +265,8 @@ def postnet(sd, mel):
 
 
 def fastspeech2_forward(sd, mc, batch, p_control=1.0, e_control=1.0, d_control=1.0, dtype=torch.float32,
-                        intermediates=False, p_targets=None, e_targets=None, d_targets=None):
+                        intermediates=False, p_targets=None, e_targets=None, d_targets=None,
+                        levels=("phoneme_level", "phoneme_level")):
     """model/fastspeech2.py:44-120 (inference: no targets).  Returns the 10-tuple, or a dict."""
     sd = _SD(sd, dtype)
     texts, src_lens = batch["texts"], batch["src_lens"]
@@ -267,9 +279,9 @@ def fastspeech2_forward(sd, mc, batch, p_control=1.0, e_control=1.0, d_control=1
         enc = enc + sd["speaker_emb.weight"][batch["speakers"]][:, None, :]  # pads included (fastspeech2.py:74-77)
     va = variance_adaptor(sd, mc, enc, src_mask, gammas, betas, p_control, e_control, d_control, d_targets=d_targets,
                           max_len=batch["max_mel_len"] if d_targets is not None else None, p_targets=p_targets,
-                          e_targets=e_targets)
+                          e_targets=e_targets, mel_mask=ref_mask if d_targets is not None else None, levels=levels)
     # teacher forcing keeps the reference mel's mask (fastspeech2.py:62-66); otherwise it is rebuilt from mel_len
-    mel_mask = ref_mask if d_targets is not None else mask_from_lengths(va["mel_len"])
+    mel_mask = va["mel_mask"]
     dec, mel_mask = decoder(sd, mc, va["x"], mel_mask, gammas, betas)
     mel = F.linear(dec, sd["mel_linear.weight"], sd["mel_linear.bias"])
     post = postnet(sd, mel) + mel

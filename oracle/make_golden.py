@@ -3,7 +3,7 @@
 Run in the build container (the reference cannot travel to the GPU box):
 
     python -m oracle.make_golden            # tiny cases + cfg1
-    python -m oracle.make_golden --large    # also cfg2 / cfg3 (minutes of CPU)
+    python -m oracle.make_golden --large    # also cfg2 / cfg3 / cfg4s / cfg5s (minutes of CPU)
 
 Weights and batches come from speakingstyle_b200/synth.py (seeded, reproducible anywhere) and are
 loaded into the reference modules with strict=True.  Small cases store every output and a few
@@ -179,6 +179,96 @@ def save_mel_frontend():
     print(f"mel_frontend -> {path} ({os.path.getsize(path) / 1024:.0f} KiB) mel {tuple(mel.shape)}")
 
 
+def _reference_model(ds):
+    d = tempfile.mkdtemp()
+    C.write_preprocessed_dir(d, ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    return rh.build_fastspeech2(pc, mc, S.fastspeech2_state_dict(mc, ds, seed=FS2_SEED))
+
+
+CFG5S_UTTS, CFG5S_MEL_STRIDE, CFG5S_WAVE_STRIDE, CFG5S_WAVE_SHARDS = 256, 64, 256, (0, 5)
+CFG4S_MELS, CFG4S_RANKS, CFG4S_FULL_EVERY = 1024, 8, 4
+
+
+def save_cfg5_shards():
+    """BASELINE configs[4] at reduced size: the first 256 utterances of the cfg5 corpus (L 40-110, Tr 200-1000) planned
+    by shard.plan_shards (batch <= 32, bucket width 16) - 9 shards - each run through the real reference as one batch.
+    Per shard: integers in full, pitch / energy predictions in full (bucket ids), a strided sample of postnet_mel and
+    per-utterance checksums; for two shards also the HiFi-GAN wave (strided sample + per-utterance |.| sums over the
+    samples vocoder_infer keeps, utils/model.py:109-113)."""
+    corpus = S.Corpus("cfg5", seed=1, n=CFG5S_UTTS)
+    plan = corpus.plan(1)
+    model = _reference_model(corpus.dataset)
+    h = C.hifigan_config()
+    gen = rh.build_generator(h, S.hifigan_state_dict(h, seed=VOC_SEED))
+    rec = {"n_shards": np.int64(len(plan.shards)), "mel_stride": np.int64(CFG5S_MEL_STRIDE),
+           "wave_stride": np.int64(CFG5S_WAVE_STRIDE), "wave_shards": np.array(CFG5S_WAVE_SHARDS)}
+    t0 = time.time()
+    for sh in plan.shards:
+        b = corpus.shard_batch(sh)
+        with torch.no_grad(), rh.quiet():
+            out = model(b["speakers"], b["texts"], b["src_lens"], b["max_src_len"], b["mels"], b["mel_lens"], b["max_mel_len"])
+        i = sh.index
+        rec[f"utts_{i}"] = np.array(sh.utterances)
+        rec[f"d_rounded_{i}"] = out[5].numpy()
+        rec[f"mel_lens_{i}"] = out[9].numpy()
+        rec[f"pitch_{i}"] = out[2].numpy()
+        rec[f"energy_{i}"] = out[3].numpy()
+        rec[f"postnet_s_{i}"] = out[1][:, ::CFG5S_MEL_STRIDE].numpy()
+        rec[f"postnet_abs_{i}"] = out[1].double().abs().sum(dim=(1, 2)).numpy()
+        if i in CFG5S_WAVE_SHARDS:
+            with torch.no_grad():
+                wave = gen(out[1].transpose(1, 2))[:, 0]
+            n = (out[9] * 256).tolist()
+            rec[f"wave_s_{i}"] = wave[:, ::CFG5S_WAVE_STRIDE].numpy()
+            rec[f"wave_abs_{i}"] = np.array([wave[r, : n[r]].double().abs().sum().item() for r in range(len(n))])
+        print(f"cfg5s shard {i}: B={len(sh.utterances)} L={sh.max_src_len} Tr={sh.max_ref_len} T={out[1].shape[1]} "
+              f"frames={int(out[9].sum())} ({time.time() - t0:.0f}s)", flush=True)
+    path = os.path.join(GOLDEN, "cfg5s.npz")
+    np.savez_compressed(path, **rec)
+    print(f"cfg5s -> {path} ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
+def save_cfg4_sweep():
+    """BASELINE configs[3] at reduced size: ReferenceEncoder alone over the first 1024 mels of the cfg4 corpus
+    (Tr 100-1000), length-bucketed (width 64, batch <= 64) and planned for 8 ranks; every shard through the real
+    reference's ReferenceEncoder.  gammas / betas in full for every 4th utterance, their sums for all."""
+    corpus = S.Corpus("cfg4", seed=1, n=CFG4S_MELS)
+    plan = corpus.plan(CFG4S_RANKS)
+    enc = _reference_model(corpus.dataset).reference_encoder
+    ns = rh.load()
+    ga = torch.zeros(CFG4S_MELS, 256)
+    be = torch.zeros(CFG4S_MELS, 256)
+    t0 = time.time()
+    for sh in plan.shards:
+        b = corpus.shard_batch(sh)
+        with torch.no_grad(), rh.quiet():
+            g_, b_ = enc(b["mels"], b["max_mel_len"], ns.get_mask_from_lengths(b["mel_lens"], b["max_mel_len"]))
+        ids = torch.tensor(sh.utterances)
+        ga[ids], be[ids] = g_[:, 0], b_[:, 0]
+    path = os.path.join(GOLDEN, "cfg4s.npz")
+    np.savez_compressed(path, gammas=ga[::CFG4S_FULL_EVERY].numpy(), betas=be[::CFG4S_FULL_EVERY].numpy(),
+                        gamma_sum=ga.double().sum(1).numpy(), beta_sum=be.double().sum(1).numpy(),
+                        gamma_abs=ga.double().abs().sum(1).numpy(), beta_abs=be.double().abs().sum(1).numpy(),
+                        every=np.int64(CFG4S_FULL_EVERY), n_shards=np.int64(len(plan.shards)))
+    print(f"cfg4s: {len(plan.shards)} shards, {time.time() - t0:.0f}s -> {path} ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
+def save_long_reference():
+    """ReferenceEncoder with reference mels LONGER than the 1001-row position table (model/modules.py:373-380: the
+    table is rebuilt on the fly for max_len > max_seq_len) - Tr = 1100 and 1003 in one batch."""
+    enc = _reference_model("BC2013").reference_encoder
+    ns = rh.load()
+    g = torch.Generator().manual_seed(606)
+    lens = torch.tensor([1100, 1003, 640])
+    mels = torch.randn(3, 1100, 80, generator=g) * (torch.arange(1100)[None, :, None] < lens[:, None, None])
+    with torch.no_grad(), rh.quiet():
+        ga, be = enc(mels, 1100, ns.get_mask_from_lengths(lens, 1100))
+    path = os.path.join(GOLDEN, "refenc_long.npz")
+    np.savez_compressed(path, mel_lens=lens.numpy(), gammas=ga.numpy(), betas=be.numpy())
+    print(f"refenc_long -> {path} ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--large", action="store_true")
@@ -193,12 +283,16 @@ def main():
         "tiny_ms": lambda: save_full("tiny_ms", "tiny_ms"),
         "tiny_ctl": lambda: save_full("tiny", "tiny_ctl", controls=(1.2, 0.8, 1.3)),
         "tiny_tf": save_teacher_forced,
+        "tiny_fl": lambda: save_full("tiny_fl", "tiny_fl"),
         "mel_frontend": save_mel_frontend,
         "cfg1": lambda: save_compact("cfg1"),
     }
+    jobs["refenc_long"] = save_long_reference
     if args.large:
         jobs["cfg2"] = lambda: save_compact("cfg2")
         jobs["cfg3"] = lambda: save_compact("cfg3")
+        jobs["cfg4s"] = save_cfg4_sweep
+        jobs["cfg5s"] = save_cfg5_shards
     for k, fn in jobs.items():
         if args.only is None or k in args.only.split(","):
             fn()

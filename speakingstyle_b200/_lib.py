@@ -32,6 +32,7 @@ class Conv1dTcParams(C.Structure):
         ("y_offset", i64), ("y_batch_elems", i64), ("B", i32), ("S_in", i32), ("S_out", i32), ("Cin", i32),
         ("Cout", i32), ("k", i32), ("dilation", i32), ("pad", i32), ("act", i32), ("slope", f32), ("act2", i32),
         ("slope2", f32), ("y_dtype", i32), ("residual_dtype", i32), ("accum_scale", f32), ("accum_init", i32),
+        ("rows", vp),
     ]
 
 
@@ -42,7 +43,7 @@ class Conv1dTf32Params(C.Structure):
         ("y_row_stride", i64), ("y_offset", i64), ("y_batch_elems", i64), ("B", i32), ("S_in", i32), ("S_out", i32),
         ("Cin", i32), ("Cout", i32), ("k", i32), ("dilation", i32), ("pad", i32), ("in_act", i32), ("in_slope", f32),
         ("act", i32), ("slope", f32), ("act2", i32), ("slope2", f32), ("accum_scale", f32), ("accum_init", i32),
-        ("k_group", i32),
+        ("k_group", i32), ("rows", vp),
     ]
 
 
@@ -73,6 +74,8 @@ _SIGNATURES = {
     "ss_conv1d_tf32x3": (C.c_int, [C.POINTER(Conv1dTf32Params), vp]),
     "ss_conv1d_tf32x3_ts": (C.c_int, [C.POINTER(Conv1dTf32Params), vp]),
     "ss_conv1d_tf32x3_ts2": (C.c_int, [C.POINTER(Conv1dTf32Params), vp]),
+    "ss_conv1d_tf32x3_panel": (C.c_int, [C.POINTER(Conv1dTf32Params), vp]),
+    "ss_conv1d_tf32x3_panel_supported": (C.c_int, [C.POINTER(Conv1dTf32Params)]),
     "ss_cast_bf16": (C.c_int, [vp, vp, i64, C.c_int, f32, vp]),
     "ss_layernorm": (C.c_int, [C.POINTER(LayerNormParams), vp]),
     "ss_attention_f32": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),

@@ -68,7 +68,13 @@ STATS = {
     },
 }
 STATS["BC2013"] = STATS["LJSpeech"]
-N_SPEAKERS = {"LJSpeech": 1, "BC2013": 1, "LibriTTS": 904}  # len(speakers.json)
+# config/LJSpeech_paper (frame-level pitch / energy, log pitch quantisation, no normalisation) ships no stats.json;
+# these are plausible UN-normalised ranges (Hz / frame energy) with LJSpeech's mean and std - synthetic, stated as such
+STATS["LJSpeech_paper"] = {
+    "pitch": [71.0, 795.8, 207.6309860026605, 46.77559025098988],
+    "energy": [0.018, 315.0, 37.32621679053821, 26.044180782835863],
+}
+N_SPEAKERS = {"LJSpeech": 1, "BC2013": 1, "LibriTTS": 904, "LJSpeech_paper": 1}  # len(speakers.json)
 
 HIFIGAN_CONFIG = {
     "resblock": "1",
@@ -96,12 +102,18 @@ def model_config(dataset="BC2013"):
     if dataset == "LibriTTS":
         cfg["multi_speaker"] = True
         cfg["vocoder"]["speaker"] = "universal"
+    elif dataset == "LJSpeech_paper":  # config/LJSpeech_paper/model.yaml:5,19 (+ the BC2013 reference_encoder block)
+        cfg["transformer"]["decoder_layer"] = 4
+        cfg["variance_embedding"]["pitch_quantization"] = "log"
     elif dataset not in ("BC2013", "LJSpeech"):
         raise ValueError(f"unknown dataset {dataset!r}")
     return cfg
 
 
 def preprocess_config(dataset="BC2013", preprocessed_path=None):
+    # config/LJSpeech_paper/preprocess.yaml:26-30: frame-level features, not normalised
+    level = "frame_level" if dataset == "LJSpeech_paper" else "phoneme_level"
+    norm = dataset != "LJSpeech_paper"
     return {
         "dataset": dataset,
         "path": {"preprocessed_path": preprocessed_path or ""},
@@ -109,8 +121,8 @@ def preprocess_config(dataset="BC2013", preprocessed_path=None):
             "audio": {"sampling_rate": 22050, "max_wav_value": 32768.0},
             "stft": {"filter_length": 1024, "hop_length": 256, "win_length": 1024},
             "mel": {"n_mel_channels": 80, "mel_fmin": 0, "mel_fmax": 8000},
-            "pitch": {"feature": "phoneme_level", "normalization": True},
-            "energy": {"feature": "phoneme_level", "normalization": True},
+            "pitch": {"feature": level, "normalization": norm},
+            "energy": {"feature": level, "normalization": norm},
         },
     }
 

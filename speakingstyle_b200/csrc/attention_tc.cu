@@ -457,10 +457,11 @@ extern "C" int ss_attention_tc(const float* qkv, const int32_t* lens, float* ctx
   rc = make_map_3d(&tmV, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, qkv, (uint64_t)3 * D, (uint64_t)S, (uint64_t)B,
                    (uint64_t)3 * D * 4, (uint64_t)S * 3 * D * 4, DK, BKV, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (rc != SS_OK) return rc;
-  static unsigned long long attr_mask = 0;  // per device
-  if (first_use_on_device(attr_mask)) {
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
     cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_attention_tc: smem opt-in");
+    attr_done_on_device(attr_mask);
   }
   dim3 grid((S + BQ - 1) / BQ, H, B);
   attention_tc_kernel<<<grid, NTHREADS, SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(tmQ, tmKV, tmV, lens, ctx, S,

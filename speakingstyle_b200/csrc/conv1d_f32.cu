@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(NT, 2) conv1d_f32_kernel(const ss_conv1d_f32_p
       v.z = ss::apply_act(v.z, p.act, p.slope);
       v.w = ss::apply_act(v.w, p.act, p.slope);
       if (p.residual) {
-        const float4 r = __ldg(reinterpret_cast<const float4*>(p.residual + ybase + off));
+        const float4 r = *reinterpret_cast<const float4*>(p.residual + ybase + off);  // plain load: may alias y
         v.x += r.x; v.y += r.y; v.z += r.z; v.w += r.w;
       }
       if (t >= len) v = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -44,8 +44,9 @@ struct Cfg {
   static constexpr int G = EpiG<BN>::value;
   static constexpr int stg_bytes = 4 * G * STG_WARP_BYTES;
   static constexpr int nthreads = 64 + 128 * G;
-  static constexpr int smem_bytes = STAGES * stage_bytes + stg_bytes + bar_bytes + 1024;  // +1024: alignment slack
-  static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
+  static constexpr int ragged_off = STAGES * stage_bytes + stg_bytes + bar_bytes;  // tile prefix table (ragged schedule)
+  static constexpr int smem_bytes = ragged_off + 1024;  // +1024: alignment slack; + (B + 1) * 4 at launch when rows are given
+  static_assert(smem_bytes + (RAGGED_MAX_B + 1) * 4 <= 227 * 1024, "shared memory budget");
 };
 
 template <int BN, int STAGES>
@@ -69,7 +70,9 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int KT = p.k * nchunk;
   constexpr int MT = C::MT;
   const int m_units = (p.m_tiles + MT - 1) / MT;
-  const int num_tiles = p.B * m_units * p.n_tiles;  // scheduling units
+  int* const rag = reinterpret_cast<int*>(smem_al + C::ragged_off);
+  const bool ragged = p.rows != nullptr;
+  if (ragged) ragged_build(p.rows, p.B, p.S_out, MT * BM, rag);
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -91,6 +94,18 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tslot_ptr;
+  const int num_tiles = ragged ? rag[p.B] * p.n_tiles : p.B * m_units * p.n_tiles;  // scheduling units
+  // linear unit index -> (column tile, unit of MT row tiles, utterance)
+  auto decode = [&](int tile, int& nt, int& um, int& b) {
+    nt = tile % p.n_tiles;
+    const int rest = tile / p.n_tiles;
+    if (ragged) {
+      ragged_decode(rag, p.B, rest, b, um);
+    } else {
+      um = rest % m_units;
+      b = rest / m_units;
+    }
+  };
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -98,10 +113,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int nt = tile % p.n_tiles;
-        const int rest = tile / p.n_tiles;
-        const int um = rest % m_units;
-        const int b = rest / m_units;
+        int nt, um, b;
+        decode(tile, nt, um, b);
         const int n0 = nt * BN;
         for (int sub = 0; sub < MT; ++sub) {
           const int mt = um * MT + sub;
@@ -133,7 +146,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t aphase = (local >> 1) & 1;
         mbar_wait(tempty0 + 8 * as, aphase ^ 1);  // epilogue has drained this accumulator buffer
         tc_fence_after();
-        const int um = (tile / p.n_tiles) % m_units;
+        int nt_, um, b_;
+        decode(tile, nt_, um, b_);
         for (int sub = 0; sub < MT; ++sub) {
           if (um * MT + sub >= p.m_tiles) break;
           const uint32_t d_tmem = tmem_base + as * C::acc_cols + sub * BN;
@@ -161,10 +175,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float* stg = stg_all + (warp - 2) * 32 * STG_PITCH;
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-      const int nt = tile % p.n_tiles;
-      const int rest = tile / p.n_tiles;
-      const int um = rest % m_units;
-      const int b = rest / m_units;
+      int nt, um, b;
+      decode(tile, nt, um, b);
       const int as = local & 1;
       const uint32_t aphase = (local >> 1) & 1;
       mbar_wait(tfull0 + 8 * as, aphase);
@@ -212,16 +224,18 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, TcArgs a, cudaStream_
   a.m_tiles = (a.S_out + BM - 1) / BM;
   const int64_t tiles = (int64_t)a.B * ((a.m_tiles + C::MT - 1) / C::MT) * a.n_tiles;  // scheduling units
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tc: too many tiles");
-  static unsigned long long attr_mask = 0;  // per device
-  if (first_use_on_device(attr_mask)) {
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
     cudaError_t e = cudaFuncSetAttribute(conv1d_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         C::smem_bytes);
+                                         C::smem_bytes + (RAGGED_MAX_B + 1) * 4);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tc: smem opt-in");
+    attr_done_on_device(attr_mask);
   }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tc: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  conv1d_tc_kernel<BN, STAGES><<<grid, C::nthreads, C::smem_bytes, st>>>(tmA, tmB, a);
+  const int smem = C::smem_bytes + (a.rows ? (a.B + 1) * 4 : 0);
+  conv1d_tc_kernel<BN, STAGES><<<grid, C::nthreads, smem, st>>>(tmA, tmB, a);
   SS_CHECK_LAUNCH("ss_conv1d_tc");
   return SS_OK;
 }
@@ -244,6 +258,8 @@ extern "C" int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream) {
   SS_REQUIRE((p->y_dtype == SS_F32 || p->y_dtype == SS_BF16) && (p->residual_dtype == SS_F32 || p->residual_dtype == SS_BF16),
              SS_ERR_INVALID, "ss_conv1d_tc: bad dtype code");
 
+  SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tc: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
   CUtensorMap tmA, tmB;
   int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in, (uint64_t)p->B, (uint64_t)p->x_row_stride * 2,
                        (uint64_t)p->x_batch_stride * 2, KCHUNK, BM);
@@ -262,6 +278,7 @@ extern "C" int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream) {
   a.m_tiles = a.n_tiles = 0;
   a.act = p->act; a.act2 = p->act2; a.y_dtype = p->y_dtype; a.residual_dtype = p->residual_dtype;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
+  a.rows = p->rows;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return launch<256, 4>(tmA, tmB, a, st);

@@ -306,11 +306,12 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
   a.m_tiles = (a.S_out + BM - 1) / BM;
   const int64_t tiles = (int64_t)a.B * a.m_tiles * a.n_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3: too many tiles");
-  static unsigned long long attr_mask = 0;  // per device
-  if (first_use_on_device(attr_mask)) {
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
     cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C::smem_bytes);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3: smem opt-in");
+    attr_done_on_device(attr_mask);
   }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3: no CUDA device");

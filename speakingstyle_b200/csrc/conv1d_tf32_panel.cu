@@ -1,0 +1,449 @@
+// 3xTF32 implicit-GEMM convolution for NARROW layers (Cin, Cout <= 64: HiFi-GAN's 64- and 32-channel MRF stages),
+// "panel" form.  Same mathematics, MMA order, accumulator handling and epilogue as conv1d_tf32_ts.cu - results are
+// bit-identical - but a different way of feeding the tensor core.
+//
+// Why: in conv1d_tf32_ts.cu every (tap, 32-channel chunk) step fetches a fresh 128-row activation tile AND its weight
+// tile by TMA, so a k = 11 layer pulls every activation row through L2 -> shared memory eleven times and the same
+// weights once per 128-row tile: 264 KB (32 channels) / 704 KB (64 channels) per tile for 16 / 32 KB of new input.
+// On the narrow layers that traffic, not the tensor pipe, sets the pace (scripts/conv_trace.py: TMA issue -> data
+// landed takes 3.4-6.8 k cycles with eight stages in flight, i.e. ~30 B/clk per SM, ~2/3 of what L2 can deliver to
+// 148 SMs; tensor pipe 13-28 % busy at 32 channels, profiles/r2a_ncu_hifigan_shapes.txt).
+//
+// Here
+//   * the activations of a tile arrive ONCE, as a panel of R = 128 + (k-1)*dilation rows per 32-channel chunk (one TMA
+//     box; rows outside the utterance are zero-filled by TMA as before).  Tap j of output row r is panel row
+//     r + j*dilation: the split warps just read a shifted row.  (A SWIZZLE_128B panel can be read at any row offset
+//     because the swizzle phase is a function of the absolute shared-memory address - scripts/desc_shift_probe.py.)
+//   * the weights of ALL taps stay resident in shared memory when they fit (32 channels: always; 64 channels: k = 3),
+//     loaded once per CTA; otherwise they stream through a ring as before.
+// Per 128-row tile that is 18-23 KB (32 ch) / 37-400 KB (64 ch) of TMA traffic instead of 264 / 704 KB.
+//
+// Warps: TMA, MMA, 4 epilogue, 8 split (two per TMEM lane group, half a row each).  TMEM: main accumulator x2 |
+// correction accumulator x2 | four A slots of (32 hi + 32 lo) columns.
+#include "tc_common.cuh"
+
+namespace {
+
+using namespace sstc;
+
+constexpr int KCHUNK = 32;
+constexpr int XF_WARPS = 8;
+constexpr int NTHREADS = 32 * (6 + XF_WARPS);
+constexpr int A_SLOTS = 4;
+constexpr int A_SLOT_COLS = 2 * KCHUNK;  // hi | lo
+constexpr int W_RING = 4;                // weight ring depth when the weights are streamed
+constexpr int MAX_PAN = 4;               // activation panel ring depth (upper bound)
+constexpr int N_BARS = 2 * MAX_PAN + 2 * W_RING + 1 + 2 * A_SLOTS + 8;
+constexpr int MAX_SMEM = 227 * 1024;
+
+struct PanelArgs {
+  int32_t R;            // panel rows = 128 + (k-1)*dilation
+  int32_t panel_bytes;  // per 32-channel chunk, multiple of 1024
+  int32_t n_pan;        // panels in the ring (each holds all chunks of one tile)
+  int32_t w_resident;   // all (tap, chunk) weight tiles stay in shared memory
+  int32_t nchunk;
+};
+
+__device__ __forceinline__ float tf32_rn(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
+
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(db), "r"(idesc), "r"(accum)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
+                         const __grid_constant__ CUtensorMap tmBl, const TcArgs p, const PanelArgs q, const int in_act,
+                         const float in_slope, const int group) {
+  constexpr int B_BYTES = BN * ROW_BYTES;  // one weight tile (hi or lo) of one (tap, chunk)
+  constexpr int WT = 2 * B_BYTES;          // hi + lo
+  constexpr int A_COL0 = 4 * BN;           // after main0, main1, corr0, corr1
+  static_assert(A_COL0 + A_SLOTS * A_SLOT_COLS <= 512, "TMEM budget");
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
+  const int nchunk = q.nchunk;
+  const int KT = p.k * nchunk;
+  const int pan_stage = nchunk * q.panel_bytes;                       // one tile's panels (all chunks)
+  const int w_off = q.n_pan * pan_stage;
+  const int w_bytes = (q.w_resident ? KT : W_RING) * WT;
+  const int stg_off = w_off + w_bytes;
+  const int bar_off = stg_off + STG_BYTES;
+  float* stg_all = reinterpret_cast<float*>(smem_al + stg_off);
+  const uint32_t bars = smem0 + bar_off;
+  const uint32_t pfull0 = bars, pempty0 = pfull0 + 8 * MAX_PAN, wfull0 = pempty0 + 8 * MAX_PAN, wempty0 = wfull0 + 8 * W_RING,
+                 wres = wempty0 + 8 * W_RING, tafull0 = wres + 8, taempty0 = tafull0 + 8 * A_SLOTS,
+                 tfull0 = taempty0 + 8 * A_SLOTS, tempty0 = tfull0 + 16, cfull0 = tempty0 + 16, cempty0 = cfull0 + 16,
+                 tslot = cempty0 + 16;
+  volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + bar_off + N_BARS * 8);
+  int* const rag = reinterpret_cast<int*>(smem_al + bar_off + N_BARS * 8 + 16);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool ragged = p.rows != nullptr;
+  if (ragged) ragged_build(p.rows, p.B, p.S_out, BM, rag);
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmBh);
+    prefetch_tmap(&tmBl);
+    for (int s = 0; s < MAX_PAN; ++s) {
+      mbar_init(pfull0 + 8 * s, 1);
+      mbar_init(pempty0 + 8 * s, XF_WARPS);  // every split warp has read its last row of the panel
+    }
+    for (int s = 0; s < W_RING; ++s) {
+      mbar_init(wfull0 + 8 * s, 1);
+      mbar_init(wempty0 + 8 * s, 1);
+    }
+    mbar_init(wres, 1);
+    for (int t = 0; t < A_SLOTS; ++t) {
+      mbar_init(tafull0 + 8 * t, XF_WARPS);
+      mbar_init(taempty0 + 8 * t, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull0 + 8 * a, 1);
+      mbar_init(tempty0 + 8 * a, 4);
+      mbar_init(cfull0 + 8 * a, 1);
+      mbar_init(cempty0 + 8 * a, 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tslot, 512u);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tslot_ptr;
+  const int num_tiles = ragged ? rag[p.B] : p.B * p.m_tiles;  // one column tile (Cout <= BN)
+  auto decode = [&](int tile, int& mt, int& b) {
+    if (ragged) {
+      ragged_decode(rag, p.B, tile, b, mt);
+    } else {
+      mt = tile % p.m_tiles;
+      b = tile / p.m_tiles;
+    }
+  };
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (elect_one()) {
+      if (q.w_resident) {  // every (tap, chunk) weight tile, once per CTA
+        mbar_expect_tx(wres, (uint32_t)(KT * WT));
+        for (int it = 0; it < KT; ++it) {
+          const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
+          tma_load_3d(smem0 + w_off + it * WT, &tmBh, wres, c0, 0, j);
+          tma_load_3d(smem0 + w_off + it * WT + B_BYTES, &tmBl, wres, c0, 0, j);
+        }
+      }
+      int ps = 0, ws = 0;
+      uint32_t pphase = 0, wphase = 0;
+      auto load_panel = [&](int tile) {
+        int mt, b;
+        decode(tile, mt, b);
+        mbar_wait(pempty0 + 8 * ps, pphase ^ 1);
+        mbar_expect_tx(pfull0 + 8 * ps, (uint32_t)(nchunk * q.R * ROW_BYTES));
+        for (int c = 0; c < nchunk; ++c)
+          tma_load_3d(smem0 + ps * pan_stage + c * q.panel_bytes, &tmA, pfull0 + 8 * ps, c * KCHUNK, mt * BM - p.pad, b);
+        if (++ps == q.n_pan) { ps = 0; pphase ^= 1; }
+      };
+      // the panel of tile i+1 is requested BEFORE the weights of tile i: the weight ring only moves as fast as the MMAs
+      // consume it, and a panel requested behind it would arrive late
+      if ((int)blockIdx.x < num_tiles) load_panel(blockIdx.x);
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        if (tile + (int)gridDim.x < num_tiles) load_panel(tile + gridDim.x);
+        if (!q.w_resident) {
+          for (int it = 0; it < KT; ++it) {
+            const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
+            mbar_wait(wempty0 + 8 * ws, wphase ^ 1);
+            mbar_expect_tx(wfull0 + 8 * ws, (uint32_t)WT);
+            tma_load_3d(smem0 + w_off + ws * WT, &tmBh, wfull0 + 8 * ws, c0, 0, j);
+            tma_load_3d(smem0 + w_off + ws * WT + B_BYTES, &tmBl, wfull0 + 8 * ws, c0, 0, j);
+            if (++ws == W_RING) { ws = 0; wphase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc(2u, BN);  // tf32 x tf32 -> f32
+      int slot = 0, ws = 0;
+      uint32_t sphase = 0, wphase = 0;
+      int local = 0, gcount = 0;
+      if (q.w_resident) mbar_wait(wres, 0);
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+        const int cs = local & 1;
+        mbar_wait(cempty0 + 8 * cs, ((local >> 1) & 1) ^ 1);  // the epilogue has drained this correction accumulator
+        const uint32_t c_tmem = tmem_base + (2 + cs) * BN;
+        for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
+          const int as = gcount & 1;
+          mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * BN;
+          const int it1 = min(it0 + group, KT);
+          for (int it = it0; it < it1; ++it) {
+            mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of this (tap, chunk) are in TMEM
+            if (!q.w_resident) mbar_wait(wfull0 + 8 * ws, wphase);
+            tc_fence_after();
+            const uint32_t a_hi = tmem_base + A_COL0 + slot * A_SLOT_COLS, a_lo = a_hi + KCHUNK;
+            const uint32_t b_hi = smem0 + w_off + (q.w_resident ? it : ws) * WT, b_lo = b_hi + B_BYTES;
+#pragma unroll
+            for (int kk = 0; kk < KCHUNK / 8; ++kk) {
+              umma_tf32_ts(c_tmem, a_lo + kk * 8, make_desc(b_hi + kk * 32), idesc, (it | kk) != 0);
+              umma_tf32_ts(c_tmem, a_hi + kk * 8, make_desc(b_lo + kk * 32), idesc, 1u);
+              umma_tf32_ts(d_tmem, a_hi + kk * 8, make_desc(b_hi + kk * 32), idesc, ((it - it0) | kk) != 0);
+            }
+            umma_commit(taempty0 + 8 * slot);
+            if (!q.w_resident) {
+              umma_commit(wempty0 + 8 * ws);
+              if (++ws == W_RING) { ws = 0; wphase ^= 1; }
+            }
+            if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
+          }
+          umma_commit(tfull0 + 8 * as);
+        }
+        umma_commit(cfull0 + 8 * cs);
+      }
+    }
+  } else if (warp < 6) {
+    // ================= epilogue (warps 2..5) =================
+    const int lg = warp & 3;
+    float* stg = stg_all + lg * 32 * STG_PITCH;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
+    int local = 0, gcount = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      int mt, b;
+      decode(tile, mt, b);
+      const int t_tile0 = mt * BM;
+      const int len = p.lens ? p.lens[b] : 0x7fffffff;
+      const bool lean = drain_is_lean<true>(p);  // warp-uniform
+      if (lean && p.residual) {  // pull this tile's residual rows into L2 while its MMAs run
+        const int t = t_tile0 + lg * 32 + lane;
+        const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride;
+        if (t < p.S_out && off >= 0 && off < p.y_batch_elems) {
+          const float* rp = static_cast<const float*>(p.residual) + (int64_t)b * p.y_batch_stride + off;
+          for (int c = 0; c < min(BN, p.Cout); c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + c));
+        }
+      }
+      float acc[BN];
+#pragma unroll
+      for (int i = 0; i < BN; ++i) acc[i] = 0.f;
+      for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
+        if (it0 + group >= KT) {  // last group: the correction terms finish with it - take them first
+          const int cs = local & 1;
+          mbar_wait(cfull0 + 8 * cs, (local >> 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(lane_base + (2 + cs) * BN + c0, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(cempty0 + 8 * cs);
+        }
+        const int as = gcount & 1;
+        mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          float v[32];
+          tmem_ld32(lane_base + as * BN + c0, v);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];  // round-to-nearest fp32 adds
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty0 + 8 * as);
+      }
+#pragma unroll
+      for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
+        if (lean)
+          drain_block_lean<true>(p, v, stg, lg, lane, b, t_tile0, false, c0, len);
+        else
+          drain_block(p, v, stg, lg, lane, b, mt, c0, len);
+      }
+    }
+  } else {
+    // ================= operand split (warps 6..13): thread = output row, half of the 32 channels each =========
+    const int lg = warp & 3;             // TMEM lane group this warp may write
+    const int xhalf = (warp - 6) >> 2;   // which half of the chunk's channels
+    const int r = lg * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16) + A_COL0;
+    int ps = 0, slot = 0;
+    uint32_t pphase = 0, sphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(pfull0 + 8 * ps, pphase);
+      const uint8_t* pan = smem_al + ps * pan_stage;
+      int prow = r, c = 0;  // panel row of this output row for the current tap (tap j reads row r + j*dilation)
+      for (int it = 0; it < KT; ++it) {
+        const uint8_t* row = pan + c * q.panel_bytes + prow * ROW_BYTES;
+        const int sw = prow & 7;  // SWIZZLE_128B: 16-byte unit u of a row sits at unit (u ^ (row & 7)); panels are 1024-aligned
+        if (++c == nchunk) { c = 0; prow += p.dilation; }
+        float hi[16], lo[16];
+#pragma unroll
+        for (int uu = 0; uu < 4; ++uu) {
+          const int u = xhalf * 4 + uu;
+          float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+          if (in_act == SS_ACT_LRELU) {
+            x.x = x.x > 0.f ? x.x : x.x * in_slope;
+            x.y = x.y > 0.f ? x.y : x.y * in_slope;
+            x.z = x.z > 0.f ? x.z : x.z * in_slope;
+            x.w = x.w > 0.f ? x.w : x.w * in_slope;
+          }
+          // lo is handed over unrounded: the MMA truncates an fp32 operand to TF32 itself (see conv1d_tf32_ts.cu)
+          hi[4 * uu + 0] = tf32_rn(x.x); lo[4 * uu + 0] = x.x - hi[4 * uu + 0];
+          hi[4 * uu + 1] = tf32_rn(x.y); lo[4 * uu + 1] = x.y - hi[4 * uu + 1];
+          hi[4 * uu + 2] = tf32_rn(x.z); lo[4 * uu + 2] = x.z - hi[4 * uu + 2];
+          hi[4 * uu + 3] = tf32_rn(x.w); lo[4 * uu + 3] = x.w - hi[4 * uu + 3];
+        }
+        if (it == KT - 1) {  // this warp has read its last row of the panel: hand it back to the TMA producer
+          __syncwarp();
+          if (lane == 0) mbar_arrive(pempty0 + 8 * ps);
+        }
+        mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
+        tc_fence_after();
+        tmem_st16(lane_base + slot * A_SLOT_COLS + xhalf * 16, hi);
+        tmem_st16(lane_base + slot * A_SLOT_COLS + KCHUNK + xhalf * 16, lo);
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tafull0 + 8 * slot);
+        if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
+      }
+      if (++ps == q.n_pan) { ps = 0; pphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512u);
+  }
+}
+
+// Shared-memory plan for one layer: returns false when not even two panels and a weight ring fit.
+template <int BN>
+bool plan_smem(int k, int dilation, int nchunk, int B_ragged, PanelArgs& q, int& smem_bytes) {
+  constexpr int WT = 2 * BN * ROW_BYTES;
+  q.nchunk = nchunk;
+  q.R = BM + (k - 1) * dilation;
+  q.panel_bytes = (q.R * ROW_BYTES + 1023) / 1024 * 1024;
+  const int fixed = STG_BYTES + N_BARS * 8 + 16 + (B_ragged ? (B_ragged + 1) * 4 : 0) + 1024;
+  const int KT = k * nchunk;
+  for (int resident = 1; resident >= 0; --resident)
+    for (int n_pan = 3; n_pan >= 2; --n_pan) {
+      const int total = n_pan * nchunk * q.panel_bytes + (resident ? KT : W_RING) * WT + fixed;
+      if (total <= MAX_SMEM) {
+        q.n_pan = n_pan;
+        q.w_resident = resident;
+        smem_bytes = total;
+        return true;
+      }
+    }
+  return false;
+}
+
+template <int BN>
+int launch(const ss_conv1d_tf32_params* p, const TcArgs& a0, int group, cudaStream_t st) {
+  TcArgs a = a0;
+  PanelArgs q;
+  int smem = 0;
+  const int nchunk = (p->Cin + KCHUNK - 1) / KCHUNK;
+  SS_REQUIRE(plan_smem<BN>(p->k, p->dilation, nchunk, p->rows ? p->B : 0, q, smem), SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_panel: k=%d dilation=%d does not fit shared memory", p->k, p->dilation);
+  CUtensorMap tmA, tmBh, tmBl;
+  int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
+                       (uint64_t)p->x_row_stride * 4, (uint64_t)p->x_batch_stride * 4, KCHUNK, (uint32_t)q.R);
+  if (rc != SS_OK) return rc;
+  rc = make_map_3d(&tmBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->w_hi, (uint64_t)p->Cin, (uint64_t)p->Cout, (uint64_t)p->k,
+                   (uint64_t)p->Cin * 4, (uint64_t)p->Cout * p->Cin * 4, KCHUNK, (uint32_t)BN);
+  if (rc != SS_OK) return rc;
+  rc = make_map_3d(&tmBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->w_lo, (uint64_t)p->Cin, (uint64_t)p->Cout, (uint64_t)p->k,
+                   (uint64_t)p->Cin * 4, (uint64_t)p->Cout * p->Cin * 4, KCHUNK, (uint32_t)BN);
+  if (rc != SS_OK) return rc;
+  a.n_tiles = 1;
+  a.m_tiles = (a.S_out + BM - 1) / BM;
+  const int64_t tiles = (int64_t)a.B * a.m_tiles;
+  SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_panel: too many tiles");
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
+    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_panel_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
+    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_panel: smem opt-in");
+    attr_done_on_device(attr_mask);
+  }
+  const int sms = sm_count();
+  SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3_panel: no CUDA device");
+  const int grid = (int)(tiles < sms ? tiles : sms);
+  conv1d_tf32_panel_kernel<BN><<<grid, NTHREADS, smem, st>>>(tmA, tmBh, tmBl, a, q, p->in_act, p->in_slope, group);
+  SS_CHECK_LAUNCH("ss_conv1d_tf32x3_panel");
+  return SS_OK;
+}
+
+}  // namespace
+
+// 1 if ss_conv1d_tf32x3_panel takes this layer: stride-1 same-length convolution with at least two taps, at most 64
+// input and output channels (whole 32-channel chunks in), a halo that fits one TMA box, plain fp32 output path.
+extern "C" int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p) {
+  if (!p) return 0;
+  return p->S_in == p->S_out && p->k >= 2 && p->Cin <= 64 && p->Cin % KCHUNK == 0 && p->Cout <= 64 && p->Cout % 4 == 0 &&
+         BM + (p->k - 1) * p->dilation <= 256 && p->pad <= (p->k - 1) * p->dilation && p->pad >= 0;
+}
+
+extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stream) {
+  SS_REQUIRE(p && p->x && p->w_hi && p->w_lo && (p->y || p->y_act || p->accum), SS_ERR_INVALID,
+             "ss_conv1d_tf32x3_panel: null pointer");
+  SS_REQUIRE(p->B > 0 && p->S_in > 0 && p->S_out > 0 && p->Cin > 0 && p->Cout > 0 && p->k > 0 && p->dilation > 0,
+             SS_ERR_INVALID, "ss_conv1d_tf32x3_panel: bad shape B=%d S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d", p->B,
+             p->S_in, p->S_out, p->Cin, p->Cout, p->k, p->dilation);
+  SS_REQUIRE(ss_conv1d_tf32x3_panel_supported(p), SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_panel: needs S_in == S_out, k >= 2, Cin in {32, 64}, Cout <= 64, 128 + (k-1)*dilation <= 256 "
+             "(got S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d pad=%d)", p->S_in, p->S_out, p->Cin, p->Cout, p->k,
+             p->dilation, p->pad);
+  SS_REQUIRE(p->x_row_stride % 4 == 0 && p->x_batch_stride % 4 == 0 && p->y_row_stride % 4 == 0 &&
+                 p->y_batch_stride % 4 == 0 && p->y_offset % 4 == 0 && p->y_batch_elems % 4 == 0,
+             SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_panel: strides/offsets must be multiples of 4 elements");
+  SS_REQUIRE(ss::aligned16(p->x) && ss::aligned16(p->w_hi) && ss::aligned16(p->w_lo) && ss::aligned16(p->y) &&
+                 ss::aligned16(p->y_act) && ss::aligned16(p->bias) && ss::aligned16(p->residual) && ss::aligned16(p->accum),
+             SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_panel: pointers must be 16-byte aligned");
+  SS_REQUIRE(p->in_act == SS_ACT_NONE || p->in_act == SS_ACT_LRELU, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_panel: in_act must be none or lrelu");
+  SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_panel: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
+  TcArgs a;
+  a.bias = p->bias; a.residual = p->residual; a.lens = p->lens; a.y = p->y;
+  a.y_act = static_cast<__nv_bfloat16*>(p->y_act); a.accum = p->accum;
+  a.y_batch_stride = p->y_batch_stride; a.y_row_stride = p->y_row_stride; a.y_offset = p->y_offset;
+  a.y_batch_elems = p->y_batch_elems;
+  a.B = p->B; a.S_out = p->S_out; a.Cin = p->Cin; a.Cout = p->Cout; a.k = p->k; a.dilation = p->dilation; a.pad = p->pad;
+  a.m_tiles = a.n_tiles = 0;
+  a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
+  a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
+  a.flat = 0; a.S_in = p->S_in; a.rows = p->rows;
+  const int group = p->k_group > 0 ? p->k_group : 8;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return p->Cout > 32 ? launch<64>(p, a, group, st) : launch<32>(p, a, group, st);
+}

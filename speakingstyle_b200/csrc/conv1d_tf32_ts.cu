@@ -40,7 +40,11 @@ struct Cfg {
   // BN = 96 is the short-reduction form: with a single accumulator restart group per tile, the one correction
   // accumulator of the BN = 128 layout stalls the tensor pipe between tiles until the epilogue has drained it
   // (~3.6 k cycles against a 7 k-cycle tile at K = 256); 4 x 96 + 128 columns fit a second one.
-  static constexpr int corr_bufs = BN == 96 ? 2 : 1;
+  // The narrow tiles (BN = 64 / 32, the HiFi-GAN 64- and 32-channel stages) have the room as well, and need it more:
+  // their tiles are short (3 to 22 chunks) and with one correction accumulator the next tile's MMAs could not start
+  // before the epilogue - still busy storing the previous tile - had read it (scripts/conv_trace.py ts 32 32 3:
+  // ~3.7 k cycles per tile against 1.1 k of main loop).
+  static constexpr int corr_bufs = BN <= 96 ? 2 : 1;
   static constexpr int a_col0 = (2 + corr_bufs) * BN;        // after main0, main1, corr (x corr_bufs)
   static constexpr int used_cols = a_col0 + A_SLOTS * A_SLOT_COLS;
   static constexpr int tmem_cols = used_cols <= 32 ? 32 : used_cols <= 64 ? 64 : used_cols <= 128 ? 128 : used_cols <= 256 ? 256 : 512;
@@ -49,8 +53,9 @@ struct Cfg {
   // the 96-column form stages a whole output row per epilogue thread (drain_tile_lean_wide)
   static constexpr int stg_pitch = BN == 96 ? BN + 4 : STG_PITCH;
   static constexpr int stg_bytes = 4 * 32 * stg_pitch * 4;
-  static constexpr int smem_bytes = STAGES * stage_bytes + stg_bytes + n_bars * 8 + 16 + 1024;
-  static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
+  static constexpr int ragged_off = STAGES * stage_bytes + stg_bytes + n_bars * 8 + 16;  // tile prefix table (ragged schedule)
+  static constexpr int smem_bytes = ragged_off + 1024;  // + (B + 1) * 4 at launch when rows are given
+  static_assert(smem_bytes + (RAGGED_MAX_B + 1) * 4 <= 227 * 1024, "shared memory budget");
 };
 
 // Debug build (-DSS_CONV_TRACE, scripts/conv_trace.py): CTA 0 stamps clock64() per K-chunk at the hand-overs.
@@ -134,7 +139,9 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
   const int KT = p.k * nchunk;
-  const int num_tiles = (p.flat ? 1 : p.B) * p.m_tiles * p.n_tiles;  // flat: m_tiles spans all utterances
+  int* const rag = reinterpret_cast<int*>(smem_al + C::ragged_off);
+  const bool ragged = p.rows != nullptr;
+  if (ragged) ragged_build(p.rows, p.B, p.S_out, BM, rag);
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -163,6 +170,19 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tslot_ptr;
+  // flat: m_tiles spans all utterances; ragged: the prefix table counts each utterance's own tiles
+  const int num_tiles = ragged ? rag[p.B] * p.n_tiles : (p.flat ? 1 : p.B) * p.m_tiles * p.n_tiles;
+  // linear tile index -> (column tile, row tile, utterance)
+  auto decode = [&](int tile, int& nt, int& mt, int& b) {
+    nt = tile % p.n_tiles;
+    const int rest = tile / p.n_tiles;
+    if (ragged) {
+      ragged_decode(rag, p.B, rest, b, mt);
+    } else {
+      mt = rest % p.m_tiles;
+      b = rest / p.m_tiles;
+    }
+  };
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -171,10 +191,8 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       uint32_t phase = 0;
       [[maybe_unused]] int gi = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int nt = tile % p.n_tiles;
-        const int rest = tile / p.n_tiles;
-        const int mt = rest % p.m_tiles;
-        const int b = rest / p.m_tiles;
+        int nt, mt, b;
+        decode(tile, nt, mt, b);
         const int t0 = mt * BM, n0 = nt * BN;
         for (int it = 0; it < KT; ++it) {
           const int j = it / nchunk;
@@ -240,10 +258,8 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
     int local = 0, gcount = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-      const int nt = tile % p.n_tiles;
-      const int rest = tile / p.n_tiles;
-      const int mt = rest % p.m_tiles;
-      const int b = rest / p.m_tiles;
+      int nt, mt, b;
+      decode(tile, nt, mt, b);
       int b_t = b, t_tile0 = mt * BM;
       bool straddle = false;
       if (p.flat) {  // un-flatten the tile's first row once; most tiles lie inside one utterance
@@ -252,7 +268,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         straddle = t_tile0 + BM > p.S_out;
       }
       const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
-      const bool lean = drain_is_lean<(BN <= 64)>(p);  // warp-uniform
+      const bool lean = drain_is_lean<(BN != 96)>(p);  // warp-uniform
       if (lean && p.residual) {
         // Pull this tile's residual rows into L2 now, while the MMAs run: the drain below keeps only four 16-byte
         // loads per lane in flight, which from HBM (~1 us) capped the whole kernel at ~1.2 TB/s of residual reads.
@@ -319,7 +335,7 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean<(BN <= 64)>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
+          drain_block_lean<(BN != 96)>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
         else
           drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
@@ -418,16 +434,19 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& t
   a.m_tiles = a.flat ? (int)(((int64_t)a.B * a.S_out + BM - 1) / BM) : (a.S_out + BM - 1) / BM;
   const int64_t tiles = (int64_t)(a.flat ? 1 : a.B) * a.m_tiles * a.n_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_ts: too many tiles");
-  static unsigned long long attr_mask = 0;  // per device
-  if (first_use_on_device(attr_mask)) {
-    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_ts_kernel<BN, STAGES>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, C::smem_bytes);
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
+    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_ts_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::smem_bytes + (RAGGED_MAX_B + 1) * 4);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_ts: smem opt-in");
+    attr_done_on_device(attr_mask);
   }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3_ts: no CUDA device");
+  // ragged schedule: `tiles` is the upper bound (every row wanted); the CTAs read the real count from the prefix table
   const int grid = (int)(tiles < sms ? tiles : sms);
-  conv1d_tf32_ts_kernel<BN, STAGES><<<grid, n_threads<BN>(), C::smem_bytes, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
+  const int smem = C::smem_bytes + (a.rows ? (a.B + 1) * 4 : 0);
+  conv1d_tf32_ts_kernel<BN, STAGES><<<grid, n_threads<BN>(), smem, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
   SS_CHECK_LAUNCH("ss_conv1d_tf32x3_ts");
   return SS_OK;
 }
@@ -467,7 +486,9 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   const int bn = short_k ? 96 : p->Cout > 64 ? 128 : p->Cout > 32 ? 64 : 32;
   // Flat tiling (see TcArgs::flat): stride-1 same-length layer, batch-contiguous input, lean epilogue, and a
   // sequence length that would otherwise leave a partly empty last tile in every utterance.
-  const bool flat = p->B > 1 && p->S_in == p->S_out && p->S_out % BM != 0 &&
+  SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_ts: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
+  const bool flat = p->rows == nullptr && p->B > 1 && p->S_in == p->S_out && p->S_out % BM != 0 &&
                     p->x_batch_stride == (int64_t)p->S_in * p->x_row_stride && (int64_t)p->B * p->S_in < (1ll << 30) &&
                     (p->accum == nullptr ? p->y != nullptr : p->Cout <= 64) && p->y_act == nullptr &&
                     p->act != SS_ACT_TANH;  // = the conditions of the lean epilogue, the only one that un-flattens rows
@@ -494,7 +515,7 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
   a.m_tiles = a.n_tiles = 0;
   a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
-  a.flat = flat ? 1 : 0; a.S_in = p->S_in;
+  a.flat = flat ? 1 : 0; a.S_in = p->S_in; a.rows = p->rows;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (bn) {
     case 128: return launch<128, 4>(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);

@@ -37,8 +37,9 @@ struct Cfg {
   static constexpr int tmem_cols = used_cols <= 32 ? 32 : used_cols <= 64 ? 64 : used_cols <= 128 ? 128 : used_cols <= 256 ? 256 : 512;
   static_assert(used_cols <= 512, "TMEM budget");
   static constexpr int n_bars = 2 * STAGES + 2 * A_SLOTS + 4 + 2;
-  static constexpr int smem_bytes = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16 + 1024;
-  static_assert(smem_bytes <= 227 * 1024, "shared memory budget");
+  static constexpr int ragged_off = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16;  // tile prefix table (ragged schedule)
+  static constexpr int smem_bytes = ragged_off + 1024;  // + (B + 1) * 4 at launch when rows are given
+  static_assert(smem_bytes + (RAGGED_MAX_B + 1) * 4 <= 227 * 1024, "shared memory budget");
 };
 
 // Debug build (-DSS_CONV2_TRACE, scripts/conv_trace.py): CTA 0 stamps clock64() per K-chunk at the hand-overs.
@@ -153,7 +154,9 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
   const int KT = p.k * nchunk;
   // p.m_tiles counts PAIR tiles (256 rows); this CTA's 128-row tile is 2 * pair_tile + rank
-  const int num_tiles = (p.flat ? 1 : p.B) * p.m_tiles * p.n_tiles;
+  int* const rag = reinterpret_cast<int*>(smem_al + C::ragged_off);
+  const bool ragged = p.rows != nullptr;
+  if (ragged) ragged_build(p.rows, p.B, p.S_out, 2 * BM, rag);  // both CTAs of the pair build the same table
   const uint32_t cta_rank = cluster_ctarank();
   const int pair0 = blockIdx.x >> 1, pair_step = gridDim.x >> 1;
 
@@ -182,6 +185,20 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   cluster_sync_all();  // barriers of both CTAs initialised, TMEM of both SMs allocated
   tc_fence_after();
   const uint32_t tmem_base = *tslot_ptr;
+  const int num_tiles = ragged ? rag[p.B] * p.n_tiles : (p.flat ? 1 : p.B) * p.m_tiles * p.n_tiles;
+  // linear pair-tile index -> (column tile, this CTA's 128-row tile, utterance)
+  auto decode = [&](int tile, int& nt, int& mt, int& b) {
+    nt = tile % p.n_tiles;
+    const int rest = tile / p.n_tiles;
+    int pm;
+    if (ragged) {
+      ragged_decode(rag, p.B, rest, b, pm);
+    } else {
+      pm = rest % p.m_tiles;
+      b = rest / p.m_tiles;
+    }
+    mt = pm * 2 + (int)cta_rank;
+  };
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -190,10 +207,8 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       uint32_t phase = 0;
       [[maybe_unused]] int gi = 0;
       for (int tile = pair0; tile < num_tiles; tile += pair_step) {
-        const int nt = tile % p.n_tiles;
-        const int rest = tile / p.n_tiles;
-        const int mt = (rest % p.m_tiles) * 2 + (int)cta_rank;
-        const int b = rest / p.m_tiles;
+        int nt, mt, b;
+        decode(tile, nt, mt, b);
         const int t0 = mt * BM, n0 = nt * BN;
         for (int it = 0; it < KT; ++it) {
           const int j = it / nchunk;
@@ -257,10 +272,8 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
     int local = 0, gcount = 0;
     for (int tile = pair0; tile < num_tiles; tile += pair_step, ++local) {
-      const int nt = tile % p.n_tiles;
-      const int rest = tile / p.n_tiles;
-      const int mt = (rest % p.m_tiles) * 2 + (int)cta_rank;
-      const int b = rest / p.m_tiles;
+      int nt, mt, b;
+      decode(tile, nt, mt, b);
       int b_t = b, t_tile0 = mt * BM;
       bool straddle = false;
       if (p.flat) {  // un-flatten the tile's first row once; most tiles lie inside one utterance
@@ -269,7 +282,7 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         straddle = t_tile0 + BM > p.S_out;
       }
       const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
-      const bool lean = drain_is_lean<(BN <= 64)>(p);  // warp-uniform
+      const bool lean = drain_is_lean<true>(p);  // warp-uniform
       if (lean && p.residual) {
         // Pull this tile's residual rows into L2 now, while the MMAs run: the drain below keeps only four 16-byte
         // loads per lane in flight, which from HBM (~1 us) capped the whole kernel at ~1.2 TB/s of residual reads.
@@ -328,7 +341,7 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean<(BN <= 64)>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
+          drain_block_lean<true>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
         else
           drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
       }
@@ -419,16 +432,18 @@ int launch2(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& 
   a.m_tiles = (int)((rows + 2 * BM - 1) / (2 * BM));  // pair tiles of 256 rows
   const int64_t tiles = (int64_t)(a.flat ? 1 : a.B) * a.m_tiles * a.n_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_ts2: too many tiles");
-  static unsigned long long attr_mask = 0;  // per device
-  if (first_use_on_device(attr_mask)) {
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
     cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_ts2_kernel<BN2, STAGES2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         C::smem_bytes);
+                                         C::smem_bytes + (RAGGED_MAX_B + 1) * 4);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_ts2: smem opt-in");
+    attr_done_on_device(attr_mask);
   }
   const int sms = sm_count();
   SS_REQUIRE(sms >= 2, SS_ERR_CUDA, "ss_conv1d_tf32x3_ts2: no CUDA device");
   const int pairs = (int)(tiles < sms / 2 ? tiles : sms / 2);
-  conv1d_tf32_ts2_kernel<BN2, STAGES2><<<2 * pairs, NTHREADS, C::smem_bytes, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
+  const int smem = C::smem_bytes + (a.rows ? (a.B + 1) * 4 : 0);
+  conv1d_tf32_ts2_kernel<BN2, STAGES2><<<2 * pairs, NTHREADS, smem, st>>>(tmA, tmBh, tmBl, a, in_act, in_slope, group);
   SS_CHECK_LAUNCH("ss_conv1d_tf32x3_ts2");
   return SS_OK;
 }
@@ -464,7 +479,9 @@ extern "C" int ss_conv1d_tf32x3_ts2(const ss_conv1d_tf32_params* p, void* stream
   const int bn = BN2 / 2;  // rows of the weight tile each CTA loads
   // Flat tiling (see TcArgs::flat): stride-1 same-length layer, batch-contiguous input, lean epilogue, and a
   // sequence length that would otherwise leave a partly empty last tile in every utterance.
-  const bool flat = p->B > 1 && p->S_in == p->S_out && p->S_out % (2 * BM) != 0 &&
+  SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_ts2: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
+  const bool flat = p->rows == nullptr && p->B > 1 && p->S_in == p->S_out && p->S_out % (2 * BM) != 0 &&
                     p->x_batch_stride == (int64_t)p->S_in * p->x_row_stride && (int64_t)p->B * p->S_in < (1ll << 30) &&
                     p->y != nullptr && p->accum == nullptr && p->y_act == nullptr && p->act != SS_ACT_TANH;
   CUtensorMap tmA, tmBh, tmBl;
@@ -490,7 +507,7 @@ extern "C" int ss_conv1d_tf32x3_ts2(const ss_conv1d_tf32_params* p, void* stream
   a.m_tiles = a.n_tiles = 0;
   a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
-  a.flat = flat ? 1 : 0; a.S_in = p->S_in;
+  a.flat = flat ? 1 : 0; a.S_in = p->S_in; a.rows = p->rows;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int group = p->k_group > 0 ? p->k_group : 8;
   return launch2(tmA, tmBh, tmBl, a, p->in_act, p->in_slope, group, st);

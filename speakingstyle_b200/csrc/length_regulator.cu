@@ -7,6 +7,8 @@
 // optional decoder position row added on the fly (transformer/Models.py:158-160), zeros on the
 // padding - with 128-bit streaming stores.  The source rows (B*L*C floats) are re-read ~8x but
 // stay in L2; algorithmic HBM bytes = 4*C*(sum_b src_len_b + B*T) + 4*B*L + 4*B.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace {
@@ -153,10 +155,16 @@ int ss_length_regulate(const float* x, const int32_t* ends, const float* pe, flo
              "ss_length_regulate: pointers must be 16-byte aligned");
   if (T == 0) return SS_OK;
   const size_t smem = (size_t)L * sizeof(int32_t);
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(length_regulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
-    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_length_regulate: smem opt-in");
+  if (smem > 48 * 1024) {  // very long token sequences only: opt in once per device, up to the 227 KB an SM offers
+    SS_REQUIRE(smem <= 227 * 1024, SS_ERR_UNSUPPORTED, "ss_length_regulate: L = %d tokens exceeds the shared-memory table", L);
+    static std::atomic<unsigned long long> attr_mask{0};
+    int d = 0;
+    cudaGetDevice(&d);
+    if ((attr_mask.load(std::memory_order_acquire) & (1ull << (d & 63))) == 0) {
+      cudaError_t e = cudaFuncSetAttribute(length_regulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      if (e != cudaSuccess) return ss::cuda_fail(e, "ss_length_regulate: smem opt-in");
+      attr_mask.fetch_or(1ull << (d & 63), std::memory_order_release);
+    }
   }
   dim3 grid((T + LR_FRAMES_PER_CTA - 1) / LR_FRAMES_PER_CTA, B);
   length_regulate_kernel<<<grid, LR_WARPS * 32, smem, (cudaStream_t)stream>>>(x, ends, pe, out, mel2phone, L, T, C);

@@ -78,12 +78,12 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
   const float4* x = reinterpret_cast<const float4*>(p.x + (int64_t)row * C);
   float4 v[V4];
 #pragma unroll
-  for (int i = 0; i < V4; ++i) v[i] = __ldg(x + lane + i * 32);
+  for (int i = 0; i < V4; ++i) v[i] = x[lane + i * 32];  // plain loads: callers run this in place (y == x), which rules out ld.global.nc
   if (p.residual) {
     const float4* r = reinterpret_cast<const float4*>(p.residual + (int64_t)row * C);
 #pragma unroll
     for (int i = 0; i < V4; ++i) {
-      const float4 a = __ldg(r + lane + i * 32);
+      const float4 a = r[lane + i * 32];  // may alias y as well
       v[i].x += a.x; v[i].y += a.y; v[i].z += a.z; v[i].w += a.w;
     }
   }

@@ -5,6 +5,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace sstc {
@@ -34,7 +36,13 @@ struct TcArgs {
   // falls outside their own utterance are zeroed by the operand-split warps, and the epilogue maps each
   // flattened row back to (utterance, frame).
   int32_t flat = 0, S_in = 0;
+  // Ragged schedule: rows[b] = number of output rows of utterance b that are wanted (clamped to [0, S_out]); tiles past
+  // that are neither computed nor written (the tile holding row rows[b]-1 is computed whole).  NULL: every row.
+  // The CTA builds the per-utterance tile prefix in shared memory once (ragged_build) and every role maps its linear
+  // tile index to (utterance, tile) with a binary search (ragged_decode); never combined with `flat`.
+  const int32_t* rows = nullptr;
 };
+constexpr int RAGGED_MAX_B = 1024;  // utterances per launch in the ragged schedule (prefix table in shared memory)
 
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -217,6 +225,42 @@ __device__ __forceinline__ void tmem_ld32x2(uint32_t ta, float (&a)[32], uint32_
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Ragged schedule helpers.  pre[0..B] (shared memory) = exclusive prefix of the utterances' scheduling units
+// (unit_rows output rows each).  ragged_build is called by every thread of the CTA before the role split (warp 0
+// does the work; the caller's __syncthreads / cluster sync publishes it).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ragged_build(const int32_t* rows, int B, int S_out, int unit_rows, int* pre) {
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  int carry = 0;
+  for (int base = 0; base < B; base += 32) {
+    const int b = base + lane;
+    int v = 0;
+    if (b < B) v = (min(max(__ldg(rows + b), 0), S_out) + unit_rows - 1) / unit_rows;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    if (b < B) pre[b] = carry + incl - v;
+    carry += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) pre[B] = carry;
+}
+// u < pre[B]: the utterance holding unit u (the LAST b with pre[b] <= u, which skips empty utterances) and the
+// unit's index inside it
+__device__ __forceinline__ void ragged_decode(const int* pre, int B, int u, int& b, int& mt) {
+  int lo = 0, hi = B;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (pre[mid] <= u) lo = mid; else hi = mid;
+  }
+  b = lo;
+  mt = u - pre[lo];
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -282,7 +326,7 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
       f = act4(f, p.act, p.slope);
       const int64_t g = ybase + off;
       if (p.residual) {  // bf16 residual
-        const uint2 r = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + g));
+        const uint2 r = *reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + g);
         float a, c;
         unpack_bf16(r.x, a, c); f.x += a; f.y += c;
         unpack_bf16(r.y, a, c); f.z += a; f.w += c;
@@ -320,7 +364,7 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
       g[u] = ybase + off;
       rpre[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       apre[u] = rpre[u];
-      if (ok[u] && pre_res) rpre[u] = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + g[u]));
+      if (ok[u] && pre_res) rpre[u] = *reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) + g[u]);  // plain load: may alias y
       if (ok[u] && pre_acc) apre[u] = *reinterpret_cast<const float4*>(p.accum + g[u]);
     }
 #pragma unroll
@@ -333,7 +377,7 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
       if (pre_res) {
         f.x += rpre[u].x; f.y += rpre[u].y; f.z += rpre[u].z; f.w += rpre[u].w;
       } else if (p.residual) {
-        const uint2 r = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + g[u]));
+        const uint2 r = *reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p.residual) + g[u]);
         float a, c;
         unpack_bf16(r.x, a, c); f.x += a; f.y += c;
         unpack_bf16(r.y, a, c); f.z += a; f.w += c;
@@ -421,7 +465,7 @@ __device__ __forceinline__ void drain_block_lean(const TcArgs& p, const float (&
       off[u] = base + off_rel;
       keep[u] = t < (straddle ? (p.lens && ok[u] ? __ldg(p.lens + bb) : 0x7fffffff) : len);
       r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (res && ok[u]) r[u] = __ldg(reinterpret_cast<const float4*>(res + off[u]));
+      if (res && ok[u]) r[u] = *reinterpret_cast<const float4*>(res + off[u]);  // plain load: the residual may be the buffer this launch writes (out == residual)
       t += 4;
       off_rel += row4;
     }
@@ -522,7 +566,7 @@ __device__ __forceinline__ void drain_tile_lean_wide(const TcArgs& p, const floa
 #pragma unroll
       for (int k = 0; k < NB; ++k) {
         r[u][k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (res && ok[u] && colok[k]) r[u][k] = __ldg(reinterpret_cast<const float4*>(res + off[u] + k * 32));
+        if (res && ok[u] && colok[k]) r[u][k] = *reinterpret_cast<const float4*>(res + off[u] + k * 32);
       }
       t += 4;
       off_rel += row4;
@@ -594,25 +638,32 @@ inline int make_map_3d(CUtensorMap* m, CUtensorMapDataType dt, const void* base,
   return SS_OK;
 }
 
-// true the first time it is called for the current device with this mask (kernel attributes such as the dynamic
-// shared-memory opt-in are per device; one process normally drives one GPU, but nothing here should assume it)
-inline bool first_use_on_device(unsigned long long& mask) {
+// Per-device, thread-safe bookkeeping of kernel attributes (the dynamic shared-memory opt-in is per device and per
+// kernel).  needs_attr_on_device() is true until attr_done_on_device() has been called for the current device; the bit
+// is published only AFTER cudaFuncSetAttribute succeeded, so a second host thread can at worst repeat the (idempotent)
+// call - it can never launch before the opt-in has landed.
+inline bool needs_attr_on_device(const std::atomic<unsigned long long>& mask) {
   int d = 0;
   if (cudaGetDevice(&d) != cudaSuccess) return true;
-  const unsigned long long bit = 1ull << (d & 63);
-  if (mask & bit) return false;
-  mask |= bit;
-  return true;
+  return (mask.load(std::memory_order_acquire) & (1ull << (d & 63))) == 0;
+}
+inline void attr_done_on_device(std::atomic<unsigned long long>& mask) {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess) return;
+  mask.fetch_or(1ull << (d & 63), std::memory_order_release);
 }
 
+// SM count of the CURRENT device (cached per device ordinal)
 inline int sm_count() {
-  static int n = []() {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-    return v;
-  }();
-  return n;
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  const int slot = dev & 63;
+  int v = cache[slot].load(std::memory_order_relaxed);
+  if (v > 0) return v;
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+  cache[slot].store(v, std::memory_order_relaxed);
+  return v;
 }
 
 }  // namespace sstc

@@ -139,6 +139,40 @@ class Generator(nn.Module, ParamCache):
         pk["post"] = wp[0].t().contiguous().reshape(-1)
         return pk
 
+    # ---------------------------------------------------------------------------------------
+    def halo_frames(self):
+        """Mel frames to the RIGHT of an utterance's last frame that can still reach one of its samples: the sum of the
+        right-hand halos of every layer (conv: dilation*(k-1)/2 rows; transposed conv: one input row), each divided by
+        the layer's rows per frame, rounded up, plus one.  utils/model.py:109-113 trims wave b to mel_len[b]*hop, so
+        nothing further right is ever observed."""
+        h = self.h
+        need = 3.0  # conv_pre, k = 7, at one row per frame
+        rate = 1
+        for i, u in enumerate(h["upsample_rates"]):
+            need += 1.0 / rate  # ConvTranspose1d: output t reads input rows <= (t + pad) / stride
+            rate *= u
+            rb = max((k - 1) // 2 * (sum(d) + len(d)) for k, d in zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"]))
+            need += rb / rate
+        need += 3.0 / rate  # conv_post, k = 7
+        return int(need) + 2
+
+    def _ragged_rows(self, frame_lens, T, dev):
+        """Per-layer row limits of the ragged schedule for utterances of ``frame_lens`` valid mel frames in a batch padded
+        to T: {rate: int32 [B]} for the layers running at ``rate`` rows per frame, {("up", i): int32 [B]} for the
+        phase-form GEMM of ups[i] (rows = input positions).  One small host -> device copy."""
+        H = self.halo_frames()
+        rates = [1]
+        for u in self.h["upsample_rates"]:
+            rates.append(rates[-1] * u)
+        keep = [min(T, max(0, int(n)) + H) for n in frame_lens]
+        # phase-form GEMM of ups[i]: row s writes output samples [u*s - pad, u*(s+1) - pad), so the samples of frame
+        # f-1 need rows <= f*rate (the kernel clamps to its own row count)
+        table = [[f * r for f in keep] for r in rates] + [[f * rates[i] + 1 for f in keep] for i in range(len(rates) - 1)]
+        t = torch.tensor(table, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+        rows = {r: t[j] for j, r in enumerate(rates)}
+        rows.update({("up", i): t[len(rates) + i] for i in range(len(rates) - 1)})
+        return rows
+
     def _post(self, xs, pk, pcm, pcm_out):
         """Output head.  pcm_out = (n_samples [B] int32 dev, out_offset [B] int64 dev, flat int16 buffer): ragged PCM
         straight into that buffer (ss_hifigan_post_trim) instead of the padded float wave."""
@@ -149,19 +183,23 @@ class Generator(nn.Module, ParamCache):
         wave = wave.unsqueeze(1)
         return (wave, pcm16) if pcm else wave
 
-    def _forward_bf16(self, x, pcm, pcm_out=None):
+    def _forward_bf16(self, x, pcm, pcm_out=None, rows=None):
         """Tensor-core path.  Convolution operands are bf16; the residual stream of every ResBlock and
         the stage mean stay fp32.  Each epilogue also emits the leaky-ReLU'd bf16 copy that the next
         convolution consumes (the activation cannot sit between TMA and the MMA)."""
         h, pk, nk = self.h, self.packed(), self.num_kernels
         L = ops.ACT_LRELU
+        rate = 1
         xa = ops.conv1d_tc(ops.cast_bf16(x), pk["pre"], self.conv_pre.bias, pad=3, want_y=False, act2=L,
-                           slope2=LRELU_SLOPE)[1]
+                           slope2=LRELU_SLOPE, rows=rows and rows[rate])[1]
         n_up = self.num_upsamples
         xs = None
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
             x32, xa = ops.conv_transpose1d_tc(xa, pk["ups"][i][0], pk["ups"][i][1], cout=self.ups[i].bias.numel(),
-                                              stride=u, pad=(k - u) // 2, act2=L, slope2=LRELU_SLOPE)
+                                              stride=u, pad=(k - u) // 2, act2=L, slope2=LRELU_SLOPE,
+                                              rows=rows and rows[("up", i)])
+            rate *= u
+            rw = rows and rows[rate]
             xs, ybuf = torch.empty_like(x32), torch.empty_like(x32)
             for j in range(nk):
                 rb = self.resblocks[i * nk + j]
@@ -170,25 +208,31 @@ class Generator(nn.Module, ParamCache):
                 nd, rk = len(rb.dilation), rb.kernel_size
                 for m, dil in enumerate(rb.dilation):
                     ta = ops.conv1d_tc(ya, w1s[m], rb.convs1[m].bias, dilation=dil, pad=get_padding(rk, dil),
-                                       want_y=False, act2=L, slope2=LRELU_SLOPE)[1]
+                                       want_y=False, act2=L, slope2=LRELU_SLOPE, rows=rw)[1]
                     if m < nd - 1:
                         y32, ya = ops.conv1d_tc(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y32,
-                                                out=ybuf, act2=L, slope2=LRELU_SLOPE)
+                                                out=ybuf, act2=L, slope2=LRELU_SLOPE, rows=rw)
                     else:
                         last_rb = j == nk - 1
                         feeds_ups = last_rb and i < n_up - 1  # the next ConvTranspose reads lrelu(mean)
                         nxt = ops.conv1d_tc(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y32,
                                             want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0),
-                                            act2=L if feeds_ups else None, slope2=LRELU_SLOPE)[1]
+                                            act2=L if feeds_ups else None, slope2=LRELU_SLOPE, rows=rw)[1]
             xa = nxt
         return self._post(xs, pk, pcm, pcm_out)
 
     @torch.no_grad()
-    def forward(self, x, channels_last=False, pcm=False, pcm_out=None):
+    def forward(self, x, channels_last=False, pcm=False, pcm_out=None, frame_lens=None):
         """x: mel [B,80,T] (reference layout) or [B,T,80] with channels_last=True.
         Returns wave [B,1,256*T] float32; with pcm=True returns (wave, int16 [B,256*T]).
         pcm_out = (n_samples [B] int32, out_offset [B] int64, flat int16 buffer - device or pinned host): the ragged
-        PCM epilogue of SURVEY 8(f1); returns that buffer and produces no padded wave."""
+        PCM epilogue of SURVEY 8(f1); returns that buffer and produces no padded wave.
+        frame_lens (host ints, one per utterance; only with pcm_out): the utterances' valid mel frames.  The caller
+        will only ever look at samples < frame_lens[b]*hop (utils/model.py:109-113), so every layer is run on the rows
+        that can reach those samples - frame_lens[b] + halo_frames() frames' worth - instead of on the whole padded
+        batch.  The samples that are written are bit-identical to the padded computation."""
+        if frame_lens is not None and pcm_out is None:
+            raise ValueError("frame_lens (ragged schedule) needs pcm_out: the padded wave would hold uncomputed samples")
         if not x.is_cuda:
             raise RuntimeError("speakingstyle_b200 Generator needs CUDA tensors; there is no CPU fallback")
         h = self.h
@@ -196,14 +240,18 @@ class Generator(nn.Module, ParamCache):
         if not channels_last:
             x = x.transpose(1, 2)
         x = x.to(torch.float32).contiguous()
+        rows = self._ragged_rows(frame_lens, x.shape[1], x.device) if frame_lens is not None else None
         if self.precision == "bf16":
-            return self._forward_bf16(x, pcm, pcm_out)
-        x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3)
+            return self._forward_bf16(x, pcm, pcm_out, rows)
+        rate = 1
+        x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3, rows=rows and rows[rate])
         nk = self.num_kernels
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
             wu, bu = pk["ups"][i]
             x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, pad=(k - u) // 2,
-                                     in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE)
+                                     in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, rows=rows and rows[("up", i)])
+            rate *= u
+            rw = rows and rows[rate]
             # four buffers per stage: x (stage input, read by all three ResBlocks), xs (their mean),
             # tbuf (output of c1) and ybuf (the running residual stream of one ResBlock).  c2 may write
             # in place over its residual operand (same element, same thread) but never over its conv input.
@@ -216,13 +264,13 @@ class Generator(nn.Module, ParamCache):
                 rk = rb.kernel_size
                 for m, dil in enumerate(rb.dilation):
                     t = ops.conv1d(y, w1s[m], rb.convs1[m].bias, k=rk, dilation=dil, pad=get_padding(rk, dil),
-                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, out=tbuf)
+                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, out=tbuf, rows=rw)
                     if m < nd - 1:
                         y = ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1),
-                                       in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, out=ybuf)
+                                       in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, out=ybuf, rows=rw)
                     else:  # last pair: x_j = c2(..) + y goes straight into the stage mean
                         ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1),
                                    in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, write_y=False,
-                                   accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0))
+                                   accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0), rows=rw)
             x = xs
         return self._post(x, pk, pcm, pcm_out)

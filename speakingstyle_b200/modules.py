@@ -110,7 +110,9 @@ class LengthRegulator(nn.Module):
 
 
 class VarianceAdaptor(nn.Module):
-    """model/modules.py:20-165 (phoneme-level pitch / energy, as in every shipped config)."""
+    """model/modules.py:20-165.  Pitch / energy are predicted per phoneme before the LengthRegulator (``phoneme_level``:
+    config/{BC2013,LJSpeech,LibriTTS,AISHELL3}/preprocess.yaml) or per frame after it (``frame_level``:
+    config/LJSpeech_paper/preprocess.yaml:26,29; modules.py:146-155)."""
 
     def __init__(self, preprocess_config, model_config):
         super().__init__()
@@ -120,9 +122,9 @@ class VarianceAdaptor(nn.Module):
         self.energy_predictor = VariancePredictor(model_config)
         self.pitch_feature_level = preprocess_config["preprocessing"]["pitch"]["feature"]
         self.energy_feature_level = preprocess_config["preprocessing"]["energy"]["feature"]
-        if self.pitch_feature_level != "phoneme_level" or self.energy_feature_level != "phoneme_level":
-            raise NotImplementedError("frame_level pitch/energy (model/modules.py:146-155) is not on the "
-                                      "B200 path; every shipped config is phoneme_level")
+        for lv in (self.pitch_feature_level, self.energy_feature_level):
+            if lv not in ("phoneme_level", "frame_level"):
+                raise ValueError(f"pitch / energy feature must be phoneme_level or frame_level, got {lv!r}")
         ve = model_config["variance_embedding"]
         n_bins = ve["n_bins"]
         with open(os.path.join(preprocess_config["path"]["preprocessed_path"], "stats.json")) as f:
@@ -153,46 +155,70 @@ class VarianceAdaptor(nn.Module):
             x = x.clone()  # the reference leaves its input untouched; the embedding adds below are in place
         # With a target the embedding comes from the target and the prediction is returned unscaled
         # (modules.py:85-86, 96-97); without, from control * prediction (88-91, 99-102).
-        pitch = self.pitch_predictor(x, src_mask, lens=lens)
-        if pitch_target is not None:
-            pitch_idx = ops.bucket_embed_add(pitch_target.to(torch.float32).contiguous().clone(), 1.0, self.pitch_bins,
-                                             self.pitch_embedding.weight, x, want_idx=return_extra)
-        else:
-            pitch_idx = ops.bucket_embed_add(pitch, p_control, self.pitch_bins, self.pitch_embedding.weight, x,
-                                             want_idx=return_extra)
         binv = getattr(self, "batch_invariant", False)
-        if binv:
-            ops.mask_rows_(x, lens)  # the pitch embedding was added at the pads too (modules.py:126)
-        energy = self.energy_predictor(x, src_mask, lens=lens)
-        if energy_target is not None:
-            energy_idx = ops.bucket_embed_add(energy_target.to(torch.float32).contiguous().clone(), 1.0,
-                                              self.energy_bins, self.energy_embedding.weight, x, want_idx=return_extra)
+
+        def embed(which, x, lens_, target, control):
+            """get_pitch_embedding / get_energy_embedding + the add (modules.py:83-103, 123-131, 146-155), in place."""
+            pred = getattr(self, which + "_predictor")(x, None, lens=lens_)
+            bins, table = getattr(self, which + "_bins"), getattr(self, which + "_embedding").weight
+            if target is not None:
+                idx = ops.bucket_embed_add(target.to(torch.float32).contiguous().clone(), 1.0, bins, table, x,
+                                           want_idx=return_extra)
+            else:
+                idx = ops.bucket_embed_add(pred, control, bins, table, x, want_idx=return_extra)
+            if binv:
+                ops.mask_rows_(x, lens_)  # the embedding was added at the pads too (modules.py:126,131)
+            return pred, idx
+
+        pitch = energy = pitch_idx = energy_idx = None
+        if self.pitch_feature_level == "phoneme_level":
+            pitch, pitch_idx = embed("pitch", x, lens, pitch_target, p_control)
+        if self.energy_feature_level == "phoneme_level":
+            energy, energy_idx = embed("energy", x, lens, energy_target, e_control)
+        frame_level = "frame_level" in (self.pitch_feature_level, self.energy_feature_level)
+        if frame_level:
+            # the frame-level predictors read the expanded sequence WITHOUT the decoder's position table, so the
+            # LengthRegulator kernel must not fuse that add here; it is applied after the embedding adds below
+            lr_pe, late_pe = None, decoder_pe
         else:
-            energy_idx = ops.bucket_embed_add(energy, e_control, self.energy_bins, self.energy_embedding.weight, x,
-                                              want_idx=return_extra)
-        if binv:
-            ops.mask_rows_(x, lens)  # ... and the energy embedding (modules.py:131)
+            lr_pe, late_pe = decoder_pe, None
         if duration_target is not None:
             # teacher forcing (modules.py:133-135): expand by the given durations to max_len; mel_mask is the caller's
             d_rounded = duration_target
             self.last_mel_len_host = None
             T = int(max_len) if max_len is not None else None
-            pe = decoder_pe(T) if (callable(decoder_pe) and T is not None) else (None if callable(decoder_pe) else decoder_pe)
+            pe = lr_pe(T) if (callable(lr_pe) and T is not None) else (None if callable(lr_pe) else lr_pe)
             out, mel_len = self.length_regulator(x, duration_target, max_len, pe=pe)
-            extra = {"mel2phone": None, "pitch_idx": pitch_idx, "energy_idx": energy_idx, "T": out.shape[1],
-                     "mel_len_expand": mel_len, "pe_added": pe is not None}
+            frame_lens = lens_from_mask(mel_mask) if mel_mask is not None else mel_len.to(torch.int32)
+            extra = {"mel2phone": None, "T": out.shape[1], "mel_len_expand": mel_len, "pe_added": pe is not None}
         else:
             d_rounded, ends, lens2 = ops.duration_scan(log_d, d_control)
             lens_host = lens2.cpu()  # one host read (the reference does B*L of them, modules.py:193)
             T = int(lens_host[0].max())
-            pe = decoder_pe(T) if callable(decoder_pe) else decoder_pe
+            pe = lr_pe(T) if callable(lr_pe) else lr_pe
             res = ops.length_regulate(x, ends, T, pe=pe, want_mel2phone=return_extra)
             out, m2p = res if return_extra else (res, None)
             mel_len = lens2[1]  # int32, from the float sum (modules.py:143)
             mel_mask = ops.length_mask(mel_len, int(lens_host[1].max()))
             self.last_mel_len_host = lens_host[1]  # already on the host: lets the wave epilogue trim without a second sync
-            extra = {"mel2phone": m2p, "pitch_idx": pitch_idx, "energy_idx": energy_idx, "T": T,
-                     "mel_len_expand": lens2[0]}
+            frame_lens = mel_len
+            extra = {"mel2phone": m2p, "T": T, "mel_len_expand": lens2[0], "pe_added": pe is not None}
+        if frame_level:
+            T = out.shape[1]
+            if mel_mask is not None and mel_mask.shape[1] != T:
+                # the reference masks the [B, T] predictions with this mask and fails on the shape (modules.py:146-155
+                # with d_control != 1, where int(sum d) != sum int(d)); say why instead
+                raise RuntimeError(f"frame-level pitch / energy: mel_mask has {mel_mask.shape[1]} frames, the expanded "
+                                   f"sequence {T} (non-integer durations); the reference fails here too")
+            if self.pitch_feature_level == "frame_level":
+                pitch, pitch_idx = embed("pitch", out, frame_lens, pitch_target, p_control)
+            if self.energy_feature_level == "frame_level":
+                energy, energy_idx = embed("energy", out, frame_lens, energy_target, e_control)
+            pe = late_pe(T) if callable(late_pe) else late_pe
+            if pe is not None:
+                out = ops.add_position(out, pe)
+                extra["pe_added"] = True
+        extra.update(pitch_idx=pitch_idx, energy_idx=energy_idx)
         ret = (out, pitch, energy, log_d, d_rounded, mel_len, mel_mask)
         return ret + (extra,) if return_extra else ret
 

@@ -130,6 +130,8 @@ tf32_k_group = int(os.environ.get("SS_TF32_KGROUP", "0"))  # 0 = library default
 # short ones (they are bit-identical; the pair form is ~3 % faster from 16 chunks up and slower on k = 1, K = 256 layers);
 # "ss": split operands in shared memory (the first version, kept as a cross-check)
 tf32_variant = os.environ.get("SS_TF32_VARIANT", "auto")
+# narrow layers (Cin, Cout <= 64, k >= 2: the HiFi-GAN 64- / 32-channel stages) go to the panel kernel in "auto"
+tf32_panel = os.environ.get("SS_TF32_PANEL", "1") != "0"
 
 
 def tf32_round(t):
@@ -186,7 +188,7 @@ def pack_conv_transpose(weight, stride):
 
 def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y_batch_stride, y_row_stride,
                y_offset, y_batch_elems, dilation, pad, in_act, in_slope, act, slope, act2, slope2, accum_scale,
-               accum_init, flops, variant=None):
+               accum_init, flops, variant=None, rows=None):
     hi, lo = W.tf32
     p = _lib.Conv1dTf32Params(
         x=x.data_ptr(), x_batch_stride=S_in * W.cin, x_row_stride=W.cin, w_hi=hi.data_ptr(), w_lo=lo.data_ptr(),
@@ -196,23 +198,28 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         y_batch_stride=y_batch_stride, y_row_stride=y_row_stride, y_offset=y_offset, y_batch_elems=y_batch_elems,
         B=B, S_in=S_in, S_out=S_out, Cin=W.cin, Cout=W.cout, k=W.k, dilation=dilation, pad=pad, in_act=in_act,
         in_slope=in_slope, act=act, slope=slope, act2=act2 or 0, slope2=slope2, accum_scale=accum_scale,
-        accum_init=int(accum_init), k_group=tf32_k_group)
+        accum_init=int(accum_init), k_group=tf32_k_group, rows=None if rows is None else rows.data_ptr())
     v = variant or tf32_variant
     if v == "auto":
-        v = "ts2" if W.k * ((W.cin + 31) // 32) >= 16 else "ts"
+        if tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2 and _lib.lib().ss_conv1d_tf32x3_panel_supported(C.byref(p)):
+            v = "panel"
+        else:
+            v = "ts2" if W.k * ((W.cin + 31) // 32) >= 16 else "ts"
     entry = {"ts": _lib.lib().ss_conv1d_tf32x3_ts, "ts2": _lib.lib().ss_conv1d_tf32x3_ts2,
-             "ss": _lib.lib().ss_conv1d_tf32x3}[v]
+             "ss": _lib.lib().ss_conv1d_tf32x3, "panel": _lib.lib().ss_conv1d_tf32x3_panel}[v]
     fn = lambda: entry(C.byref(p), _stream())  # noqa: E731
     check(conv_timer.run(flops, fn, _tag("tf32x3", p), _meta("tf32x3", p)) if conv_timer is not None else fn())
 
 
 def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.0, in_act=ACT_NONE, in_slope=0.0,
            residual=None, lens=None, out=None, accum=None, accum_scale=1.0, accum_init=False, write_y=True,
-           backend=None, s_out=None):
+           backend=None, s_out=None, rows=None):
     """fp32-accurate convolution: x [B,S,Cin] f32, w a ConvW -> y [B,S,Cout] f32.
     backend (default ops.fp32_backend): "tf32x3" = ss_conv1d_tf32x3, "ffma" = ss_conv1d_f32.
-    s_out: output length when it is not S (a "valid" convolution: pad=0, s_out = S - (k-1)*dilation); 3xTF32 only."""
-    _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias")
+    s_out: output length when it is not S (a "valid" convolution: pad=0, s_out = S - (k-1)*dilation); 3xTF32 only.
+    rows: int32 [B] on the device - ragged schedule, only rows t < rows[b] are wanted (the tensor-memory 3xTF32
+    kernels skip whole tiles past that; the cross-check backends compute every row, which gives the same wanted rows)."""
+    _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias"); _chk(rows, torch.int32, "rows")
     _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
     B, S, Cin = x.shape
     if not isinstance(w, ConvW):
@@ -233,7 +240,7 @@ def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.
                    y_batch_stride=So * Cout,
                    y_row_stride=Cout, y_offset=0, y_batch_elems=So * Cout, dilation=dilation, pad=pad, in_act=in_act,
                    in_slope=in_slope, act=act, slope=slope, act2=None, slope2=0.0, accum_scale=accum_scale,
-                   accum_init=accum_init, flops=2.0 * B * So * Cout * k * Cin)
+                   accum_init=accum_init, flops=2.0 * B * So * Cout * k * Cin, rows=rows)
         return y
     w = w.ffma
     p = _lib.Conv1dF32Params(
@@ -247,10 +254,12 @@ def conv1d(x, w, bias=None, *, k=None, dilation=1, pad=0, act=ACT_NONE, slope=0.
     return y
 
 
-def conv_transpose1d(x, w, bias, *, cout, stride, pad, in_act=ACT_NONE, in_slope=0.0, backend=None):
+def conv_transpose1d(x, w, bias, *, cout, stride, pad, in_act=ACT_NONE, in_slope=0.0, backend=None, rows=None):
     """ConvTranspose1d in phase form: x [B,S,Cin] f32, w = pack_conv_transpose(weight, stride), bias tiled to
-    [stride*cout].  Output [B, T_out, cout] with T_out = (S-1)*stride - 2*pad + taps*stride."""
-    _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias")
+    [stride*cout].  Output [B, T_out, cout] with T_out = (S-1)*stride - 2*pad + taps*stride.
+    rows (ragged schedule) counts rows of the phase-form GEMM, i.e. INPUT positions: row s writes output samples
+    [stride*s - pad, stride*(s+1) - pad)."""
+    _chk(x, torch.float32, "x"); _chk(bias, torch.float32, "bias"); _chk(rows, torch.int32, "rows")
     B, S, Cin = x.shape
     taps = w.k
     k_full = taps * stride
@@ -263,7 +272,7 @@ def conv_transpose1d(x, w, bias, *, cout, stride, pad, in_act=ACT_NONE, in_slope
                    y_batch_stride=T_out * cout,
                    y_row_stride=stride * cout, y_offset=-pad * cout, y_batch_elems=T_out * cout, dilation=1,
                    pad=taps - 1, in_act=in_act, in_slope=in_slope, act=ACT_NONE, slope=0.0, act2=None, slope2=0.0,
-                   accum_scale=0.0, accum_init=False, flops=2.0 * B * T_out * cout * taps * Cin)
+                   accum_scale=0.0, accum_init=False, flops=2.0 * B * T_out * cout * taps * Cin, rows=rows)
         return y
     w = w.ffma
     p = _lib.Conv1dF32Params(
@@ -300,7 +309,7 @@ def _tc_call(p, flops):
 
 def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, residual=None, lens=None,
               out_dtype=torch.float32, want_y=True, out=None, act2=None, slope2=0.0, accum=None, accum_scale=1.0,
-              accum_init=False):
+              accum_init=False, rows=None):
     """Tensor-core convolution.  x [B,S,Cin] bf16, w [k,Cout,Cin] bf16 (pack_conv_tc).
     Returns (y or None, y_act or None); y_act (bf16) is produced when act2 is not None."""
     if isinstance(w, ConvW):
@@ -323,12 +332,12 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
         y_batch_stride=S * Cout, y_row_stride=Cout, y_offset=0, y_batch_elems=S * Cout, B=B, S_in=S, S_out=S, Cin=Cin,
         Cout=Cout, k=k, dilation=dilation, pad=pad, act=act, slope=slope, act2=act2 or 0, slope2=slope2,
         y_dtype=_DT[y.dtype] if y is not None else F32, residual_dtype=_DT[residual.dtype] if residual is not None else F32,
-        accum_scale=accum_scale, accum_init=int(accum_init))
+        accum_scale=accum_scale, accum_init=int(accum_init), rows=None if rows is None else rows.data_ptr())
     _tc_call(p, 2.0 * B * S * Cout * k * Cin)
     return y, y_act
 
 
-def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True):
+def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True, rows=None):
     """ConvTranspose1d in phase form on tensor cores.  x [B,S,Cin] bf16; w [taps, stride*cout, Cin] bf16;
     bias tiled to [stride*cout] f32.  Returns (y f32 [B,T_out,cout] or None, y_act bf16 or None)."""
     if isinstance(w, ConvW):
@@ -345,7 +354,8 @@ def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0,
         lens=None, y=None if y is None else y.data_ptr(), y_act=None if y_act is None else y_act.data_ptr(), accum=None,
         y_batch_stride=T_out * cout, y_row_stride=stride * cout, y_offset=-pad * cout, y_batch_elems=T_out * cout, B=B,
         S_in=S, S_out=S_out, Cin=Cin, Cout=stride * cout, k=taps, dilation=1, pad=taps - 1, act=ACT_NONE, slope=0.0,
-        act2=act2 or 0, slope2=slope2, y_dtype=F32, residual_dtype=F32, accum_scale=0.0, accum_init=0)
+        act2=act2 or 0, slope2=slope2, y_dtype=F32, residual_dtype=F32, accum_scale=0.0, accum_init=0,
+        rows=None if rows is None else rows.data_ptr())
     _tc_call(p, 2.0 * B * T_out * cout * taps * Cin)
     return y, y_act
 

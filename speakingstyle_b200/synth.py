@@ -120,14 +120,26 @@ def fastspeech2_state_dict(model_config, dataset="BC2013", seed=1234, duration_b
 
     stats = C.STATS[dataset]
     nb = model_config["variance_embedding"]["n_bins"]
-    sd["variance_adaptor.pitch_bins"] = torch.linspace(stats["pitch"][0], stats["pitch"][1], nb - 1)
-    sd["variance_adaptor.energy_bins"] = torch.linspace(stats["energy"][0], stats["energy"][1], nb - 1)
+    ve = model_config["variance_embedding"]
+
+    def edges(lo, hi, quant):  # model/modules.py:51-75
+        if quant == "log":
+            return torch.exp(torch.linspace(np.log(lo), np.log(hi), nb - 1))
+        return torch.linspace(lo, hi, nb - 1)
+
+    sd["variance_adaptor.pitch_bins"] = edges(stats["pitch"][0], stats["pitch"][1], ve["pitch_quantization"])
+    sd["variance_adaptor.energy_bins"] = edges(stats["energy"][0], stats["energy"][1], ve["energy_quantization"])
     for name in ("duration_predictor", "pitch_predictor", "energy_predictor"):
         _variance_predictor(r, sd, f"variance_adaptor.{name}", d, vp["filter_size"], vp["kernel_size"])
     sd["variance_adaptor.duration_predictor.linear_layer.bias"] = torch.full((1,), float(duration_bias))
     # spread pitch / energy predictions over many buckets instead of two or three
     sd["variance_adaptor.pitch_predictor.linear_layer.weight"] *= 8.0
     sd["variance_adaptor.energy_predictor.linear_layer.weight"] *= 8.0
+    if dataset == "LJSpeech_paper":  # un-normalised features: move the predictions into the range of the bins
+        sd["variance_adaptor.pitch_predictor.linear_layer.weight"] *= 40.0
+        sd["variance_adaptor.pitch_predictor.linear_layer.bias"] = torch.full((1,), 260.0)
+        sd["variance_adaptor.energy_predictor.linear_layer.weight"] *= 20.0
+        sd["variance_adaptor.energy_predictor.linear_layer.bias"] = torch.full((1,), 120.0)
     sd["variance_adaptor.pitch_embedding.weight"] = r.normal((nb, d))
     sd["variance_adaptor.energy_embedding.weight"] = r.normal((nb, d))
 
@@ -236,6 +248,7 @@ WORKLOADS = {
     # name: (dataset, batch, src_len_range, ref_len_range, fixed_ref_len, vocoder)
     "tiny": ("BC2013", 3, (5, 12), (9, 24), None, True),
     "tiny_ms": ("LibriTTS", 2, (4, 9), (8, 16), None, True),
+    "tiny_fl": ("LJSpeech_paper", 3, (5, 12), (9, 24), None, False),  # frame-level pitch / energy, log pitch bins
     "cfg1": ("LJSpeech", 16, (80, 120), (200, 400), None, False),
     "cfg2": ("BC2013", 64, (80, 120), (800, 800), 800, False),
     "cfg3": ("LibriTTS", 32, (80, 120), (200, 400), None, True),

@@ -24,9 +24,11 @@ def get_vocoder(h=None, device="cuda", state_dict=None, precision="fp32"):
 
 
 @torch.no_grad()
-def _ragged_pcm(vocoder, mels, n_samples, channels_last):
+def _ragged_pcm(vocoder, mels, n_samples, channels_last, device_out=False):
     """Runs the vocoder with the ragged PCM epilogue writing into pinned host memory; returns one int16 numpy view
-    per utterance (no padded wave, no separate D2H copy - the kernel's stores are what crosses PCIe)."""
+    per utterance (no padded wave, no separate D2H copy - the kernel's stores are what crosses PCIe).
+    device_out: keep the trimmed waves on the device instead (one flat int16 tensor, returned as per-utterance views,
+    no synchronisation) - for callers that post-process on the GPU."""
     T = mels.shape[1] if channels_last else mels.shape[2]
     hop = 1
     for u in vocoder.h["upsample_rates"]:
@@ -35,11 +37,18 @@ def _ragged_pcm(vocoder, mels, n_samples, channels_last):
     offs = [0]
     for v in n:
         offs.append(offs[-1] + v)
-    host = torch.empty(max(offs[-1], 1), dtype=torch.int16, pin_memory=True)  # cached pinned allocator: cheap after the first call
     dev = mels.device
+    if device_out:
+        host = torch.empty(max(offs[-1], 1), dtype=torch.int16, device=dev)
+    else:
+        host = torch.empty(max(offs[-1], 1), dtype=torch.int16, pin_memory=True)  # cached pinned allocator: cheap after the first call
     n_dev = torch.tensor(n, dtype=torch.int32).to(dev, non_blocking=True)
     o_dev = torch.tensor(offs[:-1], dtype=torch.int64).to(dev, non_blocking=True)
-    vocoder(mels, channels_last=channels_last, pcm_out=(n_dev, o_dev, host))
+    # every layer runs only on the frames that can reach a returned sample (Generator.forward, frame_lens)
+    frame_lens = [-(-v // hop) for v in n]
+    vocoder(mels, channels_last=channels_last, pcm_out=(n_dev, o_dev, host), frame_lens=frame_lens)
+    if device_out:
+        return [host[offs[i]:offs[i + 1]] for i in range(len(n))]
     torch.cuda.current_stream(dev).synchronize()
     flat = host.numpy()
     return [flat[offs[i]:offs[i + 1]] for i in range(len(n))]
@@ -64,9 +73,11 @@ def vocoder_infer(mels, vocoder, model_config=None, preprocess_config=None, leng
 
 
 @torch.no_grad()
-def synthesize_batch(model, vocoder, batch, p_control=1.0, e_control=1.0, d_control=1.0, hop_length=256):
+def synthesize_batch(model, vocoder, batch, p_control=1.0, e_control=1.0, d_control=1.0, hop_length=256,
+                     device_out=False):
     """One batch of synthesize.py:128-150 + utils/tools.py:183-230 without plots and files:
-    host batch dict -> (10-tuple of model outputs, list of int16 waves or None)."""
+    host batch dict -> (10-tuple of model outputs, list of int16 waves or None).  The waves are numpy views of pinned
+    host memory, trimmed to mel_len * hop; with device_out=True they stay on the device (int16 tensors, no sync)."""
     out = model(batch["speakers"], batch["texts"], batch["src_lens"], batch["max_src_len"], batch["mels"],
                 batch["mel_lens"], batch["max_mel_len"], p_control=p_control, e_control=e_control,
                 d_control=d_control)
@@ -75,5 +86,6 @@ def synthesize_batch(model, vocoder, batch, p_control=1.0, e_control=1.0, d_cont
         mel_len = getattr(model.variance_adaptor, "last_mel_len_host", None)  # read once inside forward()
         if mel_len is None or len(mel_len) != out[9].shape[0]:
             mel_len = out[9].cpu()
-        wavs = _ragged_pcm(vocoder, out[1], [int(v) * hop_length for v in mel_len.tolist()], channels_last=True)
+        wavs = _ragged_pcm(vocoder, out[1], [int(v) * hop_length for v in mel_len.tolist()], channels_last=True,
+                           device_out=device_out)
     return out, wavs

@@ -120,14 +120,19 @@ class MultiHeadAttention(nn.Module, ParamCache):
         returned as (fp32, bf16)."""
         pk = self.packed()
         ln = self.layer_norm
+        # Ragged schedule: the attention kernel reads only Q / K / V rows below ceil128(lens) and writes zeros for the
+        # padded queries, and the LayerNorm below overwrites the padded rows with zeros without reading them - so the
+        # two k = 1 projections skip the tiles that hold nothing but padding (SubLayers.py:39-55 computes them and
+        # Layers.py:27-28 throws them away).
+        rows = lens if mask_rows else None
         if xb is not None:
-            qkv, _ = ops.conv1d_tc(xb, pk["wqkv"], pk["bqkv"])
+            qkv, _ = ops.conv1d_tc(xb, pk["wqkv"], pk["bqkv"], rows=rows)
             ctx = ops.attention(qkv, lens, self.n_head)
-            y, _ = ops.conv1d_tc(ops.cast_bf16(ctx), pk["wfc"], self.fc.bias, residual=x)
+            y, _ = ops.conv1d_tc(ops.cast_bf16(ctx), pk["wfc"], self.fc.bias, residual=x, rows=rows)
             return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y, want_bf16=True)
-        qkv = ops.conv1d(x, pk["wqkv"], pk["bqkv"])
+        qkv = ops.conv1d(x, pk["wqkv"], pk["bqkv"], rows=rows)
         ctx = ops.attention(qkv, lens, self.n_head)
-        y = ops.conv1d(ctx, pk["wfc"], self.fc.bias, residual=x)
+        y = ops.conv1d(ctx, pk["wfc"], self.fc.bias, residual=x, rows=rows)
         return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y)
 
 
@@ -151,13 +156,18 @@ class PositionwiseFeedForward(nn.Module, ParamCache):
         # Batch-invariant mode: when w_2 has a halo (the reference encoder's [3, 3] kernels) it reads w_1's output at
         # padded frames, which a lone utterance would see as zero padding - mask the intermediate there.
         hl = lens if (getattr(self, "batch_invariant", False) and k2 > 1) else None
+        # Ragged schedule (encoder / decoder blocks, w_2 with k = 1): the block's input is zero on the padded frames
+        # (the attention sub-layer masked it), w_2 reads no neighbour rows, and the LayerNorm below zeroes the padded
+        # rows without reading them - tiles of pure padding are skipped.  Not for the reference encoder's [3, 3]
+        # blocks, whose w_2 reads w_1's (non-zero) output on padded frames (SubLayers.py:88-91).
+        rows = lens if (lens is not None and k2 == 1) else None
         if xb is not None:  # tensor-core path: the 1024-channel intermediate only ever exists in bf16
             h, _ = ops.conv1d_tc(xb, pk["w1"], self.w_1.bias, pad=(k1 - 1) // 2, act=ops.ACT_RELU, lens=hl,
-                                 out_dtype=torch.bfloat16)
-            y, _ = ops.conv1d_tc(h, pk["w2"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x)
+                                 out_dtype=torch.bfloat16, rows=rows)
+            y, _ = ops.conv1d_tc(h, pk["w2"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x, rows=rows)
             return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y, want_bf16=True)
-        h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU, lens=hl)
-        y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x)
+        h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU, lens=hl, rows=rows)
+        y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x, rows=rows)
         return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y)
 
 

@@ -159,6 +159,87 @@ def test_cta_pair_conv_is_bit_identical_to_single_cta(ops, B, S, Cin, Cout, k, d
     assert torch.equal(y1, y2)
 
 
+
+@pytest.mark.parametrize("B,S,Cin,Cout,k,dil", [
+    (3, 1000, 32, 32, 11, 5),   # weights resident, halo 25 each side, three panels
+    (3, 1000, 32, 32, 3, 1),
+    (2, 777, 64, 64, 11, 5),    # weights streamed (22 tiles of 16 KB do not fit), S not a multiple of the tile
+    (2, 640, 64, 64, 3, 3),     # 64 channels with resident weights
+    (2, 900, 64, 32, 7, 3),     # Cin != Cout
+    (1, 50, 32, 64, 2, 1),      # shorter than a tile, even tap count
+    (40, 300, 32, 32, 7, 1),    # more tiles than CTAs: panel / weight ring wrap-around
+])
+def test_panel_conv_is_bit_identical_to_the_per_tap_kernel(ops, B, S, Cin, Cout, k, dil):
+    """ss_conv1d_tf32x3_panel (activation panel fetched once per tile, shifted rows per tap, resident weights) issues
+    the same MMAs in the same order as ss_conv1d_tf32x3_ts: identical bits, with every epilogue HiFi-GAN uses."""
+    g = torch.Generator().manual_seed(12)
+    x = torch.randn(B, S, Cin, generator=g).to(DEV)
+    W = ops.pack_conv(torch.randn(Cout, Cin, k, generator=g).to(DEV) / math.sqrt(Cin * k))
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    res = torch.randn(B, S, Cout, generator=g).to(DEV)
+    pad = (k - 1) * dil // 2
+    kw = dict(k=k, dilation=dil, pad=pad, in_act=ops.ACT_LRELU, in_slope=0.1)
+    for extra in (dict(), dict(residual=res), dict(residual=res, act=ops.ACT_RELU)):
+        a = ops.conv1d(x, W, bias, backend="tf32x3_ts", **kw, **extra)
+        b = ops.conv1d(x, W, bias, backend="tf32x3_panel", **kw, **extra)
+        assert torch.equal(a, b), extra
+    acc_a = torch.full((B, S, Cout), 0.25, device=DEV)
+    acc_b = acc_a.clone()
+    ops.conv1d(x, W, bias, backend="tf32x3_ts", residual=res, write_y=False, accum=acc_a, accum_scale=1 / 3, **kw)
+    ops.conv1d(x, W, bias, backend="tf32x3_panel", residual=res, write_y=False, accum=acc_b, accum_scale=1 / 3, **kw)
+    assert torch.equal(acc_a, acc_b)
+    # ragged schedule on the panel kernel
+    rows_host = ([S, 0, 1, S // 2 + 3] * 10)[:B]
+    rows = torch.tensor(rows_host, dtype=torch.int32, device=DEV)
+    full = ops.conv1d(x, W, bias, backend="tf32x3_panel", residual=res, **kw)
+    out = torch.full((B, S, Cout), 7.5, device=DEV)
+    ops.conv1d(x, W, bias, backend="tf32x3_panel", residual=res, out=out, rows=rows, **kw)
+    for b_, r in enumerate(rows_host):
+        assert torch.equal(out[b_, :r], full[b_, :r]), (b_, r)
+        assert bool((out[b_, -(-r // 128) * 128:] == 7.5).all()), (b_, r)
+    # and against fp64 directly
+    ref = torch.nn.functional.conv1d(torch.nn.functional.leaky_relu(x.double(), 0.1).transpose(1, 2),
+                                     W.kcc.permute(1, 2, 0).double(), bias.double(), padding=pad, dilation=dil).transpose(1, 2)
+    if ref.shape[1] == S:
+        assert (full.double() - res.double() - ref).abs().max().item() <= 2e-5
+
+
+@pytest.mark.parametrize("variant,B,S,Cin,Cout,k,dil", [
+    ("ts", 5, 1000, 32, 32, 11, 5),    # narrow tile (8 split warps, two correction accumulators)
+    ("ts", 4, 700, 64, 64, 3, 1),
+    ("ts", 3, 900, 256, 256, 1, 1),    # 96-column short-reduction form
+    ("ts2", 4, 1200, 128, 128, 7, 3),  # CTA pair: 256-row scheduling units
+    ("ts2", 3, 515, 256, 1024, 9, 1),
+])
+def test_conv1d_ragged_schedule(ops, variant, B, S, Cin, Cout, k, dil):
+    """rows[b]: tiles past an utterance's wanted rows are skipped; the wanted rows are bit-identical to the full
+    computation and memory past the last computed tile is left alone."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(B, S, Cin, generator=g).to(DEV)
+    W = ops.pack_conv(torch.randn(Cout, Cin, k, generator=g).to(DEV) / math.sqrt(Cin * k))
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    res = torch.randn(B, S, Cout, generator=g).to(DEV)
+    rows_host = [S, 0, 1, S // 2 + 3, 130][:B]
+    rows = torch.tensor(rows_host, dtype=torch.int32, device=DEV)
+    pad = (k - 1) // 2 * dil
+    kw = dict(k=k, dilation=dil, pad=pad, in_act=ops.ACT_LRELU, in_slope=0.1, residual=res, backend="tf32x3_" + variant)
+    full = ops.conv1d(x, W, bias, **kw)
+    out = torch.full((B, S, Cout), 7.5, device=DEV)
+    ops.conv1d(x, W, bias, out=out, rows=rows, **kw)
+    unit = 256 if variant == "ts2" and Cout > 64 else 128
+    for b, r in enumerate(rows_host):
+        assert torch.equal(out[b, :r], full[b, :r]), (b, r)
+        done = -(-r // unit) * unit  # the scheduling unit holding the last wanted row is computed whole
+        assert bool((out[b, done:] == 7.5).all()), (b, r)
+    # running-mean epilogue (HiFi-GAN MRF) on the same schedule
+    acc_full = torch.zeros(B, S, Cout, device=DEV)
+    acc = torch.zeros(B, S, Cout, device=DEV)
+    ops.conv1d(x, W, bias, write_y=False, accum=acc_full, accum_scale=1 / 3, accum_init=False, **kw)
+    ops.conv1d(x, W, bias, write_y=False, accum=acc, accum_scale=1 / 3, accum_init=False, rows=rows, **kw)
+    for b, r in enumerate(rows_host):
+        assert torch.equal(acc[b, :r], acc_full[b, :r]), (b, r)
+
+
 @pytest.mark.parametrize("Cin,Cout,k,u,S", [(512, 256, 16, 8, 13), (128, 64, 4, 2, 50), (64, 32, 4, 2, 129)])
 def test_conv_transpose_phase_form(ops, Cin, Cout, k, u, S):
     from speakingstyle_b200 import configs as C

@@ -108,3 +108,26 @@ def test_cast_bf16(ops):
     x = rnd(3, 50, 80, seed=11)
     assert torch.equal(ops.cast_bf16(x.to(DEV)).cpu(), x.to(torch.bfloat16))
     assert torch.equal(ops.cast_bf16(x.to(DEV), ops.ACT_LRELU, 0.1).cpu(), F.leaky_relu(x, 0.1).to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("B,S,Cin,Cout,k,dil", [(5, 1500, 32, 32, 11, 1), (4, 900, 64, 64, 7, 3), (3, 700, 128, 128, 3, 5),
+                                                (3, 400, 256, 256, 11, 1)])
+def test_conv1d_tc_ragged_schedule(ops, B, S, Cin, Cout, k, dil):
+    """rows[b] on the bf16 kernel (scheduling unit = 256 / BN row tiles): wanted rows bit-identical, the rest untouched."""
+    x = rnd(B, S, Cin, seed=21).to(DEV).to(torch.bfloat16)
+    w = ops.pack_conv_tc(rnd(Cout, Cin, k, seed=22, scale=1 / math.sqrt(Cin * k)).to(DEV))
+    b = rnd(Cout, seed=23).to(DEV)
+    res = rnd(B, S, Cout, seed=24).to(DEV)
+    rows_host = [S, 0, 1, S // 2 + 3, 130][:B]
+    rows = torch.tensor(rows_host, dtype=torch.int32, device=DEV)
+    pad = (k - 1) // 2 * dil
+    kw = dict(dilation=dil, pad=pad, residual=res, act2=ops.ACT_LRELU, slope2=0.1)
+    y_full, a_full = ops.conv1d_tc(x, w, b, **kw)
+    out = torch.full((B, S, Cout), 7.5, device=DEV)
+    y, a = ops.conv1d_tc(x, w, b, out=out, rows=rows, **kw)
+    bn = 256 if Cout >= 256 else 128 if Cout > 64 else 64 if Cout > 32 else 32
+    unit = 128 * max(1, 256 // bn)
+    for i, r in enumerate(rows_host):
+        assert torch.equal(y[i, :r], y_full[i, :r]) and torch.equal(a[i, :r], a_full[i, :r]), (i, r)
+        done = min(S, -(-r // unit) * unit)
+        assert bool((out[i, done:] == 7.5).all()), (i, r)

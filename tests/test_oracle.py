@@ -24,14 +24,18 @@ def _oracle_run(name, controls=(1.0, 1.0, 1.0), dtype=torch.float32):
     ds, batch, voc = S.make_workload(name)
     mc = C.model_config(ds)
     sd = S.fastspeech2_state_dict(mc, ds)
+    pp = C.preprocess_config(ds)["preprocessing"]
     with torch.no_grad():
-        r = O.fastspeech2_forward(sd, mc, batch, *controls, dtype=dtype, intermediates=True)
+        r = O.fastspeech2_forward(sd, mc, batch, *controls, dtype=dtype, intermediates=True,
+                                  levels=(pp["pitch"]["feature"], pp["energy"]["feature"]))
     return r, voc
 
 
 @pytest.mark.parametrize("name,tag,controls", [("tiny", "tiny", (1.0, 1.0, 1.0)),
                                                 ("tiny_ms", "tiny_ms", (1.0, 1.0, 1.0)),
-                                                ("tiny", "tiny_ctl", (1.2, 0.8, 1.3))])
+                                                ("tiny", "tiny_ctl", (1.2, 0.8, 1.3)),
+                                                # config/LJSpeech_paper: frame-level pitch / energy, log pitch bins
+                                                ("tiny_fl", "tiny_fl", (1.0, 1.0, 1.0))])
 def test_fastspeech2_oracle_matches_golden(golden, name, tag, controls):
     g = golden(tag)
     r, voc = _oracle_run(name, controls)
@@ -46,7 +50,9 @@ def test_fastspeech2_oracle_matches_golden(golden, name, tag, controls):
     for key, val in (("mel", out[0]), ("postnet_mel", out[1]), ("pitch", out[2]), ("energy", out[3]),
                      ("log_d", out[4]), ("gammas", r["gammas"]), ("betas", r["betas"]),
                      ("encoder", r["encoder"]), ("lr_out", r["x"]), ("decoder", r["decoder"])):
-        np.testing.assert_allclose(val.numpy(), g[key], atol=2e-5, rtol=0, err_msg=key)
+        # un-normalised frame-level features are O(100): the same relative accuracy is a larger absolute one
+        atol = 2e-3 if (name == "tiny_fl" and key in ("pitch", "energy")) else 2e-5
+        np.testing.assert_allclose(val.numpy(), g[key], atol=atol, rtol=0, err_msg=key)
     if voc and "wave" in g:
         h = C.hifigan_config()
         vsd = S.fold_weight_norm(S.hifigan_state_dict(h))
