@@ -10,8 +10,10 @@
  *   - every pointer is a DEVICE pointer unless its name ends in `_host`;
  *   - activations are channels-last, row-major: [B, S, C] with C contiguous (the reference's own
  *     layout between modules; its transposes around Conv1d disappear);
- *   - the library never allocates or frees device memory and keeps no mutable global state:
- *     the caller owns inputs, outputs and workspaces (ss_*_workspace_bytes tells the size);
+ *   - the library never allocates or frees device memory: the caller owns every input, output and scratch
+ *     buffer (each entry point documents the buffers it needs).  Its only process-wide state is the launch
+ *     counter below, per-device caches of kernel attributes / SM counts (atomics), and the built-in scratch
+ *     array of ss_length_regulate_noalloc;
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), nothing synchronises
  *     unless stated;
  *   - return value: SS_OK (0) or a negative ss_status; ss_status_string() names it and
@@ -240,10 +242,12 @@ SS_API int ss_layernorm(const ss_layernorm_params* p, void* stream);
 SS_API int ss_attention_f32(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, int dk,
                             void* stream);
 
-/* The same operation, same arguments and same fp32 accuracy class, on the tensor cores (dk == 32 only - the
- * ReferenceEncoder's 8 heads, modules.py:353): S = Q.K^T and O = P.V are 3xTF32 tcgen05.mma with accumulators
- * in TMEM, operands by TMA, V consumed as an MN-major operand (no transpose), P written by the softmax warps
- * directly in the swizzled layout the MMA reads; output accumulation across key tiles in fp32 registers. */
+/* The same operation, same arguments and same fp32 accuracy class, on the tensor cores, for dk == 32 (the
+ * ReferenceEncoder's 8 heads, modules.py:353) and dk == 128 (Encoder / Decoder, 2 heads); other head sizes return
+ * SS_ERR_UNSUPPORTED (use ss_attention_f32).  S = Q.K^T and O = P.V are 3xTF32 tcgen05.mma with accumulators in TMEM,
+ * K / V streamed by TMA up to the utterance's length, V transposed on chip by the split warps (the MMA wants it
+ * K-major), Q and P held in TMEM as the A operands, softmax statistics and the output accumulation across key tiles in
+ * fp32 registers. */
 SS_API int ss_attention_tc(const float* qkv, const int32_t* lens, float* ctx, int B, int S, int H, int dk,
                            void* stream);
 
@@ -276,6 +280,10 @@ SS_API int ss_predictor_head(const ss_predictor_head_params* p, void* stream);
  * ------------------------------------------------------------------------------------------ */
 SS_API int ss_bucket_embed_add(float* pred, float control, const float* edges, int n_edges, const float* table,
                                float* x, int32_t* idx_out, int B, int L, int C, void* stream);
+/* The same with one control value PER TOKEN, control_vec [B, L] (the fine-control notebook multiplies the prediction by
+ * a [B, L] tensor, notebooks/control.ipynb cells 17-23; model/modules.py:88,99 broadcasts either form). */
+SS_API int ss_bucket_embed_add_v(float* pred, const float* control_vec, const float* edges, int n_edges,
+                                 const float* table, float* x, int32_t* idx_out, int B, int L, int C, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Duration rounding + LengthRegulator, two calls around ONE host read of mel_len_expand:
@@ -294,6 +302,9 @@ SS_API int ss_bucket_embed_add(float* pred, float control, const float* edges, i
  * ------------------------------------------------------------------------------------------ */
 SS_API int ss_duration_scan(const float* log_d, float d_control, float* d_rounded, int32_t* ends,
                             int32_t* mel_len_expand, int32_t* mel_len_sum, int B, int L, void* stream);
+/* ss_duration_scan with a per-token d_control [B, L] (model/modules.py:137-140 with a tensor control). */
+SS_API int ss_duration_scan_v(const float* log_d, const float* d_control_vec, float* d_rounded, int32_t* ends,
+                              int32_t* mel_len_expand, int32_t* mel_len_sum, int B, int L, void* stream);
 SS_API int ss_length_regulate(const float* x, const int32_t* ends, const float* pe, float* out,
                               int32_t* mel2phone, int B, int L, int T, int C, void* stream);
 
@@ -316,7 +327,7 @@ SS_API int ss_length_regulate(const float* x, const int32_t* ends, const float* 
  * (its output buffer is [B, T, C]); an utterance longer than T is cut at T, as F.pad would not allow.
  *
  * Limits and rules:
- *   - B*L <= SS_LR_NOALLOC_MAX_TOKENS, otherwise SS_ERR_UNSUPPORTED (use the two-call form);
+ *   - B*L <= SS_LR_NOALLOC_MAX_TOKENS, L <= 12288 and B <= 65535, otherwise SS_ERR_UNSUPPORTED (use the two-call form);
  *   - no cudaMalloc / cudaFree / allocating library call is made, ever;
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with
  *     that device current) - make that first call outside any stream capture;
@@ -377,6 +388,9 @@ SS_API int ss_reflect_pad(const float* y, float* out, int B, int T, int half, in
  * padding columns (stft.py:76-79); energy [rows] = ||mag||_2 (stft.py:176), may be NULL */
 SS_API int ss_stft_magnitude(const float* spec, float* mag, float* energy, int64_t rows, int n_bins, int spec_stride,
                              int mag_stride, void* stream);
+/* *flag |= 1 if any y[i] is outside [lo, hi] or NaN (the `assert torch.min(y) >= -1 and torch.max(y) <= 1` of
+ * stft.py:168-169 as one pass with one 4-byte read-back); the caller zeroes *flag first. */
+SS_API int ss_range_flag(const float* y, int64_t n, float lo, float hi, int32_t* flag, void* stream);
 /* x[i] = log(max(x[i], clip))  in place (audio_processing.py:85-91, C = 1) */
 SS_API int ss_log_clamp(float* x, int64_t n, float clip, void* stream);
 

@@ -82,7 +82,9 @@ _SIGNATURES = {
     "ss_attention_tc": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_predictor_head": (C.c_int, [C.POINTER(PredictorHeadParams), vp]),
     "ss_bucket_embed_add": (C.c_int, [vp, f32, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_bucket_embed_add_v": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "ss_duration_scan": (C.c_int, [vp, f32, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
+    "ss_duration_scan_v": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
     "ss_length_regulate": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_length_regulate_noalloc": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_length_mask": (C.c_int, [vp, vp, C.c_int, C.c_int, vp]),
@@ -93,6 +95,7 @@ _SIGNATURES = {
     "ss_hifigan_post": (C.c_int, [vp, vp, vp, vp, vp, f32, f32, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_reflect_pad": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "ss_stft_magnitude": (C.c_int, [vp, vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp]),
+    "ss_range_flag": (C.c_int, [vp, i64, f32, f32, vp, vp]),
     "ss_log_clamp": (C.c_int, [vp, C.c_int64, f32, vp]),
     "ss_hifigan_post_trim": (C.c_int, [vp, vp, vp, vp, vp, vp, f32, f32, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
 }

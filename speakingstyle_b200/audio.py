@@ -60,9 +60,14 @@ class STFT(nn.Module):
         cutoff = filter_length // 2 + 1
         ang = 2.0 * np.pi * np.outer(np.arange(cutoff), n) / filter_length
         basis = np.vstack([np.cos(ang), -np.sin(ang)])  # rows of fft(eye): real part, then imaginary part
+        inverse = np.linalg.pinv(filter_length / hop_length * basis).T  # audio/stft.py:33-35 (inverse transform: unused here)
         basis = torch.from_numpy(basis[:, None, :]).float()
         basis = basis * torch.from_numpy(0.5 - 0.5 * np.cos(2.0 * np.pi * n / win_length)).float()  # periodic hann
         self.register_buffer("forward_basis", basis)
+        # the reference also registers the windowed pseudo-inverse basis of its inverse transform (audio/stft.py:33-49);
+        # it is not used on this path, but the buffer is kept so that state_dicts are interchangeable (strict=True)
+        self.register_buffer("inverse_basis", torch.from_numpy(inverse[:, None, :]).float()
+                             * torch.from_numpy(0.5 - 0.5 * np.cos(2.0 * np.pi * n / win_length)).float())
         self._packed = None
 
     def _weights(self):
@@ -131,12 +136,13 @@ class TacotronSTFT(nn.Module):
     def mel_spectrogram(self, y, channels_last=False):
         """y [B, T] float in [-1, 1] on the device -> (log-mel [B, n_mel, F], energy [B, F]); channels_last=True
         returns the mel as [B, F, n_mel], the layout FastSpeech2.forward takes its reference mels in."""
-        if float(y.min()) < -1 or float(y.max()) > 1:  # stft.py:168-169
-            raise AssertionError("mel_spectrogram: wave must be in [-1, 1]")
-        mag, energy = self.stft_fn._magnitude(y)
-        mel = ops.conv1d(mag, self._weights(mag.shape[-1]), None)  # [B, F, n_mel]
-        ops.log_clamp_(mel, 1e-5)
-        return (mel if channels_last else mel.transpose(1, 2)), energy
+        with torch.cuda.device(y.device):  # launches go to the wave's own device, whatever the current one is
+            if ops.out_of_range(y.contiguous(), -1.0, 1.0):  # stft.py:168-169
+                raise AssertionError("mel_spectrogram: wave must be in [-1, 1]")
+            mag, energy = self.stft_fn._magnitude(y)
+            mel = ops.conv1d(mag, self._weights(mag.shape[-1]), None)  # [B, F, n_mel]
+            ops.log_clamp_(mel, 1e-5)
+            return (mel if channels_last else mel.transpose(1, 2)), energy
 
 
 def get_mel_from_wav(audio, _stft):

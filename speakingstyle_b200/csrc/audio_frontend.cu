@@ -51,6 +51,22 @@ __global__ void log_clamp_kernel(float* __restrict__ x, int64_t n, float clip) {
 
 }  // namespace
 
+// *flag |= 1 if any y[i] lies outside [lo, hi] (NaN counts as outside); flag must be zeroed by the caller
+__global__ void __launch_bounds__(256) range_flag_kernel(const float* __restrict__ y, int64_t n, float lo, float hi,
+                                                         int32_t* __restrict__ flag) {
+  const int64_t base = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+  bool bad = false;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int64_t i = base + k * 256;
+    if (i < n) {
+      const float v = y[i];
+      bad |= !(v >= lo && v <= hi);
+    }
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
 extern "C" int ss_reflect_pad(const float* y, float* out, int B, int T, int half, int n_out, void* stream) {
   SS_REQUIRE(y && out, SS_ERR_INVALID, "ss_reflect_pad: null pointer");
   SS_REQUIRE(B > 0 && B <= 65535 && T > half && half >= 0 && n_out > 0 && n_out <= T + 2 * half, SS_ERR_INVALID,
@@ -72,6 +88,15 @@ extern "C" int ss_stft_magnitude(const float* spec, float* mag, float* energy, i
   stft_magnitude_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(spec, mag, energy, rows, n_bins, spec_stride,
                                                                           mag_stride);
   SS_CHECK_LAUNCH("ss_stft_magnitude");
+  return SS_OK;
+}
+
+extern "C" int ss_range_flag(const float* y, int64_t n, float lo, float hi, int32_t* flag, void* stream) {
+  SS_REQUIRE(y && flag && n > 0, SS_ERR_INVALID, "ss_range_flag: bad arguments");
+  const int64_t blocks = (n + 1023) / 1024;
+  SS_REQUIRE(blocks < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_range_flag: too many elements");
+  range_flag_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(y, n, lo, hi, flag);
+  SS_CHECK_LAUNCH("ss_range_flag");
   return SS_OK;
 }
 

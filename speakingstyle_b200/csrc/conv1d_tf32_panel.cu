@@ -18,8 +18,17 @@
 //     loaded once per CTA; otherwise they stream through a ring as before.
 // Per 128-row tile that is 18-23 KB (32 ch) / 37-400 KB (64 ch) of TMA traffic instead of 264 / 704 KB.
 //
-// Warps: TMA, MMA, 4 epilogue, 8 split (two per TMEM lane group, half a row each).  TMEM: main accumulator x2 |
-// correction accumulator x2 | four A slots of (32 hi + 32 lo) columns.
+//   * the MMA-issuing thread, not the tensor pipe, paced the narrow tiles (an N = 32 MMA is 16 cycles of tensor work; a
+//     microbenchmark, scripts/mma_rate_probe.py, shows the pipe itself runs back-to-back N = 32 TS-form MMAs at full
+//     rate, while the kernel's issue loop with its per-chunk barrier round trips needed ~50 cycles per MMA).  So per
+//     K-step the products hi*W_hi and hi*W_lo are ONE instruction with N = 2*BN (W_hi and W_lo tiles are adjacent in
+//     shared memory and form one [2*BN x 32] operand; the accumulator is [main | correction], 2*BN columns), followed by
+//     lo*W_hi into the correction half: 8 instructions per chunk instead of 12, and one operand hand-over covers TWO
+//     (tap, chunk) steps.  Main and correction accumulators are restarted together every k_group chunks and summed in
+//     registers by the epilogue, so results differ from conv1d_tf32_ts.cu in the last bits (same error class).
+//
+// Warps: TMA, MMA, 4 epilogue, 8 split (two per TMEM lane group, half a row each).  TMEM: [main | correction] x2 |
+// two A slots of 2 x (32 hi + 32 lo) columns.
 #include "tc_common.cuh"
 
 namespace {
@@ -29,11 +38,12 @@ using namespace sstc;
 constexpr int KCHUNK = 32;
 constexpr int XF_WARPS = 8;
 constexpr int NTHREADS = 32 * (6 + XF_WARPS);
-constexpr int A_SLOTS = 4;
-constexpr int A_SLOT_COLS = 2 * KCHUNK;  // hi | lo
+constexpr int MAX_A_SLOTS = 3;
+constexpr int A_STEPS = 2;                         // (tap, chunk) steps per operand hand-over
+constexpr int A_SLOT_COLS = A_STEPS * 2 * KCHUNK;  // [hi | lo] per step
 constexpr int W_RING = 4;                // weight ring depth when the weights are streamed
 constexpr int MAX_PAN = 4;               // activation panel ring depth (upper bound)
-constexpr int N_BARS = 2 * MAX_PAN + 2 * W_RING + 1 + 2 * A_SLOTS + 8;
+constexpr int N_BARS = 2 * MAX_PAN + 2 * W_RING + 1 + 2 * MAX_A_SLOTS + 4;
 constexpr int MAX_SMEM = 227 * 1024;
 
 struct PanelArgs {
@@ -44,18 +54,18 @@ struct PanelArgs {
   int32_t nchunk;
 };
 
-__device__ __forceinline__ float tf32_rn(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
+// Debug build (-DSS_PANEL_TRACE, scripts/panel_trace.py): CTA 0 stamps clock64() per operand hand-over.
+#ifdef SS_PANEL_TRACE
+__device__ long long g_panel_trace[8 * 256];
+#define PANEL_TRACE(ev, i)                                                        \
+  do {                                                                            \
+    if (blockIdx.x == 0 && (i) < 256) g_panel_trace[(ev) * 256 + (i)] = clock64(); \
+  } while (0)
+#else
+#define PANEL_TRACE(ev, i)
+#endif
 
-__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "r"(tmem_a), "l"(db), "r"(idesc), "r"(accum)
-      : "memory");
-}
+__device__ __forceinline__ float tf32_rn(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
 
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
   asm volatile(
@@ -75,8 +85,11 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                          const float in_slope, const int group) {
   constexpr int B_BYTES = BN * ROW_BYTES;  // one weight tile (hi or lo) of one (tap, chunk)
   constexpr int WT = 2 * B_BYTES;          // hi + lo
-  constexpr int A_COL0 = 4 * BN;           // after main0, main1, corr0, corr1
+  constexpr int A_COL0 = 4 * BN;           // after [main | corr] x 2
+  constexpr int A_SLOTS = (512 - A_COL0) / A_SLOT_COLS;  // 3 at BN = 32, 2 at BN = 64
+  static_assert(A_SLOTS >= 2 && A_SLOTS <= MAX_A_SLOTS, "operand slots");
   static_assert(A_COL0 + A_SLOTS * A_SLOT_COLS <= 512, "TMEM budget");
+  static_assert(2 * BN <= 256 && BN % 8 == 0, "[W_hi ; W_lo] must be one legal MMA operand");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
@@ -90,9 +103,8 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   float* stg_all = reinterpret_cast<float*>(smem_al + stg_off);
   const uint32_t bars = smem0 + bar_off;
   const uint32_t pfull0 = bars, pempty0 = pfull0 + 8 * MAX_PAN, wfull0 = pempty0 + 8 * MAX_PAN, wempty0 = wfull0 + 8 * W_RING,
-                 wres = wempty0 + 8 * W_RING, tafull0 = wres + 8, taempty0 = tafull0 + 8 * A_SLOTS,
-                 tfull0 = taempty0 + 8 * A_SLOTS, tempty0 = tfull0 + 16, cfull0 = tempty0 + 16, cempty0 = cfull0 + 16,
-                 tslot = cempty0 + 16;
+                 wres = wempty0 + 8 * W_RING, tafull0 = wres + 8, taempty0 = tafull0 + 8 * MAX_A_SLOTS,
+                 tfull0 = taempty0 + 8 * MAX_A_SLOTS, tempty0 = tfull0 + 16, tslot = tempty0 + 16;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + bar_off + N_BARS * 8);
   int* const rag = reinterpret_cast<int*>(smem_al + bar_off + N_BARS * 8 + 16);
 
@@ -113,15 +125,13 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       mbar_init(wempty0 + 8 * s, 1);
     }
     mbar_init(wres, 1);
-    for (int t = 0; t < A_SLOTS; ++t) {
+    for (int t = 0; t < MAX_A_SLOTS; ++t) {
       mbar_init(tafull0 + 8 * t, XF_WARPS);
       mbar_init(taempty0 + 8 * t, 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull0 + 8 * a, 1);
       mbar_init(tempty0 + 8 * a, 4);
-      mbar_init(cfull0 + 8 * a, 1);
-      mbar_init(cempty0 + 8 * a, 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -182,43 +192,52 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (elect_one()) {
-      const uint32_t idesc = make_idesc(2u, BN);  // tf32 x tf32 -> f32
+      const uint32_t idesc2 = make_idesc(2u, 2 * BN);  // hi x [W_hi ; W_lo] -> [main | corr]
+      const uint32_t idesc1 = make_idesc(2u, BN);      // lo x W_hi -> corr
+      const uint32_t w_lo0 = desc_lo(smem0 + w_off);   // descriptor low word of weight tile 0; tile t is + t * (WT >> 4)
       int slot = 0, ws = 0;
       uint32_t sphase = 0, wphase = 0;
-      int local = 0, gcount = 0;
+      int gcount = 0;
+      [[maybe_unused]] int hcount = 0;
       if (q.w_resident) mbar_wait(wres, 0);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-        const int cs = local & 1;
-        mbar_wait(cempty0 + 8 * cs, ((local >> 1) & 1) ^ 1);  // the epilogue has drained this correction accumulator
-        const uint32_t c_tmem = tmem_base + (2 + cs) * BN;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int it = 0;
         for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
           const int as = gcount & 1;
-          mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);
+          mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator pair
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + as * BN;
+          const uint32_t d_tmem = tmem_base + as * 2 * BN;
           const int it1 = min(it0 + group, KT);
-          for (int it = it0; it < it1; ++it) {
-            mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of this (tap, chunk) are in TMEM
-            if (!q.w_resident) mbar_wait(wfull0 + 8 * ws, wphase);
+          // hand-overs never straddle a group: group is even (host) or the tile ends
+          while (it < it1) {
+            const int steps = min(A_STEPS, it1 - it);
+            PANEL_TRACE(0, hcount);
+            mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of these steps are in TMEM
             tc_fence_after();
-            const uint32_t a_hi = tmem_base + A_COL0 + slot * A_SLOT_COLS, a_lo = a_hi + KCHUNK;
-            const uint32_t b_hi = smem0 + w_off + (q.w_resident ? it : ws) * WT, b_lo = b_hi + B_BYTES;
+            PANEL_TRACE(1, hcount);
+            for (int sidx = 0; sidx < steps; ++sidx, ++it) {
+              if (!q.w_resident) {
+                mbar_wait(wfull0 + 8 * ws, wphase);
+                tc_fence_after();
+              }
+              const uint32_t a_hi = tmem_base + A_COL0 + slot * A_SLOT_COLS + sidx * 2 * KCHUNK, a_lo = a_hi + KCHUNK;
+              const uint32_t bw = w_lo0 + (uint32_t)(q.w_resident ? it : ws) * (uint32_t)(WT >> 4);
 #pragma unroll
-            for (int kk = 0; kk < KCHUNK / 8; ++kk) {
-              umma_tf32_ts(c_tmem, a_lo + kk * 8, make_desc(b_hi + kk * 32), idesc, (it | kk) != 0);
-              umma_tf32_ts(c_tmem, a_hi + kk * 8, make_desc(b_lo + kk * 32), idesc, 1u);
-              umma_tf32_ts(d_tmem, a_hi + kk * 8, make_desc(b_hi + kk * 32), idesc, ((it - it0) | kk) != 0);
+              for (int kk = 0; kk < KCHUNK / 8; ++kk) {  // K = 8 tf32 per instruction: 8 TMEM columns / 32 bytes of B
+                umma_tf32_ts_w(d_tmem, a_hi + kk * 8, bw + kk * 2, idesc2, ((it - it0) | kk) != 0);
+                umma_tf32_ts_w(d_tmem + BN, a_lo + kk * 8, bw + kk * 2, idesc1, 1u);
+              }
+              if (!q.w_resident) {
+                umma_commit(wempty0 + 8 * ws);
+                if (++ws == W_RING) { ws = 0; wphase ^= 1; }
+              }
             }
             umma_commit(taempty0 + 8 * slot);
-            if (!q.w_resident) {
-              umma_commit(wempty0 + 8 * ws);
-              if (++ws == W_RING) { ws = 0; wphase ^= 1; }
-            }
+            PANEL_TRACE(2, hcount); ++hcount;
             if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
           }
           umma_commit(tfull0 + 8 * as);
         }
-        umma_commit(cfull0 + 8 * cs);
       }
     }
   } else if (warp < 6) {
@@ -226,8 +245,8 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int lg = warp & 3;
     float* stg = stg_all + lg * 32 * STG_PITCH;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
-    int local = 0, gcount = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+    int gcount = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int mt, b;
       decode(tile, mt, b);
       const int t_tile0 = mt * BM;
@@ -245,30 +264,15 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
       for (int i = 0; i < BN; ++i) acc[i] = 0.f;
       for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
-        if (it0 + group >= KT) {  // last group: the correction terms finish with it - take them first
-          const int cs = local & 1;
-          mbar_wait(cfull0 + 8 * cs, (local >> 1) & 1);
-          tc_fence_after();
-#pragma unroll
-          for (int c0 = 0; c0 < BN; c0 += 32) {
-            float v[32];
-            tmem_ld32(lane_base + (2 + cs) * BN + c0, v);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];
-          }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(cempty0 + 8 * cs);
-        }
         const int as = gcount & 1;
         mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int c0 = 0; c0 < BN; c0 += 32) {
-          float v[32];
-          tmem_ld32(lane_base + as * BN + c0, v);
+          float v[32], w[32];
+          tmem_ld32x2(lane_base + as * 2 * BN + c0, v, lane_base + as * 2 * BN + BN + c0, w);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];  // round-to-nearest fp32 adds
+          for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i] + w[i];  // round-to-nearest fp32 adds: main + correction
         }
         tc_fence_before();
         __syncwarp();
@@ -293,43 +297,61 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16) + A_COL0;
     int ps = 0, slot = 0;
     uint32_t pphase = 0, sphase = 0;
+    [[maybe_unused]] int hcount = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      if (threadIdx.x == 192) PANEL_TRACE(6, hcount);
       mbar_wait(pfull0 + 8 * ps, pphase);
+      if (threadIdx.x == 192) PANEL_TRACE(7, hcount);
       const uint8_t* pan = smem_al + ps * pan_stage;
       int prow = r, c = 0;  // panel row of this output row for the current tap (tap j reads row r + j*dilation)
-      for (int it = 0; it < KT; ++it) {
-        const uint8_t* row = pan + c * q.panel_bytes + prow * ROW_BYTES;
-        const int sw = prow & 7;  // SWIZZLE_128B: 16-byte unit u of a row sits at unit (u ^ (row & 7)); panels are 1024-aligned
-        if (++c == nchunk) { c = 0; prow += p.dilation; }
-        float hi[16], lo[16];
+      for (int it = 0; it < KT; it += A_STEPS) {
+        const int steps = min(A_STEPS, KT - it);  // the MMA issuer cuts hand-overs the same way (group is even)
+        float hi[A_STEPS][16], lo[A_STEPS][16];
 #pragma unroll
-        for (int uu = 0; uu < 4; ++uu) {
-          const int u = xhalf * 4 + uu;
-          float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
-          if (in_act == SS_ACT_LRELU) {
-            x.x = x.x > 0.f ? x.x : x.x * in_slope;
-            x.y = x.y > 0.f ? x.y : x.y * in_slope;
-            x.z = x.z > 0.f ? x.z : x.z * in_slope;
-            x.w = x.w > 0.f ? x.w : x.w * in_slope;
+        for (int sidx = 0; sidx < A_STEPS; ++sidx) {
+          if (sidx < steps) {
+            const uint8_t* row = pan + c * q.panel_bytes + prow * ROW_BYTES;
+            const int sw = prow & 7;  // SWIZZLE_128B: 16-byte unit u of a row sits at unit (u ^ (row & 7)); panels are 1024-aligned
+            if (++c == nchunk) { c = 0; prow += p.dilation; }
+#pragma unroll
+            for (int uu = 0; uu < 4; ++uu) {
+              const int u = xhalf * 4 + uu;
+              float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+              if (in_act == SS_ACT_LRELU) {
+                x.x = x.x > 0.f ? x.x : x.x * in_slope;
+                x.y = x.y > 0.f ? x.y : x.y * in_slope;
+                x.z = x.z > 0.f ? x.z : x.z * in_slope;
+                x.w = x.w > 0.f ? x.w : x.w * in_slope;
+              }
+              // lo is handed over unrounded: the MMA truncates an fp32 operand to TF32 itself (see conv1d_tf32_ts.cu)
+              hi[sidx][4 * uu + 0] = tf32_rn(x.x); lo[sidx][4 * uu + 0] = x.x - hi[sidx][4 * uu + 0];
+              hi[sidx][4 * uu + 1] = tf32_rn(x.y); lo[sidx][4 * uu + 1] = x.y - hi[sidx][4 * uu + 1];
+              hi[sidx][4 * uu + 2] = tf32_rn(x.z); lo[sidx][4 * uu + 2] = x.z - hi[sidx][4 * uu + 2];
+              hi[sidx][4 * uu + 3] = tf32_rn(x.w); lo[sidx][4 * uu + 3] = x.w - hi[sidx][4 * uu + 3];
+            }
           }
-          // lo is handed over unrounded: the MMA truncates an fp32 operand to TF32 itself (see conv1d_tf32_ts.cu)
-          hi[4 * uu + 0] = tf32_rn(x.x); lo[4 * uu + 0] = x.x - hi[4 * uu + 0];
-          hi[4 * uu + 1] = tf32_rn(x.y); lo[4 * uu + 1] = x.y - hi[4 * uu + 1];
-          hi[4 * uu + 2] = tf32_rn(x.z); lo[4 * uu + 2] = x.z - hi[4 * uu + 2];
-          hi[4 * uu + 3] = tf32_rn(x.w); lo[4 * uu + 3] = x.w - hi[4 * uu + 3];
         }
-        if (it == KT - 1) {  // this warp has read its last row of the panel: hand it back to the TMA producer
+        if (threadIdx.x == 192) PANEL_TRACE(3, hcount);
+        if (it + steps >= KT) {  // this warp has read its last row of the panel: hand it back to the TMA producer
           __syncwarp();
           if (lane == 0) mbar_arrive(pempty0 + 8 * ps);
         }
         mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
         tc_fence_after();
-        tmem_st16(lane_base + slot * A_SLOT_COLS + xhalf * 16, hi);
-        tmem_st16(lane_base + slot * A_SLOT_COLS + KCHUNK + xhalf * 16, lo);
+        if (threadIdx.x == 192) PANEL_TRACE(4, hcount);
+#pragma unroll
+        for (int sidx = 0; sidx < A_STEPS; ++sidx) {
+          if (sidx < steps) {
+            tmem_st16(lane_base + slot * A_SLOT_COLS + sidx * 2 * KCHUNK + xhalf * 16, hi[sidx]);
+            tmem_st16(lane_base + slot * A_SLOT_COLS + sidx * 2 * KCHUNK + KCHUNK + xhalf * 16, lo[sidx]);
+          }
+        }
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tafull0 + 8 * slot);
+        if (threadIdx.x == 192) PANEL_TRACE(5, hcount);
+        ++hcount;
         if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
       }
       if (++ps == q.n_pan) { ps = 0; pphase ^= 1; }
@@ -405,6 +427,12 @@ int launch(const ss_conv1d_tf32_params* p, const TcArgs& a0, int group, cudaStre
 
 }  // namespace
 
+#ifdef SS_PANEL_TRACE
+extern "C" __attribute__((visibility("default"))) int ss_debug_panel_trace(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_panel_trace, sizeof(long long) * 8 * 256);
+}
+#endif
+
 // 1 if ss_conv1d_tf32x3_panel takes this layer: stride-1 same-length convolution with at least two taps, at most 64
 // input and output channels (whole 32-channel chunks in), a halo that fits one TMA box, plain fp32 output path.
 extern "C" int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p) {
@@ -443,7 +471,7 @@ extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stre
   a.act = p->act; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   a.flat = 0; a.S_in = p->S_in; a.rows = p->rows;
-  const int group = p->k_group > 0 ? p->k_group : 8;
+  const int group = ((p->k_group > 0 ? p->k_group : 8) + 1) & ~1;  // even: operand hand-overs cover two steps
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return p->Cout > 32 ? launch<64>(p, a, group, st) : launch<32>(p, a, group, st);
 }

@@ -20,6 +20,7 @@ __device__ __forceinline__ float round_duration(float log_d, float control) {
 }
 
 __global__ void __launch_bounds__(128) duration_scan_kernel(const float* __restrict__ log_d, float control,
+                                                            const float* __restrict__ control_vec,
                                                             float* __restrict__ d_rounded,
                                                             int32_t* __restrict__ ends,
                                                             int32_t* __restrict__ mel_len_expand,
@@ -28,6 +29,7 @@ __global__ void __launch_bounds__(128) duration_scan_kernel(const float* __restr
   if (b >= B) return;
   const int lane = threadIdx.x & 31;
   const float* ld = log_d ? log_d + (int64_t)b * L : nullptr;
+  const float* cv = control_vec ? control_vec + (int64_t)b * L : nullptr;  // per-token d_control (modules.py:137-140)
   float* dr = d_rounded + (int64_t)b * L;
   int32_t* eb = ends + (int64_t)b * L;
   int carry = 0;
@@ -37,7 +39,7 @@ __global__ void __launch_bounds__(128) duration_scan_kernel(const float* __restr
     if (l < L) {
       float d;
       if (ld) {
-        d = round_duration(ld[l], control);
+        d = round_duration(ld[l], cv ? cv[l] : control);
         dr[l] = d;
       } else {
         d = dr[l];
@@ -58,7 +60,7 @@ __global__ void __launch_bounds__(128) duration_scan_kernel(const float* __restr
     if (mel_len_sum) {
       // float32 running sum in index order, then .int() (modules.py:143)
       float s = 0.0f;
-      for (int l = 0; l < L; ++l) s += ld ? round_duration(ld[l], control) : dr[l];
+      for (int l = 0; l < L; ++l) s += ld ? round_duration(ld[l], cv ? cv[l] : control) : dr[l];
       mel_len_sum[b] = (int32_t)s;
     }
   }
@@ -139,8 +141,19 @@ int ss_duration_scan(const float* log_d, float d_control, float* d_rounded, int3
   SS_REQUIRE(B > 0 && L > 0, SS_ERR_INVALID, "ss_duration_scan: bad shape B=%d L=%d", B, L);
   const int warps = 4;
   duration_scan_kernel<<<(B + warps - 1) / warps, warps * 32, 0, (cudaStream_t)stream>>>(
-      log_d, d_control, d_rounded, ends, mel_len_expand, mel_len_sum, B, L);
+      log_d, d_control, nullptr, d_rounded, ends, mel_len_expand, mel_len_sum, B, L);
   SS_CHECK_LAUNCH("ss_duration_scan");
+  return SS_OK;
+}
+
+int ss_duration_scan_v(const float* log_d, const float* d_control_vec, float* d_rounded, int32_t* ends,
+                       int32_t* mel_len_expand, int32_t* mel_len_sum, int B, int L, void* stream) {
+  SS_REQUIRE(log_d && d_control_vec && d_rounded && ends, SS_ERR_INVALID, "ss_duration_scan_v: null pointer");
+  SS_REQUIRE(B > 0 && L > 0, SS_ERR_INVALID, "ss_duration_scan_v: bad shape B=%d L=%d", B, L);
+  const int warps = 4;
+  duration_scan_kernel<<<(B + warps - 1) / warps, warps * 32, 0, (cudaStream_t)stream>>>(
+      log_d, 1.0f, d_control_vec, d_rounded, ends, mel_len_expand, mel_len_sum, B, L);
+  SS_CHECK_LAUNCH("ss_duration_scan_v");
   return SS_OK;
 }
 
@@ -241,7 +254,7 @@ extern "C" int ss_length_regulate_noalloc(const float* x, const float* durations
   // Every prefix sum this call reads ([0, B*L)) is written by the scan first, so nothing in the
   // array has to be cleared; whatever an earlier call left beyond B*L is never looked at.
   const int warps = 4;
-  duration_scan_kernel<<<(B + warps - 1) / warps, warps * 32, 0, st>>>(nullptr, 1.0f, const_cast<float*>(durations),
+  duration_scan_kernel<<<(B + warps - 1) / warps, warps * 32, 0, st>>>(nullptr, 1.0f, nullptr, const_cast<float*>(durations),
                                                                       prefix, mel_len, nullptr, B, L);
   SS_CHECK_LAUNCH("ss_length_regulate_noalloc (scan)");
   if (T == 0) return SS_OK;

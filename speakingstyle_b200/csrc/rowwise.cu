@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(256) predictor_head_kernel(const ss_predictor_
 
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) bucket_embed_add_kernel(float* __restrict__ pred, float control,
+                                                               const float* __restrict__ control_vec,
                                                                const float* __restrict__ edges, int n_edges,
                                                                const float* __restrict__ table,
                                                                float* __restrict__ x, int32_t* __restrict__ idx_out,
@@ -173,7 +174,7 @@ __global__ void __launch_bounds__(256) bucket_embed_add_kernel(float* __restrict
   const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
-  const float v = pred[row] * control;
+  const float v = pred[row] * (control_vec ? control_vec[row] : control);  // modules.py:88,99: prediction * control
   // lower bound: first edge that is >= v; NaN fails every comparison and ends at n_edges
   int lo = 0, hi = n_edges;
   while (lo < hi) {
@@ -358,13 +359,24 @@ int ss_predictor_head(const ss_predictor_head_params* p, void* stream) {
   return SS_OK;
 }
 
+int ss_bucket_embed_add_v(float* pred, const float* control_vec, const float* edges, int n_edges, const float* table,
+                          float* x, int32_t* idx_out, int B, int L, int C, void* stream) {
+  SS_REQUIRE(pred && control_vec && edges && table && x, SS_ERR_INVALID, "ss_bucket_embed_add_v: null pointer");
+  SS_REQUIRE(B > 0 && L > 0 && C > 0 && C % 4 == 0 && n_edges > 0 && n_edges <= 1024, SS_ERR_INVALID,
+             "ss_bucket_embed_add_v: bad shape");
+  bucket_embed_add_kernel<<<row_grid((int64_t)B * L), 256, n_edges * sizeof(float), (cudaStream_t)stream>>>(
+      pred, 1.0f, control_vec, edges, n_edges, table, x, idx_out, B * L, C);
+  SS_CHECK_LAUNCH("ss_bucket_embed_add_v");
+  return SS_OK;
+}
+
 int ss_bucket_embed_add(float* pred, float control, const float* edges, int n_edges, const float* table, float* x,
                         int32_t* idx_out, int B, int L, int C, void* stream) {
   SS_REQUIRE(pred && edges && table && x, SS_ERR_INVALID, "ss_bucket_embed_add: null pointer");
   SS_REQUIRE(B > 0 && L > 0 && C > 0 && C % 4 == 0 && n_edges > 0 && n_edges <= 1024, SS_ERR_INVALID,
              "ss_bucket_embed_add: bad shape");
   bucket_embed_add_kernel<<<row_grid((int64_t)B * L), 256, n_edges * sizeof(float), (cudaStream_t)stream>>>(
-      pred, control, edges, n_edges, table, x, idx_out, B * L, C);
+      pred, control, nullptr, edges, n_edges, table, x, idx_out, B * L, C);
   SS_CHECK_LAUNCH("ss_bucket_embed_add");
   return SS_OK;
 }

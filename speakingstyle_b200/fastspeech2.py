@@ -83,9 +83,21 @@ class FastSpeech2(nn.Module, ParamCache):
     def forward(self, speakers, texts, src_lens, max_src_len, mels=None, mel_lens=None, max_mel_len=None,
                 p_targets=None, e_targets=None, d_targets=None, p_control=1.0, e_control=1.0, d_control=1.0,
                 return_extra=False):
+        """model/fastspeech2.py:44-120.  p_control / e_control / d_control: numbers, or tensors with one value per
+        phoneme ([B, L], the fine-control use of notebooks/control.ipynb)."""
         dev = self.device
         if dev.type != "cuda":
             raise RuntimeError("speakingstyle_b200.FastSpeech2 needs a CUDA device (.to('cuda')); no CPU fallback")
+        # the library launches on cudart's CURRENT device and torch's current stream of that device: make the model's
+        # own device current for the duration of the call (a model on cuda:1 with device 0 current would otherwise
+        # launch on GPU 0 with GPU 1 pointers)
+        with torch.cuda.device(dev):
+            return self._forward(speakers, texts, src_lens, max_src_len, mels, mel_lens, max_mel_len, p_targets,
+                                 e_targets, d_targets, p_control, e_control, d_control, return_extra)
+
+    def _forward(self, speakers, texts, src_lens, max_src_len, mels, mel_lens, max_mel_len, p_targets, e_targets,
+                 d_targets, p_control, e_control, d_control, return_extra):
+        dev = self.device
         if mels is None or mel_lens is None:
             # the reference dereferences mel_masks / mask unconditionally (fastspeech2.py:79, modules.py:384)
             raise AttributeError("a reference mel (mels, mel_lens, max_mel_len) is mandatory at inference")
@@ -122,10 +134,10 @@ class FastSpeech2(nn.Module, ParamCache):
         T = extra["T"]
         if d_targets is not None:
             # teacher forcing: the decoder mask is the reference mel's mask (fastspeech2.py:62-66, modules.py:133-135)
-            dec_lens = torch.clamp(ref_lens32, max=T)
+            dec_lens = ref_lens32  # every kernel clamps lengths to its own row count
         else:
             # decoder key mask = mask from mel_len cropped to the expanded length (Models.py:154-162)
-            dec_lens = torch.clamp(mel_lens_out, max=T) if mel_masks.shape[1] != T else mel_lens_out
+            dec_lens = mel_lens_out  # may exceed T with d_control != 1; every kernel clamps lengths to its own row count
             if mel_masks.shape[1] != T:
                 mel_masks = ops.length_mask(dec_lens, T)
         inv_lens = dec_lens if self.batch_invariant else None  # zero the padded mel frames (mel_linear's bias)

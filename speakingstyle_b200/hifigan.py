@@ -173,17 +173,18 @@ class Generator(nn.Module, ParamCache):
         rows.update({("up", i): t[len(rates) + i] for i in range(len(rates) - 1)})
         return rows
 
-    def _post(self, xs, pk, pcm, pcm_out):
+    def _post(self, xs, pk, pcm, pcm_out, pcm_scale=32768.0):
         """Output head.  pcm_out = (n_samples [B] int32 dev, out_offset [B] int64 dev, flat int16 buffer): ragged PCM
         straight into that buffer (ss_hifigan_post_trim) instead of the padded float wave."""
         if pcm_out is not None:
-            return ops.hifigan_post_trim(xs, pk["post"], self.conv_post.bias, *pcm_out, k=7, in_slope=0.01)
+            return ops.hifigan_post_trim(xs, pk["post"], self.conv_post.bias, *pcm_out, k=7, in_slope=0.01,
+                                         pcm_scale=pcm_scale)
         wave, pcm16 = ops.hifigan_post(xs, pk["post"], self.conv_post.bias, k=7, in_slope=0.01, want_wave=True,
-                                       want_pcm=pcm)
+                                       want_pcm=pcm, pcm_scale=pcm_scale)
         wave = wave.unsqueeze(1)
         return (wave, pcm16) if pcm else wave
 
-    def _forward_bf16(self, x, pcm, pcm_out=None, rows=None):
+    def _forward_bf16(self, x, pcm, pcm_out=None, rows=None, pcm_scale=32768.0):
         """Tensor-core path.  Convolution operands are bf16; the residual stream of every ResBlock and
         the stage mean stay fp32.  Each epilogue also emits the leaky-ReLU'd bf16 copy that the next
         convolution consumes (the activation cannot sit between TMA and the MMA)."""
@@ -219,20 +220,27 @@ class Generator(nn.Module, ParamCache):
                                             want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0),
                                             act2=L if feeds_ups else None, slope2=LRELU_SLOPE, rows=rw)[1]
             xa = nxt
-        return self._post(xs, pk, pcm, pcm_out)
+        return self._post(xs, pk, pcm, pcm_out, pcm_scale)
 
     @torch.no_grad()
-    def forward(self, x, channels_last=False, pcm=False, pcm_out=None, frame_lens=None):
+    def forward(self, x, channels_last=False, pcm=False, pcm_out=None, frame_lens=None, pcm_scale=32768.0):
         """x: mel [B,80,T] (reference layout) or [B,T,80] with channels_last=True.
         Returns wave [B,1,256*T] float32; with pcm=True returns (wave, int16 [B,256*T]).
         pcm_out = (n_samples [B] int32, out_offset [B] int64, flat int16 buffer - device or pinned host): the ragged
         PCM epilogue of SURVEY 8(f1); returns that buffer and produces no padded wave.
+        pcm_scale: the int16 full scale (preprocess.yaml audio.max_wav_value, utils/model.py:105-108).
         frame_lens (host ints, one per utterance; only with pcm_out): the utterances' valid mel frames.  The caller
         will only ever look at samples < frame_lens[b]*hop (utils/model.py:109-113), so every layer is run on the rows
         that can reach those samples - frame_lens[b] + halo_frames() frames' worth - instead of on the whole padded
         batch.  The samples that are written are bit-identical to the padded computation."""
         if frame_lens is not None and pcm_out is None:
             raise ValueError("frame_lens (ragged schedule) needs pcm_out: the padded wave would hold uncomputed samples")
+        if not x.is_cuda:
+            raise RuntimeError("speakingstyle_b200 Generator needs CUDA tensors; there is no CPU fallback")
+        with torch.cuda.device(x.device):  # launches go to the tensor's own device, whatever the current one is
+            return self._forward(x, channels_last, pcm, pcm_out, frame_lens, pcm_scale)
+
+    def _forward(self, x, channels_last, pcm, pcm_out, frame_lens, pcm_scale):
         if not x.is_cuda:
             raise RuntimeError("speakingstyle_b200 Generator needs CUDA tensors; there is no CPU fallback")
         h = self.h
@@ -242,7 +250,7 @@ class Generator(nn.Module, ParamCache):
         x = x.to(torch.float32).contiguous()
         rows = self._ragged_rows(frame_lens, x.shape[1], x.device) if frame_lens is not None else None
         if self.precision == "bf16":
-            return self._forward_bf16(x, pcm, pcm_out, rows)
+            return self._forward_bf16(x, pcm, pcm_out, rows, pcm_scale)
         rate = 1
         x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3, rows=rows and rows[rate])
         nk = self.num_kernels
@@ -273,4 +281,4 @@ class Generator(nn.Module, ParamCache):
                                    in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, write_y=False,
                                    accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0), rows=rw)
             x = xs
-        return self._post(x, pk, pcm, pcm_out)
+        return self._post(x, pk, pcm, pcm_out, pcm_scale)

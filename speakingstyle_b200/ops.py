@@ -201,7 +201,10 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         accum_init=int(accum_init), k_group=tf32_k_group, rows=None if rows is None else rows.data_ptr())
     v = variant or tf32_variant
     if v == "auto":
-        if tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2 and _lib.lib().ss_conv1d_tf32x3_panel_supported(C.byref(p)):
+        # the panel kernel wins where the weights of all taps stay resident in shared memory (<= 96 KB of hi + lo: every
+        # 32-channel layer, 64-channel layers with k = 3); with streamed weights the per-tap kernel is as fast or faster
+        if (tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2 and W.k * W.cin * W.cout * 8 <= 96 * 1024
+                and _lib.lib().ss_conv1d_tf32x3_panel_supported(C.byref(p))):
             v = "panel"
         else:
             v = "ts2" if W.k * ((W.cin + 31) // 32) >= 16 else "ts"
@@ -416,14 +419,38 @@ def predictor_head(h, ln_w, ln_b, lin_w, lin_b, *, film=None, lens=None):
     return pred
 
 
+def _control_vec(control, shape, device):
+    """A control given as a tensor / array (one value per token, notebooks/control.ipynb) -> fp32 [B, L] on the device;
+    None for a plain number."""
+    if isinstance(control, (int, float)):
+        return None
+    c = torch.as_tensor(control)
+    if c.numel() == 1:
+        return None
+    c = c.to(device, torch.float32)
+    if tuple(c.shape) != tuple(shape):
+        c = c.expand(shape)  # [L] or [B, 1] broadcast as the reference's `prediction * control` would
+    return c.contiguous()
+
+
+def _control_scalar(control):
+    return float(control) if isinstance(control, (int, float)) else float(torch.as_tensor(control).reshape(-1)[0])
+
+
 def bucket_embed_add(pred, control, edges, table, x, want_idx=False):
-    """In place: pred *= control; x += table[bucketize(pred, edges)].  Returns idx (int32) if asked."""
+    """In place: pred *= control; x += table[bucketize(pred, edges)].  Returns idx (int32) if asked.
+    control: a number, or a tensor with one value per token ([B, L], model/modules.py:88,99)."""
     _chk(pred, torch.float32, "pred"); _chk(edges, torch.float32, "edges"); _chk(table, torch.float32, "table")
     _chk(x, torch.float32, "x")
     B, L, Cc = x.shape
     idx = torch.empty((B, L), dtype=torch.int32, device=x.device) if want_idx else None
-    check(_lib.lib().ss_bucket_embed_add(_ptr(pred), float(control), _ptr(edges), edges.numel(), _ptr(table), _ptr(x),
-                                         _ptr(idx), B, L, Cc, _stream()))
+    cv = _control_vec(control, (B, L), x.device)
+    if cv is not None:
+        check(_lib.lib().ss_bucket_embed_add_v(_ptr(pred), _ptr(cv), _ptr(edges), edges.numel(), _ptr(table), _ptr(x),
+                                               _ptr(idx), B, L, Cc, _stream()))
+    else:
+        check(_lib.lib().ss_bucket_embed_add(_ptr(pred), _control_scalar(control), _ptr(edges), edges.numel(), _ptr(table),
+                                             _ptr(x), _ptr(idx), B, L, Cc, _stream()))
     return idx
 
 
@@ -435,8 +462,13 @@ def duration_scan(log_d, d_control, durations=None):
     d_rounded = torch.empty_like(src) if log_d is not None else durations
     ends = torch.empty((B, L), dtype=torch.int32, device=src.device)
     lens2 = torch.empty((2, B), dtype=torch.int32, device=src.device)
-    check(_lib.lib().ss_duration_scan(_ptr(log_d), float(d_control), _ptr(d_rounded), _ptr(ends), _ptr(lens2[0]),
-                                      _ptr(lens2[1]), B, L, _stream()))
+    cv = _control_vec(d_control, (B, L), src.device) if log_d is not None else None
+    if cv is not None:
+        check(_lib.lib().ss_duration_scan_v(_ptr(log_d), _ptr(cv), _ptr(d_rounded), _ptr(ends), _ptr(lens2[0]),
+                                            _ptr(lens2[1]), B, L, _stream()))
+    else:
+        check(_lib.lib().ss_duration_scan(_ptr(log_d), _control_scalar(d_control), _ptr(d_rounded), _ptr(ends),
+                                          _ptr(lens2[0]), _ptr(lens2[1]), B, L, _stream()))
     return d_rounded, ends, lens2
 
 
@@ -529,6 +561,14 @@ def stft_magnitude(spec, n_bins, want_energy=True):
     energy = torch.empty((B, F), dtype=torch.float32, device=spec.device) if want_energy else None
     check(_lib.lib().ss_stft_magnitude(_ptr(spec), _ptr(mag), _ptr(energy), B * F, int(n_bins), W, ms, _stream()))
     return mag, energy
+
+
+def out_of_range(y, lo=-1.0, hi=1.0):
+    """ss_range_flag: True if any element of y is outside [lo, hi] or NaN (one pass, one 4-byte read-back)."""
+    _chk(y, torch.float32, "y")
+    flag = torch.zeros(1, dtype=torch.int32, device=y.device)
+    check(_lib.lib().ss_range_flag(_ptr(y), y.numel(), float(lo), float(hi), _ptr(flag), _stream()))
+    return bool(flag.item())
 
 
 def log_clamp_(x, clip=1e-5):

@@ -24,11 +24,18 @@ def get_vocoder(h=None, device="cuda", state_dict=None, precision="fp32"):
 
 
 @torch.no_grad()
-def _ragged_pcm(vocoder, mels, n_samples, channels_last, device_out=False):
+def _ragged_pcm(vocoder, mels, n_samples, channels_last, device_out=False, pcm_scale=32768.0):
     """Runs the vocoder with the ragged PCM epilogue writing into pinned host memory; returns one int16 numpy view
     per utterance (no padded wave, no separate D2H copy - the kernel's stores are what crosses PCIe).
     device_out: keep the trimmed waves on the device instead (one flat int16 tensor, returned as per-utterance views,
     no synchronisation) - for callers that post-process on the GPU."""
+    if not mels.is_cuda:
+        raise RuntimeError("speakingstyle_b200 vocoder needs CUDA tensors; there is no CPU fallback")
+    with torch.cuda.device(mels.device):  # launches and the stream synchronisation go to the mel's own device
+        return _ragged_pcm_on_device(vocoder, mels, n_samples, channels_last, device_out, pcm_scale)
+
+
+def _ragged_pcm_on_device(vocoder, mels, n_samples, channels_last, device_out, pcm_scale):
     T = mels.shape[1] if channels_last else mels.shape[2]
     hop = 1
     for u in vocoder.h["upsample_rates"]:
@@ -46,7 +53,7 @@ def _ragged_pcm(vocoder, mels, n_samples, channels_last, device_out=False):
     o_dev = torch.tensor(offs[:-1], dtype=torch.int64).to(dev, non_blocking=True)
     # every layer runs only on the frames that can reach a returned sample (Generator.forward, frame_lens)
     frame_lens = [-(-v // hop) for v in n]
-    vocoder(mels, channels_last=channels_last, pcm_out=(n_dev, o_dev, host), frame_lens=frame_lens)
+    vocoder(mels, channels_last=channels_last, pcm_out=(n_dev, o_dev, host), frame_lens=frame_lens, pcm_scale=pcm_scale)
     if device_out:
         return [host[offs[i]:offs[i + 1]] for i in range(len(n))]
     torch.cuda.current_stream(dev).synchronize()
@@ -62,14 +69,12 @@ def vocoder_infer(mels, vocoder, model_config=None, preprocess_config=None, leng
     scale = 32768.0
     if preprocess_config is not None:
         scale = float(preprocess_config["preprocessing"]["audio"]["max_wav_value"])
-    if scale != 32768.0:
-        raise NotImplementedError("max_wav_value other than 32768 is not wired into the PCM epilogue")
     B, T = mels.shape[0], mels.shape[2]
     hop = 1
     for u in vocoder.h["upsample_rates"]:
         hop *= u
     n = [T * hop] * B if lengths is None else [int(v) for v in lengths]
-    return _ragged_pcm(vocoder, mels, n, channels_last=False)
+    return _ragged_pcm(vocoder, mels, n, channels_last=False, pcm_scale=scale)
 
 
 @torch.no_grad()

@@ -169,9 +169,10 @@ def test_cta_pair_conv_is_bit_identical_to_single_cta(ops, B, S, Cin, Cout, k, d
     (1, 50, 32, 64, 2, 1),      # shorter than a tile, even tap count
     (40, 300, 32, 32, 7, 1),    # more tiles than CTAs: panel / weight ring wrap-around
 ])
-def test_panel_conv_is_bit_identical_to_the_per_tap_kernel(ops, B, S, Cin, Cout, k, dil):
-    """ss_conv1d_tf32x3_panel (activation panel fetched once per tile, shifted rows per tap, resident weights) issues
-    the same MMAs in the same order as ss_conv1d_tf32x3_ts: identical bits, with every epilogue HiFi-GAN uses."""
+def test_panel_conv_matches_the_per_tap_kernel(ops, B, S, Cin, Cout, k, dil):
+    """ss_conv1d_tf32x3_panel (activation panel fetched once per tile, shifted rows per tap, resident weights, hi*W_hi
+    and hi*W_lo as one N = 2*BN instruction) against ss_conv1d_tf32x3_ts: same products, the correction terms summed
+    per accumulator-restart group instead of per tile - equal to ~1 ulp - with every epilogue HiFi-GAN uses."""
     g = torch.Generator().manual_seed(12)
     x = torch.randn(B, S, Cin, generator=g).to(DEV)
     W = ops.pack_conv(torch.randn(Cout, Cin, k, generator=g).to(DEV) / math.sqrt(Cin * k))
@@ -182,12 +183,12 @@ def test_panel_conv_is_bit_identical_to_the_per_tap_kernel(ops, B, S, Cin, Cout,
     for extra in (dict(), dict(residual=res), dict(residual=res, act=ops.ACT_RELU)):
         a = ops.conv1d(x, W, bias, backend="tf32x3_ts", **kw, **extra)
         b = ops.conv1d(x, W, bias, backend="tf32x3_panel", **kw, **extra)
-        assert torch.equal(a, b), extra
+        assert (a - b).abs().max().item() <= 4e-6, extra
     acc_a = torch.full((B, S, Cout), 0.25, device=DEV)
     acc_b = acc_a.clone()
     ops.conv1d(x, W, bias, backend="tf32x3_ts", residual=res, write_y=False, accum=acc_a, accum_scale=1 / 3, **kw)
     ops.conv1d(x, W, bias, backend="tf32x3_panel", residual=res, write_y=False, accum=acc_b, accum_scale=1 / 3, **kw)
-    assert torch.equal(acc_a, acc_b)
+    assert (acc_a - acc_b).abs().max().item() <= 4e-6
     # ragged schedule on the panel kernel
     rows_host = ([S, 0, 1, S // 2 + 3] * 10)[:B]
     rows = torch.tensor(rows_host, dtype=torch.int32, device=DEV)

@@ -127,6 +127,63 @@ def test_frame_level_pitch_energy_vs_golden(golden):
     assert maxabs(out[0][ok], g["mel"][ok.numpy()]) <= TOL and maxabs(out[1][ok], g["postnet_mel"][ok.numpy()]) <= TOL
 
 
+def test_per_phoneme_control_vectors_match_the_oracle():
+    """p_control / e_control / d_control as [B, L] tensors (notebooks/control.ipynb cells 17-23): the reference's
+    `prediction * control` and `round(...) * d_control` broadcast a tensor just as they do a number
+    (model/modules.py:88,99,137-140)."""
+    ds, batch, voc = S.make_workload("tiny")
+    model, mc, sd = get_models(ds)
+    B, L = batch["texts"].shape
+    g = torch.Generator().manual_seed(99)
+    pc = 0.5 + torch.rand(B, L, generator=g)
+    ec = 0.5 + torch.rand(B, L, generator=g)
+    dc = torch.randint(1, 4, (B, L), generator=g).float()  # integer factors: mel_len = int(sum) is unambiguous
+    out, extra = run(model, batch, (pc, ec, dc), extra=True)
+    with torch.no_grad():
+        r = O.fastspeech2_forward(sd, mc, batch, pc, ec, dc, intermediates=True)
+    ref = r["out"]
+    assert torch.equal(out[5].cpu(), ref[5]) and torch.equal(out[9].cpu(), ref[9])
+    assert torch.equal(extra["pitch_idx"].cpu().long(), r["pitch_idx"])
+    assert torch.equal(extra["energy_idx"].cpu().long(), r["energy_idx"])
+    assert maxabs(out[2], ref[2]) <= 1e-4 and maxabs(out[3], ref[3]) <= 1e-4
+    assert maxabs(out[1], ref[1]) <= TOL
+    # a [L] vector broadcasts over the batch like the reference's multiply
+    out2 = run(model, batch, (pc[0], 1.0, 1.0))
+    with torch.no_grad():
+        ref2 = O.fastspeech2_forward(sd, mc, batch, pc[0], 1.0, 1.0)
+    assert torch.equal(out2[5].cpu(), ref2[5]) and maxabs(out2[2], ref2[2]) <= 1e-4
+
+
+def test_max_wav_value_reaches_the_pcm_epilogue(golden):
+    """utils/model.py:105-108 scales by preprocess_config audio.max_wav_value before astype(int16)."""
+    from speakingstyle_b200 import tools
+    g = golden("hifigan_small")
+    gen, h, vsd = get_vocoder()
+    mel = torch.from_numpy(g["mel"]).to(DEV)
+    pc = C.preprocess_config("BC2013")
+    pc["preprocessing"]["audio"]["max_wav_value"] = 16384.0
+    wavs = tools.vocoder_infer(mel, gen, None, pc)
+    want = (g["wave"][:, 0] * 16384.0).astype(np.int16)
+    assert all(np.abs(w.astype(np.int32) - want[i].astype(np.int32)).max() <= 2 for i, w in enumerate(wavs))
+
+
+def test_model_on_another_device_than_the_current_one():
+    """The library launches on the current device: forward() makes the model's own device current for the call."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import speakingstyle_b200 as ss
+    ds, batch, voc = S.make_workload("tiny")
+    d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
+    mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
+    sd = S.fastspeech2_state_dict(mc, ds)
+    m1 = ss.get_model(pc, mc, "cuda:1", sd)
+    assert torch.cuda.current_device() == 0
+    out1 = run(m1, batch)
+    out0 = run(get_models(ds)[0], batch)
+    assert out1[1].device.index == 1 and torch.cuda.current_device() == 0
+    assert torch.equal(out1[1].cpu(), out0[1].cpu()) and torch.equal(out1[5].cpu(), out0[5].cpu())
+
+
 def _report(line):
     import os
 

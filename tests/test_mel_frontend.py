@@ -23,6 +23,23 @@ def test_oracle_matches_reference_fixture(golden):
     assert np.array_equal(M.slaney_mel(22050, 1024, 80, 0.0, 8000.0), g["mel_basis"])
 
 
+def test_reference_state_dict_loads_strictly_and_buffers_agree():
+    """Live reference (build container only): a reference TacotronSTFT state_dict loads with strict=True and this
+    package's own buffers equal the reference's."""
+    from oracle import ref_harness as rh
+
+    if not rh.available():
+        pytest.skip("reference checkout not present")
+    from speakingstyle_b200.audio import TacotronSTFT
+
+    ref = rh.load_audio().TacotronSTFT(1024, 256, 1024, 80, 22050, 0.0, 8000.0)
+    ours = TacotronSTFT(1024, 256, 1024, 80, 22050, 0.0, 8000.0)
+    own = {k: v.clone() for k, v in ours.state_dict().items()}
+    ours.load_state_dict(ref.state_dict(), strict=True)
+    for k, v in ref.state_dict().items():
+        assert (own[k] - v).abs().max().item() <= 1e-6, k
+
+
 def test_filterbank_has_the_published_shape():
     """Properties of librosa's slaney filterbank that do not depend on its version: triangular, area-normalised,
     band edges on the Slaney mel scale (linear below 1 kHz, log above), nothing above fmax."""
@@ -42,7 +59,9 @@ def test_product_buffers_match_the_reference(golden):
 
     g = golden("mel_frontend")
     t = TacotronSTFT(1024, 256, 1024, 80, 22050, 0.0, 8000.0)
-    assert sorted(t.state_dict().keys()) == ["mel_basis", "stft_fn.forward_basis"]
+    # the reference's buffer names (audio/stft.py:48-49, 149): state_dicts are interchangeable, strict=True
+    assert sorted(t.state_dict().keys()) == ["mel_basis", "stft_fn.forward_basis", "stft_fn.inverse_basis"]
+    assert tuple(t.stft_fn.inverse_basis.shape) == (1026, 1, 1024)
     assert np.array_equal(t.mel_basis.numpy(), g["mel_basis"])
     fb = t.stft_fn.forward_basis
     assert tuple(fb.shape) == (1026, 1, 1024)

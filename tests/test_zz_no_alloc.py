@@ -71,6 +71,12 @@ def test_noalloc_length_regulator_matches_two_call_form_twice_in_a_row():
     assert want_len.tolist() == [19, 1, 99]
     assert torch.equal(got_len, want_len)
     assert torch.equal(got_out, want_out)
+    # ... and it stands on the oracle directly (model/modules.py:174-201 restated in oracle/fs2_oracle.py), not only
+    # on the library's other entry point: same rows, same zero padding, same lengths
+    from oracle import fs2_oracle as O
+
+    ref_out, ref_len, _ = O.length_regulate(x2.cpu(), d2.cpu(), T2)
+    assert torch.equal(got_out.cpu(), ref_out) and got_len.cpu().tolist() == ref_len.tolist()
 
     # and call 1 again gives call 1's answer again
     again_out, again_len = _noalloc(lib, x1, d1, T1, pe1)
