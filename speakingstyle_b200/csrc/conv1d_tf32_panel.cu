@@ -14,9 +14,9 @@
 //     box; rows outside the utterance are zero-filled by TMA as before).  Tap j of output row r is panel row
 //     r + j*dilation: the split warps just read a shifted row.  (A SWIZZLE_128B panel can be read at any row offset
 //     because the swizzle phase is a function of the absolute shared-memory address - scripts/desc_shift_probe.py.)
-//   * the weights of ALL taps stay resident in shared memory when they fit (32 channels: always; 64 channels: k = 3),
-//     loaded once per CTA; otherwise they stream through a ring as before.
-// Per 128-row tile that is 18-23 KB (32 ch) / 37-400 KB (64 ch) of TMA traffic instead of 264 / 704 KB.
+//   * the weights of ALL taps stay resident in shared memory, loaded once per CTA.  That is the condition for using this
+//     kernel (32 channels: k <= 12; 64 channels: k = 3); layers whose weights do not fit stay with conv1d_tf32_ts.cu.
+// Per 128-row tile that is 18-46 KB of TMA traffic instead of 264 / 192 KB.
 //
 //   * the MMA-issuing thread, not the tensor pipe, paced the narrow tiles (an N = 32 MMA is 16 cycles of tensor work; a
 //     microbenchmark, scripts/mma_rate_probe.py, shows the pipe itself runs back-to-back N = 32 TS-form MMAs at full
@@ -29,6 +29,8 @@
 //
 // Warps: TMA, MMA, 4 epilogue, 8 split (two per TMEM lane group, half a row each).  TMEM: [main | correction] x2 |
 // two A slots of 2 x (32 hi + 32 lo) columns.
+#include <type_traits>
+
 #include "tc_common.cuh"
 
 namespace {
@@ -41,17 +43,14 @@ constexpr int NTHREADS = 32 * (6 + XF_WARPS);
 constexpr int MAX_A_SLOTS = 3;
 constexpr int A_STEPS = 2;                         // (tap, chunk) steps per operand hand-over
 constexpr int A_SLOT_COLS = A_STEPS * 2 * KCHUNK;  // [hi | lo] per step
-constexpr int W_RING = 4;                // weight ring depth when the weights are streamed
 constexpr int MAX_PAN = 4;               // activation panel ring depth (upper bound)
-constexpr int N_BARS = 2 * MAX_PAN + 2 * W_RING + 1 + 2 * MAX_A_SLOTS + 4;
+constexpr int N_BARS = 2 * MAX_PAN + 1 + 2 * MAX_A_SLOTS + 4;
 constexpr int MAX_SMEM = 227 * 1024;
 
 struct PanelArgs {
   int32_t R;            // panel rows = 128 + (k-1)*dilation
   int32_t panel_bytes;  // per 32-channel chunk, multiple of 1024
   int32_t n_pan;        // panels in the ring (each holds all chunks of one tile)
-  int32_t w_resident;   // all (tap, chunk) weight tiles stay in shared memory
-  int32_t nchunk;
 };
 
 // Debug build (-DSS_PANEL_TRACE, scripts/panel_trace.py): CTA 0 stamps clock64() per operand hand-over.
@@ -78,7 +77,10 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) 
       : "memory");
 }
 
-template <int BN>
+// NCHUNK = Cin / 32 is a template parameter, and the weights are always resident: the MMA-issuing thread's loop is the
+// critical path of the narrow tiles (one thread, ~10 % issue efficiency on branchy code - ncu source view), so it is
+// kept free of run-time configuration branches.
+template <int BN, int NCHUNK>
 __global__ void __launch_bounds__(NTHREADS, 1)
 conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                          const __grid_constant__ CUtensorMap tmBl, const TcArgs p, const PanelArgs q, const int in_act,
@@ -93,17 +95,23 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
-  const int nchunk = q.nchunk;
+  constexpr int nchunk = NCHUNK;
+  // Split ONCE per tile (32-channel layers): the split warps rewrite the landed panel in place as hi and write lo to a
+  // second panel, then every tap only COPIES its shifted rows into TMEM.  The per-tap split did the same
+  // arithmetic k times per row and made the split warps (issue-bound, ~5 ALU operations per element and tap) the pace
+  // setter once the MMA loop was lean.  64-channel layers keep the per-tap split: two panels of [hi | lo] for two
+  // chunks do not fit next to their resident weights.
+  constexpr bool ONCE = NCHUNK == 1;
+  constexpr int PAN_PARTS = ONCE ? 2 : 1;
   const int KT = p.k * nchunk;
-  const int pan_stage = nchunk * q.panel_bytes;                       // one tile's panels (all chunks)
+  const int pan_stage = nchunk * PAN_PARTS * q.panel_bytes;           // one tile's panels (all chunks)
   const int w_off = q.n_pan * pan_stage;
-  const int w_bytes = (q.w_resident ? KT : W_RING) * WT;
+  const int w_bytes = KT * WT;
   const int stg_off = w_off + w_bytes;
   const int bar_off = stg_off + STG_BYTES;
   float* stg_all = reinterpret_cast<float*>(smem_al + stg_off);
   const uint32_t bars = smem0 + bar_off;
-  const uint32_t pfull0 = bars, pempty0 = pfull0 + 8 * MAX_PAN, wfull0 = pempty0 + 8 * MAX_PAN, wempty0 = wfull0 + 8 * W_RING,
-                 wres = wempty0 + 8 * W_RING, tafull0 = wres + 8, taempty0 = tafull0 + 8 * MAX_A_SLOTS,
+  const uint32_t pfull0 = bars, pempty0 = pfull0 + 8 * MAX_PAN, wres = pempty0 + 8 * MAX_PAN, tafull0 = wres + 8, taempty0 = tafull0 + 8 * MAX_A_SLOTS,
                  tfull0 = taempty0 + 8 * MAX_A_SLOTS, tempty0 = tfull0 + 16, tslot = tempty0 + 16;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + bar_off + N_BARS * 8);
   int* const rag = reinterpret_cast<int*>(smem_al + bar_off + N_BARS * 8 + 16);
@@ -119,10 +127,6 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     for (int s = 0; s < MAX_PAN; ++s) {
       mbar_init(pfull0 + 8 * s, 1);
       mbar_init(pempty0 + 8 * s, XF_WARPS);  // every split warp has read its last row of the panel
-    }
-    for (int s = 0; s < W_RING; ++s) {
-      mbar_init(wfull0 + 8 * s, 1);
-      mbar_init(wempty0 + 8 * s, 1);
     }
     mbar_init(wres, 1);
     for (int t = 0; t < MAX_A_SLOTS; ++t) {
@@ -153,40 +157,25 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   if (warp == 0) {
     // ================= TMA producer =================
     if (elect_one()) {
-      if (q.w_resident) {  // every (tap, chunk) weight tile, once per CTA
-        mbar_expect_tx(wres, (uint32_t)(KT * WT));
-        for (int it = 0; it < KT; ++it) {
-          const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
-          tma_load_3d(smem0 + w_off + it * WT, &tmBh, wres, c0, 0, j);
-          tma_load_3d(smem0 + w_off + it * WT + B_BYTES, &tmBl, wres, c0, 0, j);
-        }
+      // every (tap, chunk) weight tile, once per CTA
+      mbar_expect_tx(wres, (uint32_t)(KT * WT));
+      for (int it = 0; it < KT; ++it) {
+        const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
+        tma_load_3d(smem0 + w_off + it * WT, &tmBh, wres, c0, 0, j);
+        tma_load_3d(smem0 + w_off + it * WT + B_BYTES, &tmBl, wres, c0, 0, j);
       }
-      int ps = 0, ws = 0;
-      uint32_t pphase = 0, wphase = 0;
-      auto load_panel = [&](int tile) {
+      int ps = 0;
+      uint32_t pphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mt, b;
         decode(tile, mt, b);
         mbar_wait(pempty0 + 8 * ps, pphase ^ 1);
         mbar_expect_tx(pfull0 + 8 * ps, (uint32_t)(nchunk * q.R * ROW_BYTES));
+#pragma unroll
         for (int c = 0; c < nchunk; ++c)
-          tma_load_3d(smem0 + ps * pan_stage + c * q.panel_bytes, &tmA, pfull0 + 8 * ps, c * KCHUNK, mt * BM - p.pad, b);
+          tma_load_3d(smem0 + ps * pan_stage + c * PAN_PARTS * q.panel_bytes, &tmA, pfull0 + 8 * ps, c * KCHUNK,
+                      mt * BM - p.pad, b);
         if (++ps == q.n_pan) { ps = 0; pphase ^= 1; }
-      };
-      // the panel of tile i+1 is requested BEFORE the weights of tile i: the weight ring only moves as fast as the MMAs
-      // consume it, and a panel requested behind it would arrive late
-      if ((int)blockIdx.x < num_tiles) load_panel(blockIdx.x);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        if (tile + (int)gridDim.x < num_tiles) load_panel(tile + gridDim.x);
-        if (!q.w_resident) {
-          for (int it = 0; it < KT; ++it) {
-            const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
-            mbar_wait(wempty0 + 8 * ws, wphase ^ 1);
-            mbar_expect_tx(wfull0 + 8 * ws, (uint32_t)WT);
-            tma_load_3d(smem0 + w_off + ws * WT, &tmBh, wfull0 + 8 * ws, c0, 0, j);
-            tma_load_3d(smem0 + w_off + ws * WT + B_BYTES, &tmBl, wfull0 + 8 * ws, c0, 0, j);
-            if (++ws == W_RING) { ws = 0; wphase ^= 1; }
-          }
-        }
       }
     }
   } else if (warp == 1) {
@@ -195,46 +184,50 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const uint32_t idesc2 = make_idesc(2u, 2 * BN);  // hi x [W_hi ; W_lo] -> [main | corr]
       const uint32_t idesc1 = make_idesc(2u, BN);      // lo x W_hi -> corr
       const uint32_t w_lo0 = desc_lo(smem0 + w_off);   // descriptor low word of weight tile 0; tile t is + t * (WT >> 4)
-      int slot = 0, ws = 0;
-      uint32_t sphase = 0, wphase = 0;
+      constexpr uint32_t WSTEP = WT >> 4;
+      const uint32_t a_base = tmem_base + A_COL0;
+      int slot = 0;
+      uint32_t sphase = 0;
       int gcount = 0;
       [[maybe_unused]] int hcount = 0;
-      if (q.w_resident) mbar_wait(wres, 0);
+      mbar_wait(wres, 0);
+      // one operand hand-over: STEPS (tap, chunk) steps, 8 MMAs each, straight-line
+      auto hand_over = [&](auto steps_c, uint32_t d_tmem, uint32_t bw, uint32_t& accum) {
+        constexpr int STEPS = decltype(steps_c)::value;
+        PANEL_TRACE(0, hcount);
+        mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of these steps are in TMEM
+        tc_fence_after();
+        PANEL_TRACE(1, hcount);
+        const uint32_t a0 = a_base + slot * A_SLOT_COLS;
+#pragma unroll
+        for (int sidx = 0; sidx < STEPS; ++sidx) {
+#pragma unroll
+          for (int kk = 0; kk < KCHUNK / 8; ++kk) {  // K = 8 tf32 per instruction: 8 TMEM columns / 32 bytes of B
+            umma_tf32_ts_w(d_tmem, a0 + sidx * 2 * KCHUNK + kk * 8, bw + sidx * WSTEP + kk * 2, idesc2, accum);
+            accum = 1u;
+            umma_tf32_ts_w(d_tmem + BN, a0 + sidx * 2 * KCHUNK + KCHUNK + kk * 8, bw + sidx * WSTEP + kk * 2, idesc1, 1u);
+          }
+        }
+        umma_commit(taempty0 + 8 * slot);
+        PANEL_TRACE(2, hcount); ++hcount;
+        if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
+      };
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        int it = 0;
+        uint32_t bw = w_lo0;
         for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
           const int as = gcount & 1;
           mbar_wait(tempty0 + 8 * as, ((gcount >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator pair
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * 2 * BN;
-          const int it1 = min(it0 + group, KT);
-          // hand-overs never straddle a group: group is even (host) or the tile ends
-          while (it < it1) {
-            const int steps = min(A_STEPS, it1 - it);
-            PANEL_TRACE(0, hcount);
-            mbar_wait(tafull0 + 8 * slot, sphase);  // hi / lo of these steps are in TMEM
-            tc_fence_after();
-            PANEL_TRACE(1, hcount);
-            for (int sidx = 0; sidx < steps; ++sidx, ++it) {
-              if (!q.w_resident) {
-                mbar_wait(wfull0 + 8 * ws, wphase);
-                tc_fence_after();
-              }
-              const uint32_t a_hi = tmem_base + A_COL0 + slot * A_SLOT_COLS + sidx * 2 * KCHUNK, a_lo = a_hi + KCHUNK;
-              const uint32_t bw = w_lo0 + (uint32_t)(q.w_resident ? it : ws) * (uint32_t)(WT >> 4);
-#pragma unroll
-              for (int kk = 0; kk < KCHUNK / 8; ++kk) {  // K = 8 tf32 per instruction: 8 TMEM columns / 32 bytes of B
-                umma_tf32_ts_w(d_tmem, a_hi + kk * 8, bw + kk * 2, idesc2, ((it - it0) | kk) != 0);
-                umma_tf32_ts_w(d_tmem + BN, a_lo + kk * 8, bw + kk * 2, idesc1, 1u);
-              }
-              if (!q.w_resident) {
-                umma_commit(wempty0 + 8 * ws);
-                if (++ws == W_RING) { ws = 0; wphase ^= 1; }
-              }
-            }
-            umma_commit(taempty0 + 8 * slot);
-            PANEL_TRACE(2, hcount); ++hcount;
-            if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
+          const int n = min(group, KT - it0);  // steps of this group; hand-overs never straddle a group (group is even)
+          uint32_t accum = 0u;                 // the first MMA of a group restarts [main | corr]
+          for (int h = 0; h < (n >> 1); ++h) {
+            hand_over(std::integral_constant<int, 2>{}, d_tmem, bw, accum);
+            bw += 2 * WSTEP;
+          }
+          if (n & 1) {
+            hand_over(std::integral_constant<int, 1>{}, d_tmem, bw, accum);
+            bw += WSTEP;
           }
           umma_commit(tfull0 + 8 * as);
         }
@@ -302,7 +295,28 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if (threadIdx.x == 192) PANEL_TRACE(6, hcount);
       mbar_wait(pfull0 + 8 * ps, pphase);
       if (threadIdx.x == 192) PANEL_TRACE(7, hcount);
-      const uint8_t* pan = smem_al + ps * pan_stage;
+      uint8_t* pan = smem_al + ps * pan_stage;
+      if constexpr (ONCE) {
+        // phase 1: split the whole panel (R rows, halo included) element-wise, 16-byte units dealt round-robin to the
+        // 256 split threads - in place, so the swizzle never has to be decoded
+        const int tid = threadIdx.x - 6 * 32;
+        const int n_units = q.R * (ROW_BYTES / 16);
+        for (int un = tid; un < n_units; un += XF_WARPS * 32) {
+          float4* ph = reinterpret_cast<float4*>(pan + un * 16);
+          float4 x = *ph;
+          if (in_act == SS_ACT_LRELU) {
+            x.x = fmaxf(x.x, x.x * in_slope);
+            x.y = fmaxf(x.y, x.y * in_slope);
+            x.z = fmaxf(x.z, x.z * in_slope);
+            x.w = fmaxf(x.w, x.w * in_slope);
+          }
+          const float4 h = make_float4(tf32_rn(x.x), tf32_rn(x.y), tf32_rn(x.z), tf32_rn(x.w));
+          *ph = h;
+          // lo stays unrounded: the MMA truncates an fp32 operand to TF32 itself (see conv1d_tf32_ts.cu)
+          *reinterpret_cast<float4*>(pan + q.panel_bytes + un * 16) = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(XF_WARPS * 32) : "memory");  // the split warps only
+      }
       int prow = r, c = 0;  // panel row of this output row for the current tap (tap j reads row r + j*dilation)
       for (int it = 0; it < KT; it += A_STEPS) {
         const int steps = min(A_STEPS, KT - it);  // the MMA issuer cuts hand-overs the same way (group is even)
@@ -310,24 +324,31 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
         for (int sidx = 0; sidx < A_STEPS; ++sidx) {
           if (sidx < steps) {
-            const uint8_t* row = pan + c * q.panel_bytes + prow * ROW_BYTES;
+            const uint8_t* row = pan + c * PAN_PARTS * q.panel_bytes + prow * ROW_BYTES;
             const int sw = prow & 7;  // SWIZZLE_128B: 16-byte unit u of a row sits at unit (u ^ (row & 7)); panels are 1024-aligned
             if (++c == nchunk) { c = 0; prow += p.dilation; }
 #pragma unroll
             for (int uu = 0; uu < 4; ++uu) {
               const int u = xhalf * 4 + uu;
-              float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
-              if (in_act == SS_ACT_LRELU) {
-                x.x = x.x > 0.f ? x.x : x.x * in_slope;
-                x.y = x.y > 0.f ? x.y : x.y * in_slope;
-                x.z = x.z > 0.f ? x.z : x.z * in_slope;
-                x.w = x.w > 0.f ? x.w : x.w * in_slope;
+              if constexpr (ONCE) {  // phase 2: copy the shifted row of the hi and lo panels
+                const float4 h = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+                const float4 l = *reinterpret_cast<const float4*>(row + q.panel_bytes + ((u ^ sw) << 4));
+                hi[sidx][4 * uu + 0] = h.x; hi[sidx][4 * uu + 1] = h.y; hi[sidx][4 * uu + 2] = h.z; hi[sidx][4 * uu + 3] = h.w;
+                lo[sidx][4 * uu + 0] = l.x; lo[sidx][4 * uu + 1] = l.y; lo[sidx][4 * uu + 2] = l.z; lo[sidx][4 * uu + 3] = l.w;
+              } else {
+                float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
+                if (in_act == SS_ACT_LRELU) {
+                  x.x = fmaxf(x.x, x.x * in_slope);
+                  x.y = fmaxf(x.y, x.y * in_slope);
+                  x.z = fmaxf(x.z, x.z * in_slope);
+                  x.w = fmaxf(x.w, x.w * in_slope);
+                }
+                // lo is handed over unrounded: the MMA truncates an fp32 operand to TF32 itself (see conv1d_tf32_ts.cu)
+                hi[sidx][4 * uu + 0] = tf32_rn(x.x); lo[sidx][4 * uu + 0] = x.x - hi[sidx][4 * uu + 0];
+                hi[sidx][4 * uu + 1] = tf32_rn(x.y); lo[sidx][4 * uu + 1] = x.y - hi[sidx][4 * uu + 1];
+                hi[sidx][4 * uu + 2] = tf32_rn(x.z); lo[sidx][4 * uu + 2] = x.z - hi[sidx][4 * uu + 2];
+                hi[sidx][4 * uu + 3] = tf32_rn(x.w); lo[sidx][4 * uu + 3] = x.w - hi[sidx][4 * uu + 3];
               }
-              // lo is handed over unrounded: the MMA truncates an fp32 operand to TF32 itself (see conv1d_tf32_ts.cu)
-              hi[sidx][4 * uu + 0] = tf32_rn(x.x); lo[sidx][4 * uu + 0] = x.x - hi[sidx][4 * uu + 0];
-              hi[sidx][4 * uu + 1] = tf32_rn(x.y); lo[sidx][4 * uu + 1] = x.y - hi[sidx][4 * uu + 1];
-              hi[sidx][4 * uu + 2] = tf32_rn(x.z); lo[sidx][4 * uu + 2] = x.z - hi[sidx][4 * uu + 2];
-              hi[sidx][4 * uu + 3] = tf32_rn(x.w); lo[sidx][4 * uu + 3] = x.w - hi[sidx][4 * uu + 3];
             }
           }
         }
@@ -367,36 +388,31 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   }
 }
 
-// Shared-memory plan for one layer: returns false when not even two panels and a weight ring fit.
-template <int BN>
-bool plan_smem(int k, int dilation, int nchunk, int B_ragged, PanelArgs& q, int& smem_bytes) {
-  constexpr int WT = 2 * BN * ROW_BYTES;
-  q.nchunk = nchunk;
+// Shared-memory plan for one layer (all weight tiles resident + 2 or 3 activation panels): false when it does not fit.
+inline bool plan_smem(int bn, int k, int dilation, int nchunk, int B_ragged, PanelArgs& q, int& smem_bytes) {
+  const int wt = 2 * bn * ROW_BYTES;
   q.R = BM + (k - 1) * dilation;
   q.panel_bytes = (q.R * ROW_BYTES + 1023) / 1024 * 1024;
   const int fixed = STG_BYTES + N_BARS * 8 + 16 + (B_ragged ? (B_ragged + 1) * 4 : 0) + 1024;
-  const int KT = k * nchunk;
-  for (int resident = 1; resident >= 0; --resident)
-    for (int n_pan = 3; n_pan >= 2; --n_pan) {
-      const int total = n_pan * nchunk * q.panel_bytes + (resident ? KT : W_RING) * WT + fixed;
-      if (total <= MAX_SMEM) {
-        q.n_pan = n_pan;
-        q.w_resident = resident;
-        smem_bytes = total;
-        return true;
-      }
+  const int parts = nchunk == 1 ? 2 : 1;  // 32-channel layers keep [hi | lo] panels (split once per tile)
+  for (int n_pan = 3; n_pan >= 2; --n_pan) {
+    const int total = n_pan * nchunk * parts * q.panel_bytes + k * nchunk * wt + fixed;
+    if (total <= MAX_SMEM) {
+      q.n_pan = n_pan;
+      smem_bytes = total;
+      return true;
     }
+  }
   return false;
 }
 
-template <int BN>
+template <int BN, int NCHUNK>
 int launch(const ss_conv1d_tf32_params* p, const TcArgs& a0, int group, cudaStream_t st) {
   TcArgs a = a0;
   PanelArgs q;
   int smem = 0;
-  const int nchunk = (p->Cin + KCHUNK - 1) / KCHUNK;
-  SS_REQUIRE(plan_smem<BN>(p->k, p->dilation, nchunk, p->rows ? p->B : 0, q, smem), SS_ERR_UNSUPPORTED,
-             "ss_conv1d_tf32x3_panel: k=%d dilation=%d does not fit shared memory", p->k, p->dilation);
+  SS_REQUIRE(plan_smem(BN, p->k, p->dilation, NCHUNK, p->rows ? p->B : 0, q, smem), SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_panel: the weights of k=%d taps (dilation %d) do not fit shared memory", p->k, p->dilation);
   CUtensorMap tmA, tmBh, tmBl;
   int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
                        (uint64_t)p->x_row_stride * 4, (uint64_t)p->x_batch_stride * 4, KCHUNK, (uint32_t)q.R);
@@ -413,14 +429,14 @@ int launch(const ss_conv1d_tf32_params* p, const TcArgs& a0, int group, cudaStre
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_panel: too many tiles");
   static std::atomic<unsigned long long> attr_mask{0};  // per device
   if (needs_attr_on_device(attr_mask)) {
-    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_panel_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_panel_kernel<BN, NCHUNK>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_panel: smem opt-in");
     attr_done_on_device(attr_mask);
   }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3_panel: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  conv1d_tf32_panel_kernel<BN><<<grid, NTHREADS, smem, st>>>(tmA, tmBh, tmBl, a, q, p->in_act, p->in_slope, group);
+  conv1d_tf32_panel_kernel<BN, NCHUNK><<<grid, NTHREADS, smem, st>>>(tmA, tmBh, tmBl, a, q, p->in_act, p->in_slope, group);
   SS_CHECK_LAUNCH("ss_conv1d_tf32x3_panel");
   return SS_OK;
 }
@@ -433,12 +449,18 @@ extern "C" __attribute__((visibility("default"))) int ss_debug_panel_trace(long 
 }
 #endif
 
-// 1 if ss_conv1d_tf32x3_panel takes this layer: stride-1 same-length convolution with at least two taps, at most 64
-// input and output channels (whole 32-channel chunks in), a halo that fits one TMA box, plain fp32 output path.
+// 1 if ss_conv1d_tf32x3_panel takes this layer: stride-1 same-length convolution with at least two taps, 32 or 64 input
+// channels, at most 64 output channels, a halo that fits one TMA box, and the weights of all taps fitting shared memory
+// next to two activation panels.
 extern "C" int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p) {
   if (!p) return 0;
-  return p->S_in == p->S_out && p->k >= 2 && p->Cin <= 64 && p->Cin % KCHUNK == 0 && p->Cout <= 64 && p->Cout % 4 == 0 &&
-         BM + (p->k - 1) * p->dilation <= 256 && p->pad <= (p->k - 1) * p->dilation && p->pad >= 0;
+  if (!(p->S_in == p->S_out && p->k >= 2 && (p->Cin == 32 || p->Cin == 64) && p->Cout > 0 && p->Cout <= 64 &&
+        p->Cout % 4 == 0 && p->dilation > 0 && BM + (p->k - 1) * p->dilation <= 256 && p->pad >= 0 &&
+        p->pad <= (p->k - 1) * p->dilation))
+    return 0;
+  PanelArgs q;
+  int smem = 0;
+  return plan_smem(p->Cout > 32 ? 64 : 32, p->k, p->dilation, p->Cin / KCHUNK, p->rows ? p->B : 0, q, smem) ? 1 : 0;
 }
 
 extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stream) {
@@ -449,7 +471,7 @@ extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stre
              p->S_in, p->S_out, p->Cin, p->Cout, p->k, p->dilation);
   SS_REQUIRE(ss_conv1d_tf32x3_panel_supported(p), SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_panel: needs S_in == S_out, k >= 2, Cin in {32, 64}, Cout <= 64, 128 + (k-1)*dilation <= 256 "
-             "(got S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d pad=%d)", p->S_in, p->S_out, p->Cin, p->Cout, p->k,
+             "and all weight tiles resident in shared memory (got S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d pad=%d)", p->S_in, p->S_out, p->Cin, p->Cout, p->k,
              p->dilation, p->pad);
   SS_REQUIRE(p->x_row_stride % 4 == 0 && p->x_batch_stride % 4 == 0 && p->y_row_stride % 4 == 0 &&
                  p->y_batch_stride % 4 == 0 && p->y_offset % 4 == 0 && p->y_batch_elems % 4 == 0,
@@ -459,6 +481,8 @@ extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stre
              SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_panel: pointers must be 16-byte aligned");
   SS_REQUIRE(p->in_act == SS_ACT_NONE || p->in_act == SS_ACT_LRELU, SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_panel: in_act must be none or lrelu");
+  SS_REQUIRE(p->in_act != SS_ACT_LRELU || (p->in_slope >= 0.f && p->in_slope <= 1.f), SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_panel: leaky-ReLU on load is computed as max(x, slope*x) and needs 0 <= slope <= 1 (got %g)", p->in_slope);
   SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_panel: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
   TcArgs a;
@@ -473,5 +497,6 @@ extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stre
   a.flat = 0; a.S_in = p->S_in; a.rows = p->rows;
   const int group = ((p->k_group > 0 ? p->k_group : 8) + 1) & ~1;  // even: operand hand-overs cover two steps
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return p->Cout > 32 ? launch<64>(p, a, group, st) : launch<32>(p, a, group, st);
+  if (p->Cin == 32) return p->Cout > 32 ? launch<64, 1>(p, a, group, st) : launch<32, 1>(p, a, group, st);
+  return p->Cout > 32 ? launch<64, 2>(p, a, group, st) : launch<32, 2>(p, a, group, st);
 }

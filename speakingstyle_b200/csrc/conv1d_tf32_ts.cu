@@ -377,10 +377,10 @@ conv1d_tf32_ts_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const int u = xhalf * NU + uu;
           float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
           if (in_act == SS_ACT_LRELU) {
-            x.x = x.x > 0.f ? x.x : x.x * in_slope;
-            x.y = x.y > 0.f ? x.y : x.y * in_slope;
-            x.z = x.z > 0.f ? x.z : x.z * in_slope;
-            x.w = x.w > 0.f ? x.w : x.w * in_slope;
+            x.x = fmaxf(x.x, x.x * in_slope);
+            x.y = fmaxf(x.y, x.y * in_slope);
+            x.z = fmaxf(x.z, x.z * in_slope);
+            x.w = fmaxf(x.w, x.w * in_slope);
           }
           hi[4 * uu + 0] = tf32_rn(x.x); lo[4 * uu + 0] = LO_RN(x.x - hi[4 * uu + 0]);
           hi[4 * uu + 1] = tf32_rn(x.y); lo[4 * uu + 1] = LO_RN(x.y - hi[4 * uu + 1]);
@@ -475,6 +475,8 @@ extern "C" int ss_conv1d_tf32x3_ts(const ss_conv1d_tf32_params* p, void* stream)
              SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_ts: pointers must be 16-byte aligned");
   SS_REQUIRE(p->in_act == SS_ACT_NONE || p->in_act == SS_ACT_LRELU, SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_ts: in_act must be none or lrelu");
+  SS_REQUIRE(p->in_act != SS_ACT_LRELU || (p->in_slope >= 0.f && p->in_slope <= 1.f), SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_ts: leaky-ReLU on load is computed as max(x, slope*x) and needs 0 <= slope <= 1 (got %g)", p->in_slope);
 
   const int group = p->k_group > 0 ? p->k_group : 8;
   const int chunks = p->k * ((p->Cin + KCHUNK - 1) / KCHUNK);

@@ -380,10 +380,10 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         for (int u = 0; u < 8; ++u) {  // 16-byte unit u of the row sits at unit (u ^ (row & 7)) - SWIZZLE_128B
           float4 x = *reinterpret_cast<const float4*>(row + ((u ^ sw) << 4));
           if (in_act == SS_ACT_LRELU) {
-            x.x = x.x > 0.f ? x.x : x.x * in_slope;
-            x.y = x.y > 0.f ? x.y : x.y * in_slope;
-            x.z = x.z > 0.f ? x.z : x.z * in_slope;
-            x.w = x.w > 0.f ? x.w : x.w * in_slope;
+            x.x = fmaxf(x.x, x.x * in_slope);
+            x.y = fmaxf(x.y, x.y * in_slope);
+            x.z = fmaxf(x.z, x.z * in_slope);
+            x.w = fmaxf(x.w, x.w * in_slope);
           }
           hi[4 * u + 0] = tf32_rn(x.x); lo[4 * u + 0] = x.x - hi[4 * u + 0];  // truncated to TF32 by the MMA (see conv1d_tf32_ts.cu)
           hi[4 * u + 1] = tf32_rn(x.y); lo[4 * u + 1] = x.y - hi[4 * u + 1];  // truncated to TF32 by the MMA (see conv1d_tf32_ts.cu)
@@ -474,6 +474,8 @@ extern "C" int ss_conv1d_tf32x3_ts2(const ss_conv1d_tf32_params* p, void* stream
              SS_ERR_ALIGNMENT, "ss_conv1d_tf32x3_ts2: pointers must be 16-byte aligned");
   SS_REQUIRE(p->in_act == SS_ACT_NONE || p->in_act == SS_ACT_LRELU, SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_ts2: in_act must be none or lrelu");
+  SS_REQUIRE(p->in_act != SS_ACT_LRELU || (p->in_slope >= 0.f && p->in_slope <= 1.f), SS_ERR_UNSUPPORTED,
+             "ss_conv1d_tf32x3_ts2: leaky-ReLU on load is computed as max(x, slope*x) and needs 0 <= slope <= 1 (got %g)", p->in_slope);
 
   if (p->Cout <= 64) return ss_conv1d_tf32x3_ts(p, stream);  // narrow layers: the single-CTA kernel's BN = 64 / 32 forms
   const int bn = BN2 / 2;  // rows of the weight tile each CTA loads

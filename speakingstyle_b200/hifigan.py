@@ -271,14 +271,17 @@ class Generator(nn.Module, ParamCache):
                 nd = len(rb.dilation)
                 rk = rb.kernel_size
                 for m, dil in enumerate(rb.dilation):
+                    # c1's output is only ever read through the leaky-ReLU in front of c2 (hifigan/models.py:98-101), so c1's
+                    # epilogue applies it once per element and c2 takes its input as is - the same fp32 operation on the
+                    # same value, done once instead of once per tap in c2's operand split
                     t = ops.conv1d(y, w1s[m], rb.convs1[m].bias, k=rk, dilation=dil, pad=get_padding(rk, dil),
-                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, out=tbuf, rows=rw)
+                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, act=ops.ACT_LRELU, slope=LRELU_SLOPE,
+                                   out=tbuf, rows=rw)
                     if m < nd - 1:
-                        y = ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1),
-                                       in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, out=ybuf, rows=rw)
+                        y = ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1), residual=y, out=ybuf,
+                                       rows=rw)
                     else:  # last pair: x_j = c2(..) + y goes straight into the stage mean
-                        ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1),
-                                   in_act=ops.ACT_LRELU, in_slope=LRELU_SLOPE, residual=y, write_y=False,
+                        ops.conv1d(t, w2s[m], rb.convs2[m].bias, k=rk, pad=get_padding(rk, 1), residual=y, write_y=False,
                                    accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0), rows=rw)
             x = xs
         return self._post(x, pk, pcm, pcm_out, pcm_scale)

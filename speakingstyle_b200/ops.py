@@ -201,9 +201,9 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         accum_init=int(accum_init), k_group=tf32_k_group, rows=None if rows is None else rows.data_ptr())
     v = variant or tf32_variant
     if v == "auto":
-        # the panel kernel wins where the weights of all taps stay resident in shared memory (<= 96 KB of hi + lo: every
-        # 32-channel layer, 64-channel layers with k = 3); with streamed weights the per-tap kernel is as fast or faster
-        if (tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2 and W.k * W.cin * W.cout * 8 <= 96 * 1024
+        # the panel kernel takes the narrow layers whose weights (all taps, hi + lo) stay resident in shared memory:
+        # every 32-channel layer, 64-channel layers with k = 3
+        if (tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2
                 and _lib.lib().ss_conv1d_tf32x3_panel_supported(C.byref(p))):
             v = "panel"
         else:
