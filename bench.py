@@ -538,13 +538,17 @@ def main():
             roof["tf32x3_ceiling_at_sampled_clock"] = ceil
             roof["frac_of_3xtf32_ceiling"] = d_ach / ceil
             roof_all["frac_of_3xtf32_ceiling"] = ach / ceil
-        try:  # DRAM bytes of one launch of the same family from the committed ncu --set full capture
+        try:  # DRAM bytes of the same conv family from the committed ncu --set full capture (profiles/traffic.json)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
             v_ = tj.get(f"{key[0]} Cin={key[1]} Cout={key[2]} k={key[3]} dil={key[4]}")
             if v_:
-                roof["traffic"] = v_["bytes"]
-                roof["algorithmic_bytes"] = v_["algorithmic_bytes"]
-                roof["traffic_source"] = v_["source"]
+                # the capture is one fixed-size launch with every row computed; the launches timed here are ragged
+                # and of several sizes, so the captured bytes are scaled by FLOPs to "per launch like achieved"
+                scale = roof["flops_per_launch"] / v_["flops"]
+                roof["traffic"] = v_["bytes"] * scale
+                roof["algorithmic_bytes"] = v_["algorithmic_bytes"] * scale
+                roof["traffic_capture"] = {"bytes": v_["bytes"], "algorithmic_bytes": v_["algorithmic_bytes"],
+                                           "shape": v_["shape"], "mix": v_["mix"], "source": v_["source"]}
         except Exception:
             pass
         inf0 = runner.info[0]

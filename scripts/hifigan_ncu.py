@@ -52,12 +52,13 @@ for C, up in shapes:
         flops = 2.0 * B * S * C * C * k
         pad = (k * dil - dil) // 2
         if mode in ("fp32", "both"):
-            run(lambda: ops.conv1d(x, W, bias, k=k, dilation=dil, pad=pad, in_act=L, in_slope=0.1, out=t), flops,
-                f"fp32 c1 C={C} S={S} k={k} dil={dil}")
+            # as hifigan.py issues them: c1 = leaky-ReLU on load and in the epilogue, c2 = plain input + residual (+ mean)
+            run(lambda: ops.conv1d(x, W, bias, k=k, dilation=dil, pad=pad, in_act=L, in_slope=0.1, act=L, slope=0.1, out=t),
+                flops, f"fp32 c1 C={C} S={S} k={k} dil={dil}")
             if dil == 1:
-                run(lambda: ops.conv1d(t, W, bias, k=k, pad=pad, in_act=L, in_slope=0.1, residual=x, out=y), flops,
+                run(lambda: ops.conv1d(t, W, bias, k=k, pad=pad, residual=x, out=y), flops,
                     f"fp32 c2+res C={C} S={S} k={k}")
-                run(lambda: ops.conv1d(t, W, bias, k=k, pad=pad, in_act=L, in_slope=0.1, residual=x, write_y=False,
+                run(lambda: ops.conv1d(t, W, bias, k=k, pad=pad, residual=x, write_y=False,
                                        accum=xs, accum_scale=1.0 / 3, accum_init=False), flops,
                     f"fp32 c2+res+mean C={C} S={S} k={k}")
         if mode in ("bf16", "both"):
