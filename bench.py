@@ -131,12 +131,16 @@ def resolve_workload(name, world):
 # ---------------------------------------------------------------------------------------------
 # the work of one rank: a list of batches (one for the single-batch workloads, its shards for a sweep)
 # ---------------------------------------------------------------------------------------------
-def rank_batches(workload, rank, world, limit=None):
-    """(dataset, [batch, ...], vocoder?, text?, plan-or-None).  ``limit`` caps the corpus of a sweep (utterances)."""
+def rank_batches(workload, rank, world, limit=None, all_shards=False):
+    """(dataset, [batch, ...], vocoder?, text?, plan-or-None).  ``limit`` caps the corpus of a sweep (utterances).
+    all_shards (dynamic schedule): every rank holds every shard, most expensive first."""
     if workload in SWEEPS:
         corpus = S.Corpus(workload, seed=1, n=limit)
         plan = corpus.plan(world)
-        return corpus.dataset, [corpus.shard_batch(s) for s in plan.shards_of(rank)], corpus.vocoder, corpus.text, plan
+        from speakingstyle_b200 import shard as SH
+
+        mine = SH.dynamic_order(plan) if all_shards else plan.shards_of(rank)
+        return corpus.dataset, [corpus.shard_batch(s) for s in mine], corpus.vocoder, corpus.text, plan
     ds, batch, voc = S.make_workload(workload, seed=1 + rank)
     return ds, [batch], voc, True, None
 
@@ -272,11 +276,15 @@ def lr_roofline(dev, pk):
 class Runner:
     """Model(s) of one workload on one device plus this rank's batches; ``step(src)`` = one pass over them."""
 
-    def __init__(self, workload, precision, dev, rank=0, world=1, limit=None):
+    def __init__(self, workload, precision, dev, rank=0, world=1, limit=None, queue=None):
         import speakingstyle_b200 as ss
 
         self.ss, self.dev, self.workload, self.precision = ss, dev, workload, precision
-        ds, batches, voc, text, plan = rank_batches(workload, rank, world, limit)
+        # queue (dynamic schedule of a sweep on several GPUs): a callable returning the next unclaimed position in the
+        # cost-ordered shard list, shared by all ranks - see shard_queue()
+        self.queue = queue if (queue is not None and workload in SWEEPS and world > 1) else None
+        self.rank, self.world = rank, world
+        ds, batches, voc, text, plan = rank_batches(workload, rank, world, limit, all_shards=self.queue is not None)
         self.text, self.plan, self.vocoder = text, plan, voc
         d = C.write_preprocessed_dir(tempfile.mkdtemp(), ds)
         mc, pc = C.model_config(ds), C.preprocess_config(ds, d)
@@ -317,10 +325,27 @@ class Runner:
             d2h += o[1].numel() * 4 + o[9].numel() * 4
         return o, d2h, None
 
+    def _positions(self):
+        """Which of this rank's batches a step runs, in order.  Static schedule: all of them.  Dynamic: the first pass
+        runs every shard once (it fills the per-shard sizes every rank needs for its bookkeeping); from then on each
+        rank claims the next unclaimed shard of the cost-ordered list until the list is exhausted."""
+        if self.queue is None or any(i is None for i in self.info):
+            yield from range(len(self.host))
+            return
+        self.sweeps = getattr(self, "sweeps", 0) + 1
+        while True:
+            i = self.queue(self.sweeps)
+            if i >= len(self.host):
+                return
+            yield i
+
     def step(self, e2e=False):
         d2h = 0
         src = self.host if e2e else self.resident
-        for i, b in enumerate(src):
+        self.ran = []
+        for i in self._positions():
+            b = src[i]
+            self.ran.append(i)
             o, nb, _ = self._one(b, i, e2e)
             d2h += nb
             if self.info[i] is None:
@@ -333,7 +358,7 @@ class Runner:
                 self.info[i] = inf
         return d2h
 
-    # totals of this rank over one step
+    # totals of this rank over one step (dynamic schedule: every rank holds every shard, so these are the whole job's)
     def frames(self):
         return sum((i["frames"] if self.text else i["ref_frames"]) for i in self.info)
 
@@ -353,6 +378,18 @@ class Runner:
         if S_in == inf["Tr"]:
             return inf["ref_frames"] / (inf["B"] * inf["Tr"])
         return 1.0
+
+
+def shard_queue():
+    """Dynamic schedule of a sweep (speakingstyle_b200.shard.ShardQueue): ranks claim the planned shards, most expensive
+    first, from one counter per sweep in the process group's store.  None when no store is available."""
+    from speakingstyle_b200 import shard as SH
+
+    try:
+        q = SH.ShardQueue(prefix="ss_bench_sweep")
+    except Exception:
+        return None
+    return q.claim
 
 
 def time_steps(runner, steps, flush, barrier, e2e):
@@ -394,8 +431,9 @@ def quick_measure(workload, precision, dev, steps=10, warmup=3, limit=None):
     if r.vocoder:
         res["audio_seconds_per_s"] = res["mel_frames_per_s"] * HOP / SR
         res["e2e_audio_seconds_per_s"] = res["e2e_mel_frames_per_s"] * HOP / SR
-    if limit is not None:
+    if r.plan is not None:
         res["corpus_limit"] = limit
+        res["utterances"] = sum(len(s_.utterances) for s_ in r.plan.shards)
         res["shards"] = len(r.host)
     return res
 
@@ -412,6 +450,9 @@ def main():
                     help="fp32: all kernels fp32-accurate (mel / wave max-abs <= 1e-3); bf16: Decoder/PostNet/HiFi-GAN "
                          "on tcgen05 with bf16 operands (relative L2 <= 1e-2); integers identical in both")
     ap.add_argument("--limit", type=int, default=None, help="sweeps: use only the first LIMIT utterances of the corpus")
+    ap.add_argument("--schedule", default="dynamic", choices=["dynamic", "static"],
+                    help="sweeps on several GPUs: dynamic = ranks claim the planned shards from a shared counter (default); "
+                         "static = each rank runs the shards shard.plan_shards assigned to it")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads / bf16 mode block")
     ap.add_argument("--conv-breakdown", action="store_true", help="print per-shape conv timings to stderr")
@@ -439,7 +480,8 @@ def main():
     workload = resolve_workload(args.workload, world)
     sweep = workload in SWEEPS
 
-    runner = Runner(workload, args.precision, dev, rank, world, args.limit)
+    queue = shard_queue() if (sweep and world > 1 and args.schedule == "dynamic") else None
+    runner = Runner(workload, args.precision, dev, rank, world, args.limit, queue=queue)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     for _ in range(args.warmup):
         runner.step()
@@ -476,7 +518,12 @@ def main():
     per_rank = [t.clone() for _ in range(world)]
     if world > 1:
         dist.all_gather(per_rank, t)
-        dist.all_reduce(f, op=dist.ReduceOp.SUM)
+        if runner.queue is None:
+            dist.all_reduce(f, op=dist.ReduceOp.SUM)
+        else:  # every rank holds every shard: frames / h2d are already the whole job's; d2h is what THIS rank read back
+            d = f[2:3].clone()
+            dist.all_reduce(d, op=dist.ReduceOp.SUM)
+            f[2] = d[0]
     else:
         per_rank = [t]
     dev_ms_max = max(x[0].item() for x in per_rank)
@@ -558,7 +605,8 @@ def main():
         if sweep:
             plan = runner.plan
             cfg.update(utterances=sum(len(s.utterances) for s in plan.shards), shards=len(plan.shards),
-                       shards_rank0=len(runner.host), planner_imbalance=plan.imbalance(),
+                       schedule="dynamic (shared counter, planned shards, most expensive first)" if runner.queue else "static (shard.plan_shards assignment)",
+                       shards_rank0_last_sweep=len(runner.ran), planner_imbalance=plan.imbalance(),
                        per_rank_ms_per_step=[x[0].item() / args.steps for x in per_rank],
                        # no communication on the data path: one GPU would need the sum of the ranks' times, so
                        # mean / max over ranks IS the strong-scaling efficiency of this run
@@ -592,12 +640,16 @@ def main():
             torch.cuda.empty_cache()
             extra = []
             other = "bf16" if args.precision == "fp32" else "fp32"
-            jobs = [(workload, other, None)]
-            jobs += [(w, "fp32", lim) for w, lim in (("cfg2", None), ("cfg1", None), ("cfg5", 256), ("cfg4", 1024))
+            # (workload, precision, corpus limit, steps, warm-up).  The cfg5 entry is the WHOLE 2048-utterance sweep on this
+            # one GPU - the same workload `--gpus N` runs - so that strong scaling can be read against a one-GPU figure
+            # of the same corpus (3 timed sweeps of ~4 s each)
+            jobs = [(workload, other, None, 10, 3)]
+            jobs += [(w, "fp32", lim, st, wu) for w, lim, st, wu in (("cfg2", None, 10, 3), ("cfg1", None, 10, 3),
+                                                                     ("cfg5", None, 3, 3), ("cfg4", 1024, 10, 3))
                      if w != workload]
-            for wl, pr, lim in jobs:
+            for wl, pr, lim, st, wu in jobs:
                 try:
-                    extra.append(quick_measure(wl, pr, dev, limit=lim))
+                    extra.append(quick_measure(wl, pr, dev, steps=st, warmup=wu, limit=lim))
                 except Exception as e:  # pragma: no cover
                     extra.append({"workload": wl, "precision_mode": pr, "error": str(e)})
                 torch.cuda.empty_cache()

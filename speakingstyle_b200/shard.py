@@ -21,7 +21,9 @@ import torch
 # Relative per-unit costs (algorithmic MFLOP): encoder+predictors per phoneme, reference
 # encoder per reference frame, decoder+postnet per output frame, vocoder per output frame.
 COST_PHONEME, COST_REF_FRAME, COST_FRAME, COST_VOC_FRAME = 25.8, 31.6, 48.2, 614.1
-EXPECTED_FRAMES_PER_PHONEME = 7.0
+EXPECTED_FRAMES_PER_PHONEME = 5.5   # what the synthetic weights of synth.py produce; a real model's own mean belongs here
+VOCODER_HALO_FRAMES = 15            # hifigan.Generator.halo_frames(): frames computed beyond each utterance's own
+FIXED_COST = 6.0e5                  # per shard: ~210 launches and one host read, ~3 ms, in the same MFLOP units
 
 
 @dataclass
@@ -49,14 +51,20 @@ class ShardPlan:
         return max(self.rank_cost) / mean if mean > 0 else 1.0
 
 
-def shard_cost(n, max_src, max_ref, vocoder=True, text=True):
-    """Padded work of one batch (what the GPU actually executes)."""
-    frames = max_src * EXPECTED_FRAMES_PER_PHONEME
-    c = n * max_ref * COST_REF_FRAME
+def shard_cost(n, max_src, max_ref, vocoder=True, text=True, sum_src=None):
+    """Work of one batch as the GPU executes it: the reference encoder, the encoder and the predictors run on the
+    PADDED batch (n x max length); the decoder's FFT blocks and the vocoder run a ragged schedule, so
+    their work follows the utterances' own (expected) frame counts plus the vocoder's halo; mel_linear / PostNet are
+    padded again.  ``sum_src`` = sum of the utterances' phoneme counts (default: n * max_src, the padded bound)."""
+    if sum_src is None:
+        sum_src = n * max_src
+    c = FIXED_COST + n * max_ref * COST_REF_FRAME
     if text:
-        c += n * (max_src * COST_PHONEME + frames * COST_FRAME)
+        padded_frames = n * max_src * EXPECTED_FRAMES_PER_PHONEME
+        own_frames = sum_src * EXPECTED_FRAMES_PER_PHONEME
+        c += n * max_src * COST_PHONEME + own_frames * (COST_FRAME - 8.7) + padded_frames * 8.7  # 8.7: mel_linear + PostNet
         if vocoder:
-            c += n * frames * COST_VOC_FRAME
+            c += (own_frames + n * VOCODER_HALO_FRAMES) * COST_VOC_FRAME
     return c
 
 
@@ -84,7 +92,8 @@ def plan_shards(src_lens: Sequence[int], ref_lens: Sequence[int], max_batch: int
         if cur and (i is None or b != cur_bucket or len(cur) == max_batch):
             ms = max(src[j] for j in cur) if text else 0
             mr = max(ref[j] for j in cur)
-            shards.append(Shard(len(shards), cur, ms, mr, shard_cost(len(cur), ms, mr, vocoder, text)))
+            shards.append(Shard(len(shards), cur, ms, mr,
+                                shard_cost(len(cur), ms, mr, vocoder, text, sum(src[j] for j in cur) if text else None)))
             cur = []
         if i is not None:
             cur.append(i)
@@ -95,7 +104,47 @@ def plan_shards(src_lens: Sequence[int], ref_lens: Sequence[int], max_batch: int
         r = min(range(n_ranks), key=lambda k: (rank_cost[k], k))
         s.rank = r
         rank_cost[r] += s.cost
+    _refine(shards, rank_cost)
     return ShardPlan(shards, n_ranks, rank_cost)
+
+
+def _refine(shards: List[Shard], rank_cost: List[float], max_rounds: int = 200) -> None:
+    """Deterministic local search after LPT: move one shard from the most loaded rank to another, or swap one of its
+    shards with one of another rank's, whenever that lowers the larger of the two loads; stop when nothing does.
+    With ~8 shards per rank LPT alone leaves ~2 % between the extremes; this brings it to a few tenths."""
+    n = len(rank_cost)
+    if n < 2:
+        return
+    for _ in range(max_rounds):
+        hi = max(range(n), key=lambda k: (rank_cost[k], -k))
+        best = None  # (new larger load, tie-breakers..., action)
+        mine = [s for s in shards if s.rank == hi]
+        for lo in range(n):
+            if lo == hi:
+                continue
+            theirs = [s for s in shards if s.rank == lo]
+            for a in mine:
+                new_hi, new_lo = rank_cost[hi] - a.cost, rank_cost[lo] + a.cost  # move a
+                cand = (max(new_hi, new_lo), a.index, -1, lo)
+                if cand[0] < rank_cost[hi] - 1e-9 and (best is None or cand < best):
+                    best = cand
+                for b in theirs:  # swap a <-> b
+                    new_hi, new_lo = rank_cost[hi] - a.cost + b.cost, rank_cost[lo] + a.cost - b.cost
+                    cand = (max(new_hi, new_lo), a.index, b.index, lo)
+                    if cand[0] < rank_cost[hi] - 1e-9 and (best is None or cand < best):
+                        best = cand
+        if best is None:
+            return
+        _, ai, bi, lo = best
+        a = next(s for s in shards if s.index == ai)
+        rank_cost[hi] -= a.cost
+        rank_cost[lo] += a.cost
+        a.rank = lo
+        if bi >= 0:
+            b = next(s for s in shards if s.index == bi)
+            rank_cost[lo] -= b.cost
+            rank_cost[hi] += b.cost
+            b.rank = hi
 
 
 def make_shard_batch(shard: Shard, speakers, texts: Sequence[torch.Tensor], mels: Sequence[torch.Tensor]) -> Dict:
@@ -123,6 +172,49 @@ def run_rank(plan: ShardPlan, rank: int, compute, speakers, texts, mels) -> Dict
     for shard in plan.shards_of(rank):
         batch = make_shard_batch(shard, speakers, texts, mels)
         res = compute(batch)
+        for row, uid in enumerate(shard.utterances):
+            out[uid] = {k: v[row] for k, v in res.items()}
+    return out
+
+
+def dynamic_order(plan: ShardPlan) -> List[Shard]:
+    """The planned shards, most expensive first: the order in which ranks claim them under the dynamic schedule."""
+    return sorted(plan.shards, key=lambda s: (-s.cost, s.index))
+
+
+class ShardQueue:
+    """Dynamic schedule for one node: ranks claim positions of ``dynamic_order(plan)`` from one counter per sweep in the
+    process group's key-value store (``TCPStore.add`` is atomic).  Host-side control plane only - no GPU data moves
+    and nothing is added to the data path; the shards themselves stay exactly as planned (so results are unchanged and
+    an oracle can still be run on the very same batches), only WHICH GPU runs a shard is decided at run time.  That
+    absorbs what a static assignment cannot see: GPUs of one box differ by a few per cent under their power caps."""
+
+    def __init__(self, store=None, prefix="ss_shard_queue"):
+        if store is None:
+            import torch.distributed as dist
+
+            store = dist.distributed_c10d._get_default_store()
+        self.store, self.prefix = store, prefix
+
+    def claim(self, sweep: int) -> int:
+        """Next unclaimed position of sweep number ``sweep`` (every rank must number its sweeps the same way)."""
+        return int(self.store.add(f"{self.prefix}_{sweep}", 1)) - 1
+
+    def positions(self, sweep: int, n: int):
+        while True:
+            i = self.claim(sweep)
+            if i >= n:
+                return
+            yield i
+
+
+def run_rank_dynamic(plan: ShardPlan, queue: ShardQueue, sweep: int, compute, speakers, texts, mels) -> Dict[int, Dict]:
+    """Like run_rank, but this rank processes whichever planned shards it manages to claim."""
+    order = dynamic_order(plan)
+    out: Dict[int, Dict] = {}
+    for pos in queue.positions(sweep, len(order)):
+        shard = order[pos]
+        res = compute(make_shard_batch(shard, speakers, texts, mels))
         for row, uid in enumerate(shard.utterances):
             out[uid] = {k: v[row] for k, v in res.items()}
     return out

@@ -109,3 +109,48 @@ def test_two_ranks_gloo_match_single_process():
         assert int(single[uid]["mel_len"]) == int(merged[uid]["mel_len"])
         assert torch.equal(single[uid]["postnet_mel"], merged[uid]["postnet_mel"])
     assert r[0]["tot"]["frames"] == float(sum(int(v["mel_len"]) for v in single.values()))
+
+
+def _dynamic_worker(rank, world, port, outdir):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(2)
+    mc = C.model_config("BC2013")
+    sd = S.fastspeech2_state_dict(mc, "BC2013")
+    speakers, texts, mels = _utterances(10, seed=5)
+    plan = SH.plan_shards([t.numel() for t in texts], [m.shape[0] for m in mels], max_batch=3, bucket_width=4,
+                          n_ranks=world, vocoder=False)
+    queue = SH.ShardQueue()
+    out = {}
+    for sweep in (1, 2):  # two sweeps, one counter each
+        out[sweep] = SH.run_rank_dynamic(plan, queue, sweep, _oracle_compute(sd, mc), speakers, texts, mels)
+    torch.save(out, os.path.join(outdir, f"dyn{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_dynamic_schedule_two_ranks_claim_every_shard_exactly_once():
+    """ShardQueue: ranks claim the planned shards from a shared counter; whichever rank runs a shard, the shard is the
+    planned batch, so the union over ranks equals the static / single-process result bit for bit."""
+    world = 2
+    outdir = tempfile.mkdtemp()
+    mp.spawn(_dynamic_worker, args=(world, _free_port(), outdir), nprocs=world, join=True)
+    r = [torch.load(os.path.join(outdir, f"dyn{k}.pt"), weights_only=False) for k in range(world)]
+    mc = C.model_config("BC2013")
+    sd = S.fastspeech2_state_dict(mc, "BC2013")
+    speakers, texts, mels = _utterances(10, seed=5)
+    plan = SH.plan_shards([t.numel() for t in texts], [m.shape[0] for m in mels], max_batch=3, bucket_width=4,
+                          n_ranks=1, vocoder=False)
+    torch.set_num_threads(2)
+    single = SH.run_rank(plan, 0, _oracle_compute(sd, mc), speakers, texts, mels)
+    for sweep in (1, 2):
+        a, b = r[0][sweep], r[1][sweep]
+        assert not (set(a) & set(b)) and sorted({**a, **b}) == list(range(10))
+        merged = {**a, **b}
+        for uid in range(10):
+            assert torch.equal(single[uid]["d_rounded"], merged[uid]["d_rounded"])
+            assert torch.equal(single[uid]["postnet_mel"], merged[uid]["postnet_mel"])
+    order = SH.dynamic_order(plan)
+    assert [s.cost for s in order] == sorted((s.cost for s in plan.shards), reverse=True)
