@@ -56,9 +56,6 @@ __device__ long long g_conv_ss_trace[8 * 256];
 #define CONV_TRACE(ev, i)
 #endif
 
-__device__ __forceinline__ float tf32_rn(float x) {
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
-}
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(NTHREADS, 1)
