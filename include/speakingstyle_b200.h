@@ -194,11 +194,12 @@ SS_API int ss_conv1d_tf32x3_ts2(const ss_conv1d_tf32_params* p, void* stream);
 
 /* Same contract, for the NARROW layers (HiFi-GAN's 64- and 32-channel MRF stages, hifigan/models.py:96-103): the
  * activations of a 128-row tile are fetched once as a panel of 128 + (k-1)*dilation rows (tap j of row r is panel row
- * r + j*dilation) and the weights of all taps stay resident in shared memory, instead of one TMA fetch of both per
- * (tap, chunk) step; hi*W_hi and hi*W_lo are one N = 2*Cout instruction.  Same products as ss_conv1d_tf32x3_ts, equal
- * to ~1 ulp (the correction terms are summed per accumulator-restart group).  Takes: S_in == S_out, k >= 2,
- * Cin in {32, 64}, Cout <= 64, 128 + (k-1)*dilation <= 256 and weights that fit (32 channels: k <= 12, 64 channels:
- * k <= 3): ss_conv1d_tf32x3_panel_supported() returns 1; anything else is SS_ERR_UNSUPPORTED. */
+ * r + j*dilation) and the weights of all taps stay resident in shared memory when they fit (32 channels: k <= 12,
+ * 64 channels: k <= 3) or stream through a ring once per tile, instead of one TMA fetch of both per (tap, chunk) step;
+ * hi*W_hi and hi*W_lo are one N = 2*Cout instruction.  Same products as ss_conv1d_tf32x3_ts, equal to ~1 ulp (the
+ * correction terms are summed per accumulator-restart group).  Takes: S_in == S_out, k >= 2, Cin in {32, 64},
+ * Cout <= 64, 128 + (k-1)*dilation <= 256: ss_conv1d_tf32x3_panel_supported() returns 1 (resident weights) or 2
+ * (streamed); anything else is 0 / SS_ERR_UNSUPPORTED. */
 SS_API int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stream);
 SS_API int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p);
 

@@ -44,7 +44,8 @@ constexpr int MAX_A_SLOTS = 3;
 constexpr int A_STEPS = 2;                         // (tap, chunk) steps per operand hand-over
 constexpr int A_SLOT_COLS = A_STEPS * 2 * KCHUNK;  // [hi | lo] per step
 constexpr int MAX_PAN = 4;               // activation panel ring depth (upper bound)
-constexpr int N_BARS = 2 * MAX_PAN + 1 + 2 * MAX_A_SLOTS + 4;
+constexpr int W_RING = 4;                // weight ring depth when the weights of all taps do not fit (64 channels, k > 3)
+constexpr int N_BARS = 2 * MAX_PAN + 2 * W_RING + 1 + 2 * MAX_A_SLOTS + 4;
 constexpr int MAX_SMEM = 227 * 1024;
 
 struct PanelArgs {
@@ -69,7 +70,10 @@ __device__ long long g_panel_trace[8 * 256];
 // NCHUNK = Cin / 32 is a template parameter, and the weights are always resident: the MMA-issuing thread's loop is the
 // critical path of the narrow tiles (one thread, ~10 % issue efficiency on branchy code - ncu source view), so it is
 // kept free of run-time configuration branches.
-template <int BN, int NCHUNK>
+// RESIDENT: the weights of all taps stay in shared memory (loaded once per CTA); otherwise one [W_hi ; W_lo] tile per
+// (tap, chunk) step streams through a W_RING-deep ring, fetched once per 128-row tile - still half of the per-tap
+// kernel's L2 -> shared-memory traffic, because the activations come once per tile.
+template <int BN, int NCHUNK, bool RESIDENT>
 __global__ void __launch_bounds__(NTHREADS, 1)
 conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                          const __grid_constant__ CUtensorMap tmBl, const TcArgs p, const PanelArgs q, const int in_act,
@@ -95,12 +99,13 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   const int KT = p.k * nchunk;
   const int pan_stage = nchunk * PAN_PARTS * q.panel_bytes;           // one tile's panels (all chunks)
   const int w_off = q.n_pan * pan_stage;
-  const int w_bytes = KT * WT;
+  const int w_bytes = (RESIDENT ? KT : W_RING) * WT;
   const int stg_off = w_off + w_bytes;
   const int bar_off = stg_off + STG_BYTES;
   float* stg_all = reinterpret_cast<float*>(smem_al + stg_off);
   const uint32_t bars = smem0 + bar_off;
-  const uint32_t pfull0 = bars, pempty0 = pfull0 + 8 * MAX_PAN, wres = pempty0 + 8 * MAX_PAN, tafull0 = wres + 8, taempty0 = tafull0 + 8 * MAX_A_SLOTS,
+  const uint32_t pfull0 = bars, pempty0 = pfull0 + 8 * MAX_PAN, wfull0 = pempty0 + 8 * MAX_PAN, wempty0 = wfull0 + 8 * W_RING,
+                 wres = wempty0 + 8 * W_RING, tafull0 = wres + 8, taempty0 = tafull0 + 8 * MAX_A_SLOTS,
                  tfull0 = taempty0 + 8 * MAX_A_SLOTS, tempty0 = tfull0 + 16, tslot = tempty0 + 16;
   volatile uint32_t* tslot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + bar_off + N_BARS * 8);
   int* const rag = reinterpret_cast<int*>(smem_al + bar_off + N_BARS * 8 + 16);
@@ -116,6 +121,10 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     for (int s = 0; s < MAX_PAN; ++s) {
       mbar_init(pfull0 + 8 * s, 1);
       mbar_init(pempty0 + 8 * s, XF_WARPS);  // every split warp has read its last row of the panel
+    }
+    for (int w = 0; w < W_RING; ++w) {
+      mbar_init(wfull0 + 8 * w, 1);
+      mbar_init(wempty0 + 8 * w, 1);
     }
     mbar_init(wres, 1);
     for (int t = 0; t < MAX_A_SLOTS; ++t) {
@@ -146,16 +155,17 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   if (warp == 0) {
     // ================= TMA producer =================
     if (elect_one()) {
-      // every (tap, chunk) weight tile, once per CTA
-      mbar_expect_tx(wres, (uint32_t)(KT * WT));
-      for (int it = 0; it < KT; ++it) {
-        const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
-        tma_load_3d(smem0 + w_off + it * WT, &tmBh, wres, c0, 0, j);
-        tma_load_3d(smem0 + w_off + it * WT + B_BYTES, &tmBl, wres, c0, 0, j);
+      if constexpr (RESIDENT) {  // every (tap, chunk) weight tile, once per CTA
+        mbar_expect_tx(wres, (uint32_t)(KT * WT));
+        for (int it = 0; it < KT; ++it) {
+          const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
+          tma_load_3d(smem0 + w_off + it * WT, &tmBh, wres, c0, 0, j);
+          tma_load_3d(smem0 + w_off + it * WT + B_BYTES, &tmBl, wres, c0, 0, j);
+        }
       }
-      int ps = 0;
-      uint32_t pphase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int ps = 0, ws = 0;
+      uint32_t pphase = 0, wphase = 0;
+      auto load_panel = [&](int tile) {
         int mt, b;
         decode(tile, mt, b);
         mbar_wait(pempty0 + 8 * ps, pphase ^ 1);
@@ -165,6 +175,24 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           tma_load_3d(smem0 + ps * pan_stage + c * PAN_PARTS * q.panel_bytes, &tmA, pfull0 + 8 * ps, c * KCHUNK,
                       mt * BM - p.pad, b);
         if (++ps == q.n_pan) { ps = 0; pphase ^= 1; }
+      };
+      if constexpr (RESIDENT) {
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) load_panel(tile);
+      } else {
+        // the panel of tile i+1 is requested BEFORE the weights of tile i: the weight ring only moves as fast as the
+        // MMAs consume it, and a panel requested behind it would arrive late
+        if ((int)blockIdx.x < num_tiles) load_panel(blockIdx.x);
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+          if (tile + (int)gridDim.x < num_tiles) load_panel(tile + gridDim.x);
+          for (int it = 0; it < KT; ++it) {
+            const int j = it / nchunk, c0 = (it - j * nchunk) * KCHUNK;
+            mbar_wait(wempty0 + 8 * ws, wphase ^ 1);
+            mbar_expect_tx(wfull0 + 8 * ws, (uint32_t)WT);
+            tma_load_3d(smem0 + w_off + ws * WT, &tmBh, wfull0 + 8 * ws, c0, 0, j);
+            tma_load_3d(smem0 + w_off + ws * WT + B_BYTES, &tmBl, wfull0 + 8 * ws, c0, 0, j);
+            if (++ws == W_RING) { ws = 0; wphase ^= 1; }
+          }
+        }
       }
     }
   } else if (warp == 1) {
@@ -177,9 +205,11 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const uint32_t a_base = tmem_base + A_COL0;
       int slot = 0;
       uint32_t sphase = 0;
+      [[maybe_unused]] int ws = 0;
+      [[maybe_unused]] uint32_t wphase = 0;
       int gcount = 0;
       [[maybe_unused]] int hcount = 0;
-      mbar_wait(wres, 0);
+      if constexpr (RESIDENT) mbar_wait(wres, 0);
       // one operand hand-over: STEPS (tap, chunk) steps, 8 MMAs each, straight-line
       auto hand_over = [&](auto steps_c, uint32_t d_tmem, uint32_t bw, uint32_t& accum) {
         constexpr int STEPS = decltype(steps_c)::value;
@@ -190,11 +220,21 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const uint32_t a0 = a_base + slot * A_SLOT_COLS;
 #pragma unroll
         for (int sidx = 0; sidx < STEPS; ++sidx) {
+          uint32_t bws = bw + sidx * WSTEP;  // resident: weight tile `it` of the tile
+          if constexpr (!RESIDENT) {       // streamed: the ring slot this step's weights landed in
+            mbar_wait(wfull0 + 8 * ws, wphase);
+            tc_fence_after();
+            bws = w_lo0 + ws * WSTEP;
+          }
 #pragma unroll
           for (int kk = 0; kk < KCHUNK / 8; ++kk) {  // K = 8 tf32 per instruction: 8 TMEM columns / 32 bytes of B
-            umma_tf32_ts_w(d_tmem, a0 + sidx * 2 * KCHUNK + kk * 8, bw + sidx * WSTEP + kk * 2, idesc2, accum);
+            umma_tf32_ts_w(d_tmem, a0 + sidx * 2 * KCHUNK + kk * 8, bws + kk * 2, idesc2, accum);
             accum = 1u;
-            umma_tf32_ts_w(d_tmem + BN, a0 + sidx * 2 * KCHUNK + KCHUNK + kk * 8, bw + sidx * WSTEP + kk * 2, idesc1, 1u);
+            umma_tf32_ts_w(d_tmem + BN, a0 + sidx * 2 * KCHUNK + KCHUNK + kk * 8, bws + kk * 2, idesc1, 1u);
+          }
+          if constexpr (!RESIDENT) {
+            umma_commit(wempty0 + 8 * ws);
+            if (++ws == W_RING) { ws = 0; wphase ^= 1; }
           }
         }
         umma_commit(taempty0 + 8 * slot);
@@ -377,22 +417,39 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   }
 }
 
-// Shared-memory plan for one layer (all weight tiles resident + 2 or 3 activation panels): false when it does not fit.
-inline bool plan_smem(int bn, int k, int dilation, int nchunk, int B_ragged, PanelArgs& q, int& smem_bytes) {
+// Shared-memory plan for one layer: weights resident (all taps) or streamed through a ring, plus 2 or 3 activation
+// panels.  Returns 0 when nothing fits, 1 for resident weights, 2 for streamed.
+inline int plan_smem(int bn, int k, int dilation, int nchunk, int B_ragged, PanelArgs& q, int& smem_bytes) {
   const int wt = 2 * bn * ROW_BYTES;
   q.R = BM + (k - 1) * dilation;
   q.panel_bytes = (q.R * ROW_BYTES + 1023) / 1024 * 1024;
   const int fixed = STG_BYTES + N_BARS * 8 + 16 + (B_ragged ? (B_ragged + 1) * 4 : 0) + 1024;
   const int parts = nchunk == 1 ? 2 : 1;  // 32-channel layers keep [hi | lo] panels (split once per tile)
-  for (int n_pan = 3; n_pan >= 2; --n_pan) {
-    const int total = n_pan * nchunk * parts * q.panel_bytes + k * nchunk * wt + fixed;
-    if (total <= MAX_SMEM) {
-      q.n_pan = n_pan;
-      smem_bytes = total;
-      return true;
+  for (int resident = 1; resident >= 0; --resident)
+    for (int n_pan = 3; n_pan >= 2; --n_pan) {
+      const int total = n_pan * nchunk * parts * q.panel_bytes + (resident ? k * nchunk : W_RING) * wt + fixed;
+      if (total <= MAX_SMEM) {
+        q.n_pan = n_pan;
+        smem_bytes = total;
+        return resident ? 1 : 2;
+      }
     }
+  return 0;
+}
+
+template <int BN, int NCHUNK, bool RESIDENT>
+int launch_k(const CUtensorMap& tmA, const CUtensorMap& tmBh, const CUtensorMap& tmBl, const TcArgs& a, const PanelArgs& q,
+             int smem, int grid, int in_act, float in_slope, int group, cudaStream_t st) {
+  static std::atomic<unsigned long long> attr_mask{0};  // per device
+  if (needs_attr_on_device(attr_mask)) {
+    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_panel_kernel<BN, NCHUNK, RESIDENT>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
+    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_panel: smem opt-in");
+    attr_done_on_device(attr_mask);
   }
-  return false;
+  conv1d_tf32_panel_kernel<BN, NCHUNK, RESIDENT><<<grid, NTHREADS, smem, st>>>(tmA, tmBh, tmBl, a, q, in_act, in_slope, group);
+  SS_CHECK_LAUNCH("ss_conv1d_tf32x3_panel");
+  return SS_OK;
 }
 
 template <int BN, int NCHUNK>
@@ -400,8 +457,9 @@ int launch(const ss_conv1d_tf32_params* p, const TcArgs& a0, int group, cudaStre
   TcArgs a = a0;
   PanelArgs q;
   int smem = 0;
-  SS_REQUIRE(plan_smem(BN, p->k, p->dilation, NCHUNK, p->rows ? p->B : 0, q, smem), SS_ERR_UNSUPPORTED,
-             "ss_conv1d_tf32x3_panel: the weights of k=%d taps (dilation %d) do not fit shared memory", p->k, p->dilation);
+  const int mode = plan_smem(BN, p->k, p->dilation, NCHUNK, p->rows ? p->B : 0, q, smem);
+  SS_REQUIRE(mode != 0, SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_panel: k=%d dilation=%d does not fit shared memory", p->k,
+             p->dilation);
   CUtensorMap tmA, tmBh, tmBl;
   int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, p->x, (uint64_t)p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
                        (uint64_t)p->x_row_stride * 4, (uint64_t)p->x_batch_stride * 4, KCHUNK, (uint32_t)q.R);
@@ -416,18 +474,11 @@ int launch(const ss_conv1d_tf32_params* p, const TcArgs& a0, int group, cudaStre
   a.m_tiles = (a.S_out + BM - 1) / BM;
   const int64_t tiles = (int64_t)a.B * a.m_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_tf32x3_panel: too many tiles");
-  static std::atomic<unsigned long long> attr_mask{0};  // per device
-  if (needs_attr_on_device(attr_mask)) {
-    cudaError_t e = cudaFuncSetAttribute(conv1d_tf32_panel_kernel<BN, NCHUNK>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
-    if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_tf32x3_panel: smem opt-in");
-    attr_done_on_device(attr_mask);
-  }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_tf32x3_panel: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  conv1d_tf32_panel_kernel<BN, NCHUNK><<<grid, NTHREADS, smem, st>>>(tmA, tmBh, tmBl, a, q, p->in_act, p->in_slope, group);
-  SS_CHECK_LAUNCH("ss_conv1d_tf32x3_panel");
-  return SS_OK;
+  return mode == 1 ? launch_k<BN, NCHUNK, true>(tmA, tmBh, tmBl, a, q, smem, grid, p->in_act, p->in_slope, group, st)
+                   : launch_k<BN, NCHUNK, false>(tmA, tmBh, tmBl, a, q, smem, grid, p->in_act, p->in_slope, group, st);
 }
 
 }  // namespace
@@ -438,9 +489,9 @@ extern "C" __attribute__((visibility("default"))) int ss_debug_panel_trace(long 
 }
 #endif
 
-// 1 if ss_conv1d_tf32x3_panel takes this layer: stride-1 same-length convolution with at least two taps, 32 or 64 input
-// channels, at most 64 output channels, a halo that fits one TMA box, and the weights of all taps fitting shared memory
-// next to two activation panels.
+// Non-zero if ss_conv1d_tf32x3_panel takes this layer: stride-1 same-length convolution with at least two taps, 32 or 64
+// input channels, at most 64 output channels, a halo that fits one TMA box.  1: the weights of all taps stay resident in
+// shared memory; 2: they stream through a ring once per 128-row tile.
 extern "C" int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p) {
   if (!p) return 0;
   if (!(p->S_in == p->S_out && p->k >= 2 && (p->Cin == 32 || p->Cin == 64) && p->Cout > 0 && p->Cout <= 64 &&
@@ -449,7 +500,7 @@ extern "C" int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p) 
     return 0;
   PanelArgs q;
   int smem = 0;
-  return plan_smem(p->Cout > 32 ? 64 : 32, p->k, p->dilation, p->Cin / KCHUNK, p->rows ? p->B : 0, q, smem) ? 1 : 0;
+  return plan_smem(p->Cout > 32 ? 64 : 32, p->k, p->dilation, p->Cin / KCHUNK, p->rows ? p->B : 0, q, smem);
 }
 
 extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stream) {
@@ -460,7 +511,7 @@ extern "C" int ss_conv1d_tf32x3_panel(const ss_conv1d_tf32_params* p, void* stre
              p->S_in, p->S_out, p->Cin, p->Cout, p->k, p->dilation);
   SS_REQUIRE(ss_conv1d_tf32x3_panel_supported(p), SS_ERR_UNSUPPORTED,
              "ss_conv1d_tf32x3_panel: needs S_in == S_out, k >= 2, Cin in {32, 64}, Cout <= 64, 128 + (k-1)*dilation <= 256 "
-             "and all weight tiles resident in shared memory (got S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d pad=%d)", p->S_in, p->S_out, p->Cin, p->Cout, p->k,
+             "(got S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d pad=%d)", p->S_in, p->S_out, p->Cin, p->Cout, p->k,
              p->dilation, p->pad);
   SS_REQUIRE(p->x_row_stride % 4 == 0 && p->x_batch_stride % 4 == 0 && p->y_row_stride % 4 == 0 &&
                  p->y_batch_stride % 4 == 0 && p->y_offset % 4 == 0 && p->y_batch_elems % 4 == 0,

@@ -127,11 +127,13 @@ fp32_backend = "tf32x3"  # "tf32x3": 3xTF32 tcgen05 kernel (default); "ffma": th
 # experiment knobs (environment overrides are for A/B timing only; the defaults are what the tests pin)
 tf32_k_group = int(os.environ.get("SS_TF32_KGROUP", "0"))  # 0 = library default (accumulator restart every 8 chunks)
 # "auto": A operand in tensor memory - the CTA-pair kernel ("ts2") for long reductions, the single-CTA one ("ts") for
-# short ones (they are bit-identical; the pair form is ~3 % faster from 16 chunks up and slower on k = 1, K = 256 layers);
+# short ones (they are bit-identical; the pair form is faster from 12 chunks up and slower on k = 1, K = 256 layers);
 # "ss": split operands in shared memory (the first version, kept as a cross-check)
 tf32_variant = os.environ.get("SS_TF32_VARIANT", "auto")
 # narrow layers (Cin, Cout <= 64, k >= 2: the HiFi-GAN 64- / 32-channel stages) go to the panel kernel in "auto"
 tf32_panel = os.environ.get("SS_TF32_PANEL", "1") != "0"
+# ... including those whose weights stream through a ring (64 channels, k > 3); "0": those stay on the per-tap kernel
+tf32_panel_streamed = os.environ.get("SS_TF32_PANEL_STREAMED", "1") != "0"
 
 
 def tf32_round(t):
@@ -201,13 +203,16 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
         accum_init=int(accum_init), k_group=tf32_k_group, rows=None if rows is None else rows.data_ptr())
     v = variant or tf32_variant
     if v == "auto":
-        # the panel kernel takes the narrow layers whose weights (all taps, hi + lo) stay resident in shared memory:
-        # every 32-channel layer, 64-channel layers with k = 3
-        if (tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2
-                and _lib.lib().ss_conv1d_tf32x3_panel_supported(C.byref(p))):
+        # the panel kernel takes the narrow layers: 1 = weights of all taps resident in shared memory (every 32-channel
+        # layer, 64-channel layers with k = 3), 2 = weights streamed once per tile (64 channels, k = 7 / 11)
+        mode = (_lib.lib().ss_conv1d_tf32x3_panel_supported(C.byref(p))
+                if (tf32_panel and W.cin <= 64 and W.cout <= 64 and W.k >= 2) else 0)
+        if mode == 1 or (mode == 2 and tf32_panel_streamed):
             v = "panel"
         else:
-            v = "ts2" if W.k * ((W.cin + 31) // 32) >= 16 else "ts"
+            # CTA pair from 12 chunks up (128-channel k = 3 layers: 5-13 % faster than the single-CTA kernel,
+            # scripts/hifigan_ncu.py with SS_TF32_VARIANT=ts2); slower on the 8-chunk layers (K = 256, k = 1)
+            v = "ts2" if W.k * ((W.cin + 31) // 32) >= 12 else "ts"
     entry = {"ts": _lib.lib().ss_conv1d_tf32x3_ts, "ts2": _lib.lib().ss_conv1d_tf32x3_ts2,
              "ss": _lib.lib().ss_conv1d_tf32x3, "panel": _lib.lib().ss_conv1d_tf32x3_panel}[v]
     fn = lambda: entry(C.byref(p), _stream())  # noqa: E731

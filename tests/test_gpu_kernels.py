@@ -164,6 +164,8 @@ def test_cta_pair_conv_is_bit_identical_to_single_cta(ops, B, S, Cin, Cout, k, d
     (3, 1000, 32, 32, 11, 5),   # weights resident, halo 25 each side, three panels
     (3, 1000, 32, 32, 3, 1),
     (2, 777, 64, 64, 3, 5),     # 64 channels, S not a multiple of the tile
+    (2, 777, 64, 64, 11, 5),    # weights streamed (22 tiles of 16 KB do not fit)
+    (20, 300, 64, 64, 7, 1),    # streamed, more tiles than CTAs: weight ring wrap-around across tiles
     (2, 640, 64, 64, 3, 3),
     (2, 900, 64, 32, 7, 3),     # Cin != Cout
     (1, 50, 32, 64, 2, 1),      # shorter than a tile, even tap count
@@ -198,12 +200,6 @@ def test_panel_conv_matches_the_per_tap_kernel(ops, B, S, Cin, Cout, k, dil):
     for b_, r in enumerate(rows_host):
         assert torch.equal(out[b_, :r], full[b_, :r]), (b_, r)
         assert bool((out[b_, -(-r // 128) * 128:] == 7.5).all()), (b_, r)
-    # layers whose weights do not fit shared memory are refused (they stay with the per-tap kernel)
-    if Cin == 64 and Cout == 64:
-        from speakingstyle_b200._lib import SSError
-        W11 = ops.pack_conv(torch.randn(64, 64, 11, generator=g).to(DEV) / 26.5)
-        with pytest.raises(SSError):
-            ops.conv1d(x, W11, bias, k=11, pad=5, backend="tf32x3_panel")
     # and against fp64 directly
     ref = torch.nn.functional.conv1d(torch.nn.functional.leaky_relu(x.double(), 0.1).transpose(1, 2),
                                      W.kcc.permute(1, 2, 0).double(), bias.double(), padding=pad, dilation=dil).transpose(1, 2)
