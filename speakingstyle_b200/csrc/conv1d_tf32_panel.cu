@@ -274,12 +274,16 @@ conv1d_tf32_panel_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int t_tile0 = mt * BM;
       const int len = p.lens ? p.lens[b] : 0x7fffffff;
       const bool lean = drain_is_lean<true>(p);  // warp-uniform
-      if (lean && p.residual) {  // pull this tile's residual rows into L2 while its MMAs run
+      const bool pre_accum = lean && p.accum != nullptr && !p.accum_init;  // running mean: read-modify-write
+      if (lean && (p.residual || pre_accum)) {  // pull this tile's residual / running-mean rows into L2 while its MMAs run
         const int t = t_tile0 + lg * 32 + lane;
         const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride;
         if (t < p.S_out && off >= 0 && off < p.y_batch_elems) {
-          const float* rp = static_cast<const float*>(p.residual) + (int64_t)b * p.y_batch_stride + off;
-          for (int c = 0; c < min(BN, p.Cout); c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + c));
+          const int64_t g0 = (int64_t)b * p.y_batch_stride + off;
+          for (int c = 0; c < min(BN, p.Cout); c += 32) {
+            if (p.residual) asm volatile("prefetch.global.L2 [%0];" ::"l"(static_cast<const float*>(p.residual) + g0 + c));
+            if (pre_accum) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.accum + g0 + c));
+          }
         }
       }
       float acc[BN];

@@ -265,7 +265,8 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       }
       const int len = p.lens ? p.lens[b_t] : 0x7fffffff;
       const bool lean = drain_is_lean<true>(p);  // warp-uniform
-      if (lean && p.residual) {
+      const bool pre_accum = lean && p.accum != nullptr && !p.accum_init;  // running mean: read-modify-write
+      if (lean && (p.residual || pre_accum)) {
         // Pull this tile's residual rows into L2 now, while the MMAs run: the drain below keeps only four 16-byte
         // loads per lane in flight, which from HBM (~1 us) capped the whole kernel at ~1.2 TB/s of residual reads.
         int t = t_tile0 + lg * 32 + lane, bb = b_t;
@@ -273,10 +274,12 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           while (t >= p.S_out) { t -= p.S_out; ++bb; }
         const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + nt * BN;
         if (bb < p.B && t < p.S_out && off >= 0 && off < p.y_batch_elems) {
-          const float* rp = static_cast<const float*>(p.residual) + (int64_t)bb * p.y_batch_stride + off;
+          const int64_t g0 = (int64_t)bb * p.y_batch_stride + off;
           const int ncol = min(BN, p.Cout - nt * BN);
-          for (int c = 0; c < ncol; c += 32)  // one 128-byte line per step
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + c));
+          for (int c = 0; c < ncol; c += 32) {  // one 128-byte line per step
+            if (p.residual) asm volatile("prefetch.global.L2 [%0];" ::"l"(static_cast<const float*>(p.residual) + g0 + c));
+            if (pre_accum) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.accum + g0 + c));
+          }
         }
       }
       float acc[BN];

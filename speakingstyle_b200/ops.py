@@ -213,6 +213,11 @@ def _tf32_call(x, W, bias, residual, lens, y, y_act, accum, *, B, S_in, S_out, y
             # CTA pair from 12 chunks up (128-channel k = 3 layers: 5-13 % faster than the single-CTA kernel,
             # scripts/hifigan_ncu.py with SS_TF32_VARIANT=ts2); slower on the 8-chunk layers (K = 256, k = 1)
             v = "ts2" if W.k * ((W.cin + 31) // 32) >= 12 else "ts"
+            # ragged schedule on short sequences (FFT blocks: a few hundred frames per utterance): the pair kernel
+            # schedules 256-row units, so an utterance of 534 frames costs 768 rows against 640 with 128-row tiles -
+            # more than the pair form gains
+            if v == "ts2" and rows is not None and S_out <= 2048:
+                v = "ts"
     entry = {"ts": _lib.lib().ss_conv1d_tf32x3_ts, "ts2": _lib.lib().ss_conv1d_tf32x3_ts2,
              "ss": _lib.lib().ss_conv1d_tf32x3, "panel": _lib.lib().ss_conv1d_tf32x3_panel}[v]
     fn = lambda: entry(C.byref(p), _stream())  # noqa: E731
