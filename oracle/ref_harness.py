@@ -95,7 +95,7 @@ _loaded = {}
 
 def load():
     """Returns a namespace with the reference's FastSpeech2, Generator, AttrDict and helpers."""
-    if _loaded:
+    if "ns" in _loaded:
         return _loaded["ns"]
     if not available():
         raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
