@@ -22,9 +22,15 @@ namespace {
 using namespace sstc;
 
 constexpr int KCHUNK = 32;  // fp32 elements per 128-byte swizzle row
-constexpr int NTHREADS = 320;
+// Eight epilogue warps: two per TMEM lane group, each owning 64 of the tile's 128 columns (accumulator row of 64 floats
+// per thread instead of 128).  With four, the epilogue of a 128 x 128 tile took ~18 k cycles - longer than the main loop
+// of a 12-chunk tile (128 channels, k = 3), and because the correction accumulator is single-buffered the next tile's
+// MMAs waited ~8 k cycles for the slower CTA's epilogue (scripts/conv_trace.py ts2 128 128 3).
+constexpr int EPI_WARPS = 8;
+constexpr int NTHREADS = 32 * (2 + EPI_WARPS + 4);
+constexpr int EPI_STG_BYTES = EPI_WARPS * STG_WARP_BYTES;
 constexpr int BN2 = 128;      // tile width; each CTA of the pair holds BN2 / 2 weight rows
-constexpr int STAGES2 = 6;
+constexpr int STAGES2 = 5;  // 5 x 32 KB + 8 staging tiles
 constexpr int A_SLOTS = 2;
 constexpr int A_SLOT_COLS = 2 * KCHUNK;  // hi | lo
 
@@ -37,7 +43,7 @@ struct Cfg {
   static constexpr int tmem_cols = used_cols <= 32 ? 32 : used_cols <= 64 ? 64 : used_cols <= 128 ? 128 : used_cols <= 256 ? 256 : 512;
   static_assert(used_cols <= 512, "TMEM budget");
   static constexpr int n_bars = 2 * STAGES + 2 * A_SLOTS + 4 + 2;
-  static constexpr int ragged_off = STAGES * stage_bytes + STG_BYTES + n_bars * 8 + 16;  // tile prefix table (ragged schedule)
+  static constexpr int ragged_off = STAGES * stage_bytes + EPI_STG_BYTES + n_bars * 8 + 16;  // tile prefix table (ragged schedule)
   static constexpr int smem_bytes = ragged_off + 1024;  // + (B + 1) * 4 at launch when rows are given
   static_assert(smem_bytes + (RAGGED_MAX_B + 1) * 4 <= 227 * 1024, "shared memory budget");
 };
@@ -125,12 +131,12 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   auto off_bh = [](int s) { return s * C::stage_bytes + A_BYTES; };
   auto off_bl = [](int s) { return s * C::stage_bytes + A_BYTES + C::b_bytes; };
   float* stg_all = reinterpret_cast<float*>(smem_al + STAGES * C::stage_bytes);
-  const uint32_t bars = smem0 + STAGES * C::stage_bytes + STG_BYTES;
+  const uint32_t bars = smem0 + STAGES * C::stage_bytes + EPI_STG_BYTES;
   const uint32_t full0 = bars, empty0 = full0 + 8 * STAGES, tafull0 = empty0 + 8 * STAGES,
                  taempty0 = tafull0 + 8 * A_SLOTS, tfull0 = taempty0 + 8 * A_SLOTS, tempty0 = tfull0 + 16,
                  cfull = tempty0 + 16, cempty = cfull + 8, tslot = cempty + 8;
   volatile uint32_t* tslot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + STG_BYTES + C::n_bars * 8);
+      reinterpret_cast<volatile uint32_t*>(smem_al + STAGES * C::stage_bytes + EPI_STG_BYTES + C::n_bars * 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunk = (p.Cin + KCHUNK - 1) / KCHUNK;
@@ -156,10 +162,10 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull0 + 8 * a, 1);
-      mbar_init(tempty0 + 8 * a, 8);  // epilogue warps of both CTAs
+      mbar_init(tempty0 + 8 * a, 2 * EPI_WARPS);  // epilogue warps of both CTAs
     }
     mbar_init(cfull, 1);
-    mbar_init(cempty, 8);
+    mbar_init(cempty, 2 * EPI_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc2(tslot, (uint32_t)C::tmem_cols);
@@ -247,10 +253,12 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         umma_commit2(cfull);
       }
     }
-  } else if (warp < 6) {
-    // ================= epilogue (warps 2..5) =================
+  } else if (warp < 2 + EPI_WARPS) {
+    // ================= epilogue (warps 2..9): warp w and w + 4 share a lane group, 64 columns each =================
+    const int chalf = (warp - 2) >> 2;          // which 64-column half of the tile this warp owns
+    constexpr int CW = BN / 2;                  // columns per epilogue warp
     const int lg = warp & 3;
-    float* stg = stg_all + lg * 32 * STG_PITCH;
+    float* stg = stg_all + (warp - 2) * 32 * STG_PITCH;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
     int local = 0, gcount = 0;
     for (int tile = pair0; tile < num_tiles; tile += pair_step, ++local) {
@@ -272,19 +280,19 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         int t = t_tile0 + lg * 32 + lane, bb = b_t;
         if (straddle)
           while (t >= p.S_out) { t -= p.S_out; ++bb; }
-        const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + nt * BN;
+        const int64_t off = p.y_offset + (int64_t)t * p.y_row_stride + nt * BN + chalf * CW;
         if (bb < p.B && t < p.S_out && off >= 0 && off < p.y_batch_elems) {
           const int64_t g0 = (int64_t)bb * p.y_batch_stride + off;
-          const int ncol = min(BN, p.Cout - nt * BN);
+          const int ncol = min(CW, p.Cout - nt * BN - chalf * CW);
           for (int c = 0; c < ncol; c += 32) {  // one 128-byte line per step
             if (p.residual) asm volatile("prefetch.global.L2 [%0];" ::"l"(static_cast<const float*>(p.residual) + g0 + c));
             if (pre_accum) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.accum + g0 + c));
           }
         }
       }
-      float acc[BN];
+      float acc[CW];
 #pragma unroll
-      for (int i = 0; i < BN; ++i) acc[i] = 0.f;
+      for (int i = 0; i < CW; ++i) acc[i] = 0.f;
       for (int it0 = 0; it0 < KT; it0 += group, ++gcount) {
         if (it0 + group >= KT) {
           // Last group: its MMAs and the correction terms finish together.  Take the (single-buffered) correction
@@ -294,9 +302,9 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           tc_fence_after();
           if (threadIdx.x == 64) CONV_TRACE(10, local * KT + KT - 1);
 #pragma unroll
-          for (int c0 = 0; c0 < BN; c0 += 32) {
+          for (int c0 = 0; c0 < CW; c0 += 32) {
             float v[32];
-            tmem_ld32(lane_base + 2 * BN + c0, v);
+            tmem_ld32(lane_base + 2 * BN + chalf * CW + c0, v);
 #pragma unroll
             for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];
           }
@@ -309,9 +317,9 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         mbar_wait(tfull0 + 8 * as, (gcount >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = 0; c0 < CW; c0 += 32) {
           float v[32];
-          tmem_ld32(lane_base + as * BN + c0, v);
+          tmem_ld32(lane_base + as * BN + chalf * CW + c0, v);
 #pragma unroll
           for (int i = 0; i < 32; ++i) acc[c0 + i] += v[i];  // round-to-nearest fp32 adds
         }
@@ -321,18 +329,18 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         if (threadIdx.x == 64) CONV_TRACE(7, local * KT + min(it0 + group, KT) - 1);  // stamped at the group's last chunk
       }
 #pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
+      for (int c0 = 0; c0 < CW; c0 += 32) {  // TMEM is free again: the stores overlap the next tile's MMAs
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = acc[c0 + i];
         if (lean)
-          drain_block_lean<true>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + c0, len);
+          drain_block_lean<true>(p, v, stg, lg, lane, b_t, t_tile0, straddle, nt * BN + chalf * CW + c0, len);
         else
-          drain_block(p, v, stg, lg, lane, b, mt, nt * BN + c0, len);
+          drain_block(p, v, stg, lg, lane, b, mt, nt * BN + chalf * CW + c0, len);
       }
     }
   } else {
-    // ================= operand split (warps 6..9): thread = row, shared memory -> registers -> TMEM =========
+    // ================= operand split (warps 10..13): thread = row, shared memory -> registers -> TMEM =========
     const int lg = warp & 3;  // TMEM lane group this warp may write
     const int r = lg * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16) + C::a_col0;
@@ -355,7 +363,7 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       int t_src = t_row - p.pad, cleft = nchunk;  // source frame of this row for the current tap
       for (int it = 0; it < KT; ++it) {
         mbar_wait(full0 + 8 * stage, phase);
-        if (threadIdx.x == 192) CONV_TRACE(1, gi);
+        if (threadIdx.x == 320) CONV_TRACE(1, gi);
         const uint8_t* row = smem_al + off_a(stage) + r * ROW_BYTES;
         // flat tiling: a tap that leaves this row's utterance must read the zero padding, not the neighbour's frames
         const bool outside = edge_tile && (t_src < 0 || t_src >= p.S_in);
@@ -382,17 +390,17 @@ conv1d_tf32_ts2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             lo[i] = outside ? 0.f : lo[i];
           }
         }
-        if (threadIdx.x == 192) CONV_TRACE(5, gi);
+        if (threadIdx.x == 320) CONV_TRACE(5, gi);
         mbar_wait(taempty0 + 8 * slot, sphase ^ 1);  // the MMAs that read this TMEM slot have completed
         tc_fence_after();
-        if (threadIdx.x == 192) CONV_TRACE(6, gi);
+        if (threadIdx.x == 320) CONV_TRACE(6, gi);
         tmem_st32(lane_base + slot * A_SLOT_COLS, hi);
         tmem_st32(lane_base + slot * A_SLOT_COLS + KCHUNK, lo);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cta(tafull0 + 8 * slot, 0);
-        if (threadIdx.x == 192) CONV_TRACE(2, gi);
+        if (threadIdx.x == 320) CONV_TRACE(2, gi);
         ++gi;
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
         if (++slot == A_SLOTS) { slot = 0; sphase ^= 1; }
