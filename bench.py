@@ -560,7 +560,8 @@ def main():
             sys.stderr.write(f"step {dev_ms / args.steps:.3f} ms, convs {tot_ms / args.steps:.3f} ms\n")
         ach = tot_valid / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0
         roof_all = {"kernel": "all conv / linear launches of the step (3xTF32 tcgen05 kernels"
-                              + (" + bf16 tcgen05 kernel)" if args.precision == "bf16" else ")"),
+                              + (" + bf16 tcgen05 kernel)" if args.precision == "bf16" else
+                                 " + split-bf16 bf16x3 tcgen05 kernel for the HiFi-GAN ResBlocks)"),
                     "bound": "tensor", "achieved": ach, "achieved_padded": tot_padded / (tot_ms * 1e-3) / 1e12 if tot_ms else 0.0,
                     "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tflops_sustained"],
                     "launches": len(rows), "avg_launch_ms": tot_ms / max(len(rows), 1), "share_of_step": tot_ms / dev_ms}
@@ -569,6 +570,8 @@ def main():
         key, (c, ms, wv, wp) = next(iter(fam.items()))
         d_ach = wv / (ms * 1e-3) / 1e12
         kname = {"tf32x3": "3xTF32 tcgen05 implicit-GEMM conv (fp32-accurate; conv1d_tf32_ts / _ts2 / hifigan kernels)",
+                 "bf16x3": "conv1d_bf16x3_kernel (split-bf16 tcgen05 implicit-GEMM conv: 3 bf16 MMAs per algorithmic MAC, "
+                           "fp32-class accuracy; HiFi-GAN ResBlocks of the fp32 mode)",
                  "tc": "conv1d_tc_kernel (bf16 tcgen05 implicit-GEMM conv)", "f32": "conv1d_f32_kernel (FP32 pipe)"}[key[0]]
         roof = {"kernel": kname, "shape": f"Cin={key[1]} Cout={key[2]} k={key[3]} dil={key[4]}", "bound": "tensor",
                 "achieved": d_ach, "achieved_padded": wp / (ms * 1e-3) / 1e12, "peak": pk["tflops_sustained"],
@@ -579,12 +582,15 @@ def main():
                 "note": "achieved counts FLOPs on valid positions only (SURVEY 8d); achieved_padded counts every row the "
                         "launch computed.  frac divides by the measured bf16 peak as the contract asks.  A 3xTF32 kernel "
                         "issues 3 TF32 MMAs per algorithmic MAC and the TF32 pipe retires 2048 MAC/clk/SM (half of bf16), "
-                        "so its own ceiling at the SM clock sampled during the run is 148*2048*2*f/3"}
+                        "so its own ceiling at the SM clock sampled during the run is 148*2048*2*f/3; a split-bf16 "
+                        "(bf16x3) kernel issues 3 bf16 MMAs per algorithmic MAC: ceiling = measured bf16 peak / 3"}
         if key[0] == "tf32x3" and clocks.get("sm_mhz"):
             ceil = 148 * 2048 * 2 * clocks["sm_mhz"] * 1e6 / 3.0 / 1e12
             roof["tf32x3_ceiling_at_sampled_clock"] = ceil
             roof["frac_of_3xtf32_ceiling"] = d_ach / ceil
-            roof_all["frac_of_3xtf32_ceiling"] = ach / ceil
+        if key[0] == "bf16x3":
+            roof["bf16x3_ceiling"] = pk["tflops_sustained"] / 3.0
+            roof["frac_of_bf16x3_ceiling"] = d_ach / roof["bf16x3_ceiling"]
         try:  # DRAM bytes of the same conv family from the committed ncu --set full capture (profiles/traffic.json)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
             v_ = tj.get(f"{key[0]} Cin={key[1]} Cout={key[2]} k={key[3]} dil={key[4]}")

@@ -207,6 +207,27 @@ SS_API int ss_conv1d_tf32x3_panel_supported(const ss_conv1d_tf32_params* p);
 SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Split-bf16 ("bf16x3") convolution: fp32-class accuracy from three bf16 tensor-core products per multiply
+ * (x_hi*w_hi + x_hi*w_lo + x_lo*w_hi, fp32 accumulation; ~2^-16 relative per product).  Used by the fp32 mode of
+ * hifigan.Generator for the MRF ResBlock convolutions (reference hifigan/models.py:96-103), where it replaces
+ * ss_conv1d_tf32x3 at twice the tensor-pipe rate.  Same parameter block and epilogue as ss_conv1d_tc, except:
+ *   x      PAIR rows [B, S_in, 2*Cin] bf16 = [hi(Cin) | lo(Cin)], hi = bf16(v), lo = bf16(v - hi)
+ *          (x_row_stride >= 2*Cin); produced by ss_split_bf16 or by this kernel's own y_act
+ *   w      weight tiles packed for the tile width BN = ss_conv1d_bf16x3_plan(Cin, Cout, k, dilation) (0 = layer not
+ *          handled: Cin must be 32 with Cout 32, or a multiple of 64 with Cout 64 or a multiple of 128;
+ *          128 + (k-1)*dilation <= 256).  With W_hi = bf16(W), W_lo = bf16(W - W_hi), W[j, co, ci]:
+ *            Cin % 64 == 0: tile (nt, c, j), index (nt*(Cin/64) + c)*k + j, is [2*BN rows, 64] bf16 with
+ *                           row r < BN = W_hi[j, nt*BN + r, 64c .. 64c+64), row BN + r = W_lo[same]
+ *            Cin == 32:     tile (nt, q), index nt*ceil(k/2) + q, is [64 rows, 64]: row r < 32 =
+ *                           [W_hi[2q, nt*32 + r, 0..32) | W_hi[2q+1, ..]], row 32 + r the same of W_lo (tap k: zeros)
+ *   y_act  PAIR rows [.., 2*Cout] of act2(v) for the next convolution (row-major over the same rows as y)
+ * ss_split_bf16: out[r, 0:C] | out[r, C:2C] = hi | lo of act(x[r, :]), rows x C fp32 in, C % 8 == 0.
+ * ------------------------------------------------------------------------------------------ */
+SS_API int ss_conv1d_bf16x3(const ss_conv1d_tc_params* p, void* stream);
+SS_API int ss_conv1d_bf16x3_plan(int Cin, int Cout, int k, int dilation);
+SS_API int ss_split_bf16(const float* x, void* out, int64_t rows, int C, int act, float slope, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Row-wise LayerNorm with the element-wise steps the reference applies around it, one pass:
  *   v = x (+ residual); v = relu(v) if pre_relu; y = LN(v)*ln_w + ln_b  (eps 1e-5, biased var);
  *   FiLM (model/blocks.py:60-62): y = (s_gamma*gamma[b,:] + 1)*y + s_beta*beta[b,:] if gamma given;

@@ -291,6 +291,30 @@ __global__ void cast_bf16_kernel(const float* __restrict__ x, uint4* __restrict_
   }
 }
 
+// act(x) as split-bf16 pair rows: out[r, 0:C] = hi = bf16(v), out[r, C:2C] = lo = bf16(v - hi); 8 channels per thread
+__global__ void split_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t n8, int C8, int C,
+                                  int act, float slope) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = ss::ld_stream(reinterpret_cast<const float4*>(x) + 2 * i);
+    const float4 b = ss::ld_stream(reinterpret_cast<const float4*>(x) + 2 * i + 1);
+    float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float v0 = ss::apply_act(f[2 * j], act, slope), v1 = ss::apply_act(f[2 * j + 1], act, slope);
+      __nv_bfloat162 hh = __floats2bfloat162_rn(v0, v1);
+      __nv_bfloat162 ll = __floats2bfloat162_rn(v0 - __low2float(hh), v1 - __high2float(hh));
+      h[j] = *reinterpret_cast<uint32_t*>(&hh);
+      l[j] = *reinterpret_cast<uint32_t*>(&ll);
+    }
+    const int64_t row = i / C8;
+    const int c = (int)(i - row * C8) * 8;
+    __nv_bfloat16* dst = out + row * 2 * C + c;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<uint4*>(dst + C) = make_uint4(l[0], l[1], l[2], l[3]);
+  }
+}
+
 inline int row_grid(int64_t rows) { return (int)((rows + ROWS_PER_CTA - 1) / ROWS_PER_CTA); }
 
 }  // namespace
@@ -321,6 +345,18 @@ int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slope, voi
   const int grid = (int)(want < 148 * 16 ? want : 148 * 16);
   cast_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(out), n8, act, slope);
   SS_CHECK_LAUNCH("ss_cast_bf16");
+  return SS_OK;
+}
+
+int ss_split_bf16(const float* x, void* out, int64_t rows, int C, int act, float slope, void* stream) {
+  SS_REQUIRE(x && out && rows > 0 && C > 0 && C % 8 == 0, SS_ERR_INVALID,
+             "ss_split_bf16: bad argument (C must be a multiple of 8)");
+  SS_REQUIRE(ss::aligned16(x) && ss::aligned16(out), SS_ERR_ALIGNMENT, "ss_split_bf16: 16-byte alignment");
+  const int64_t n8 = rows * (C / 8);
+  const int64_t want = (n8 + 255) / 256;
+  const int grid = (int)(want < 148 * 16 ? want : 148 * 16);
+  split_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, static_cast<__nv_bfloat16*>(out), n8, C / 8, C, act, slope);
+  SS_CHECK_LAUNCH("ss_split_bf16");
   return SS_OK;
 }
 

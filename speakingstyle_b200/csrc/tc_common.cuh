@@ -41,6 +41,10 @@ struct TcArgs {
   // The CTA builds the per-utterance tile prefix in shared memory once (ragged_build) and every role maps its linear
   // tile index to (utterance, tile) with a binary search (ragged_decode); never combined with `flat`.
   const int32_t* rows = nullptr;
+  // Split-bf16 pair output (conv1d_bf16x3.cu): when pair_c > 0, y_act is not a plain bf16 copy laid out like y but a
+  // tensor of PAIR rows [.., 2*pair_c] = [hi(pair_c) | lo(pair_c)], hi = bf16(v), lo = bf16(v - hi), for the element
+  // that y holds at flat index g = (row)*pair_c + channel (pair_c = channels per output row).
+  int32_t pair_c = 0;
 };
 constexpr int RAGGED_MAX_B = 1024;  // utterances per launch in the ragged schedule (prefix table in shared memory)
 
@@ -328,6 +332,22 @@ __device__ __forceinline__ float4 act4(float4 f, int act, float slope) {
   return f;
 }
 
+// The activated copy of four consecutive channels whose y index is g: a plain bf16 copy, or (pair_c > 0) the hi / lo
+// halves of a split-bf16 pair row.  co = channel of the first of the four inside its row (only used for pairs).
+__device__ __forceinline__ void store_act4(const TcArgs& p, int64_t g, int co, float4 f) {
+  if (p.pair_c == 0) {
+    *reinterpret_cast<uint2*>(p.y_act + g) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+    return;
+  }
+  const uint2 hi = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+  float a, b, c, d;
+  unpack_bf16(hi.x, a, b);
+  unpack_bf16(hi.y, c, d);
+  __nv_bfloat16* dst = p.y_act + 2 * (g - co) + co;
+  *reinterpret_cast<uint2*>(dst) = hi;
+  *reinterpret_cast<uint2*>(dst + p.pair_c) = make_uint2(pack_bf16(f.x - a, f.y - b), pack_bf16(f.z - c, f.w - d));
+}
+
 // One 32-column block: v[] holds this thread's ROW (TMEM lane) of the block; n_blk = first column.
 __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane, int b,
                                             int mt, int n_blk, int len) {
@@ -343,6 +363,7 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
   if (n >= p.Cout) return;
   float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
   if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+  const int pair_co = p.pair_c > 0 ? n % p.pair_c : 0;
   const int t_first = mt * BM + lg * 32 + rsub;
   const int64_t ybase = (int64_t)b * p.y_batch_stride;
   const float* src = stg + rsub * STG_PITCH + col;
@@ -379,7 +400,7 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
       }
       if (p.y_act) {
         f = act4(f, p.act2, p.slope2);
-        *reinterpret_cast<uint2*>(p.y_act + g) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+        store_act4(p, g, pair_co, f);
       }
     }
     return;
@@ -434,7 +455,7 @@ __device__ __forceinline__ void drain_block(const TcArgs& p, const float (&v)[32
       }
       if (p.y_act) {
         f = act4(f, p.act2, p.slope2);
-        *reinterpret_cast<uint2*>(p.y_act + g[u]) = make_uint2(pack_bf16(f.x, f.y), pack_bf16(f.z, f.w));
+        store_act4(p, g[u], pair_co, f);
       }
     }
   }

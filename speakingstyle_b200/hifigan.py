@@ -13,6 +13,8 @@ Kernel mapping:
                                accumulates (1/3) into the stage mean (xs / num_kernels)
   leaky_relu(0.01) + conv_post + tanh -> ss_hifigan_post (optionally straight to int16 PCM)
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -94,6 +96,11 @@ class Generator(nn.Module, ParamCache):
         if precision not in ("fp32", "bf16"):
             raise ValueError("precision must be 'fp32' or 'bf16'")
         self.precision = precision  # "bf16": tcgen05 convolutions (wave relative L2 <= 1e-2)
+        # fp32 mode, MRF ResBlock convolutions: "bf16x3" = split-bf16 pairs, three bf16 tensor-core products per multiply
+        # (ss_conv1d_bf16x3; wave within ~1e-5 of the reference), "tf32x3" = the 3xTF32 kernels used everywhere else
+        self.fp32_convs = os.environ.get("SS_HIFIGAN_FP32_CONVS", "bf16x3")
+        if self.fp32_convs not in ("bf16x3", "tf32x3"):
+            raise ValueError("SS_HIFIGAN_FP32_CONVS must be 'bf16x3' or 'tf32x3'")
         self.num_kernels = len(h["resblock_kernel_sizes"])
         self.num_upsamples = len(h["upsample_rates"])
         c0 = h["upsample_initial_channel"]
@@ -137,6 +144,8 @@ class Generator(nn.Module, ParamCache):
                               [pack_conv(c.folded_weight()) for c in rb.convs2]))
         wp = self.conv_post.folded_weight()  # [1, C, k] -> [k*C]
         pk["post"] = wp[0].t().contiguous().reshape(-1)
+        # every ResBlock layer must be a shape ss_conv1d_bf16x3 handles, or the whole generator stays on 3xTF32
+        pk["x3"] = all(w.bf16x3 is not None for w1s, w2s in pk["res"] for w in w1s + w2s)
         return pk
 
     # ---------------------------------------------------------------------------------------
@@ -222,6 +231,41 @@ class Generator(nn.Module, ParamCache):
             xa = nxt
         return self._post(xs, pk, pcm, pcm_out, pcm_scale)
 
+    def _forward_x3(self, x, pcm, pcm_out=None, rows=None, pcm_scale=32768.0):
+        """fp32 mode with split-bf16 ResBlocks.  conv_pre and the transposed convolutions stay on the 3xTF32 kernels
+        (fp32 in, fp32 out); inside a stage the residual stream y and the stage mean xs are fp32, and every convolution
+        reads its input as split-bf16 PAIR rows of leaky_relu(.) written by the epilogue that produced it (c1 -> c2:
+        hifigan/models.py:98-101; c2 -> next c1: the residual sum).  Dataflow as in _forward_bf16."""
+        h, pk, nk = self.h, self.packed(), self.num_kernels
+        L = ops.ACT_LRELU
+        rate = 1
+        x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3, rows=rows and rows[rate])
+        for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
+            wu, bu = pk["ups"][i]
+            x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, pad=(k - u) // 2,
+                                     in_act=L, in_slope=LRELU_SLOPE, rows=rows and rows[("up", i)])
+            rate *= u
+            rw = rows and rows[rate]
+            xa = ops.split_bf16(x, act=L, slope=LRELU_SLOPE)  # read by the first c1 of all three ResBlocks
+            xs, ybuf = torch.empty_like(x), torch.empty_like(x)
+            tbuf, yabuf = torch.empty_like(xa), torch.empty_like(xa)
+            for j in range(nk):
+                rb = self.resblocks[i * nk + j]
+                w1s, w2s = pk["res"][i * nk + j]
+                y, ya = x, xa
+                nd, rk = len(rb.dilation), rb.kernel_size
+                for m, dil in enumerate(rb.dilation):
+                    ta = ops.conv1d_x3(ya, w1s[m], rb.convs1[m].bias, dilation=dil, pad=get_padding(rk, dil), want_y=False,
+                                       act2=L, slope2=LRELU_SLOPE, rows=rw, out_pair=tbuf)[1]
+                    if m < nd - 1:
+                        y, ya = ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y, out=ybuf,
+                                              act2=L, slope2=LRELU_SLOPE, rows=rw, out_pair=yabuf)
+                    else:  # last pair: x_j = c2(..) + y goes straight into the stage mean
+                        ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y, want_y=False,
+                                      accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0), rows=rw)
+            x = xs
+        return self._post(x, pk, pcm, pcm_out, pcm_scale)
+
     @torch.no_grad()
     def forward(self, x, channels_last=False, pcm=False, pcm_out=None, frame_lens=None, pcm_scale=32768.0):
         """x: mel [B,80,T] (reference layout) or [B,T,80] with channels_last=True.
@@ -251,6 +295,8 @@ class Generator(nn.Module, ParamCache):
         rows = self._ragged_rows(frame_lens, x.shape[1], x.device) if frame_lens is not None else None
         if self.precision == "bf16":
             return self._forward_bf16(x, pcm, pcm_out, rows, pcm_scale)
+        if self.fp32_convs == "bf16x3" and pk["x3"]:
+            return self._forward_x3(x, pcm, pcm_out, rows, pcm_scale)
         rate = 1
         x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3, rows=rows and rows[rate])
         nk = self.num_kernels

@@ -149,7 +149,7 @@ class ConvW:
     def __init__(self, kcc):
         self.kcc = kcc.contiguous()
         self.k, self.cout, self.cin = self.kcc.shape
-        self._ffma = self._tf32 = self._bf16 = None
+        self._ffma = self._tf32 = self._bf16 = self._bf16x3 = None
 
     @property
     def ffma(self):
@@ -169,6 +169,33 @@ class ConvW:
         if self._bf16 is None:
             self._bf16 = self.kcc.to(torch.bfloat16)
         return self._bf16
+
+
+    @property
+    def bf16x3(self):
+        """Split-bf16 weight tiles for ss_conv1d_bf16x3 (layout: include/speakingstyle_b200.h), or None when the layer
+        shape is not handled by that kernel."""
+        if self._bf16x3 is None:
+            bn = _lib.lib().ss_conv1d_bf16x3_plan(self.cin, self.cout, self.k, 1)
+            if bn == 0:
+                self._bf16x3 = False
+            else:
+                hi = self.kcc.to(torch.bfloat16)
+                lo = (self.kcc - hi.float()).to(torch.bfloat16)
+                if self.cin == 32:  # two taps per 128-byte row
+                    npair = (self.k + 1) // 2
+
+                    def tiles(w):
+                        wp = torch.zeros(2 * npair, self.cout, 32, dtype=w.dtype, device=w.device)
+                        wp[: self.k] = w
+                        return wp.view(npair, 2, self.cout // 32, 32, 32).permute(2, 0, 3, 1, 4).reshape(-1, 32, 64)
+                else:
+                    nch = self.cin // 64
+
+                    def tiles(w):
+                        return w.view(self.k, self.cout // bn, bn, nch, 64).permute(1, 3, 0, 2, 4).reshape(-1, bn, 64)
+                self._bf16x3 = torch.cat([tiles(hi), tiles(lo)], dim=1).contiguous()
+        return None if self._bf16x3 is False else self._bf16x3
 
 
 def pack_conv(weight):
@@ -348,6 +375,49 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
         accum_scale=accum_scale, accum_init=int(accum_init), rows=None if rows is None else rows.data_ptr())
     _tc_call(p, 2.0 * B * S * Cout * k * Cin)
     return y, y_act
+
+
+def split_bf16(x, act=ACT_NONE, slope=0.0):
+    """act(x) [.., C] fp32 -> split-bf16 pair rows [.., 2, C]: hi = bf16(v), lo = bf16(v - hi) (ss_conv1d_bf16x3's input)."""
+    _chk(x, torch.float32, "x")
+    Cn = x.shape[-1]
+    out = torch.empty(x.shape[:-1] + (2, Cn), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().ss_split_bf16(_ptr(x), _ptr(out), x.numel() // Cn, Cn, act, float(slope), _stream()))
+    return out
+
+
+def conv1d_x3(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, residual=None, lens=None, want_y=True,
+              out=None, act2=None, slope2=0.0, accum=None, accum_scale=1.0, accum_init=False, rows=None, out_pair=None):
+    """Split-bf16 convolution (ss_conv1d_bf16x3).  x: pair rows [B,S,2,Cin] bf16 (split_bf16 or a previous y_pair);
+    w: ConvW.  Returns (y fp32 or None, y_pair [B,S,2,Cout] bf16 of act2(v) or None)."""
+    wt = w.bf16x3
+    if wt is None:
+        raise _lib.SSError(f"conv1d_x3: layer Cin={w.cin} Cout={w.cout} k={w.k} is not handled by ss_conv1d_bf16x3")
+    _chk(x, torch.bfloat16, "x"); _chk(bias, torch.float32, "bias")
+    _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum"); _chk(residual, torch.float32, "residual")
+    B, S, two, Cin = x.shape
+    if two != 2 or Cin != w.cin:
+        raise _lib.SSError(f"conv1d_x3: x must be pair rows [B,S,2,{w.cin}], got {tuple(x.shape)}")
+    Cout, k = w.cout, w.k
+    y = None
+    if want_y:
+        y = out if out is not None else torch.empty((B, S, Cout), dtype=torch.float32, device=x.device)
+    y_pair = None
+    if act2 is not None:
+        y_pair = out_pair if out_pair is not None else torch.empty((B, S, 2, Cout), dtype=torch.bfloat16, device=x.device)
+    p = _lib.Conv1dTcParams(
+        x=x.data_ptr(), x_batch_stride=S * 2 * Cin, x_row_stride=2 * Cin, w=wt.data_ptr(),
+        bias=None if bias is None else bias.data_ptr(), residual=None if residual is None else residual.data_ptr(),
+        lens=None if lens is None else lens.data_ptr(), y=None if y is None else y.data_ptr(),
+        y_act=None if y_pair is None else y_pair.data_ptr(), accum=None if accum is None else accum.data_ptr(),
+        y_batch_stride=S * Cout, y_row_stride=Cout, y_offset=0, y_batch_elems=S * Cout, B=B, S_in=S, S_out=S, Cin=Cin,
+        Cout=Cout, k=k, dilation=dilation, pad=pad, act=act, slope=slope, act2=act2 or 0, slope2=slope2,
+        y_dtype=F32, residual_dtype=F32, accum_scale=accum_scale, accum_init=int(accum_init),
+        rows=None if rows is None else rows.data_ptr())
+    fn = lambda: _lib.lib().ss_conv1d_bf16x3(C.byref(p), _stream())  # noqa: E731
+    flops = 2.0 * B * S * Cout * k * Cin
+    check(conv_timer.run(flops, fn, _tag("bf16x3", p), _meta("bf16x3", p)) if conv_timer is not None else fn())
+    return y, y_pair
 
 
 def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True, rows=None):
