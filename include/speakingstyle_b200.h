@@ -140,6 +140,8 @@ typedef struct {
   float accum_scale;
   int32_t accum_init;
   const int32_t* rows;     /* [B] or NULL - ragged schedule, see ss_conv1d_tf32_params */
+  int32_t pair_c;          /* ss_conv1d_bf16x3 only: channels per row of the pair tensor y_act (0 = Cout; the phase
+                              form of a transposed convolution has Cout = stride*cout GEMM columns but cout channels) */
 } ss_conv1d_tc_params;
 SS_API int ss_conv1d_tc(const ss_conv1d_tc_params* p, void* stream);
 

@@ -32,7 +32,7 @@ class Conv1dTcParams(C.Structure):
         ("y_offset", i64), ("y_batch_elems", i64), ("B", i32), ("S_in", i32), ("S_out", i32), ("Cin", i32),
         ("Cout", i32), ("k", i32), ("dilation", i32), ("pad", i32), ("act", i32), ("slope", f32), ("act2", i32),
         ("slope2", f32), ("y_dtype", i32), ("residual_dtype", i32), ("accum_scale", f32), ("accum_init", i32),
-        ("rows", vp),
+        ("rows", vp), ("pair_c", i32),
     ]
 
 

@@ -445,7 +445,9 @@ extern "C" int ss_conv1d_bf16x3(const ss_conv1d_tc_params* p, void* stream) {
   TcArgs a;
   a.bias = p->bias; a.residual = p->residual; a.lens = p->lens; a.y = p->y;
   a.y_act = static_cast<__nv_bfloat16*>(p->y_act); a.accum = p->accum;
-  a.pair_c = p->y_act ? p->Cout : 0;  // the activated copy is a pair row [hi(Cout) | lo(Cout)]
+  a.pair_c = p->y_act ? (p->pair_c > 0 ? p->pair_c : p->Cout) : 0;  // the activated copy is a pair row [hi | lo]
+  SS_REQUIRE(a.pair_c % 8 == 0 && (a.pair_c == 0 || p->Cout % a.pair_c == 0), SS_ERR_INVALID,
+             "ss_conv1d_bf16x3: pair_c (%d) must be a multiple of 8 that divides Cout (%d)", a.pair_c, p->Cout);
   a.y_batch_stride = p->y_batch_stride; a.y_row_stride = p->y_row_stride; a.y_offset = p->y_offset;
   a.y_batch_elems = p->y_batch_elems;
   a.B = p->B; a.S_out = p->S_out; a.Cin = p->Cin; a.Cout = p->Cout; a.k = p->k; a.dilation = p->dilation; a.pad = p->pad;

@@ -232,23 +232,35 @@ class Generator(nn.Module, ParamCache):
         return self._post(xs, pk, pcm, pcm_out, pcm_scale)
 
     def _forward_x3(self, x, pcm, pcm_out=None, rows=None, pcm_scale=32768.0):
-        """fp32 mode with split-bf16 ResBlocks.  conv_pre and the transposed convolutions stay on the 3xTF32 kernels
-        (fp32 in, fp32 out); inside a stage the residual stream y and the stage mean xs are fp32, and every convolution
-        reads its input as split-bf16 PAIR rows of leaky_relu(.) written by the epilogue that produced it (c1 -> c2:
-        hifigan/models.py:98-101; c2 -> next c1: the residual sum).  Dataflow as in _forward_bf16."""
+        """fp32 mode on the split-bf16 kernel (ss_conv1d_bf16x3): transposed convolutions (phase form) and ResBlocks.
+        The residual stream y and the stage mean xs are fp32; every convolution reads its input as split-bf16 PAIR
+        rows of leaky_relu(.) written by the epilogue that produced it (c1 -> c2: hifigan/models.py:98-101; c2 -> next
+        c1: the residual sum; last c2 of a stage -> next transposed convolution: the stage mean).  conv_pre (80 input
+        channels) stays on the 3xTF32 kernel, and so does any transposed convolution whose shape the split-bf16
+        kernel does not take.  Dataflow as in _forward_bf16."""
         h, pk, nk = self.h, self.packed(), self.num_kernels
         L = ops.ACT_LRELU
         rate = 1
         x = ops.conv1d(x, pk["pre"], self.conv_pre.bias, k=7, pad=3, rows=rows and rows[rate])
+        n_up = self.num_upsamples
+        xa = None  # pair rows of leaky_relu(x) when the next transposed convolution runs on the split-bf16 kernel
         for i, (u, k) in enumerate(zip(h["upsample_rates"], h["upsample_kernel_sizes"])):
             wu, bu = pk["ups"][i]
-            x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, pad=(k - u) // 2,
-                                     in_act=L, in_slope=LRELU_SLOPE, rows=rows and rows[("up", i)])
+            if wu.bf16x3 is not None:
+                if xa is None:
+                    xa = ops.split_bf16(x, act=L, slope=LRELU_SLOPE)
+                x, xa = ops.conv_transpose1d_x3(xa, wu, bu, cout=self.ups[i].bias.numel(), stride=u, pad=(k - u) // 2,
+                                                act2=L, slope2=LRELU_SLOPE, rows=rows and rows[("up", i)])
+            else:
+                x = ops.conv_transpose1d(x, wu, bu, cout=self.ups[i].bias.numel(), stride=u, pad=(k - u) // 2,
+                                         in_act=L, in_slope=LRELU_SLOPE, rows=rows and rows[("up", i)])
+                xa = ops.split_bf16(x, act=L, slope=LRELU_SLOPE)
+            # x: the stage input (fp32 residual stream), xa: its leaky-ReLU'd pair, read by the first c1 of all ResBlocks
             rate *= u
             rw = rows and rows[rate]
-            xa = ops.split_bf16(x, act=L, slope=LRELU_SLOPE)  # read by the first c1 of all three ResBlocks
             xs, ybuf = torch.empty_like(x), torch.empty_like(x)
             tbuf, yabuf = torch.empty_like(xa), torch.empty_like(xa)
+            nxt = None
             for j in range(nk):
                 rb = self.resblocks[i * nk + j]
                 w1s, w2s = pk["res"][i * nk + j]
@@ -261,9 +273,14 @@ class Generator(nn.Module, ParamCache):
                         y, ya = ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y, out=ybuf,
                                               act2=L, slope2=LRELU_SLOPE, rows=rw, out_pair=yabuf)
                     else:  # last pair: x_j = c2(..) + y goes straight into the stage mean
-                        ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y, want_y=False,
-                                      accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0), rows=rw)
-            x = xs
+                        # the last ResBlock's epilogue also emits leaky_relu(mean) as the pair the next transposed
+                        # convolution reads (hifigan/models.py:152-153), when that one runs on the split-bf16 kernel
+                        feeds = j == nk - 1 and i < n_up - 1 and pk["ups"][i + 1][0].bf16x3 is not None
+                        nxt = ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y,
+                                            want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0),
+                                            act2=L if feeds else None, slope2=LRELU_SLOPE, rows=rw,
+                                            out_pair=yabuf if feeds else None)[1]
+            x, xa = xs, nxt
         return self._post(x, pk, pcm, pcm_out, pcm_scale)
 
     @torch.no_grad()

@@ -420,6 +420,36 @@ def conv1d_x3(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
     return y, y_pair
 
 
+def conv_transpose1d_x3(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True, rows=None):
+    """ConvTranspose1d in phase form on the split-bf16 kernel.  x: pair rows [B,S,2,Cin] bf16; w: ConvW from
+    pack_conv_transpose; bias tiled to [stride*cout].  Returns (y f32 [B,T_out,cout] or None, pair rows
+    [B,T_out,2,cout] of act2(y) or None)."""
+    wt = w.bf16x3
+    if wt is None:
+        raise _lib.SSError(f"conv_transpose1d_x3: layer Cin={w.cin} Cout={w.cout} is not handled by ss_conv1d_bf16x3")
+    _chk(x, torch.bfloat16, "x"); _chk(bias, torch.float32, "bias")
+    B, S, two, Cin = x.shape
+    if two != 2 or Cin != w.cin or w.cout != stride * cout:
+        raise _lib.SSError(f"conv_transpose1d_x3: x {tuple(x.shape)} / weight [{w.k},{w.cout},{w.cin}] mismatch")
+    taps = w.k
+    T_out = (S - 1) * stride - 2 * pad + taps * stride
+    S_out = (T_out - 1 + pad) // stride + 1
+    y = torch.empty((B, T_out, cout), dtype=torch.float32, device=x.device) if want_y else None
+    y_pair = torch.empty((B, T_out, 2, cout), dtype=torch.bfloat16, device=x.device) if act2 is not None else None
+    p = _lib.Conv1dTcParams(
+        x=x.data_ptr(), x_batch_stride=S * 2 * Cin, x_row_stride=2 * Cin, w=wt.data_ptr(), bias=bias.data_ptr(),
+        residual=None, lens=None, y=None if y is None else y.data_ptr(),
+        y_act=None if y_pair is None else y_pair.data_ptr(), accum=None, y_batch_stride=T_out * cout,
+        y_row_stride=stride * cout, y_offset=-pad * cout, y_batch_elems=T_out * cout, B=B, S_in=S, S_out=S_out, Cin=Cin,
+        Cout=stride * cout, k=taps, dilation=1, pad=taps - 1, act=ACT_NONE, slope=0.0, act2=act2 or 0, slope2=slope2,
+        y_dtype=F32, residual_dtype=F32, accum_scale=0.0, accum_init=0, rows=None if rows is None else rows.data_ptr(),
+        pair_c=cout)
+    fn = lambda: _lib.lib().ss_conv1d_bf16x3(C.byref(p), _stream())  # noqa: E731
+    flops = 2.0 * B * T_out * cout * taps * Cin
+    check(conv_timer.run(flops, fn, _tag("bf16x3", p), _meta("bf16x3", p)) if conv_timer is not None else fn())
+    return y, y_pair
+
+
 def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True, rows=None):
     """ConvTranspose1d in phase form on tensor cores.  x [B,S,Cin] bf16; w [taps, stride*cout, Cin] bf16;
     bias tiled to [stride*cout] f32.  Returns (y f32 [B,T_out,cout] or None, y_act bf16 or None)."""

@@ -113,6 +113,32 @@ def test_conv1d_x3_ragged_schedule(ops, B, S, C, k, dil):
         assert bool((out[i, done:] == -5.0).all()) and bool((outp[i, done:] == -5.0).all())
 
 
+@pytest.mark.parametrize("Cin,Cout,k,u,S", [(512, 256, 16, 8, 50), (256, 128, 16, 8, 333), (128, 64, 4, 2, 1000),
+                                            (64, 32, 4, 2, 2001)])
+def test_conv_transpose_x3(ops, Cin, Cout, k, u, S):
+    """HiFi-GAN's four up-sampling layers (hifigan/models.py:124-127) in phase form, pair rows in and out."""
+    B = 2
+    x = rnd(B, S, Cin, seed=12).to(DEV)
+    w = rnd(Cin, Cout, k, seed=13, scale=1.0 / math.sqrt(Cin * k / u)).to(DEV)
+    b = rnd(Cout, seed=14).to(DEV)
+    W = ops.pack_conv_transpose(w, u)
+    assert W.bf16x3 is not None
+    pad = (k - u) // 2
+    y, yp = ops.conv_transpose1d_x3(ops.split_bf16(x), W, b.repeat(u).contiguous(), cout=Cout, stride=u, pad=pad,
+                                    act2=ops.ACT_LRELU, slope2=0.1)
+    ref = F.conv_transpose1d(x.transpose(1, 2).double(), w.double(), b.double(), stride=u, padding=pad).transpose(1, 2)
+    assert y.shape == ref.shape and yp.shape == (B, ref.shape[1], 2, Cout)
+    scale = ref.abs().max().item()
+    assert (y.double() - ref).abs().max().item() <= TOL * scale
+    assert (unpair(yp) - F.leaky_relu(y, 0.1).double()).abs().max().item() <= 2.0 ** -16 * scale
+    # ragged: rows of the phase-form GEMM (input positions)
+    rows = torch.tensor([S // 3, S], dtype=torch.int32, device=DEV)
+    y2, _ = ops.conv_transpose1d_x3(ops.split_bf16(x), W, b.repeat(u).contiguous(), cout=Cout, stride=u, pad=pad,
+                                    act2=ops.ACT_LRELU, slope2=0.1, rows=rows)
+    n = (S // 3 - 1) * u - pad  # samples fully determined by GEMM rows < S // 3
+    assert torch.equal(y2[0, :n], y[0, :n]) and torch.equal(y2[1], y[1])
+
+
 def test_conv1d_x3_plan_rejects_other_shapes(ops):
     assert ops.pack_conv(torch.zeros(80, 80, 3, device=DEV)).bf16x3 is None
     assert ops.pack_conv(torch.zeros(32, 64, 3, device=DEV)).bf16x3 is None  # [Cout, Cin, k]: Cin 64 -> Cout 32
