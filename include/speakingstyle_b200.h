@@ -252,6 +252,7 @@ typedef struct {
   float* y;
   void* y_bf16;          /* optional bf16 copy of y (A operand of the next tensor-core convolution), or NULL */
   int32_t B, S, C, pre_relu;
+  int32_t bf16_pair;     /* y_bf16 is [B,S,2*C]: split-bf16 pair rows [hi(C) | lo(C)] for ss_conv1d_bf16x3 */
 } ss_layernorm_params;
 SS_API int ss_layernorm(const ss_layernorm_params* p, void* stream);
 

@@ -51,6 +51,7 @@ class LayerNormParams(C.Structure):
     _fields_ = [
         ("x", vp), ("residual", vp), ("ln_w", vp), ("ln_b", vp), ("gamma", vp), ("beta", vp), ("s_gamma", vp),
         ("s_beta", vp), ("lens", vp), ("pe", vp), ("y", vp), ("y_bf16", vp), ("B", i32), ("S", i32), ("C", i32), ("pre_relu", i32),
+        ("bf16_pair", i32),
     ]
 
 

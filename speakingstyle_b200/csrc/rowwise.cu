@@ -34,6 +34,16 @@ __device__ __forceinline__ uint2 pack4_bf16(const float4& o) {
   return make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
 }
 
+__device__ __forceinline__ void store_bf16_or_pair(uint2* yb, int c, int lo_off, int pair, const float4& o) {
+  const uint2 hi = pack4_bf16(o);
+  yb[c] = hi;
+  if (pair) {
+    const float4 r = make_float4(o.x - __uint_as_float(hi.x << 16), o.y - __uint_as_float(hi.x & 0xFFFF0000u),
+                                 o.z - __uint_as_float(hi.y << 16), o.w - __uint_as_float(hi.y & 0xFFFF0000u));
+    yb[c + lo_off] = pack4_bf16(r);
+  }
+}
+
 // LayerNorm over C = 128*V4 floats held in registers (V4 float4 per lane).
 template <int V4>
 __device__ __forceinline__ void ln_normalize(float4 (&v)[V4], int C) {
@@ -63,7 +73,10 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
   const int C = p.C;
   const bool masked = p.lens && t >= p.lens[b];
   float4* y = reinterpret_cast<float4*>(p.y + (int64_t)row * C);
-  uint2* yb = p.y_bf16 ? reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y_bf16) + (int64_t)row * C) : nullptr;
+  // bf16 copy of y, or (bf16_pair) the split-bf16 pair row [hi(C) | lo(C)] that ss_conv1d_bf16x3 reads
+  uint2* yb = p.y_bf16 ? reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.y_bf16) + (int64_t)row * C * (p.bf16_pair ? 2 : 1))
+                       : nullptr;
+  const int lo_off = C / 4;  // uint2 units from hi to lo inside a pair row
   if (masked) {  // result is known without touching x
 #pragma unroll
     for (int i = 0; i < V4; ++i) {
@@ -71,7 +84,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
       float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
       if (p.pe) o = __ldg(reinterpret_cast<const float4*>(p.pe + (int64_t)t * C) + c);
       y[c] = o;
-      if (yb) yb[c] = pack4_bf16(o);
+      if (yb) store_bf16_or_pair(yb, c, lo_off, p.bf16_pair, o);
     }
     return;
   }
@@ -116,7 +129,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const ss_layernorm_param
       o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
     }
     y[c] = o;
-    if (yb) yb[c] = pack4_bf16(o);
+    if (yb) store_bf16_or_pair(yb, c, lo_off, p.bf16_pair, o);
   }
 }
 

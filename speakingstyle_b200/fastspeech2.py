@@ -149,9 +149,12 @@ class FastSpeech2(nn.Module, ParamCache):
             mel, melb = ops.conv1d_tc(xb, self.packed()["mel_w"], self.mel_linear.bias, act2=ops.ACT_NONE, lens=inv_lens)
             postnet_mel = self.postnet(mel, residual=mel, precision="bf16", xb=melb, lens=inv_lens)
         else:
-            x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True)
+            # Everything up to here decides integers (durations, bucket ids) and runs on the 3xTF32 kernels.  From the
+            # decoder on only the mel is produced: its wide layers take the split-bf16 kernels (ops.fp32_convs()).
+            prec = "bf16x3" if ops.fp32_convs() == "bf16x3" else "fp32"
+            x, _ = self.decoder(x, mel_masks, gammas, betas, lens=dec_lens, pe_added=True, precision=prec)
             mel = ops.conv1d(x, self.packed()["mel_w"], self.mel_linear.bias, lens=inv_lens)
-            postnet_mel = self.postnet(mel, residual=mel, lens=inv_lens)
+            postnet_mel = self.postnet(mel, residual=mel, lens=inv_lens, precision=prec)
         out = (mel, postnet_mel, p_pred, e_pred, log_d, d_rounded, src_masks, mel_masks, src_lens_in, mel_lens_out)
         if return_extra:
             extra.update(gammas=gammas, betas=betas)

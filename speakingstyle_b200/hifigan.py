@@ -13,8 +13,6 @@ Kernel mapping:
                                accumulates (1/3) into the stage mean (xs / num_kernels)
   leaky_relu(0.01) + conv_post + tanh -> ss_hifigan_post (optionally straight to int16 PCM)
 """
-import os
-
 import torch
 import torch.nn as nn
 
@@ -96,11 +94,9 @@ class Generator(nn.Module, ParamCache):
         if precision not in ("fp32", "bf16"):
             raise ValueError("precision must be 'fp32' or 'bf16'")
         self.precision = precision  # "bf16": tcgen05 convolutions (wave relative L2 <= 1e-2)
-        # fp32 mode, MRF ResBlock convolutions: "bf16x3" = split-bf16 pairs, three bf16 tensor-core products per multiply
-        # (ss_conv1d_bf16x3; wave within ~1e-5 of the reference), "tf32x3" = the 3xTF32 kernels used everywhere else
-        self.fp32_convs = os.environ.get("SS_HIFIGAN_FP32_CONVS", "bf16x3")
-        if self.fp32_convs not in ("bf16x3", "tf32x3"):
-            raise ValueError("SS_HIFIGAN_FP32_CONVS must be 'bf16x3' or 'tf32x3'")
+        # fp32 mode: "bf16x3" = split-bf16 pairs, three bf16 tensor-core products per multiply (ss_conv1d_bf16x3; wave
+        # within ~2e-5 of the reference), "tf32x3" = the 3xTF32 kernels (environment variable SS_FP32_CONVS)
+        self.fp32_convs = ops.fp32_convs()
         self.num_kernels = len(h["resblock_kernel_sizes"])
         self.num_upsamples = len(h["upsample_rates"])
         c0 = h["upsample_initial_channel"]

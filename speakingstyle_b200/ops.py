@@ -377,6 +377,20 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
     return y, y_act
 
 
+def x3_ok(w):
+    """True when ss_conv1d_bf16x3 handles this ConvW's shape."""
+    return isinstance(w, ConvW) and w.bf16x3 is not None
+
+
+def fp32_convs():
+    """Which kernels the fp32 mode uses where no integer decision is downstream (HiFi-GAN, FastSpeech2's decoder and
+    PostNet): "bf16x3" (split-bf16, default) or "tf32x3" (environment variable SS_FP32_CONVS)."""
+    v = os.environ.get("SS_FP32_CONVS", "bf16x3")
+    if v not in ("bf16x3", "tf32x3"):
+        raise ValueError("SS_FP32_CONVS must be 'bf16x3' or 'tf32x3'")
+    return v
+
+
 def split_bf16(x, act=ACT_NONE, slope=0.0):
     """act(x) [.., C] fp32 -> split-bf16 pair rows [.., 2, C]: hi = bf16(v), lo = bf16(v - hi) (ss_conv1d_bf16x3's input)."""
     _chk(x, torch.float32, "x")
@@ -474,8 +488,9 @@ def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0,
 
 
 def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pre_relu=False, out=None,
-              want_bf16=False):
-    """film = (gamma [B,C], beta [B,C], s_gamma [1], s_beta [1]) or None.  With want_bf16 returns (y, y_bf16)."""
+              want_bf16=False, want_pair=False):
+    """film = (gamma [B,C], beta [B,C], s_gamma [1], s_beta [1]) or None.  With want_bf16 returns (y, y_bf16); with
+    want_pair (y, split-bf16 pair rows [B,S,2,C])."""
     _chk(x, torch.float32, "x"); _chk(residual, torch.float32, "residual"); _chk(lens, torch.int32, "lens")
     _chk(pe, torch.float32, "pe"); _chk(ln_w, torch.float32, "ln_w"); _chk(ln_b, torch.float32, "ln_b")
     B, S, Cc = x.shape
@@ -483,6 +498,8 @@ def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pr
         raise _lib.SSError("layernorm: position table too small")
     y = out if out is not None else torch.empty_like(x)
     yb = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if want_bf16 else None
+    if want_pair:
+        yb = torch.empty((B, S, 2, Cc), dtype=torch.bfloat16, device=x.device)
     g = be = sg = sb = None
     if film is not None:
         g, be, sg, sb = film
@@ -493,9 +510,9 @@ def layernorm(x, ln_w, ln_b, *, residual=None, film=None, lens=None, pe=None, pr
         ln_b=ln_b.data_ptr(), gamma=None if g is None else g.data_ptr(), beta=None if be is None else be.data_ptr(),
         s_gamma=None if sg is None else sg.data_ptr(), s_beta=None if sb is None else sb.data_ptr(),
         lens=None if lens is None else lens.data_ptr(), pe=None if pe is None else pe.data_ptr(), y=y.data_ptr(),
-        y_bf16=None if yb is None else yb.data_ptr(), B=B, S=S, C=Cc, pre_relu=int(pre_relu))
+        y_bf16=None if yb is None else yb.data_ptr(), B=B, S=S, C=Cc, pre_relu=int(pre_relu), bf16_pair=int(want_pair))
     check(_lib.lib().ss_layernorm(C.byref(p), _stream()))
-    return (y, yb) if want_bf16 else y
+    return (y, yb) if (want_bf16 or want_pair) else y
 
 
 def attention(qkv, lens, n_head, backend=None):

@@ -114,10 +114,11 @@ class MultiHeadAttention(nn.Module, ParamCache):
             "wfc": pack_conv(self.fc.weight),
         }
 
-    def forward(self, x, lens, mask_rows=True, xb=None):
+    def forward(self, x, lens, mask_rows=True, xb=None, xp=None):
         """x [B,S,D] -> LayerNorm(fc(attention) + x), rows >= lens zeroed (Layers.py:27-28).
         With ``xb`` (bf16 copy of x) the two projections run on the tensor cores and the result is
-        returned as (fp32, bf16)."""
+        returned as (fp32, bf16).  With ``xp`` (split-bf16 pair rows of x) they run on ss_conv1d_bf16x3 (fp32-class
+        accuracy) and the result is (fp32, pair rows)."""
         pk = self.packed()
         ln = self.layer_norm
         # Ragged schedule: the attention kernel reads only Q / K / V rows below ceil128(lens) and writes zeros for the
@@ -130,6 +131,11 @@ class MultiHeadAttention(nn.Module, ParamCache):
             ctx = ops.attention(qkv, lens, self.n_head)
             y, _ = ops.conv1d_tc(ops.cast_bf16(ctx), pk["wfc"], self.fc.bias, residual=x, rows=rows)
             return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y, want_bf16=True)
+        if xp is not None:
+            qkv, _ = ops.conv1d_x3(xp, pk["wqkv"], pk["bqkv"], rows=rows)
+            ctx = ops.attention(qkv, lens, self.n_head)
+            y, _ = ops.conv1d_x3(ops.split_bf16(ctx), pk["wfc"], self.fc.bias, residual=x, rows=rows)
+            return ops.layernorm(y, ln.weight, ln.bias, lens=lens if mask_rows else None, out=y, want_pair=True)
         qkv = ops.conv1d(x, pk["wqkv"], pk["bqkv"], rows=rows)
         ctx = ops.attention(qkv, lens, self.n_head)
         y = ops.conv1d(ctx, pk["wfc"], self.fc.bias, residual=x, rows=rows)
@@ -149,7 +155,7 @@ class PositionwiseFeedForward(nn.Module, ParamCache):
     def _pack(self):
         return {"w1": pack_conv(self.w_1.weight), "w2": pack_conv(self.w_2.weight)}
 
-    def forward(self, x, lens=None, film=None, xb=None):
+    def forward(self, x, lens=None, film=None, xb=None, xp=None):
         pk = self.packed()
         k1, k2 = self.kernel_size
         ln = self.layer_norm
@@ -166,6 +172,11 @@ class PositionwiseFeedForward(nn.Module, ParamCache):
                                  out_dtype=torch.bfloat16, rows=rows)
             y, _ = ops.conv1d_tc(h, pk["w2"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x, rows=rows)
             return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y, want_bf16=True)
+        if xp is not None:  # split-bf16 path: the 1024-channel intermediate only ever exists as pair rows of relu(.)
+            _, hp = ops.conv1d_x3(xp, pk["w1"], self.w_1.bias, pad=(k1 - 1) // 2, want_y=False, act2=ops.ACT_RELU, lens=hl,
+                                  rows=rows)
+            y, _ = ops.conv1d_x3(hp, pk["w2"], self.w_2.bias, pad=(k2 - 1) // 2, residual=x, rows=rows)
+            return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y, want_pair=True)
         h = ops.conv1d(x, pk["w1"], self.w_1.bias, k=k1, pad=(k1 - 1) // 2, act=ops.ACT_RELU, lens=hl, rows=rows)
         y = ops.conv1d(h, pk["w2"], self.w_2.bias, k=k2, pad=(k2 - 1) // 2, residual=x, rows=rows)
         return ops.layernorm(y, ln.weight, ln.bias, film=film, lens=lens, out=y)
@@ -181,7 +192,7 @@ class FFTBlock(nn.Module):
         if film:
             self.film = FiLM()
 
-    def forward(self, enc_input, gammas=None, betas=None, mask=None, slf_attn_mask=None, lens=None, xb=None):
+    def forward(self, enc_input, gammas=None, betas=None, mask=None, slf_attn_mask=None, lens=None, xb=None, xp=None):
         """Returns (output, None): the attention probabilities the reference returns here are
         dropped by every caller (Models.py:98-101) and are never materialised.
         With ``xb`` (bf16 copy of the input) the block runs its projections and convolutions on the
@@ -192,6 +203,9 @@ class FFTBlock(nn.Module):
         if xb is not None:
             x, xb = self.slf_attn(enc_input, lens, xb=xb)
             return self.pos_ffn(x, lens=lens, film=film, xb=xb), None
+        if xp is not None:  # split-bf16 pair rows: ((fp32, pair), None)
+            x, xp = self.slf_attn(enc_input, lens, xp=xp)
+            return self.pos_ffn(x, lens=lens, film=film, xp=xp), None
         x = self.slf_attn(enc_input, lens)
         x = self.pos_ffn(x, lens=lens, film=film)
         return x, None
@@ -267,6 +281,15 @@ class Decoder(nn.Module, _PositionTable):
             for layer in self.layer_stack:
                 (x, xb), _ = layer(x, gammas=gammas, betas=betas, lens=lens, xb=xb)
             return ((x, xb), mask) if return_bf16 else (x, mask)
+        if precision == "bf16x3" and all(ops.x3_ok(w) for layer in self.layer_stack for w in (
+                layer.slf_attn.packed()["wqkv"], layer.slf_attn.packed()["wfc"], layer.pos_ffn.packed()["w1"],
+                layer.pos_ffn.packed()["w2"])):
+            # fp32 mode, split-bf16 kernels: nothing downstream of the decoder decides an integer, and the mel stays
+            # within ~1e-5 of the 3xTF32 path (bar 1e-3)
+            xp = ops.split_bf16(x)
+            for layer in self.layer_stack:
+                (x, xp), _ = layer(x, gammas=gammas, betas=betas, lens=lens, xp=xp)
+            return x, mask
         for layer in self.layer_stack:
             x, _ = layer(x, gammas=gammas, betas=betas, lens=lens)
         return x, mask
@@ -337,8 +360,19 @@ class PostNet(nn.Module, ParamCache):
                                      residual=residual if last else None, lens=lens,
                                      out_dtype=torch.float32 if last else torch.bfloat16)
             return h
+        xp = None
         for i, (w, b) in enumerate(pk):
             last = i == n - 1
-            x = ops.conv1d(x, w, b, k=k, pad=(k - 1) // 2, act=ops.ACT_NONE if last else ops.ACT_TANH,
-                           residual=residual if last else None, lens=lens)
+            act = ops.ACT_NONE if last else ops.ACT_TANH
+            if precision == "bf16x3" and ops.x3_ok(w):
+                # split-bf16 kernel for the 512 -> 512 layers; the next layer takes pair rows of tanh(.) if it runs on
+                # this kernel too, else fp32
+                if xp is None:
+                    xp = ops.split_bf16(x)
+                nxt_x3 = not last and ops.x3_ok(pk[i + 1][0])
+                x, xp = ops.conv1d_x3(xp, w, b, pad=(k - 1) // 2, act=act, residual=residual if last else None, lens=lens,
+                                      want_y=not nxt_x3, act2=ops.ACT_NONE if nxt_x3 else None)
+            else:
+                x = ops.conv1d(x, w, b, k=k, pad=(k - 1) // 2, act=act, residual=residual if last else None, lens=lens)
+                xp = None
         return x
