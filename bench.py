@@ -572,7 +572,8 @@ def main():
         kname = {"tf32x3": "3xTF32 tcgen05 implicit-GEMM conv (fp32-accurate; conv1d_tf32_ts / _ts2 / hifigan kernels)",
                  "bf16x3": "conv1d_bf16x3_kernel (split-bf16 tcgen05 implicit-GEMM conv: 3 bf16 MMAs per algorithmic MAC, "
                            "fp32-class accuracy; HiFi-GAN ResBlocks of the fp32 mode)",
-                 "tc": "conv1d_tc_kernel (bf16 tcgen05 implicit-GEMM conv)", "f32": "conv1d_f32_kernel (FP32 pipe)"}[key[0]]
+                 "tc": "conv1d_tc_kernel (bf16 tcgen05 implicit-GEMM conv)",
+                 "tcp": "conv1d_bf16x3_kernel<SPLIT=false> (bf16 tcgen05 implicit-GEMM conv, panel feeding)", "f32": "conv1d_f32_kernel (FP32 pipe)"}[key[0]]
         roof = {"kernel": kname, "shape": f"Cin={key[1]} Cout={key[2]} k={key[3]} dil={key[4]}", "bound": "tensor",
                 "achieved": d_ach, "achieved_padded": wp / (ms * 1e-3) / 1e12, "peak": pk["tflops_sustained"],
                 "unit": "TFLOP/s", "frac": d_ach / pk["tflops_sustained"], "traffic": None, "launches": c,

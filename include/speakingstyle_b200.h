@@ -227,6 +227,10 @@ SS_API int ss_cast_bf16(const float* x, void* out, int64_t n, int act, float slo
  * ------------------------------------------------------------------------------------------ */
 SS_API int ss_conv1d_bf16x3(const ss_conv1d_tc_params* p, void* stream);
 SS_API int ss_conv1d_bf16x3_plan(int Cin, int Cout, int k, int dilation);
+/* The same kernel with ONE bf16 number per value: ss_conv1d_tc's contract (x [B,S_in,Cin] bf16, y_act a plain bf16 copy)
+ * for the layer shapes ss_conv1d_bf16x3_plan accepts, with the activations fetched once per tile instead of once per tap.
+ * w: the W_hi half of the tiles above ([BN rows, 64] per tile, same order). */
+SS_API int ss_conv1d_bf16_panel(const ss_conv1d_tc_params* p, void* stream);
 SS_API int ss_split_bf16(const float* x, void* out, int64_t rows, int C, int act, float slope, void* stream);
 
 /* ------------------------------------------------------------------------------------------

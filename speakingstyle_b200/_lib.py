@@ -79,6 +79,7 @@ _SIGNATURES = {
     "ss_conv1d_tf32x3_panel_supported": (C.c_int, [C.POINTER(Conv1dTf32Params)]),
     "ss_cast_bf16": (C.c_int, [vp, vp, i64, C.c_int, f32, vp]),
     "ss_conv1d_bf16x3": (C.c_int, [C.POINTER(Conv1dTcParams), vp]),
+    "ss_conv1d_bf16_panel": (C.c_int, [C.POINTER(Conv1dTcParams), vp]),
     "ss_conv1d_bf16x3_plan": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "ss_split_bf16": (C.c_int, [vp, vp, i64, C.c_int, C.c_int, f32, vp]),
     "ss_layernorm": (C.c_int, [C.POINTER(LayerNormParams), vp]),

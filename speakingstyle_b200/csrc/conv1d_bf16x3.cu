@@ -76,7 +76,7 @@ __device__ __forceinline__ void umma_bf16_w(uint32_t tmem_d, uint32_t a_lo, uint
 __device__ __forceinline__ bool drain_is_dense(const TcArgs& p) {
   return p.act == SS_ACT_NONE && p.y_dtype == SS_F32 && p.residual_dtype == SS_F32 && p.lens == nullptr &&
          p.y_offset == 0 && p.y_row_stride == p.Cout && p.y_batch_stride == (int64_t)p.S_out * p.Cout &&
-         p.y_batch_elems == (int64_t)p.S_out * p.Cout && (p.y_act == nullptr || p.pair_c == p.Cout);
+         p.y_batch_elems == (int64_t)p.S_out * p.Cout && (p.y_act == nullptr || p.pair_c == p.Cout || p.pair_c == 0);
 }
 __device__ __forceinline__ void drain_block_dense(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane, int b,
                                                   int mt, int n_blk) {
@@ -98,7 +98,8 @@ __device__ __forceinline__ void drain_block_dense(const TcArgs& p, const float (
   const bool pre_acc = p.accum != nullptr && !p.accum_init;
   float* const y = p.y ? static_cast<float*>(p.y) + g0 : nullptr;
   float* const acc = p.accum ? p.accum + g0 : nullptr;
-  __nv_bfloat16* const pair = p.y_act ? p.y_act + 2 * g0 - n : nullptr;
+  const bool plain = p.pair_c == 0;  // y_act is a plain bf16 copy laid out like y, not a pair row
+  __nv_bfloat16* const pair = p.y_act ? (plain ? p.y_act + g0 : p.y_act + 2 * g0 - n) : nullptr;
 #pragma unroll
   for (int half = 0; half < 2; ++half) {
     float4 rpre[4], apre[4];
@@ -132,30 +133,38 @@ __device__ __forceinline__ void drain_block_dense(const TcArgs& p, const float (
         float a0, a1, a2, a3;
         unpack_bf16(hi.x, a0, a1);
         unpack_bf16(hi.y, a2, a3);
-        __nv_bfloat16* dst = pair + 2 * i * gstep;
-        *reinterpret_cast<uint2*>(dst) = hi;
-        *reinterpret_cast<uint2*>(dst + p.Cout) = make_uint2(pack_bf16(f.x - a0, f.y - a1), pack_bf16(f.z - a2, f.w - a3));
+        if (plain) {
+          *reinterpret_cast<uint2*>(pair + i * gstep) = hi;
+        } else {
+          __nv_bfloat16* dst = pair + 2 * i * gstep;
+          *reinterpret_cast<uint2*>(dst) = hi;
+          *reinterpret_cast<uint2*>(dst + p.Cout) = make_uint2(pack_bf16(f.x - a0, f.y - a1), pack_bf16(f.z - a2, f.w - a3));
+        }
       }
     }
   }
 }
 
-template <int BN, bool NARROW, bool RESIDENT>
+// SPLIT = false is the plain bf16 convolution of the bf16 mode (ss_conv1d_bf16_panel): the same feeding and roles with
+// one bf16 number per value - activation rows [B, S, C], weight tiles of BN rows, one accumulator, a third of the MMAs.
+template <int BN, bool NARROW, bool RESIDENT, bool SPLIT>
 __global__ void __launch_bounds__(nthreads_of(BN), 1)
 conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const TcArgs p,
                      const X3Args q) {
-  constexpr int WT = 2 * BN * ROW_BYTES;  // one weight tile: [W_hi rows ; W_lo rows] x 128 bytes
+  constexpr int NP = SPLIT ? 2 : 1;        // bf16 numbers per value
+  constexpr int WT = NP * BN * ROW_BYTES;  // one weight tile: [W_hi rows ; W_lo rows] x 128 bytes
+  constexpr int ACC = NP * BN;             // columns of one accumulator buffer: [main | correction]
   constexpr int NBUF = nbuf_of(BN);
   constexpr int EPI_WARPS = 4 * NBUF;
-  constexpr int TMEM_COLS = NBUF * 2 * BN;
+  constexpr int TMEM_COLS = NBUF * ACC;
   static_assert(TMEM_COLS <= 512 && TMEM_COLS >= 32 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && 2 * BN <= 256,
                 "TMEM / MMA N budget");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
   const int nchunk = NARROW ? 1 : p.Cin / 64;
-  const int a_stage = (NARROW ? 1 : 2) * q.panel_bytes;
-  const uint32_t a_tx = (uint32_t)((NARROW ? 1 : 2) * q.R * ROW_BYTES);
+  const int a_stage = (NARROW ? 1 : NP) * q.panel_bytes;
+  const uint32_t a_tx = (uint32_t)((NARROW ? 1 : NP) * q.R * ROW_BYTES);
   const int w_off = q.n_a * a_stage;
   const int stg_off = w_off + q.n_w * WT;
   const int bar_off = stg_off + EPI_WARPS * STG_WARP_BYTES;
@@ -225,10 +234,11 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           mbar_expect_tx(afull0 + 8 * as, a_tx);
           const uint32_t dst = smem0 + as * a_stage;
           if (NARROW) {
-            tma_load_3d(dst, &tmA, afull0 + 8 * as, 0, t0, b);  // [hi(32) | lo(32)] is one 128-byte row
+            // [hi(32) | lo(32)] is one 128-byte row; plain bf16: [x(32) | zero fill past the 32 channels]
+            tma_load_3d(dst, &tmA, afull0 + 8 * as, 0, t0, b);
           } else {
-            tma_load_3d(dst, &tmA, afull0 + 8 * as, 64 * c, t0, b);                         // hi
-            tma_load_3d(dst + q.panel_bytes, &tmA, afull0 + 8 * as, p.Cin + 64 * c, t0, b);  // lo
+            tma_load_3d(dst, &tmA, afull0 + 8 * as, 64 * c, t0, b);                                     // hi
+            if (SPLIT) tma_load_3d(dst + q.panel_bytes, &tmA, afull0 + 8 * as, p.Cin + 64 * c, t0, b);  // lo
           }
           if (++as == q.n_a) { as = 0; aph ^= 1; }
           if (!RESIDENT) {
@@ -245,7 +255,7 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (elect_one()) {
-      const uint32_t idesc_m = make_idesc(1u, 2 * BN);  // x_hi * [W_hi ; W_lo] -> [main | correction]
+      const uint32_t idesc_m = make_idesc(1u, ACC);     // x_hi * [W_hi ; W_lo] -> [main | correction]
       const uint32_t idesc_h = make_idesc(1u, BN);      // x_lo * W_hi -> correction
       const uint32_t w_lo0 = desc_lo(smem0 + w_off);
       const uint32_t tap_step = (uint32_t)(p.dilation * ROW_BYTES) >> 4;  // descriptor units (16 bytes) per tap
@@ -259,7 +269,7 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const int ab = local % NBUF;
         mbar_wait(tempty0 + 8 * ab, ((local / NBUF) & 1) ^ 1);  // epilogue set ab has read this buffer
         tc_fence_after();
-        const uint32_t d_main = tmem_base + ab * 2 * BN, d_corr = d_main + BN;
+        const uint32_t d_main = tmem_base + ab * ACC, d_corr = d_main + BN;
         for (int c = 0; c < nchunk; ++c) {
           mbar_wait(afull0 + 8 * as, aph);
           tc_fence_after();
@@ -271,8 +281,10 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               const uint32_t b = w_lo0 + (uint32_t)(j >> 1) * (WT >> 4) + (uint32_t)(j & 1) * 4;
               umma_bf16_w(d_main, a, b, idesc_m, j != 0);
               umma_bf16_w(d_main, a + 2, b + 2, idesc_m, 1);
-              umma_bf16_w(d_corr, a + 4, b, idesc_h, 1);
-              umma_bf16_w(d_corr, a + 6, b + 2, idesc_h, 1);
+              if (SPLIT) {
+                umma_bf16_w(d_corr, a + 4, b, idesc_h, 1);
+                umma_bf16_w(d_corr, a + 6, b + 2, idesc_h, 1);
+              }
             }
           } else {
             uint32_t ah = a0;
@@ -291,10 +303,12 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               umma_bf16_w(d_main, ah + 2, b + 2, idesc_m, 1);
               umma_bf16_w(d_main, ah + 4, b + 4, idesc_m, 1);
               umma_bf16_w(d_main, ah + 6, b + 6, idesc_m, 1);
-              umma_bf16_w(d_corr, al, b, idesc_h, 1);
-              umma_bf16_w(d_corr, al + 2, b + 2, idesc_h, 1);
-              umma_bf16_w(d_corr, al + 4, b + 4, idesc_h, 1);
-              umma_bf16_w(d_corr, al + 6, b + 6, idesc_h, 1);
+              if (SPLIT) {
+                umma_bf16_w(d_corr, al, b, idesc_h, 1);
+                umma_bf16_w(d_corr, al + 2, b + 2, idesc_h, 1);
+                umma_bf16_w(d_corr, al + 4, b + 4, idesc_h, 1);
+                umma_bf16_w(d_corr, al + 6, b + 6, idesc_h, 1);
+              }
               if (!RESIDENT) {
                 umma_commit(wempty0 + 8 * ws);
                 if (++ws == q.n_w) { ws = 0; wph ^= 1; }
@@ -312,7 +326,7 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const int e = (warp - 2) >> 2, lg = warp & 3;
     const bool dense = drain_is_dense(p);  // warp-uniform
     float* stg = stg_all + (warp - 2) * 32 * STG_PITCH;
-    const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + e * 2 * BN;
+    const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + e * ACC;
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       if (local % NBUF != e) continue;
@@ -323,10 +337,15 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       tc_fence_after();
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        float v[32], cr[32];
-        tmem_ld32x2(acc + c0, v, acc + BN + c0, cr);
+        float v[32];
+        if constexpr (SPLIT) {
+          float cr[32];
+          tmem_ld32x2(acc + c0, v, acc + BN + c0, cr);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] += cr[i];
+          for (int i = 0; i < 32; ++i) v[i] += cr[i];
+        } else {
+          tmem_ld32(acc + c0, v);
+        }
         if (c0 + 32 >= BN) {  // the accumulator is in registers: hand the buffer back before the global round trips
           tc_fence_before();
           __syncwarp();
@@ -363,12 +382,13 @@ int plan_bn(int Cin, int Cout, int k, int dilation) {
 }
 
 // Shared-memory plan: returns 1 (weights resident), 0 (weight ring) or -1 (does not fit).
-int plan_smem(int bn, bool narrow, int Cin, int Cout, int k, int dilation, int ragged_b, X3Args* q) {
+int plan_smem(int bn, bool narrow, bool split, int Cin, int Cout, int k, int dilation, int ragged_b, X3Args* q) {
   const int FIXED_SMEM = bn <= 64 ? fixed_smem_of(32) : fixed_smem_of(128);
   q->R = 128 + (k - 1) * dilation;
   q->panel_bytes = (q->R * ROW_BYTES + 1023) & ~1023;
-  const int a_stage = (narrow ? 1 : 2) * q->panel_bytes;
-  const int WT = 2 * bn * ROW_BYTES;
+  const int np = split ? 2 : 1;
+  const int a_stage = (narrow ? 1 : np) * q->panel_bytes;
+  const int WT = np * bn * ROW_BYTES;
   const int avail = MAX_SMEM - FIXED_SMEM - (ragged_b > 0 ? (ragged_b + 1) * 4 : 0);
   const int n_tiles = (Cout + bn - 1) / bn;
   const int n_wt = narrow ? (k + 1) / 2 : (Cin / 64) * k;
@@ -387,12 +407,12 @@ int plan_smem(int bn, bool narrow, int Cin, int Cout, int k, int dilation, int r
   return 0;
 }
 
-template <int BN, bool NARROW, bool RESIDENT>
+template <int BN, bool NARROW, bool RESIDENT, bool SPLIT>
 int launch_k(const CUtensorMap& tmA, const CUtensorMap& tmW, const TcArgs& a, const X3Args& q, int64_t tiles,
              cudaStream_t st) {
   static std::atomic<unsigned long long> attr_mask{0};  // per device
   if (needs_attr_on_device(attr_mask)) {
-    cudaError_t e = cudaFuncSetAttribute(conv1d_bf16x3_kernel<BN, NARROW, RESIDENT>,
+    cudaError_t e = cudaFuncSetAttribute(conv1d_bf16x3_kernel<BN, NARROW, RESIDENT, SPLIT>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_conv1d_bf16x3: smem opt-in");
     attr_done_on_device(attr_mask);
@@ -400,54 +420,49 @@ int launch_k(const CUtensorMap& tmA, const CUtensorMap& tmW, const TcArgs& a, co
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_conv1d_bf16x3: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  const int a_stage = (NARROW ? 1 : 2) * q.panel_bytes;
-  const int smem = fixed_smem_of(BN) + q.n_a * a_stage + q.n_w * 2 * BN * ROW_BYTES + (a.rows ? (a.B + 1) * 4 : 0);
+  constexpr int NP = SPLIT ? 2 : 1;
+  const int a_stage = (NARROW ? 1 : NP) * q.panel_bytes;
+  const int smem = fixed_smem_of(BN) + q.n_a * a_stage + q.n_w * NP * BN * ROW_BYTES + (a.rows ? (a.B + 1) * 4 : 0);
   SS_REQUIRE(smem <= MAX_SMEM, SS_ERR_UNSUPPORTED, "ss_conv1d_bf16x3: shared-memory plan of %d bytes", smem);
-  conv1d_bf16x3_kernel<BN, NARROW, RESIDENT><<<grid, nthreads_of(BN), smem, st>>>(tmA, tmW, a, q);
+  conv1d_bf16x3_kernel<BN, NARROW, RESIDENT, SPLIT><<<grid, nthreads_of(BN), smem, st>>>(tmA, tmW, a, q);
   SS_CHECK_LAUNCH("ss_conv1d_bf16x3");
   return SS_OK;
 }
 
-}  // namespace
-
-extern "C" int ss_conv1d_bf16x3_plan(int Cin, int Cout, int k, int dilation) {
-  const int bn = plan_bn(Cin, Cout, k, dilation);
-  if (bn == 0) return 0;
-  X3Args q;
-  return plan_smem(bn, Cin == 32, Cin, Cout, k, dilation, RAGGED_MAX_B, &q) < 0 ? 0 : bn;
-}
-
-extern "C" int ss_conv1d_bf16x3(const ss_conv1d_tc_params* p, void* stream) {
-  SS_REQUIRE(p && p->x && p->w && (p->y || p->y_act || p->accum), SS_ERR_INVALID, "ss_conv1d_bf16x3: null pointer");
+template <bool SPLIT>
+int run(const ss_conv1d_tc_params* p, void* stream, const char* who) {
+  constexpr int NP = SPLIT ? 2 : 1;
+  SS_REQUIRE(p && p->x && p->w && (p->y || p->y_act || p->accum), SS_ERR_INVALID, "%s: null pointer", who);
   SS_REQUIRE(p->B > 0 && p->S_in > 0 && p->S_out > 0 && p->Cin > 0 && p->Cout > 0 && p->k > 0 && p->dilation > 0,
-             SS_ERR_INVALID, "ss_conv1d_bf16x3: bad shape B=%d S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d", p->B,
-             p->S_in, p->S_out, p->Cin, p->Cout, p->k, p->dilation);
+             SS_ERR_INVALID, "%s: bad shape B=%d S_in=%d S_out=%d Cin=%d Cout=%d k=%d dil=%d", who, p->B, p->S_in,
+             p->S_out, p->Cin, p->Cout, p->k, p->dilation);
   const int bn = plan_bn(p->Cin, p->Cout, p->k, p->dilation);
-  SS_REQUIRE(bn != 0, SS_ERR_UNSUPPORTED, "ss_conv1d_bf16x3: layer Cin=%d Cout=%d k=%d dil=%d is not handled", p->Cin,
-             p->Cout, p->k, p->dilation);
-  SS_REQUIRE(p->x_row_stride >= 2 * p->Cin && p->x_row_stride % 8 == 0 && p->x_batch_stride % 8 == 0 &&
+  SS_REQUIRE(bn != 0, SS_ERR_UNSUPPORTED, "%s: layer Cin=%d Cout=%d k=%d dil=%d is not handled", who, p->Cin, p->Cout,
+             p->k, p->dilation);
+  SS_REQUIRE(p->x_row_stride >= NP * p->Cin && p->x_row_stride % 8 == 0 && p->x_batch_stride % 8 == 0 &&
                  p->y_row_stride % 8 == 0 && p->y_batch_stride % 8 == 0 && p->y_offset % 8 == 0 &&
                  p->y_batch_elems % 8 == 0,
-             SS_ERR_ALIGNMENT, "ss_conv1d_bf16x3: strides/offsets must be multiples of 8 elements (pair rows: 2*Cin)");
+             SS_ERR_ALIGNMENT, "%s: strides/offsets must be multiples of 8 elements (rows of %d*Cin)", who, NP);
   SS_REQUIRE(ss::aligned16(p->x) && ss::aligned16(p->w) && ss::aligned16(p->y) && ss::aligned16(p->y_act) &&
                  ss::aligned16(p->bias) && ss::aligned16(p->residual) && ss::aligned16(p->accum),
-             SS_ERR_ALIGNMENT, "ss_conv1d_bf16x3: pointers must be 16-byte aligned");
+             SS_ERR_ALIGNMENT, "%s: pointers must be 16-byte aligned", who);
   SS_REQUIRE((p->y_dtype == SS_F32 || p->y_dtype == SS_BF16) && (p->residual_dtype == SS_F32 || p->residual_dtype == SS_BF16),
-             SS_ERR_INVALID, "ss_conv1d_bf16x3: bad dtype code");
+             SS_ERR_INVALID, "%s: bad dtype code", who);
   SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
-             "ss_conv1d_bf16x3: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
+             "%s: the ragged schedule (rows) takes at most %d utterances per call", who, RAGGED_MAX_B);
   const bool narrow = p->Cin == 32;
   X3Args q;
-  const int resident = plan_smem(bn, narrow, p->Cin, p->Cout, p->k, p->dilation, p->rows ? p->B : 0, &q);
-  SS_REQUIRE(resident >= 0, SS_ERR_UNSUPPORTED, "ss_conv1d_bf16x3: no shared-memory plan for Cin=%d k=%d dil=%d", p->Cin,
-             p->k, p->dilation);
+  const int resident = plan_smem(bn, narrow, SPLIT, p->Cin, p->Cout, p->k, p->dilation, p->rows ? p->B : 0, &q);
+  SS_REQUIRE(resident >= 0, SS_ERR_UNSUPPORTED, "%s: no shared-memory plan for Cin=%d k=%d dil=%d", who, p->Cin, p->k,
+             p->dilation);
 
   TcArgs a;
   a.bias = p->bias; a.residual = p->residual; a.lens = p->lens; a.y = p->y;
   a.y_act = static_cast<__nv_bfloat16*>(p->y_act); a.accum = p->accum;
-  a.pair_c = p->y_act ? (p->pair_c > 0 ? p->pair_c : p->Cout) : 0;  // the activated copy is a pair row [hi | lo]
+  // split: the activated copy is a pair row [hi | lo] of pair_c channels; plain: a bf16 copy laid out like y
+  a.pair_c = (SPLIT && p->y_act) ? (p->pair_c > 0 ? p->pair_c : p->Cout) : 0;
   SS_REQUIRE(a.pair_c % 8 == 0 && (a.pair_c == 0 || p->Cout % a.pair_c == 0), SS_ERR_INVALID,
-             "ss_conv1d_bf16x3: pair_c (%d) must be a multiple of 8 that divides Cout (%d)", a.pair_c, p->Cout);
+             "%s: pair_c (%d) must be a multiple of 8 that divides Cout (%d)", who, a.pair_c, p->Cout);
   a.y_batch_stride = p->y_batch_stride; a.y_row_stride = p->y_row_stride; a.y_offset = p->y_offset;
   a.y_batch_elems = p->y_batch_elems;
   a.B = p->B; a.S_out = p->S_out; a.Cin = p->Cin; a.Cout = p->Cout; a.k = p->k; a.dilation = p->dilation; a.pad = p->pad;
@@ -457,18 +472,39 @@ extern "C" int ss_conv1d_bf16x3(const ss_conv1d_tc_params* p, void* stream) {
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   a.rows = p->rows;
   const int64_t tiles = (int64_t)a.B * a.m_tiles * a.n_tiles;
-  SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_conv1d_bf16x3: too many tiles");
+  SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "%s: too many tiles", who);
 
   CUtensorMap tmA, tmW;
-  int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p->x, (uint64_t)2 * p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
+  // rows of NP*Cin bf16; a 64-element box past the row's end (plain, 32 channels) is zero-filled by TMA
+  int rc = make_map_3d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p->x, (uint64_t)NP * p->Cin, (uint64_t)p->S_in, (uint64_t)p->B,
                        (uint64_t)p->x_row_stride * 2, (uint64_t)p->x_batch_stride * 2, 64, (uint32_t)q.R);
   if (rc != SS_OK) return rc;
   const int wt_total = a.n_tiles * (narrow ? (p->k + 1) / 2 : (p->Cin / 64) * p->k);
-  rc = make_map_3d(&tmW, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p->w, 64, (uint64_t)2 * bn, (uint64_t)wt_total, 128,
-                   (uint64_t)2 * bn * 128, 64, (uint32_t)(2 * bn));
+  rc = make_map_3d(&tmW, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p->w, 64, (uint64_t)NP * bn, (uint64_t)wt_total, 128,
+                   (uint64_t)NP * bn * 128, 64, (uint32_t)(NP * bn));
   if (rc != SS_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (narrow) return launch_k<32, true, true>(tmA, tmW, a, q, tiles, st);
-  if (bn == 64) return resident ? launch_k<64, false, true>(tmA, tmW, a, q, tiles, st) : launch_k<64, false, false>(tmA, tmW, a, q, tiles, st);
-  return resident ? launch_k<128, false, true>(tmA, tmW, a, q, tiles, st) : launch_k<128, false, false>(tmA, tmW, a, q, tiles, st);
+  if (narrow) return launch_k<32, true, true, SPLIT>(tmA, tmW, a, q, tiles, st);
+  if (bn == 64)
+    return resident ? launch_k<64, false, true, SPLIT>(tmA, tmW, a, q, tiles, st)
+                    : launch_k<64, false, false, SPLIT>(tmA, tmW, a, q, tiles, st);
+  return resident ? launch_k<128, false, true, SPLIT>(tmA, tmW, a, q, tiles, st)
+                  : launch_k<128, false, false, SPLIT>(tmA, tmW, a, q, tiles, st);
+}
+
+}  // namespace
+
+extern "C" int ss_conv1d_bf16x3_plan(int Cin, int Cout, int k, int dilation) {
+  const int bn = plan_bn(Cin, Cout, k, dilation);
+  if (bn == 0) return 0;
+  X3Args q;
+  return plan_smem(bn, Cin == 32, true, Cin, Cout, k, dilation, RAGGED_MAX_B, &q) < 0 ? 0 : bn;
+}
+
+extern "C" int ss_conv1d_bf16x3(const ss_conv1d_tc_params* p, void* stream) {
+  return run<true>(p, stream, "ss_conv1d_bf16x3");
+}
+
+extern "C" int ss_conv1d_bf16_panel(const ss_conv1d_tc_params* p, void* stream) {
+  return run<false>(p, stream, "ss_conv1d_bf16_panel");
 }

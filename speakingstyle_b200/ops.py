@@ -149,7 +149,7 @@ class ConvW:
     def __init__(self, kcc):
         self.kcc = kcc.contiguous()
         self.k, self.cout, self.cin = self.kcc.shape
-        self._ffma = self._tf32 = self._bf16 = self._bf16x3 = None
+        self._ffma = self._tf32 = self._bf16 = self._bf16x3 = self._bf16p = None
 
     @property
     def ffma(self):
@@ -171,9 +171,20 @@ class ConvW:
         return self._bf16
 
 
+    def _panel_tiles(self, w, bn):
+        """[k, Cout, Cin] -> the weight tiles of the panel kernels (layout: include/speakingstyle_b200.h), one number per
+        value: [tiles, bn rows, 64]."""
+        if self.cin == 32:  # two taps per 128-byte row
+            npair = (self.k + 1) // 2
+            wp = torch.zeros(2 * npair, self.cout, 32, dtype=w.dtype, device=w.device)
+            wp[: self.k] = w
+            return wp.view(npair, 2, self.cout // 32, 32, 32).permute(2, 0, 3, 1, 4).reshape(-1, 32, 64)
+        nch = self.cin // 64
+        return w.view(self.k, self.cout // bn, bn, nch, 64).permute(1, 3, 0, 2, 4).reshape(-1, bn, 64)
+
     @property
     def bf16x3(self):
-        """Split-bf16 weight tiles for ss_conv1d_bf16x3 (layout: include/speakingstyle_b200.h), or None when the layer
+        """Split-bf16 weight tiles for ss_conv1d_bf16x3 ([W_hi rows ; W_lo rows] per tile), or None when the layer
         shape is not handled by that kernel."""
         if self._bf16x3 is None:
             bn = _lib.lib().ss_conv1d_bf16x3_plan(self.cin, self.cout, self.k, 1)
@@ -182,20 +193,16 @@ class ConvW:
             else:
                 hi = self.kcc.to(torch.bfloat16)
                 lo = (self.kcc - hi.float()).to(torch.bfloat16)
-                if self.cin == 32:  # two taps per 128-byte row
-                    npair = (self.k + 1) // 2
-
-                    def tiles(w):
-                        wp = torch.zeros(2 * npair, self.cout, 32, dtype=w.dtype, device=w.device)
-                        wp[: self.k] = w
-                        return wp.view(npair, 2, self.cout // 32, 32, 32).permute(2, 0, 3, 1, 4).reshape(-1, 32, 64)
-                else:
-                    nch = self.cin // 64
-
-                    def tiles(w):
-                        return w.view(self.k, self.cout // bn, bn, nch, 64).permute(1, 3, 0, 2, 4).reshape(-1, bn, 64)
-                self._bf16x3 = torch.cat([tiles(hi), tiles(lo)], dim=1).contiguous()
+                self._bf16x3 = torch.cat([self._panel_tiles(hi, bn), self._panel_tiles(lo, bn)], dim=1).contiguous()
         return None if self._bf16x3 is False else self._bf16x3
+
+    @property
+    def bf16p(self):
+        """bf16 weight tiles for ss_conv1d_bf16_panel, or None when the layer shape is not handled by that kernel."""
+        if self._bf16p is None:
+            bn = _lib.lib().ss_conv1d_bf16x3_plan(self.cin, self.cout, self.k, 1)
+            self._bf16p = False if bn == 0 else self._panel_tiles(self.kcc.to(torch.bfloat16), bn).contiguous()
+        return None if self._bf16p is False else self._bf16p
 
 
 def pack_conv(weight):
@@ -342,9 +349,17 @@ def pack_conv_tc(weight):
     return pack_conv(weight).bf16
 
 
-def _tc_call(p, flops):
-    fn = lambda: _lib.lib().ss_conv1d_tc(C.byref(p), _stream())  # noqa: E731
-    check(conv_timer.run(flops, fn, _tag("tc", p), _meta("tc", p)) if conv_timer is not None else fn())
+def bf16_panel_enabled():
+    """bf16 mode: ss_conv1d_bf16_panel for the layer shapes it takes (default), or always ss_conv1d_tc
+    (environment variable SS_BF16_PANEL=0)."""
+    return os.environ.get("SS_BF16_PANEL", "1") != "0"
+
+
+def _tc_call(p, flops, panel=False):
+    f = _lib.lib().ss_conv1d_bf16_panel if panel else _lib.lib().ss_conv1d_tc
+    kind = "tcp" if panel else "tc"
+    fn = lambda: f(C.byref(p), _stream())  # noqa: E731
+    check(conv_timer.run(flops, fn, _tag(kind, p), _meta(kind, p)) if conv_timer is not None else fn())
 
 
 def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, residual=None, lens=None,
@@ -352,12 +367,17 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
               accum_init=False, rows=None):
     """Tensor-core convolution.  x [B,S,Cin] bf16, w [k,Cout,Cin] bf16 (pack_conv_tc).
     Returns (y or None, y_act or None); y_act (bf16) is produced when act2 is not None."""
+    panel = None  # ss_conv1d_bf16_panel (activations fetched once per tile) where the layer shape allows
     if isinstance(w, ConvW):
-        w = w.bf16
+        if bf16_panel_enabled() and dilation * (w.k - 1) <= 128:
+            panel = w.bf16p
+        k, Cout, cin_w = w.k, w.cout, w.cin
+        w = panel if panel is not None else w.bf16
+    else:
+        k, Cout, cin_w = w.shape
     _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(bias, torch.float32, "bias")
     _chk(lens, torch.int32, "lens"); _chk(accum, torch.float32, "accum")
     B, S, Cin = x.shape
-    k, Cout, cin_w = w.shape
     if cin_w != Cin:
         raise _lib.SSError(f"conv1d_tc: weight Cin {cin_w} != input Cin {Cin}")
     y = None
@@ -373,7 +393,7 @@ def conv1d_tc(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
         Cout=Cout, k=k, dilation=dilation, pad=pad, act=act, slope=slope, act2=act2 or 0, slope2=slope2,
         y_dtype=_DT[y.dtype] if y is not None else F32, residual_dtype=_DT[residual.dtype] if residual is not None else F32,
         accum_scale=accum_scale, accum_init=int(accum_init), rows=None if rows is None else rows.data_ptr())
-    _tc_call(p, 2.0 * B * S * Cout * k * Cin)
+    _tc_call(p, 2.0 * B * S * Cout * k * Cin, panel is not None)
     return y, y_act
 
 
@@ -467,11 +487,16 @@ def conv_transpose1d_x3(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0,
 def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True, rows=None):
     """ConvTranspose1d in phase form on tensor cores.  x [B,S,Cin] bf16; w [taps, stride*cout, Cin] bf16;
     bias tiled to [stride*cout] f32.  Returns (y f32 [B,T_out,cout] or None, y_act bf16 or None)."""
+    panel = None
     if isinstance(w, ConvW):
-        w = w.bf16
+        if bf16_panel_enabled():
+            panel = w.bf16p
+        taps = w.k
+        w = panel if panel is not None else w.bf16
+    else:
+        taps = w.shape[0]
     _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(bias, torch.float32, "bias")
     B, S, Cin = x.shape
-    taps = w.shape[0]
     T_out = (S - 1) * stride - 2 * pad + taps * stride
     S_out = (T_out - 1 + pad) // stride + 1
     y = torch.empty((B, T_out, cout), dtype=torch.float32, device=x.device) if want_y else None
@@ -483,7 +508,7 @@ def conv_transpose1d_tc(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0,
         S_in=S, S_out=S_out, Cin=Cin, Cout=stride * cout, k=taps, dilation=1, pad=taps - 1, act=ACT_NONE, slope=0.0,
         act2=act2 or 0, slope2=slope2, y_dtype=F32, residual_dtype=F32, accum_scale=0.0, accum_init=0,
         rows=None if rows is None else rows.data_ptr())
-    _tc_call(p, 2.0 * B * T_out * cout * taps * Cin)
+    _tc_call(p, 2.0 * B * T_out * cout * taps * Cin, panel is not None)
     return y, y_act
 
 

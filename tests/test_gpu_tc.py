@@ -131,3 +131,40 @@ def test_conv1d_tc_ragged_schedule(ops, B, S, Cin, Cout, k, dil):
         assert torch.equal(y[i, :r], y_full[i, :r]) and torch.equal(a[i, :r], a_full[i, :r]), (i, r)
         done = min(S, -(-r // unit) * unit)
         assert bool((out[i, done:] == 7.5).all()), (i, r)
+
+
+@pytest.mark.parametrize("B,S,C,k,dil", [(3, 300, 32, 3, 1), (2, 1000, 32, 11, 5), (3, 500, 64, 7, 3), (2, 900, 64, 11, 1),
+                                         (2, 700, 128, 11, 5), (3, 260, 256, 3, 1), (2, 300, 256, 7, 1)])
+def test_bf16_panel_kernel_matches_conv1d_tc(ops, B, S, C, k, dil):
+    """ss_conv1d_bf16_panel (what conv1d_tc dispatches to when it is given a ConvW of a shape that kernel takes) against
+    ss_conv1d_tc on the same bf16 operands: same products, fp32 accumulation in a different order."""
+    x = rnd(B, S, C, seed=21).to(DEV).to(torch.bfloat16)
+    w = rnd(C, C, k, seed=22, scale=1.0 / math.sqrt(C * k)).to(DEV)
+    b = rnd(C, seed=23).to(DEV)
+    res = rnd(B, S, C, seed=24).to(DEV)
+    W = ops.pack_conv(w)
+    assert W.bf16p is not None
+    pad = (k - 1) // 2 * dil
+    y0, a0 = ops.conv1d_tc(x, W.bf16, b, dilation=dil, pad=pad, residual=res, act2=ops.ACT_LRELU, slope2=0.1)
+    y1, a1 = ops.conv1d_tc(x, W, b, dilation=dil, pad=pad, residual=res, act2=ops.ACT_LRELU, slope2=0.1)
+    assert (y0 - y1).abs().max().item() <= 2e-5 * y0.abs().max().item()
+    assert (a0.float() - a1.float()).abs().max().item() <= 2.0 ** -7 * y0.abs().max().item()
+    rows = torch.tensor([S, 129, 0][:B], dtype=torch.int32, device=DEV)
+    out = torch.full_like(y1, -5.0)
+    ops.conv1d_tc(x, W, b, dilation=dil, pad=pad, residual=res, rows=rows, out=out)
+    for i, r in enumerate(rows.tolist()):
+        done = min(S, (r + 127) // 128 * 128)
+        assert torch.equal(out[i, :r], y1[i, :r]) and bool((out[i, done:] == -5.0).all())
+
+
+@pytest.mark.parametrize("Cin,Cout,k,u,S", [(512, 256, 16, 8, 50), (128, 64, 4, 2, 1000), (64, 32, 4, 2, 2001)])
+def test_bf16_panel_conv_transpose(ops, Cin, Cout, k, u, S):
+    x = rnd(2, S, Cin, seed=25).to(DEV).to(torch.bfloat16)
+    w = rnd(Cin, Cout, k, seed=26, scale=1.0 / math.sqrt(Cin * k / u)).to(DEV)
+    b = rnd(Cout, seed=27).to(DEV).repeat(u).contiguous()
+    W = ops.pack_conv_transpose(w, u)
+    assert W.bf16p is not None
+    y0, a0 = ops.conv_transpose1d_tc(x, W.bf16, b, cout=Cout, stride=u, pad=(k - u) // 2, act2=ops.ACT_LRELU, slope2=0.1)
+    y1, a1 = ops.conv_transpose1d_tc(x, W, b, cout=Cout, stride=u, pad=(k - u) // 2, act2=ops.ACT_LRELU, slope2=0.1)
+    assert (y0 - y1).abs().max().item() <= 2e-5 * y0.abs().max().item()
+    assert (a0.float() - a1.float()).abs().max().item() <= 2.0 ** -7 * y0.abs().max().item()
