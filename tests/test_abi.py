@@ -67,6 +67,10 @@ def test_compute_entry_points_reject_bad_arguments_without_a_gpu(lib):
     assert lib.ss_conv1d_f32(ctypes.byref(p), None) == -1
     assert lib.ss_attention_f32(None, None, None, 1, 1, 1, 32, None) == -1
     assert lib.ss_length_regulate(None, None, None, None, None, 1, 1, 1, 4, None) == -1
+    q = _lib.Conv1dTcParams()
+    assert lib.ss_conv1d_bf16x3(ctypes.byref(q), None) == -1 and b"ss_conv1d_bf16x3" in lib.ss_last_error()
+    assert lib.ss_conv1d_bf16_panel(ctypes.byref(q), None) == -1 and b"ss_conv1d_bf16_panel" in lib.ss_last_error()
+    assert lib.ss_split_bf16(None, None, 1, 8, 0, 0.0, None) == -1
 
 
 def test_state_dict_contract_and_no_cpu_fallback():
@@ -114,3 +118,55 @@ def test_product_path_does_not_import_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in text and "from oracle" not in text, f
                 assert "/root/reference" not in text, f
+
+
+def test_split_bf16_weight_tiles_follow_the_header_layout(lib):
+    """ops.ConvW.bf16x3 / .bf16p against a loop restatement of the tile layout include/speakingstyle_b200.h states for
+    ss_conv1d_bf16x3 (no GPU: packing is host-side torch indexing; the plan call only inspects shapes)."""
+    import torch
+
+    from speakingstyle_b200 import ops
+
+    def check(cin, cout, k):
+        w = torch.randn(cout, cin, k, generator=torch.Generator().manual_seed(cin + cout + k))
+        W = ops.pack_conv(w)
+        bn = lib.ss_conv1d_bf16x3_plan(cin, cout, k, 1)
+        assert bn in (32, 64, 128)
+        hi = W.kcc.to(torch.bfloat16)
+        lo = (W.kcc - hi.float()).to(torch.bfloat16)
+        tiles = W.bf16x3
+        plain = W.bf16p
+        if cin == 32:
+            npair = (k + 1) // 2
+            assert tiles.shape == (cout // 32 * npair, 64, 64) and plain.shape == (cout // 32 * npair, 32, 64)
+            for nt in range(cout // 32):
+                for q in range(npair):
+                    t = tiles[nt * npair + q]
+                    for h in range(2):
+                        j = 2 * q + h
+                        want_hi = hi[j, nt * 32:nt * 32 + 32] if j < k else torch.zeros(32, 32, dtype=torch.bfloat16)
+                        want_lo = lo[j, nt * 32:nt * 32 + 32] if j < k else torch.zeros(32, 32, dtype=torch.bfloat16)
+                        assert torch.equal(t[:32, 32 * h:32 * h + 32], want_hi)
+                        assert torch.equal(t[32:, 32 * h:32 * h + 32], want_lo)
+                        assert torch.equal(plain[nt * npair + q][:, 32 * h:32 * h + 32], want_hi)
+        else:
+            nch = cin // 64
+            assert tiles.shape == (cout // bn * nch * k, 2 * bn, 64)
+            for nt in range(cout // bn):
+                for c in range(nch):
+                    for j in range(k):
+                        t = tiles[(nt * nch + c) * k + j]
+                        assert torch.equal(t[:bn], hi[j, nt * bn:(nt + 1) * bn, 64 * c:64 * c + 64])
+                        assert torch.equal(t[bn:], lo[j, nt * bn:(nt + 1) * bn, 64 * c:64 * c + 64])
+                        assert torch.equal(plain[(nt * nch + c) * k + j], t[:bn])
+        # hi + lo carries 16 significant bits of the weight
+        assert ((hi.float() + lo.float()) - W.kcc).abs().max() <= 2.0 ** -17 * W.kcc.abs().max()
+
+    check(32, 32, 3)
+    check(32, 32, 11)
+    check(64, 64, 7)
+    check(128, 128, 3)
+    check(256, 1024, 2)
+    assert lib.ss_conv1d_bf16x3_plan(80, 512, 7, 1) == 0 and lib.ss_conv1d_bf16x3_plan(256, 80, 1, 1) == 0
+    assert lib.ss_conv1d_bf16x3_plan(32, 32, 11, 13) == 0  # 128 + (k-1)*dilation > 256 rows: no panel
+    assert ops.pack_conv(torch.zeros(80, 256, 1)).bf16x3 is None
