@@ -572,6 +572,8 @@ def main():
         kname = {"tf32x3": "3xTF32 tcgen05 implicit-GEMM conv (fp32-accurate; conv1d_tf32_ts / _ts2 / hifigan kernels)",
                  "bf16x3": "conv1d_bf16x3_kernel (split-bf16 tcgen05 implicit-GEMM conv: 3 bf16 MMAs per algorithmic MAC, "
                            "fp32-class accuracy; HiFi-GAN ResBlocks of the fp32 mode)",
+                 "resunit": "resunit32_kernel (split-bf16 c1 -> leaky ReLU -> c2 + residual of one HiFi-GAN ResBlock unit, "
+                            "intermediate in shared memory)",
                  "tc": "conv1d_tc_kernel (bf16 tcgen05 implicit-GEMM conv)",
                  "tcp": "conv1d_bf16x3_kernel<SPLIT=false> (bf16 tcgen05 implicit-GEMM conv, panel feeding)", "f32": "conv1d_f32_kernel (FP32 pipe)"}[key[0]]
         roof = {"kernel": kname, "shape": f"Cin={key[1]} Cout={key[2]} k={key[3]} dil={key[4]}", "bound": "tensor",
@@ -589,7 +591,7 @@ def main():
             ceil = 148 * 2048 * 2 * clocks["sm_mhz"] * 1e6 / 3.0 / 1e12
             roof["tf32x3_ceiling_at_sampled_clock"] = ceil
             roof["frac_of_3xtf32_ceiling"] = d_ach / ceil
-        if key[0] == "bf16x3":
+        if key[0] in ("bf16x3", "resunit"):
             roof["bf16x3_ceiling"] = pk["tflops_sustained"] / 3.0
             roof["frac_of_bf16x3_ceiling"] = d_ach / roof["bf16x3_ceiling"]
         try:  # DRAM bytes of the same conv family from the committed ncu --set full capture (profiles/traffic.json)

@@ -231,6 +231,36 @@ SS_API int ss_conv1d_bf16x3_plan(int Cin, int Cout, int k, int dilation);
  * for the layer shapes ss_conv1d_bf16x3_plan accepts, with the activations fetched once per tile instead of once per tap.
  * w: the W_hi half of the tiles above ([BN rows, 64] per tile, same order). */
 SS_API int ss_conv1d_bf16_panel(const ss_conv1d_tc_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * One HiFi-GAN ResBlock unit in one launch (hifigan/models.py:96-103), split-bf16 arithmetic:
+ *   t = leaky_relu(c1(x) + b1, slope)   x: pair rows [B,S,2*C] of leaky_relu(y); c1: k taps, `dilation`; t stays on chip
+ *   v = c2(t) + b2 + residual           c2: k taps, dilation 1; residual = y [B,S,C] f32
+ *   y = v (if given; may alias residual);  accum / accum_scale / accum_init and y_pair = pair rows of act2(v): as in
+ *   ss_conv1d_bf16x3.  Bit-identical to two ss_conv1d_bf16x3 launches; 16 instead of 24 bytes of HBM traffic per
+ *   element.  w1 / w2: ss_conv1d_bf16x3 weight tiles (Cin == 32 form).  y_pair must not alias x.
+ * ss_resunit_bf16x3_supported(C, k, dilation): 1 for C == 32, k odd <= 17, 128 + (k-1)*dilation <= 256.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* x;           /* bf16 pair rows [B,S,2*C] */
+  const float* residual;   /* f32 [B,S,C] or NULL */
+  const void* w1;          /* bf16 tiles of c1 */
+  const float* b1;         /* f32 [C] */
+  const void* w2;          /* bf16 tiles of c2 */
+  const float* b2;         /* f32 [C] */
+  float* y;                /* f32 [B,S,C] or NULL */
+  void* y_pair;            /* bf16 pair rows [B,S,2*C] or NULL */
+  float* accum;            /* f32 [B,S,C] or NULL */
+  const int32_t* rows;     /* [B] or NULL - ragged schedule */
+  int32_t B, S, C, k, dilation;
+  float slope;             /* leaky-ReLU between c1 and c2 */
+  int32_t act2;
+  float slope2;
+  float accum_scale;
+  int32_t accum_init;
+} ss_resunit_params;
+SS_API int ss_resunit_bf16x3(const ss_resunit_params* p, void* stream);
+SS_API int ss_resunit_bf16x3_supported(int channels, int k, int dilation);
 SS_API int ss_split_bf16(const float* x, void* out, int64_t rows, int C, int act, float slope, void* stream);
 
 /* ------------------------------------------------------------------------------------------

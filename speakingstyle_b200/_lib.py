@@ -36,6 +36,14 @@ class Conv1dTcParams(C.Structure):
     ]
 
 
+class ResUnitParams(C.Structure):
+    _fields_ = [
+        ("x", vp), ("residual", vp), ("w1", vp), ("b1", vp), ("w2", vp), ("b2", vp), ("y", vp), ("y_pair", vp),
+        ("accum", vp), ("rows", vp), ("B", i32), ("S", i32), ("C", i32), ("k", i32), ("dilation", i32), ("slope", f32),
+        ("act2", i32), ("slope2", f32), ("accum_scale", f32), ("accum_init", i32),
+    ]
+
+
 class Conv1dTf32Params(C.Structure):
     _fields_ = [
         ("x", vp), ("x_batch_stride", i64), ("x_row_stride", i64), ("w_hi", vp), ("w_lo", vp), ("bias", vp),
@@ -80,6 +88,8 @@ _SIGNATURES = {
     "ss_cast_bf16": (C.c_int, [vp, vp, i64, C.c_int, f32, vp]),
     "ss_conv1d_bf16x3": (C.c_int, [C.POINTER(Conv1dTcParams), vp]),
     "ss_conv1d_bf16_panel": (C.c_int, [C.POINTER(Conv1dTcParams), vp]),
+    "ss_resunit_bf16x3": (C.c_int, [C.POINTER(ResUnitParams), vp]),
+    "ss_resunit_bf16x3_supported": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "ss_conv1d_bf16x3_plan": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "ss_split_bf16": (C.c_int, [vp, vp, i64, C.c_int, C.c_int, f32, vp]),
     "ss_layernorm": (C.c_int, [C.POINTER(LayerNormParams), vp]),

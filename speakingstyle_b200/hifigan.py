@@ -255,7 +255,7 @@ class Generator(nn.Module, ParamCache):
             rate *= u
             rw = rows and rows[rate]
             xs, ybuf = torch.empty_like(x), torch.empty_like(x)
-            tbuf, yabuf = torch.empty_like(xa), torch.empty_like(xa)
+            tbuf, yabufs = torch.empty_like(xa), (torch.empty_like(xa), torch.empty_like(xa))
             nxt = None
             for j in range(nk):
                 rb = self.resblocks[i * nk + j]
@@ -263,19 +263,28 @@ class Generator(nn.Module, ParamCache):
                 y, ya = x, xa
                 nd, rk = len(rb.dilation), rb.kernel_size
                 for m, dil in enumerate(rb.dilation):
-                    ta = ops.conv1d_x3(ya, w1s[m], rb.convs1[m].bias, dilation=dil, pad=get_padding(rk, dil), want_y=False,
-                                       act2=L, slope2=LRELU_SLOPE, rows=rw, out_pair=tbuf)[1]
-                    if m < nd - 1:
-                        y, ya = ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y, out=ybuf,
-                                              act2=L, slope2=LRELU_SLOPE, rows=rw, out_pair=yabuf)
-                    else:  # last pair: x_j = c2(..) + y goes straight into the stage mean
-                        # the last ResBlock's epilogue also emits leaky_relu(mean) as the pair the next transposed
-                        # convolution reads (hifigan/models.py:152-153), when that one runs on the split-bf16 kernel
-                        feeds = j == nk - 1 and i < n_up - 1 and pk["ups"][i + 1][0].bf16x3 is not None
-                        nxt = ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y,
-                                            want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0),
-                                            act2=L if feeds else None, slope2=LRELU_SLOPE, rows=rw,
-                                            out_pair=yabuf if feeds else None)[1]
+                    last = m == nd - 1
+                    # the last ResBlock's last epilogue also emits leaky_relu(mean) as the pair the next transposed
+                    # convolution reads (hifigan/models.py:152-153), when that one runs on the split-bf16 kernel
+                    feeds = last and j == nk - 1 and i < n_up - 1 and pk["ups"][i + 1][0].bf16x3 is not None
+                    tail = dict(act2=L if (not last or feeds) else None, slope2=LRELU_SLOPE, rows=rw,
+                                out_pair=yabufs[m & 1] if (not last or feeds) else None)  # never the pair being read
+                    if last:  # x_j = c2(..) + y goes straight into the stage mean
+                        tail.update(want_y=False, accum=xs, accum_scale=1.0 / nk, accum_init=(j == 0))
+                    else:
+                        tail.update(out=ybuf)
+                    if ops.resunit_ok(w1s[m], w2s[m], dil):  # 32-channel stage: c1 -> c2 in one launch
+                        y_new, ya_new = ops.resunit_x3(ya, y, w1s[m], rb.convs1[m].bias, w2s[m], rb.convs2[m].bias,
+                                                       dilation=dil, slope=LRELU_SLOPE, **tail)
+                    else:
+                        ta = ops.conv1d_x3(ya, w1s[m], rb.convs1[m].bias, dilation=dil, pad=get_padding(rk, dil),
+                                           want_y=False, act2=L, slope2=LRELU_SLOPE, rows=rw, out_pair=tbuf)[1]
+                        y_new, ya_new = ops.conv1d_x3(ta, w2s[m], rb.convs2[m].bias, pad=get_padding(rk, 1), residual=y,
+                                                      **tail)
+                    if last:
+                        nxt = ya_new
+                    else:
+                        y, ya = y_new, ya_new
             x, xa = xs, nxt
         return self._post(x, pk, pcm, pcm_out, pcm_scale)
 

@@ -454,6 +454,42 @@ def conv1d_x3(x, w, bias=None, *, dilation=1, pad=0, act=ACT_NONE, slope=0.0, re
     return y, y_pair
 
 
+def resunit_ok(w1, w2, dilation):
+    """True when ss_resunit_bf16x3 takes this c1 / c2 pair (HiFi-GAN's 32-channel stage)."""
+    return (isinstance(w1, ConvW) and isinstance(w2, ConvW) and w1.cin == w1.cout == w2.cin == w2.cout and w1.k == w2.k
+            and os.environ.get("SS_RESUNIT", "1") != "0"
+            and _lib.lib().ss_resunit_bf16x3_supported(w1.cin, w1.k, dilation) == 1 and w1.bf16x3 is not None)
+
+
+def resunit_x3(x, residual, w1, b1, w2, b2, *, dilation, slope, want_y=True, out=None, act2=None, slope2=0.0, accum=None,
+               accum_scale=1.0, accum_init=False, rows=None, out_pair=None):
+    """One ResBlock unit y' = residual + c2(leaky_relu(c1(x))) in one launch (ss_resunit_bf16x3).  x: pair rows
+    [B,S,2,C] of leaky_relu(y); residual [B,S,C] f32.  Returns (y' or None, pair rows of act2(y') or None)."""
+    _chk(x, torch.bfloat16, "x"); _chk(residual, torch.float32, "residual"); _chk(accum, torch.float32, "accum")
+    _chk(b1, torch.float32, "b1"); _chk(b2, torch.float32, "b2")
+    B, S, two, Cn = x.shape
+    if two != 2 or Cn != w1.cin:
+        raise _lib.SSError(f"resunit_x3: x must be pair rows [B,S,2,{w1.cin}], got {tuple(x.shape)}")
+    y = None
+    if want_y:
+        y = out if out is not None else torch.empty((B, S, Cn), dtype=torch.float32, device=x.device)
+    y_pair = None
+    if act2 is not None:
+        y_pair = out_pair if out_pair is not None else torch.empty((B, S, 2, Cn), dtype=torch.bfloat16, device=x.device)
+    p = _lib.ResUnitParams(
+        x=x.data_ptr(), residual=None if residual is None else residual.data_ptr(), w1=w1.bf16x3.data_ptr(),
+        b1=b1.data_ptr(), w2=w2.bf16x3.data_ptr(), b2=b2.data_ptr(), y=None if y is None else y.data_ptr(),
+        y_pair=None if y_pair is None else y_pair.data_ptr(), accum=None if accum is None else accum.data_ptr(),
+        rows=None if rows is None else rows.data_ptr(), B=B, S=S, C=Cn, k=w1.k, dilation=dilation, slope=slope,
+        act2=act2 or 0, slope2=slope2, accum_scale=accum_scale, accum_init=int(accum_init))
+    fn = lambda: _lib.lib().ss_resunit_bf16x3(C.byref(p), _stream())  # noqa: E731
+    flops = 2.0 * 2.0 * B * S * Cn * w1.k * Cn  # both convolutions
+    meta = ("resunit", B, S, Cn, Cn, w1.k, dilation)
+    tag = f"resunit B={B} S={S} Cin={Cn} Cout={Cn} k={w1.k} dil={dilation}"
+    check(conv_timer.run(flops, fn, tag, meta) if conv_timer is not None else fn())
+    return y, y_pair
+
+
 def conv_transpose1d_x3(x, w, bias, *, cout, stride, pad, act2=None, slope2=0.0, want_y=True, rows=None):
     """ConvTranspose1d in phase form on the split-bf16 kernel.  x: pair rows [B,S,2,Cin] bf16; w: ConvW from
     pack_conv_transpose; bias tiled to [stride*cout].  Returns (y f32 [B,T_out,cout] or None, pair rows

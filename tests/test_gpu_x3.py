@@ -142,3 +142,37 @@ def test_conv_transpose_x3(ops, Cin, Cout, k, u, S):
 def test_conv1d_x3_plan_rejects_other_shapes(ops):
     assert ops.pack_conv(torch.zeros(80, 80, 3, device=DEV)).bf16x3 is None
     assert ops.pack_conv(torch.zeros(32, 64, 3, device=DEV)).bf16x3 is None  # [Cout, Cin, k]: Cin 64 -> Cout 32
+
+
+@pytest.mark.parametrize("k,dil,S", [(3, 1, 1000), (3, 5, 126), (7, 3, 777), (11, 1, 2500), (11, 5, 118), (11, 3, 4000)])
+def test_resunit_is_bit_identical_to_two_launches(ops, k, dil, S):
+    """ss_resunit_bf16x3 (c1 -> leaky ReLU -> c2 + residual in one launch, intermediate in shared memory) against the
+    two ss_conv1d_bf16x3 launches it replaces: same MMAs in the same order, same epilogue arithmetic."""
+    B, C = 3, 32
+    L = ops.ACT_LRELU
+    y = rnd(B, S, C, seed=31).to(DEV)
+    xp = ops.split_bf16(y, act=L, slope=0.1)
+    W1 = ops.pack_conv(rnd(C, C, k, seed=32, scale=1.0 / math.sqrt(C * k)).to(DEV))
+    W2 = ops.pack_conv(rnd(C, C, k, seed=33, scale=1.0 / math.sqrt(C * k)).to(DEV))
+    b1, b2 = rnd(C, seed=34).to(DEV), rnd(C, seed=35).to(DEV)
+    assert ops.resunit_ok(W1, W2, dil)
+    _, tp = ops.conv1d_x3(xp, W1, b1, dilation=dil, pad=(k - 1) // 2 * dil, want_y=False, act2=L, slope2=0.1)
+    y2, yp2 = ops.conv1d_x3(tp, W2, b2, pad=(k - 1) // 2, residual=y, act2=L, slope2=0.1)
+    y1, yp1 = ops.resunit_x3(xp, y, W1, b1, W2, b2, dilation=dil, slope=0.1, act2=L, slope2=0.1)
+    torch.cuda.synchronize()
+    assert torch.equal(y1, y2) and torch.equal(yp1, yp2)
+    # running-mean form, in place over the residual, ragged rows
+    acc2 = torch.full((B, S, C), 0.25, device=DEV)
+    acc1 = acc2.clone()
+    ops.conv1d_x3(tp, W2, b2, pad=(k - 1) // 2, residual=y, want_y=False, accum=acc2, accum_scale=1.0 / 3)
+    ops.resunit_x3(xp, y, W1, b1, W2, b2, dilation=dil, slope=0.1, want_y=False, accum=acc1, accum_scale=1.0 / 3)
+    assert torch.equal(acc1, acc2)
+    rows = torch.tensor([S, min(S, 130), 0], dtype=torch.int32, device=DEV)
+    out = torch.full((B, S, C), -5.0, device=DEV)
+    outp = torch.full((B, S, 2, C), -5.0, device=DEV, dtype=torch.bfloat16)
+    ops.resunit_x3(xp, y, W1, b1, W2, b2, dilation=dil, slope=0.1, act2=L, slope2=0.1, rows=rows, out=out, out_pair=outp)
+    TM = 128 - (k - 1)
+    for i, r in enumerate(rows.tolist()):
+        done = min(S, (r + TM - 1) // TM * TM)
+        assert torch.equal(out[i, :r], y2[i, :r]) and torch.equal(outp[i, :r], yp2[i, :r])
+        assert bool((out[i, done:] == -5.0).all()) and bool((outp[i, done:] == -5.0).all())
