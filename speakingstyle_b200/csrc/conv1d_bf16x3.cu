@@ -241,6 +241,7 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       int nt, mt, b;
       decode(tile, nt, mt, b);
       const int len = p.lens ? p.lens[b] : 0x7fffffff;
+      if (dense) prefetch_epilogue_rows(p, lg, lane, b, mt * BM, p.S_out - mt * BM, nt * BN, min(BN, p.Cout - nt * BN));
       mbar_wait(tfull0 + 8 * e, (local / NBUF) & 1);
       tc_fence_after();
 #pragma unroll 1
@@ -379,6 +380,7 @@ int run(const ss_conv1d_tc_params* p, void* stream, const char* who) {
   a.act = p->act; a.act2 = p->act2; a.y_dtype = p->y_dtype; a.residual_dtype = p->residual_dtype;
   a.accum_init = p->accum_init; a.slope = p->slope; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   a.rows = p->rows;
+  a.l2_prefetch = x3_prefetch_default();
   const int64_t tiles = (int64_t)a.B * a.m_tiles * a.n_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "%s: too many tiles", who);
 

@@ -235,6 +235,8 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if ((i & 1) != e) continue;
       int mt, b;
       decode(tile, mt, b);
+      const int row0 = mt * q.TM, nrows = min(q.TM, p.S_out - row0);
+      prefetch_epilogue_rows(p, lg, lane, b, row0, nrows, 0, C);
       mbar_wait(t2full0 + 8 * e, (i >> 1) & 1);
       tc_fence_after();
       float v[32], cr[32];
@@ -244,8 +246,7 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(t2empty0 + 8 * e);
-      const int row0 = mt * q.TM;
-      drain_block_dense(p, v, stg, lg, lane, b, row0, min(q.TM, p.S_out - row0), 0);
+      drain_block_dense(p, v, stg, lg, lane, b, row0, nrows, 0);
     }
   }
 
@@ -310,6 +311,7 @@ extern "C" int ss_resunit_bf16x3(const ss_resunit_params* p, void* stream) {
   a.act = SS_ACT_NONE; a.act2 = p->act2; a.y_dtype = SS_F32; a.residual_dtype = SS_F32;
   a.accum_init = p->accum_init; a.slope = 0.f; a.slope2 = p->slope2; a.accum_scale = p->accum_scale;
   a.rows = p->rows;
+  a.l2_prefetch = x3_prefetch_default();
   const int64_t tiles = (int64_t)a.B * a.m_tiles;
   SS_REQUIRE(tiles < (1ll << 31), SS_ERR_UNSUPPORTED, "ss_resunit_bf16x3: too many tiles");
 

@@ -45,6 +45,7 @@ struct TcArgs {
   // tensor of PAIR rows [.., 2*pair_c] = [hi(pair_c) | lo(pair_c)], hi = bf16(v), lo = bf16(v - hi), for the element
   // that y holds at flat index g = (row)*pair_c + channel (pair_c = channels per output row).
   int32_t pair_c = 0;
+  int32_t l2_prefetch = 0;  // split-bf16 kernels: prefetch a tile's residual / running-mean rows into L2 (x3_common.cuh)
 };
 constexpr int RAGGED_MAX_B = 1024;  // utterances per launch in the ragged schedule (prefix table in shared memory)
 

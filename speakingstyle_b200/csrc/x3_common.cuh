@@ -1,9 +1,20 @@
 // Pieces shared by the split-bf16 kernels (conv1d_bf16x3.cu, resunit_bf16x3.cu): the low-word-descriptor bf16 MMA and
 // the dense epilogue.
 #pragma once
+#include <cstdlib>
+
 #include "tc_common.cuh"
 
 namespace sstc {
+
+// debug switch for A/B runs: SS_X3_PREFETCH=0 turns the epilogue's L2 prefetch off
+inline int x3_prefetch_default() {
+  static const int v = [] {
+    const char* e = getenv("SS_X3_PREFETCH");
+    return (e && e[0] == '0') ? 0 : 1;
+  }();
+  return v;
+}
 
 __device__ __forceinline__ void umma_bf16_w(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accum) {
   asm volatile(
@@ -30,6 +41,21 @@ __device__ __forceinline__ bool drain_is_dense(const TcArgs& p) {
          p.y_offset == 0 && p.y_row_stride == p.Cout && p.y_batch_stride == (int64_t)p.S_out * p.Cout &&
          p.y_batch_elems == (int64_t)p.S_out * p.Cout && (p.y_act == nullptr || p.pair_c == p.Cout || p.pair_c == 0);
 }
+// Pull the residual / running-mean rows a tile's epilogue will read into L2 ahead of time (called before the warp waits
+// for the tile's accumulator): drain_block_dense keeps only four 16-byte loads per lane in flight, which from HBM
+// (~1-2 us under load) is too few to keep a bandwidth-bound launch fed.  Dense layout only.
+__device__ __forceinline__ void prefetch_epilogue_rows(const TcArgs& p, int lg, int lane, int b, int row0, int nrows,
+                                                       int n0, int ncols) {
+  const bool pre_acc = p.accum != nullptr && !p.accum_init;
+  const int r = lg * 32 + lane;
+  if (!p.l2_prefetch || (p.residual == nullptr && !pre_acc) || r >= nrows) return;
+  const int64_t g = ((int64_t)b * p.S_out + row0 + r) * p.Cout + n0;
+  for (int c = 0; c < ncols; c += 32) {  // one 128-byte line per step
+    if (p.residual) asm volatile("prefetch.global.L2 [%0];" ::"l"(static_cast<const float*>(p.residual) + g + c));
+    if (pre_acc) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.accum + g + c));
+  }
+}
+
 // The block holds rows row0 + [32*lg, 32*lg + 32) of utterance b; only the tile's first `nrows` rows are stored.
 __device__ __forceinline__ void drain_block_dense(const TcArgs& p, const float (&v)[32], float* stg, int lg, int lane, int b,
                                                   int row0, int nrows, int n_blk) {
