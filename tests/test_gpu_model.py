@@ -618,3 +618,33 @@ def test_teacher_forced_path_vs_golden(golden):
         else:
             assert np.array_equal(o.cpu().numpy(), g[n]), n
     assert out[9].dtype == torch.int64 and out[5].dtype == torch.int64
+
+
+def test_fp32_mode_on_3xtf32_kernels_only(golden, monkeypatch):
+    """SS_FP32_CONVS=tf32x3: the fp32 mode without the split-bf16 kernels - HiFi-GAN, decoder and PostNet on
+    the 3xTF32 kernels, as before they existed.  Same fixtures, the tighter bars that path reaches."""
+    import speakingstyle_b200 as ss
+    from speakingstyle_b200 import ops
+
+    monkeypatch.setenv("SS_FP32_CONVS", "tf32x3")
+    assert ops.fp32_convs() == "tf32x3"
+    g = golden("hifigan_small")
+    h = C.hifigan_config()
+    gen = ss.get_vocoder(h, DEV, S.hifigan_state_dict(h))
+    assert gen.fp32_convs == "tf32x3"
+    timer, ops.conv_timer = ops.conv_timer, ops.KernelTimer()
+    try:
+        wave = gen(torch.from_numpy(g["mel"]).to(DEV))
+        kinds = {m[0] for _, _, _, _, m in ops.conv_timer.rows()}
+    finally:
+        ops.conv_timer = timer
+    assert kinds == {"tf32x3"}, kinds
+    assert maxabs(wave, g["wave"]) <= 2e-5
+    g = golden("tiny")
+    ds, batch, _ = S.make_workload("tiny")
+    model, mc, sd = get_models(ds)
+    out = run(model, batch)  # FastSpeech2 reads the environment variable per call
+    assert maxabs(out[0], g["mel"]) <= 2e-5 and maxabs(out[1], g["postnet_mel"]) <= 2e-5
+    monkeypatch.delenv("SS_FP32_CONVS")
+    wave_default = get_vocoder()[0](torch.from_numpy(golden("hifigan_small")["mel"]).to(DEV))
+    assert maxabs(wave_default, wave.cpu()) <= 1e-4  # the two fp32 forms agree far inside the 1e-3 bar
