@@ -59,6 +59,7 @@ template <int BN, bool NARROW, bool RESIDENT, bool SPLIT>
 __global__ void __launch_bounds__(nthreads_of(BN), 1)
 conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const TcArgs p,
                      const X3Args q) {
+  pdl_launch_dependents();
   constexpr int NP = SPLIT ? 2 : 1;        // bf16 numbers per value
   constexpr int WT = NP * BN * ROW_BYTES;  // one weight tile: [W_hi rows ; W_lo rows] x 128 bytes
   constexpr int ACC = NP * BN;             // columns of one accumulator buffer: [main | correction]
@@ -110,6 +111,7 @@ conv1d_bf16x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();  // everything below may touch memory the previous launch wrote
   const uint32_t tmem_base = *tslot_ptr;
   const int num_tiles = ragged ? rag[p.B] * p.n_tiles : p.B * p.m_tiles * p.n_tiles;
   auto decode = [&](int tile, int& nt, int& mt, int& b) {
@@ -333,7 +335,8 @@ int launch_k(const CUtensorMap& tmA, const CUtensorMap& tmW, const TcArgs& a, co
   const int a_stage = (NARROW ? 1 : NP) * q.panel_bytes;
   const int smem = fixed_smem_of(BN) + q.n_a * a_stage + q.n_w * NP * BN * ROW_BYTES + (a.rows ? (a.B + 1) * 4 : 0);
   SS_REQUIRE(smem <= MAX_SMEM, SS_ERR_UNSUPPORTED, "ss_conv1d_bf16x3: shared-memory plan of %d bytes", smem);
-  conv1d_bf16x3_kernel<BN, NARROW, RESIDENT, SPLIT><<<grid, nthreads_of(BN), smem, st>>>(tmA, tmW, a, q);
+  cudaError_t le = launch_pdl(conv1d_bf16x3_kernel<BN, NARROW, RESIDENT, SPLIT>, grid, nthreads_of(BN), smem, st, tmA, tmW, a, q);
+  if (le != cudaSuccess) return ss::cuda_fail(le, "ss_conv1d_bf16x3: launch");
   SS_CHECK_LAUNCH("ss_conv1d_bf16x3");
   return SS_OK;
 }

@@ -51,6 +51,7 @@ struct UnitArgs {
 __global__ void __launch_bounds__(NTHREADS, 1)
 resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW1,
                  const __grid_constant__ CUtensorMap tmW2, const TcArgs p, const UnitArgs q) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
@@ -93,6 +94,7 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();  // everything below may touch memory the previous launch wrote
   const uint32_t tmem_base = *tslot_ptr;
   const int num_tiles = ragged ? rag[p.B] : p.B * p.m_tiles;
   auto decode = [&](int tile, int& mt, int& b) {
@@ -336,7 +338,8 @@ extern "C" int ss_resunit_bf16x3(const ss_resunit_params* p, void* stream) {
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_resunit_bf16x3: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
   const int smem = FIXED_SMEM + q.n_a * q.panel_bytes + 2 * q.npair * WT + (a.rows ? (a.B + 1) * 4 : 0);
-  resunit32_kernel<<<grid, NTHREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmW1, tmW2, a, q);
+  cudaError_t le = launch_pdl(resunit32_kernel, grid, NTHREADS, smem, static_cast<cudaStream_t>(stream), tmA, tmW1, tmW2, a, q);
+  if (le != cudaSuccess) return ss::cuda_fail(le, "ss_resunit_bf16x3: launch");
   SS_CHECK_LAUNCH("ss_resunit_bf16x3");
   return SS_OK;
 }

@@ -7,6 +7,35 @@
 
 namespace sstc {
 
+// Programmatic dependent launch: the split-bf16 kernels are launched with programmaticStreamSerialization, announce
+// `launch_dependents` at their first instruction and do their prologue (barrier init, TMEM allocation, tensor-map
+// prefetch) before `griddepcontrol.wait`; nothing that reads or writes activation memory precedes the wait.  A CTA of the
+// next launch therefore takes over an SM the moment this launch's CTA leaves it, instead of after the whole grid has
+// drained and the next one has been scheduled (~300 convolution launches per cfg3 step).  SS_PDL=0 turns it off.
+inline int x3_pdl_enabled() {
+  static const int v = [] {
+    const char* e = getenv("SS_PDL");
+    return (e && e[0] == '0') ? 0 : 1;
+  }();
+  return v;
+}
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), int grid, int threads, int smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)threads);
+  cfg.dynamicSmemBytes = (size_t)smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = x3_pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // debug switch for A/B runs: SS_X3_PREFETCH=0 turns the epilogue's L2 prefetch off
 inline int x3_prefetch_default() {
   static const int v = [] {
