@@ -20,4 +20,8 @@ for cfg in "32 3" "32 11" "64 11" "128 3" "128 11" "256 11"; do
   timeout 600 ncu --set full --import-source on --clock-control none -k regex:bf16x3 -s 8 -c 4 -f -o /tmp/x3_$1_$2 python scripts/x3_one.py $1 $2 > $O/ncu2.log 2>&1
   ncu -i /tmp/x3_$1_$2.ncu-rep --page raw --csv 2>/dev/null | gzip > $O/r2z_x3_$1_$2_raw.csv.gz
 done
+python scripts/resunit_one.py > $O/r2z_resunit_timings.txt 2>&1
+timeout 200 python scripts/resunit_one.py --ncu > $O/plain3.log 2>&1 &&
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:resunit -f -o /tmp/resunit python scripts/resunit_one.py --ncu > $O/ncu3.log 2>&1
+ncu -i /tmp/resunit.ncu-rep --page raw --csv 2>/dev/null | gzip > $O/r2z_resunit_raw.csv.gz
 ls -la $O | tail -30
