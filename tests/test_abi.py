@@ -43,9 +43,9 @@ def test_struct_layouts_match_c(lib):
     """sizeof of every params struct as the C compiler sees it == ctypes.sizeof."""
     from speakingstyle_b200 import _lib
 
-    src = '#include <stdio.h>\n#include "speakingstyle_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu\\n",' \
+    src = '#include <stdio.h>\n#include "speakingstyle_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",' \
           'sizeof(ss_conv1d_f32_params),sizeof(ss_layernorm_params),sizeof(ss_predictor_head_params),' \
-          'sizeof(ss_conv1d_tc_params),sizeof(ss_conv1d_tf32_params));return 0;}'
+          'sizeof(ss_conv1d_tc_params),sizeof(ss_conv1d_tf32_params),sizeof(ss_resunit_params));return 0;}'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c")
         open(c, "w").write(src)
@@ -54,7 +54,7 @@ def test_struct_layouts_match_c(lib):
         sizes = [int(v) for v in subprocess.check_output([exe]).split()]
     assert sizes == [ctypes.sizeof(_lib.Conv1dF32Params), ctypes.sizeof(_lib.LayerNormParams),
                      ctypes.sizeof(_lib.PredictorHeadParams), ctypes.sizeof(_lib.Conv1dTcParams),
-                     ctypes.sizeof(_lib.Conv1dTf32Params)]
+                     ctypes.sizeof(_lib.Conv1dTf32Params), ctypes.sizeof(_lib.ResUnitParams)]
 
 
 def test_compute_entry_points_reject_bad_arguments_without_a_gpu(lib):
