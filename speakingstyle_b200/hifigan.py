@@ -145,34 +145,46 @@ class Generator(nn.Module, ParamCache):
         return pk
 
     # ---------------------------------------------------------------------------------------
-    def halo_frames(self):
-        """Mel frames to the RIGHT of an utterance's last frame that can still reach one of its samples: the sum of the
-        right-hand halos of every layer (conv: dilation*(k-1)/2 rows; transposed conv: one input row), each divided by
-        the layer's rows per frame, rounded up, plus one.  utils/model.py:109-113 trims wave b to mel_len[b]*hop, so
-        nothing further right is ever observed."""
+    def _halo_by_rate(self):
+        """{rows per frame: mel frames} - how far to the RIGHT of an utterance's last frame the layers running at that rate
+        must still be computed so that every sample of the utterance is exact: the sum of the right-hand halos of all
+        layers DOWNSTREAM of them (conv: dilation*(k-1)/2 rows; transposed conv: one input row), each divided by that
+        layer's rows per frame - counting, for the layers of a stage, the whole stage (its first convolution has the
+        other eleven behind it) - rounded up, plus one.  utils/model.py:109-113 trims wave b to mel_len[b]*hop, so
+        nothing further right is ever observed.  Deep stages need little: 2-3 frames at 256 / 128 / 64 rows per
+        frame, 11 at 8 rows per frame, 15 for conv_pre."""
         h = self.h
-        need = 3.0  # conv_pre, k = 7, at one row per frame
-        rate = 1
-        for i, u in enumerate(h["upsample_rates"]):
-            need += 1.0 / rate  # ConvTranspose1d: output t reads input rows <= (t + pad) / stride
-            rate *= u
+        rates = [1]
+        for u in h["upsample_rates"]:
+            rates.append(rates[-1] * u)
+        need = 3.0 / rates[-1]  # conv_post, k = 7
+        halo = {}
+        for i in reversed(range(len(h["upsample_rates"]))):
             rb = max((k - 1) // 2 * (sum(d) + len(d)) for k, d in zip(h["resblock_kernel_sizes"], h["resblock_dilation_sizes"]))
-            need += rb / rate
-        need += 3.0 / rate  # conv_post, k = 7
-        return int(need) + 2
+            need += rb / rates[i + 1]
+            halo[rates[i + 1]] = int(need) + 2
+            need += 1.0 / rates[i]  # ConvTranspose1d: output t reads input rows <= (t + pad) / stride
+        halo[1] = int(need) + 2  # conv_pre's output
+        return halo
+
+    def halo_frames(self):
+        """The largest of the per-rate halos (that of conv_pre's output): mel frames past an utterance's end that can
+        still reach one of its samples."""
+        return max(self._halo_by_rate().values())
 
     def _ragged_rows(self, frame_lens, T, dev):
         """Per-layer row limits of the ragged schedule for utterances of ``frame_lens`` valid mel frames in a batch padded
         to T: {rate: int32 [B]} for the layers running at ``rate`` rows per frame, {("up", i): int32 [B]} for the
         phase-form GEMM of ups[i] (rows = input positions).  One small host -> device copy."""
-        H = self.halo_frames()
+        halo = self._halo_by_rate()
         rates = [1]
         for u in self.h["upsample_rates"]:
             rates.append(rates[-1] * u)
-        keep = [min(T, max(0, int(n)) + H) for n in frame_lens]
+        keep = {r: [min(T, max(0, int(n)) + halo[r]) for n in frame_lens] for r in rates}
         # phase-form GEMM of ups[i]: row s writes output samples [u*s - pad, u*(s+1) - pad), so the samples of frame
-        # f-1 need rows <= f*rate (the kernel clamps to its own row count)
-        table = [[f * r for f in keep] for r in rates] + [[f * rates[i] + 1 for f in keep] for i in range(len(rates) - 1)]
+        # f-1 of its OUTPUT stage need rows <= f*rate (the kernel clamps to its own row count)
+        table = [[f * r for f in keep[r]] for r in rates] + \
+                [[f * rates[i] + 1 for f in keep[rates[i + 1]]] for i in range(len(rates) - 1)]
         t = torch.tensor(table, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
         rows = {r: t[j] for j, r in enumerate(rates)}
         rows.update({("up", i): t[len(rates) + i] for i in range(len(rates) - 1)})

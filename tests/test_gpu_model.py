@@ -332,8 +332,11 @@ def test_ragged_vocoder_schedule_returns_the_same_samples(precision):
     from speakingstyle_b200 import tools
     gen, h, vsd = get_vocoder()
     T = 150
-    mel = torch.randn(5, 80, T, generator=torch.Generator().manual_seed(31)).to(DEV)
-    lengths = [T * 256, 0, 256 * 3 + 1, 256 * 61, 256 * (T - gen.halo_frames() + 1) - 5]
+    mel = torch.randn(12, 80, T, generator=torch.Generator().manual_seed(31)).to(DEV)
+    # full length, empty, a few frames, mid-batch, just inside the largest halo, and odd sample counts around tile /
+    # frame boundaries of the deep stages (their halos are only 2-3 frames, _halo_by_rate)
+    lengths = [T * 256, 0, 256 * 3 + 1, 256 * 61, 256 * (T - gen.halo_frames() + 1) - 5, 256 * 100 + 255, 256 * 127,
+               256 * 128 + 1, 1, 256 * 33 - 1, 256 * (T - 2), 256 * (T - 3) + 17]
     gen.precision = precision
     try:
         _, pcm = gen(mel, pcm=True)
@@ -346,7 +349,9 @@ def test_ragged_vocoder_schedule_returns_the_same_samples(precision):
         assert np.array_equal(w, pcm[i, :lengths[i]]), i
     # the halo really is what bounds the schedule: stage-0 rows of utterance 2 stop well before the padded length
     rows = gen._ragged_rows([4], T, mel.device)
-    assert int(rows[8][0]) == (4 + gen.halo_frames()) * 8 < T * 8
+    halo = gen._halo_by_rate()
+    assert int(rows[8][0]) == (4 + halo[8]) * 8 < T * 8 and int(rows[256][0]) == (4 + halo[256]) * 256
+    assert halo[256] <= halo[128] <= halo[64] <= halo[8] <= halo[1] == gen.halo_frames()
 
 
 @pytest.mark.parametrize("name", ["tiny", "tiny_ms"])
