@@ -238,8 +238,9 @@ SS_API int ss_conv1d_bf16_panel(const ss_conv1d_tc_params* p, void* stream);
  *   v = c2(t) + b2 + residual           c2: k taps, dilation 1; residual = y [B,S,C] f32
  *   y = v (if given; may alias residual);  accum / accum_scale / accum_init and y_pair = pair rows of act2(v): as in
  *   ss_conv1d_bf16x3.  Bit-identical to two ss_conv1d_bf16x3 launches; 16 instead of 24 bytes of HBM traffic per
- *   element.  w1 / w2: ss_conv1d_bf16x3 weight tiles (Cin == 32 form).  y_pair must not alias x.
- * ss_resunit_bf16x3_supported(C, k, dilation): 1 for C == 32, k odd <= 17, 128 + (k-1)*dilation <= 256.
+ *   element.  w1 / w2: ss_conv1d_bf16x3 weight tiles of the layer's channel count.  y_pair must not alias x.
+ * ss_resunit_bf16x3_supported(C, k, dilation): 1 for C == 32 with k odd <= 17 and for C == 64 with k odd <= 9 whose
+ * weights fit next to the panels (k = 3), 128 + (k-1)*dilation <= 256; else 0.
  * ------------------------------------------------------------------------------------------ */
 typedef struct {
   const void* x;           /* bf16 pair rows [B,S,2*C] */

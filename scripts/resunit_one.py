@@ -1,9 +1,11 @@
-"""One fused ResBlock unit launch per kernel size at HiFi-GAN's 32-channel stage shape (B = 32, 163 840 rows), timed
-next to the two launches it replaces; with --ncu only the fused launches (for `ncu -k regex:resunit`)."""
+"""One fused ResBlock unit launch per kernel size at HiFi-GAN's 32-channel (default) or 64-channel stage shape (B = 32,
+163 840 / 81 920 rows), timed next to the two launches it replaces; with --ncu only the fused launches (for
+`ncu -k regex:resunit`).  usage: python scripts/resunit_one.py [32|64] [--ncu]"""
 import math, sys, torch
 sys.path.insert(0, ".")
 from speakingstyle_b200 import ops
-B, S, C = 32, 640 * 256, 32
+C = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 32
+B, S = 32, 640 * 8192 // C
 L = ops.ACT_LRELU
 y = torch.randn(B, S, C, device="cuda:0")
 xp = ops.split_bf16(y, act=L, slope=0.1)
@@ -23,7 +25,7 @@ def timed(fn, n=5):
     return a.elapsed_time(b) / n * 1e3
 
 
-for k, dil in ((3, 1), (7, 3), (11, 5)):
+for k, dil in (((3, 1), (7, 3), (11, 5)) if C == 32 else ((3, 1), (3, 5))):
     W1 = ops.pack_conv(torch.randn(C, C, k, device="cuda:0") / math.sqrt(C * k))
     W2 = ops.pack_conv(torch.randn(C, C, k, device="cuda:0") / math.sqrt(C * k))
     b1, b2 = torch.randn(C, device="cuda:0"), torch.randn(C, device="cuda:0")

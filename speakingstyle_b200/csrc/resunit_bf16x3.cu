@@ -1,5 +1,5 @@
 // One HiFi-GAN ResBlock unit, fused (hifigan/models.py:96-103):  y' = y + c2( leaky_relu( c1( leaky_relu(y) ) ) )
-// for the 32-channel stage, on the split-bf16 arithmetic of conv1d_bf16x3.cu (same MMAs in the same order, same
+// for the 32-channel stage (every kernel size) and the 64-channel k = 3 units, on the split-bf16 arithmetic of conv1d_bf16x3.cu (same MMAs in the same order, same
 // epilogue arithmetic: results are bit-identical to the two-launch form).
 //
 // Why: at 32 channels both convolutions are HBM-bound (8 bytes per element for c1, 16 for c2).  The intermediate
@@ -20,43 +20,63 @@
 //   5. Final warps (two sets, alternate tiles): accumulator 2 + bias + residual -> y', pair rows of leaky_relu(y') for
 //      the next unit, or the running stage mean.
 // The MMA thread issues c1 of tile i+1 before c2 of tile i, so the tensor pipe has work while the middle warps run.
+// 64 channels (hi and lo panels are separate 128-byte-row panels; weights of both convolutions resident only for
+// k = 3): shared memory holds ONE intermediate panel pair and one set of final warps, so c2 of tile i and the middle
+// warps' conversion of tile i+1 alternate on it; the unit is HBM-bound either way.
 #include "x3_common.cuh"
 
 namespace {
 
 using namespace sstc;
 
-constexpr int C = 32;                       // channels (both convolutions)
-constexpr int WT = 2 * C * ROW_BYTES;       // one weight tile: [W_hi rows ; W_lo rows], two taps per row
-constexpr int T_ROWS = 128 + 16;            // rows of a t panel: 128 written + up to 16 read past them
-constexpr int T_BYTES = T_ROWS * ROW_BYTES;  // 18 KB, a multiple of 1024
-constexpr int MID_WARPS = 4, FIN_WARPS = 8;
-constexpr int NTHREADS = 32 * (2 + MID_WARPS + FIN_WARPS);
+constexpr int MID_WARPS = 4;
 constexpr int MAX_A = 4;
 constexpr int N_BARS = 2 * MAX_A + 1 + 12;
 constexpr int MAX_SMEM = 227 * 1024;
-constexpr int FIXED_SMEM = 1024 + 2 * T_BYTES + FIN_WARPS * STG_WARP_BYTES + N_BARS * 8 + 16;
+// per channel count: 32 = one 128-byte row [hi | lo] per time step, two taps per weight row, double-buffered t panel, two
+// sets of final warps; 64 = hi panel + lo panel, one tap per weight tile, one t panel pair, one set of final warps
+template <int C> struct Unit {
+  static constexpr bool narrow = C == 32;
+  static constexpr int np = narrow ? 1 : 2;                 // 128-byte-row panels per operand (hi | lo in one, or two)
+  static constexpr int t_rows = narrow ? 128 + 16 : 128 + 8;  // rows of a t panel: 128 written + up to k-1 read past them
+  static constexpr int T_BYTES = t_rows * ROW_BYTES;        // a multiple of 1024
+  static constexpr int WT = 2 * C * ROW_BYTES;              // one weight tile: [W_hi rows ; W_lo rows]
+  static constexpr int NT = narrow ? 2 : 1;                 // t panel buffers
+  static constexpr int FIN_WARPS = narrow ? 8 : 4;
+  static constexpr int NSET = FIN_WARPS / 4;
+  static constexpr int nthreads = 32 * (2 + MID_WARPS + FIN_WARPS);
+  static constexpr int tmem_cols = 8 * C;                   // accumulator 1 x 2, accumulator 2 x 2, [main | correction] each
+  static constexpr int fixed_smem = 1024 + NT * np * T_BYTES + FIN_WARPS * STG_WARP_BYTES + N_BARS * 8 + 16;
+  static constexpr int tiles_per_conv(int k) { return narrow ? (k + 1) / 2 : k; }
+};
 
 struct UnitArgs {
   const float* b1;
   int32_t R1;           // input panel rows = 128 + (k-1)*dilation
   int32_t panel_bytes;  // R1 * 128 rounded up to 1024
   int32_t n_a;          // input panels in the ring
-  int32_t npair;        // weight tiles per convolution = ceil(k/2)
+  int32_t npair;        // weight tiles per convolution: ceil(k/2) at 32 channels (two taps per row), k at 64
   int32_t TM;           // output rows per tile = 128 - (k-1)
   int32_t dilation;     // of c1 (c2: 1)
   float slope;          // leaky-ReLU between c1 and c2
 };
 
-__global__ void __launch_bounds__(NTHREADS, 1)
-resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW1,
-                 const __grid_constant__ CUtensorMap tmW2, const TcArgs p, const UnitArgs q) {
+template <int C>
+__global__ void __launch_bounds__(Unit<C>::nthreads, 1)
+resunit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW1,
+               const __grid_constant__ CUtensorMap tmW2, const TcArgs p, const UnitArgs q) {
+  using U = Unit<C>;
+  constexpr bool NARROW = U::narrow;
+  constexpr int WT = U::WT, NT = U::NT, FIN_WARPS = U::FIN_WARPS, NSET = U::NSET;
+  constexpr int T_BYTES = U::T_BYTES;
+  constexpr int TP = U::np * T_BYTES;  // one t panel buffer (hi | lo in one panel, or hi panel + lo panel)
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_al = smem_raw + (smem0 - smem_u32(smem_raw));
-  const int t_off = q.n_a * q.panel_bytes;
-  const int w_off = t_off + 2 * T_BYTES;
+  const int a_stage = U::np * q.panel_bytes;
+  const int t_off = q.n_a * a_stage;
+  const int w_off = t_off + NT * TP;
   const int stg_off = w_off + 2 * q.npair * WT;
   const int bar_off = stg_off + FIN_WARPS * STG_WARP_BYTES;
   float* stg_all = reinterpret_cast<float*>(smem_al + stg_off);
@@ -90,7 +110,7 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(tslot, 256u);  // accumulator 1 x 2 (64 columns each), accumulator 2 x 2
+  if (warp == 1) tmem_alloc(tslot, (uint32_t)U::tmem_cols);  // accumulator 1 x 2 (2*C columns each), accumulator 2 x 2
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -121,8 +141,9 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int mt, b;
         decode(tile, mt, b);
         mbar_wait(aempty0 + 8 * as, aph ^ 1);
-        mbar_expect_tx(afull0 + 8 * as, (uint32_t)(q.R1 * ROW_BYTES));
-        tma_load_3d(smem0 + as * q.panel_bytes, &tmA, afull0 + 8 * as, 0, mt * q.TM - p2 - p1, b);
+        mbar_expect_tx(afull0 + 8 * as, (uint32_t)(U::np * q.R1 * ROW_BYTES));
+        tma_load_3d(smem0 + as * a_stage, &tmA, afull0 + 8 * as, 0, mt * q.TM - p2 - p1, b);
+        if (!NARROW) tma_load_3d(smem0 + as * a_stage + q.panel_bytes, &tmA, afull0 + 8 * as, C, mt * q.TM - p2 - p1, b);
         if (++as == q.n_a) { as = 0; aph ^= 1; }
       }
     }
@@ -140,15 +161,28 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int as = 0;
       uint32_t aph = 0;
       // one convolution of one tile: taps are shifted views of the operand panel
-      auto conv = [&](uint32_t d_main, uint32_t a0, uint32_t step, uint32_t w_lo) {
+      // lo_off: descriptor units from the hi panel to the lo panel of the operand (64 channels only)
+      auto conv = [&](uint32_t d_main, uint32_t a0, uint32_t step, uint32_t w_lo, uint32_t lo_off) {
         const uint32_t d_corr = d_main + C;
         uint32_t a = a0;
         for (int j = 0; j < p.k; ++j, a += step) {
-          const uint32_t b = w_lo + (uint32_t)(j >> 1) * (WT >> 4) + (uint32_t)(j & 1) * 4;
-          umma_bf16_w(d_main, a, b, idesc_m, j != 0);
-          umma_bf16_w(d_main, a + 2, b + 2, idesc_m, 1);
-          umma_bf16_w(d_corr, a + 4, b, idesc_h, 1);
-          umma_bf16_w(d_corr, a + 6, b + 2, idesc_h, 1);
+          if constexpr (NARROW) {
+            const uint32_t b = w_lo + (uint32_t)(j >> 1) * (WT >> 4) + (uint32_t)(j & 1) * 4;
+            umma_bf16_w(d_main, a, b, idesc_m, j != 0);
+            umma_bf16_w(d_main, a + 2, b + 2, idesc_m, 1);
+            umma_bf16_w(d_corr, a + 4, b, idesc_h, 1);
+            umma_bf16_w(d_corr, a + 6, b + 2, idesc_h, 1);
+          } else {
+            const uint32_t b = w_lo + (uint32_t)j * (WT >> 4), al = a + lo_off;
+            umma_bf16_w(d_main, a, b, idesc_m, j != 0);
+            umma_bf16_w(d_main, a + 2, b + 2, idesc_m, 1);
+            umma_bf16_w(d_main, a + 4, b + 4, idesc_m, 1);
+            umma_bf16_w(d_main, a + 6, b + 6, idesc_m, 1);
+            umma_bf16_w(d_corr, al, b, idesc_h, 1);
+            umma_bf16_w(d_corr, al + 2, b + 2, idesc_h, 1);
+            umma_bf16_w(d_corr, al + 4, b + 4, idesc_h, 1);
+            umma_bf16_w(d_corr, al + 6, b + 6, idesc_h, 1);
+          }
         }
       };
       auto issue1 = [&](int i) {
@@ -156,19 +190,19 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(t1empty0 + 8 * ab, ((i >> 1) & 1) ^ 1);  // middle warps have read this accumulator
         mbar_wait(afull0 + 8 * as, aph);
         tc_fence_after();
-        conv(tmem_base + ab * 2 * C, desc_lo(smem0 + as * q.panel_bytes), step1, w1_lo);
+        conv(tmem_base + ab * 2 * C, desc_lo(smem0 + as * a_stage), step1, w1_lo, (uint32_t)q.panel_bytes >> 4);
         umma_commit(aempty0 + 8 * as);
         umma_commit(t1full0 + 8 * ab);
         if (++as == q.n_a) { as = 0; aph ^= 1; }
       };
       auto issue2 = [&](int i) {
-        const int pb = i & 1;
-        mbar_wait(t2empty0 + 8 * pb, ((i >> 1) & 1) ^ 1);  // final warps have read this accumulator
-        mbar_wait(pfull0 + 8 * pb, (i >> 1) & 1);          // t panel written (generic proxy -> fence.proxy.async)
+        const int ab = i & 1, pb = i % NT;
+        mbar_wait(t2empty0 + 8 * ab, ((i >> 1) & 1) ^ 1);  // final warps have read this accumulator
+        mbar_wait(pfull0 + 8 * pb, (i / NT) & 1);          // t panel written (generic proxy -> fence.proxy.async)
         tc_fence_after();
-        conv(tmem_base + 4 * C + pb * 2 * C, desc_lo(smem0 + t_off + pb * T_BYTES), step2, w2_lo);
+        conv(tmem_base + 4 * C + ab * 2 * C, desc_lo(smem0 + t_off + pb * TP), step2, w2_lo, (uint32_t)T_BYTES >> 4);
         umma_commit(pempty0 + 8 * pb);
-        umma_commit(t2full0 + 8 * pb);
+        umma_commit(t2full0 + 8 * ab);
       };
       if (my_tiles > 0) issue1(0);
       for (int i = 0; i < my_tiles; ++i) {
@@ -180,75 +214,89 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ================= middle warps: accumulator 1 -> t panel =================
     const int lg = warp & 3;
     const int r = lg * 32 + lane;  // row of t this thread owns
-    float bias[C];
-#pragma unroll
-    for (int c = 0; c < C; c += 4) {
-      const float4 b4 = __ldg(reinterpret_cast<const float4*>(q.b1 + c));
-      bias[c] = b4.x; bias[c + 1] = b4.y; bias[c + 2] = b4.z; bias[c + 3] = b4.w;
-    }
     const uint32_t lane_base = tmem_base + ((uint32_t)(lg * 32) << 16);
     const uint32_t sw = (uint32_t)(r & 7);
     int i = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++i) {
       int mt, b;
       decode(tile, mt, b);
-      const int ab = i & 1;
+      const int ab = i & 1, pb = i % NT;
       mbar_wait(t1full0 + 8 * ab, (i >> 1) & 1);
       tc_fence_after();
-      float v[32], cr[32];
-      tmem_ld32x2(lane_base + ab * 2 * C, v, lane_base + ab * 2 * C + C, cr);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(t1empty0 + 8 * ab);
       const int g = mt * q.TM - p2 + r;  // global row of this t row: outside [0, S) it is c2's zero padding
       const bool inside = g >= 0 && g < p.S_out;
-      uint32_t hi[16], lo[16];
+      uint8_t* const row = smem_al + t_off + pb * TP + r * ROW_BYTES;
 #pragma unroll
-      for (int c = 0; c < 32; c += 2) {
-        float f0 = (v[c] + cr[c]) + bias[c], f1 = (v[c + 1] + cr[c + 1]) + bias[c + 1];
-        f0 = f0 > 0.f ? f0 : f0 * q.slope;
-        f1 = f1 > 0.f ? f1 : f1 * q.slope;
-        if (!inside) f0 = f1 = 0.f;
-        const uint32_t h = pack_bf16(f0, f1);
-        float a0, a1;
-        unpack_bf16(h, a0, a1);
-        hi[c >> 1] = h;
-        lo[c >> 1] = pack_bf16(f0 - a0, f1 - a1);
-      }
-      mbar_wait(pempty0 + 8 * ab, ((i >> 1) & 1) ^ 1);  // c2 of tile i-2 has read this panel
-      uint8_t* row = smem_al + t_off + ab * T_BYTES + r * ROW_BYTES;
+      for (int h = 0; h < C / 32; ++h) {  // 32 channels at a time
+        float v[32], cr[32];
+        tmem_ld32x2(lane_base + ab * 2 * C + 32 * h, v, lane_base + ab * 2 * C + C + 32 * h, cr);
+        if (h == C / 32 - 1) {  // accumulator 1 is in registers: hand it back
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t1empty0 + 8 * ab);
+        }
+        uint32_t hi[16], lo[16];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {  // logical 16-byte chunks 0..3 = hi, 4..7 = lo; physical chunk = logical ^ (r & 7)
-        *reinterpret_cast<uint4*>(row + (((uint32_t)c ^ sw) << 4)) = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
-        *reinterpret_cast<uint4*>(row + (((uint32_t)(c + 4) ^ sw) << 4)) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
+        for (int c = 0; c < 32; c += 4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(q.b1 + 32 * h + c));
+          const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+          for (int u = 0; u < 4; u += 2) {
+            float f0 = (v[c + u] + cr[c + u]) + bb[u], f1 = (v[c + u + 1] + cr[c + u + 1]) + bb[u + 1];
+            f0 = f0 > 0.f ? f0 : f0 * q.slope;
+            f1 = f1 > 0.f ? f1 : f1 * q.slope;
+            if (!inside) f0 = f1 = 0.f;
+            const uint32_t hh = pack_bf16(f0, f1);
+            float a0, a1;
+            unpack_bf16(hh, a0, a1);
+            hi[(c + u) >> 1] = hh;
+            lo[(c + u) >> 1] = pack_bf16(f0 - a0, f1 - a1);
+          }
+        }
+        if (h == 0) mbar_wait(pempty0 + 8 * pb, ((i / NT) & 1) ^ 1);  // c2 of the tile before has read this panel
+        // physical 16-byte chunk = logical ^ (r & 7).  32 channels: logical chunks 0..3 = hi, 4..7 = lo of ONE panel;
+        // 64 channels: chunks 4h..4h+3 of the hi panel and of the lo panel
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t ch = NARROW ? (uint32_t)c : (uint32_t)(4 * h + c), cl = NARROW ? (uint32_t)(c + 4) : ch;
+          uint8_t* const lo_row = NARROW ? row : row + T_BYTES;
+          *reinterpret_cast<uint4*>(row + ((ch ^ sw) << 4)) = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
+          *reinterpret_cast<uint4*>(lo_row + ((cl ^ sw) << 4)) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
+        }
       }
       fence_proxy_async();  // generic-proxy writes -> visible to the MMA's operand reads
       __syncwarp();
-      if (lane == 0) mbar_arrive(pfull0 + 8 * ab);
+      if (lane == 0) mbar_arrive(pfull0 + 8 * pb);
     }
   } else {
-    // ================= final warps: accumulator 2 -> global memory; set e = tiles with (i & 1) == e =================
+    // ================= final warps: accumulator 2 -> global memory; set e = tiles with i % NSET == e =================
     const int w = warp - 2 - MID_WARPS;
     const int e = w >> 2, lg = warp & 3;
     float* stg = stg_all + w * 32 * STG_PITCH;
-    const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + 4 * C + e * 2 * C;
     int i = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++i) {
-      if ((i & 1) != e) continue;
+      if (i % NSET != e) continue;
       int mt, b;
       decode(tile, mt, b);
+      const int ab = i & 1;
+      const uint32_t acc = tmem_base + ((uint32_t)(lg * 32) << 16) + 4 * C + ab * 2 * C;
       const int row0 = mt * q.TM, nrows = min(q.TM, p.S_out - row0);
       prefetch_epilogue_rows(p, lg, lane, b, row0, nrows, 0, C);
-      mbar_wait(t2full0 + 8 * e, (i >> 1) & 1);
+      mbar_wait(t2full0 + 8 * ab, (i >> 1) & 1);
       tc_fence_after();
-      float v[32], cr[32];
-      tmem_ld32x2(acc, v, acc + C, cr);
+#pragma unroll 1
+      for (int c0 = 0; c0 < C; c0 += 32) {
+        float v[32], cr[32];
+        tmem_ld32x2(acc + c0, v, acc + C + c0, cr);
 #pragma unroll
-      for (int c = 0; c < 32; ++c) v[c] += cr[c];
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(t2empty0 + 8 * e);
-      drain_block_dense(p, v, stg, lg, lane, b, row0, nrows, 0);
+        for (int c = 0; c < 32; ++c) v[c] += cr[c];
+        if (c0 + 32 >= C) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t2empty0 + 8 * ab);
+        }
+        drain_block_dense(p, v, stg, lg, lane, b, row0, nrows, c0);
+      }
     }
   }
 
@@ -257,48 +305,33 @@ resunit32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1) {
     __syncwarp();
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256u);
+    tmem_dealloc(tmem_base, (uint32_t)U::tmem_cols);
   }
 }
 
 // Shared-memory plan; false when the layer does not fit.
+template <int C>
 bool plan(int k, int dilation, int ragged_b, UnitArgs* q) {
-  if (k < 1 || k > 17 || (k & 1) == 0 || dilation < 1) return false;
+  using U = Unit<C>;
+  if (k < 1 || k - 1 > U::t_rows - 128 || (k & 1) == 0 || dilation < 1) return false;
   q->R1 = 128 + (k - 1) * dilation;
   if (q->R1 > 256) return false;
   q->panel_bytes = (q->R1 * ROW_BYTES + 1023) & ~1023;
-  q->npair = (k + 1) / 2;
+  q->npair = U::tiles_per_conv(k);
   q->TM = 128 - (k - 1);
   q->dilation = dilation;
-  const int avail = MAX_SMEM - FIXED_SMEM - 2 * q->npair * WT - (ragged_b > 0 ? (ragged_b + 1) * 4 : 0);
-  q->n_a = avail / q->panel_bytes;
+  const int avail = MAX_SMEM - U::fixed_smem - 2 * q->npair * U::WT - (ragged_b > 0 ? (ragged_b + 1) * 4 : 0);
+  q->n_a = avail / (U::np * q->panel_bytes);
   if (q->n_a > MAX_A) q->n_a = MAX_A;
   return q->n_a >= 2;
 }
 
-}  // namespace
-
-extern "C" int ss_resunit_bf16x3_supported(int channels, int k, int dilation) {
+template <int C>
+int run(const ss_resunit_params* p, void* stream) {
+  using U = Unit<C>;
   UnitArgs q;
-  return channels == C && plan(k, dilation, RAGGED_MAX_B, &q) ? 1 : 0;
-}
-
-extern "C" int ss_resunit_bf16x3(const ss_resunit_params* p, void* stream) {
-  SS_REQUIRE(p && p->x && p->w1 && p->w2 && p->b1 && p->b2 && (p->y || p->y_pair || p->accum), SS_ERR_INVALID,
-             "ss_resunit_bf16x3: null pointer");
-  SS_REQUIRE(p->B > 0 && p->S > 0 && p->C == C, SS_ERR_UNSUPPORTED, "ss_resunit_bf16x3: B=%d S=%d C=%d (C must be %d)",
-             p->B, p->S, p->C, C);
-  SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
-             "ss_resunit_bf16x3: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
-  UnitArgs q;
-  SS_REQUIRE(plan(p->k, p->dilation, p->rows ? p->B : 0, &q), SS_ERR_UNSUPPORTED,
-             "ss_resunit_bf16x3: k=%d dilation=%d is not handled", p->k, p->dilation);
-  SS_REQUIRE(ss::aligned16(p->x) && ss::aligned16(p->w1) && ss::aligned16(p->w2) && ss::aligned16(p->y) &&
-                 ss::aligned16(p->y_pair) && ss::aligned16(p->b1) && ss::aligned16(p->b2) &&
-                 ss::aligned16(p->residual) && ss::aligned16(p->accum),
-             SS_ERR_ALIGNMENT, "ss_resunit_bf16x3: pointers must be 16-byte aligned");
-  SS_REQUIRE(p->y_pair == nullptr || p->y_pair != p->x, SS_ERR_INVALID,
-             "ss_resunit_bf16x3: y_pair must not alias x (other tiles still read their halo rows of x)");
+  SS_REQUIRE(plan<C>(p->k, p->dilation, p->rows ? p->B : 0, &q), SS_ERR_UNSUPPORTED,
+             "ss_resunit_bf16x3: C=%d k=%d dilation=%d is not handled", C, p->k, p->dilation);
   q.b1 = p->b1;
   q.slope = p->slope;
 
@@ -330,16 +363,42 @@ extern "C" int ss_resunit_bf16x3(const ss_resunit_params* p, void* stream) {
 
   static std::atomic<unsigned long long> attr_mask{0};  // per device
   if (needs_attr_on_device(attr_mask)) {
-    cudaError_t e = cudaFuncSetAttribute(resunit32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(resunit_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM);
     if (e != cudaSuccess) return ss::cuda_fail(e, "ss_resunit_bf16x3: smem opt-in");
     attr_done_on_device(attr_mask);
   }
   const int sms = sm_count();
   SS_REQUIRE(sms > 0, SS_ERR_CUDA, "ss_resunit_bf16x3: no CUDA device");
   const int grid = (int)(tiles < sms ? tiles : sms);
-  const int smem = FIXED_SMEM + q.n_a * q.panel_bytes + 2 * q.npair * WT + (a.rows ? (a.B + 1) * 4 : 0);
-  cudaError_t le = launch_pdl(resunit32_kernel, grid, NTHREADS, smem, static_cast<cudaStream_t>(stream), tmA, tmW1, tmW2, a, q);
+  const int smem = U::fixed_smem + q.n_a * U::np * q.panel_bytes + 2 * q.npair * U::WT + (a.rows ? (a.B + 1) * 4 : 0);
+  cudaError_t le = launch_pdl(resunit_kernel<C>, grid, U::nthreads, smem, static_cast<cudaStream_t>(stream), tmA, tmW1,
+                              tmW2, a, q);
   if (le != cudaSuccess) return ss::cuda_fail(le, "ss_resunit_bf16x3: launch");
   SS_CHECK_LAUNCH("ss_resunit_bf16x3");
   return SS_OK;
+}
+
+}  // namespace
+
+extern "C" int ss_resunit_bf16x3_supported(int channels, int k, int dilation) {
+  UnitArgs q;
+  if (channels == 32) return plan<32>(k, dilation, RAGGED_MAX_B, &q) ? 1 : 0;
+  if (channels == 64) return plan<64>(k, dilation, RAGGED_MAX_B, &q) ? 1 : 0;
+  return 0;
+}
+
+extern "C" int ss_resunit_bf16x3(const ss_resunit_params* p, void* stream) {
+  SS_REQUIRE(p && p->x && p->w1 && p->w2 && p->b1 && p->b2 && (p->y || p->y_pair || p->accum), SS_ERR_INVALID,
+             "ss_resunit_bf16x3: null pointer");
+  SS_REQUIRE(p->B > 0 && p->S > 0 && (p->C == 32 || p->C == 64), SS_ERR_UNSUPPORTED,
+             "ss_resunit_bf16x3: B=%d S=%d C=%d (C must be 32 or 64)", p->B, p->S, p->C);
+  SS_REQUIRE(p->rows == nullptr || p->B <= RAGGED_MAX_B, SS_ERR_UNSUPPORTED,
+             "ss_resunit_bf16x3: the ragged schedule (rows) takes at most %d utterances per call", RAGGED_MAX_B);
+  SS_REQUIRE(ss::aligned16(p->x) && ss::aligned16(p->w1) && ss::aligned16(p->w2) && ss::aligned16(p->y) &&
+                 ss::aligned16(p->y_pair) && ss::aligned16(p->b1) && ss::aligned16(p->b2) &&
+                 ss::aligned16(p->residual) && ss::aligned16(p->accum),
+             SS_ERR_ALIGNMENT, "ss_resunit_bf16x3: pointers must be 16-byte aligned");
+  SS_REQUIRE(p->y_pair == nullptr || p->y_pair != p->x, SS_ERR_INVALID,
+             "ss_resunit_bf16x3: y_pair must not alias x (other tiles still read their halo rows of x)");
+  return p->C == 32 ? run<32>(p, stream) : run<64>(p, stream);
 }

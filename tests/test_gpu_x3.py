@@ -144,11 +144,12 @@ def test_conv1d_x3_plan_rejects_other_shapes(ops):
     assert ops.pack_conv(torch.zeros(32, 64, 3, device=DEV)).bf16x3 is None  # [Cout, Cin, k]: Cin 64 -> Cout 32
 
 
-@pytest.mark.parametrize("k,dil,S", [(3, 1, 1000), (3, 5, 126), (7, 3, 777), (11, 1, 2500), (11, 5, 118), (11, 3, 4000)])
-def test_resunit_is_bit_identical_to_two_launches(ops, k, dil, S):
+@pytest.mark.parametrize("C,k,dil,S", [(32, 3, 1, 1000), (32, 3, 5, 126), (32, 7, 3, 777), (32, 11, 1, 2500), (32, 11, 5, 118),
+                                       (32, 11, 3, 4000), (64, 3, 1, 1000), (64, 3, 3, 126), (64, 3, 5, 5000)])
+def test_resunit_is_bit_identical_to_two_launches(ops, C, k, dil, S):
     """ss_resunit_bf16x3 (c1 -> leaky ReLU -> c2 + residual in one launch, intermediate in shared memory) against the
     two ss_conv1d_bf16x3 launches it replaces: same MMAs in the same order, same epilogue arithmetic."""
-    B, C = 3, 32
+    B = 3
     L = ops.ACT_LRELU
     y = rnd(B, S, C, seed=31).to(DEV)
     xp = ops.split_bf16(y, act=L, slope=0.1)
